@@ -1,0 +1,260 @@
+"""Generate the known-answer fixtures under ``tests/golden/`` FROM THE REFERENCE ITSELF.
+
+TEST INFRASTRUCTURE.  Runs only in the build container (needs ``/root/reference``);
+the fixtures it writes are committed so the GPU box never needs the reference.
+
+    python -m oracle.gen_golden            # rewrites tests/golden/*.npz
+
+What is imported from the reference (read-only, unmodified):
+  * ``P/dlrm_s_pytorch.py``  -> ``DLRM_Net`` (model, interaction), ``LRPolicyScheduler``
+  * ``P/extend_distributed.py`` -> ``get_my_slice`` / ``get_split_lengths``
+  * ``T/dlrm_data_pytorch.py`` -> ``generate_uniform_input_batch`` (ragged multi-hot bags)
+with ``P/`` = applications/ai/quickstart/models/recommendation/pytorch/dlrm/product and
+``T/`` = .../dlrm/training/bfloat16.  Absent third-party modules (mlperf_logging) are
+stubbed in ``sys.modules``; nothing in the reference tree is edited.
+"""
+from __future__ import annotations
+
+import importlib
+import importlib.machinery
+import importlib.util
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+REF = "/root/reference/applications/ai/quickstart/models/recommendation/pytorch/dlrm"
+P_DIR = os.path.join(REF, "product")
+T_DIR = os.path.join(REF, "training", "bfloat16")
+OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+
+_SHARED_NAMES = ["data_utils", "data_loader_terabyte", "extend_distributed", "dlrm_data_pytorch",
+                 "mlperf_logger"]
+
+
+def _stub(name, **attrs):
+    m = types.ModuleType(name)
+    m.__spec__ = importlib.machinery.ModuleSpec(name, loader=None)
+    for k, v in attrs.items():
+        setattr(m, k, v)
+    sys.modules[name] = m
+    return m
+
+
+def load_T_generator():
+    """T/dlrm_data_pytorch.generate_uniform_input_batch, loaded in isolation."""
+    sys.dont_write_bytecode = True
+    consts = _stub("mlperf_logging.mllog.constants")
+    mllog = _stub("mlperf_logging.mllog", constants=consts,
+                  get_mllogger=lambda: types.SimpleNamespace())
+    _stub("mlperf_logging", mllog=mllog)
+    sys.path.insert(0, T_DIR)
+    try:
+        mod = importlib.import_module("dlrm_data_pytorch")
+    finally:
+        sys.path.remove(T_DIR)
+    for n in _SHARED_NAMES:  # P/ has modules of the same names
+        sys.modules.pop(n, None)
+    return mod
+
+
+def load_P():
+    sys.dont_write_bytecode = True
+    sys.path.insert(0, P_DIR)
+    try:
+        M = importlib.import_module("dlrm_s_pytorch")
+        X = importlib.import_module("extend_distributed")
+    finally:
+        sys.path.remove(P_DIR)
+    # apply_emb / interact_features read a module-global ``args`` (P/dlrm_s_pytorch.py:288,310)
+    M.args = types.SimpleNamespace(ipex=False, ipex_interaction=False)
+    return M, X
+
+
+def _state(model):
+    return {k: v.detach().numpy().copy() for k, v in model.state_dict().items()}
+
+
+def gen_interaction(M):
+    """Reference interact_features forward + autograd backward."""
+    net = M.DLRM_Net.__new__(M.DLRM_Net)  # interact_features uses no attributes
+    out = {}
+    x = torch.tensor([[1.0, 2.0]])
+    ly = [torch.tensor([[3.0, 4.0]]), torch.tensor([[5.0, 6.0]])]
+    out["kat_R"] = M.DLRM_Net.interact_features(net, x, ly).numpy()
+    rs = np.random.RandomState(11)
+    for tag, (B, F, D) in {"a": (5, 4, 8), "b": (3, 27, 16), "c": (2, 27, 128)}.items():
+        x = torch.tensor(rs.randn(B, D).astype(np.float32), requires_grad=True)
+        ly = [torch.tensor(rs.randn(B, D).astype(np.float32), requires_grad=True) for _ in range(F - 1)]
+        R = M.DLRM_Net.interact_features(net, x, ly)
+        dR = torch.tensor(rs.randn(*R.shape).astype(np.float32))
+        R.backward(dR)
+        out[f"{tag}_x"] = x.detach().numpy()
+        out[f"{tag}_ly"] = np.stack([t.detach().numpy() for t in ly])
+        out[f"{tag}_R"] = R.detach().numpy()
+        out[f"{tag}_dR"] = dR.numpy()
+        out[f"{tag}_dx"] = x.grad.numpy()
+        out[f"{tag}_dly"] = np.stack([t.grad.numpy() for t in ly])
+    np.savez_compressed(os.path.join(OUT, "interaction.npz"), **out)
+
+
+def gen_index_kats(X):
+    """Sparse-grad structure / bucketing KAT + table partition."""
+    out = {}
+    idx = torch.tensor([3, 1, 3, 7, 7, 7, 0, 9])
+    off = torch.tensor([0, 2, 2, 5])
+    E = torch.nn.EmbeddingBag(10, 4, mode="sum", sparse=True)
+    y = E(idx, off)
+    g = torch.arange(16, dtype=torch.float32).view(4, 4)
+    y.backward(g)
+    G = E.weight.grad
+    out["idx"], out["off"], out["gout"] = idx.numpy(), off.numpy(), g.numpy()
+    out["coo_indices"] = G._indices().numpy()[0]
+    out["coo_values"] = G._values().numpy()
+    C = G.coalesce()
+    out["coalesced_indices"] = C.indices().numpy()[0]
+    out["coalesced_values"] = C.values().numpy()
+    s, perm = torch.sort(idx, stable=True)
+    u, inv, cnt = torch.unique(idx, sorted=True, return_inverse=True, return_counts=True)
+    out["sorted"], out["perm"] = s.numpy(), perm.numpy()
+    out["unique"], out["inverse"], out["counts"] = u.numpy(), inv.numpy(), cnt.numpy()
+    _, o2b, bag_size, _ = torch._embedding_bag(E.weight.detach(), idx, off, False, 1)  # mode=mean fills offset2bag
+    out["offset2bag"], out["bag_size"] = o2b.numpy(), bag_size.numpy()
+    # table partition from the reference's own functions, with a fake process group
+    rows = []
+    for world in (1, 2, 3, 4, 8):
+        for rank in range(world):
+            X.dist = types.SimpleNamespace(get_world_size=lambda w=world: w, get_rank=lambda r=rank: r)
+            for n in (26, 8, 5, 16):
+                sl = X.get_my_slice(n)
+                my_len, splits = X.get_split_lengths(n)
+                rows.append([world, rank, n, sl.start, sl.stop, my_len] +
+                            (list(splits) + [-1] * (8 - world) if splits else [-1] * 8))
+    out["partition"] = np.array(rows, dtype=np.int64)
+    np.savez_compressed(os.path.join(OUT, "index_kats.npz"), **out)
+
+
+def _run_reference_model(M, seed, D, ln_emb, ln_bot, ln_top, batches, lr):
+    """Train the reference DLRM_Net with torch.optim.SGD exactly as the loop at
+    P/dlrm_s_pytorch.py:1029-1059 does (fp32, no IPEX)."""
+    np.random.seed(seed)
+    torch.manual_seed(seed)
+    net = M.DLRM_Net(D, np.asarray(ln_emb), np.asarray(ln_bot), np.asarray(ln_top),
+                     sigmoid_bot=-1, sigmoid_top=len(ln_top) - 2, np_init_emb_weight=True)
+    init = _state(net)
+    opt = torch.optim.SGD(net.parameters(), lr=lr)
+    losses = []
+    for (X, lS_o, lS_i, T) in batches:
+        Z = net(X, lS_o, lS_i).float()
+        E = net.loss_fn(Z, T)
+        losses.append(float(E.detach().cpu().numpy()))
+        opt.zero_grad(set_to_none=True)
+        E.backward()
+        opt.step()
+    return net, init, np.array(losses, dtype=np.float64)
+
+
+def gen_small_model(M, G):
+    """Tiny ragged multi-hot model; full init/inputs/final weights stored."""
+    seed, D = 123, 8
+    ln_emb = [40, 30, 20, 10]
+    F = len(ln_emb) + 1
+    ln_bot = [13, 16, D]
+    ln_top = [D + F * (F - 1) // 2, 16, 1]
+    B, steps, lr = 6, 4, 0.1
+    G.ra.seed(seed + 1)
+    batches = []
+    for _ in range(steps):
+        X, lS_o, lS_i = G.generate_uniform_input_batch(13, np.asarray(ln_emb), B, 5, False)
+        T = G.generate_random_output_batch(B, 1, round_targets=True)
+        batches.append((X, lS_o, lS_i, T))
+    net, init, losses = _run_reference_model(M, seed, D, ln_emb, ln_bot, ln_top, batches, lr)
+    out = {"seed": seed, "D": D, "ln_emb": np.array(ln_emb), "ln_bot": np.array(ln_bot),
+           "ln_top": np.array(ln_top), "lr": lr, "losses": losses, "steps": steps, "B": B}
+    for k, v in init.items():
+        out["init/" + k] = v
+    for k, v in _state(net).items():
+        out["final/" + k] = v
+    for s, (X, lS_o, lS_i, T) in enumerate(batches):
+        out[f"X{s}"], out[f"T{s}"] = X.numpy(), T.numpy()
+        for t in range(len(ln_emb)):
+            out[f"o{s}_{t}"], out[f"i{s}_{t}"] = lS_o[t].numpy(), lS_i[t].numpy()
+    np.savez_compressed(os.path.join(OUT, "small_model.npz"), **out)
+
+
+KAGGLE_ROWS = [1460, 583, 1000000, 1000000, 305, 24, 12517, 633, 3, 93145, 5683, 1000000, 3194, 27,
+               14992, 1000000, 10, 5652, 2173, 4, 1000000, 18, 15, 286181, 105, 142572]
+
+
+def gen_kaggle_c1(M, G):
+    """BASELINE config 1 shape (T/bench/dlrm_s_criteo_kaggle.sh:24): 26 tables capped at
+    1M rows, D=16, bot 13-512-256-64-16, top 512-256-1, B=128, SGD lr 0.1, BCE, one-hot.
+    Weights are regenerated from the seed by the port; inputs + loss trace + a sample of
+    the updated rows are stored."""
+    seed, D, B, steps, lr = 727, 16, 128, 8, 0.1
+    ln_bot = [13, 512, 256, 64, 16]
+    F = 27
+    ln_top = [D + F * (F - 1) // 2, 512, 256, 1]
+    G.ra.seed(seed + 1)
+    batches = []
+    for _ in range(steps):
+        X, lS_o, lS_i = G.generate_uniform_input_batch(13, np.asarray(KAGGLE_ROWS), B, 1, True)
+        T = G.generate_random_output_batch(B, 1, round_targets=True)
+        batches.append((X, lS_o, lS_i, T))
+    net, init, losses = _run_reference_model(M, seed, D, KAGGLE_ROWS, ln_bot, ln_top, batches, lr)
+    out = {"seed": seed, "D": D, "ln_emb": np.array(KAGGLE_ROWS), "ln_bot": np.array(ln_bot),
+           "ln_top": np.array(ln_top), "lr": lr, "losses": losses, "steps": steps, "B": B}
+    out["X"] = np.stack([b[0].numpy() for b in batches])
+    out["T"] = np.stack([b[3].numpy() for b in batches])
+    out["idx"] = np.stack([np.stack([t.numpy() for t in b[2]]) for b in batches]).astype(np.int32)
+    out["off"] = np.stack([np.stack([t.numpy() for t in b[1]]) for b in batches]).astype(np.int32)
+    fin = _state(net)
+    # pins on the weights: float64 sums of init tables (checks the port's RNG stream) and
+    # the rows of table 2 / table 23 touched in the last step after all updates
+    out["init_table_sums"] = np.array([init[f"emb_l.{t}.weight"].astype(np.float64).sum()
+                                       for t in range(26)])
+    out["final_table_sums"] = np.array([fin[f"emb_l.{t}.weight"].astype(np.float64).sum()
+                                        for t in range(26)])
+    for t in (2, 23):
+        rows = np.unique(out["idx"][-1, t])
+        out[f"rows_t{t}"] = rows
+        out[f"final_rows_t{t}"] = fin[f"emb_l.{t}.weight"][rows]
+    out["final_top0_w"] = fin["top_l.0.weight"][:8]
+    out["final_bot0_w"] = fin["bot_l.0.weight"]
+    np.savez_compressed(os.path.join(OUT, "kaggle_c1.npz"), **out)
+
+
+def gen_lr_policy(M):
+    """LRPolicyScheduler trace (P/dlrm_s_pytorch.py:133-167)."""
+    p = torch.nn.Parameter(torch.zeros(1))
+    cfgs = [(1.0, 5, 8, 6), (18.0, 2, 3, 4), (0.5, 4, 4, 0)]  # warm-up 0 trips an upstream AttributeError (last_lr unset)
+    out = {"cfgs": np.array(cfgs, dtype=np.float64)}
+    for c, (base, warm, start, nsteps) in enumerate(cfgs):
+        opt = torch.optim.SGD([p], lr=base)
+        sch = M.LRPolicyScheduler(opt, warm, start, nsteps)
+        trace = []
+        for _ in range(20):
+            trace.append(sch.get_last_lr()[0])
+            opt.step()
+            sch.step()
+        out[f"trace{c}"] = np.array(trace, dtype=np.float64)
+    np.savez_compressed(os.path.join(OUT, "lr_policy.npz"), **out)
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    G = load_T_generator()
+    M, X = load_P()
+    gen_interaction(M)
+    gen_index_kats(X)
+    gen_lr_policy(M)
+    gen_small_model(M, G)
+    gen_kaggle_c1(M, G)
+    for f in sorted(os.listdir(OUT)):
+        print(f, os.path.getsize(os.path.join(OUT, f)))
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,152 @@
+"""Pin the CPU oracle (oracle/ops_numpy.py, oracle/dlrm_port.py) against the fixtures
+written by oracle/gen_golden.py from the reference's own code (CPU-only tests)."""
+import numpy as np
+import torch
+
+from oracle import ops_numpy as ops
+from oracle.dlrm_port import DLRMPort, train_step
+
+
+def test_interaction_kat(golden):
+    g = golden("interaction")
+    R = ops.interact_fwd(np.array([[1.0, 2.0]]), [np.array([[3.0, 4.0]]), np.array([[5.0, 6.0]])])
+    np.testing.assert_array_equal(R, [[1, 2, 11, 17, 39]])
+    np.testing.assert_array_equal(g["kat_R"], R)
+
+
+def test_interaction_fwd_bwd(golden):
+    g = golden("interaction")
+    for tag in "abc":
+        x, ly = g[f"{tag}_x"], list(g[f"{tag}_ly"])
+        R = ops.interact_fwd(x, ly)
+        np.testing.assert_allclose(R, g[f"{tag}_R"], rtol=1e-5, atol=1e-5)
+        dx, dly = ops.interact_bwd(x, ly, g[f"{tag}_dR"])
+        np.testing.assert_allclose(dx, g[f"{tag}_dx"], rtol=1e-5, atol=2e-5)
+        np.testing.assert_allclose(np.stack(dly), g[f"{tag}_dly"], rtol=1e-5, atol=2e-5)
+
+
+def test_index_kats(golden):
+    g = golden("index_kats")
+    idx, off = g["idx"], g["off"]
+    np.testing.assert_array_equal(ops.offset2bag(off, len(idx)), g["offset2bag"])
+    np.testing.assert_array_equal(ops.bag_lengths(off, len(idx)), g["bag_size"])
+    skeys, perm, uniq, counts, seg = ops.sort_dedup(idx)
+    np.testing.assert_array_equal(skeys, g["sorted"])
+    np.testing.assert_array_equal(perm, g["perm"])
+    np.testing.assert_array_equal(uniq, g["unique"])
+    np.testing.assert_array_equal(uniq, g["coalesced_indices"])
+    np.testing.assert_array_equal(counts, g["counts"])
+    np.testing.assert_array_equal(seg, np.concatenate([[0], np.cumsum(g["counts"])]))
+    ci, cv = ops.embedding_bag_sparse_grad(idx, off, g["gout"])
+    np.testing.assert_array_equal(ci, g["coo_indices"])
+    np.testing.assert_array_equal(cv, g["coo_values"])
+    # coalesced values == per-unique-row sums
+    acc = np.zeros((len(uniq), 4), np.float32)
+    np.add.at(acc, np.searchsorted(uniq, ci), cv)
+    np.testing.assert_allclose(acc, g["coalesced_values"], rtol=1e-6)
+
+
+def test_partition(golden):
+    for row in golden("index_kats")["partition"]:
+        world, rank, n, start, stop, my_len = (int(v) for v in row[:6])
+        sl = ops.get_my_slice(n, world, rank)
+        assert (sl.start, sl.stop) == (start, stop)
+        ml, splits = ops.get_split_lengths(n, world, rank)
+        assert ml == my_len
+        ref = [int(v) for v in row[6:6 + world]]
+        assert (splits is None and ref[0] == -1) or splits == ref
+
+
+def test_lr_policy(golden):
+    g = golden("lr_policy")
+    for c, (base, warm, start, nsteps) in enumerate(g["cfgs"]):
+        last = None
+        for step0, want in enumerate(g[f"trace{c}"]):
+            # get_last_lr() after k scheduler steps was computed at _step_count = k+1
+            lr = ops.lr_policy(step0 + 1, base, int(warm), int(start), int(nsteps), last)
+            last = lr
+            assert abs(lr - want) <= 1e-12 * max(1.0, abs(want)), (c, step0, lr, want)
+
+
+def test_embedding_bag_and_sgd_match_torch():
+    rs = np.random.RandomState(5)
+    W = rs.randn(50, 8).astype(np.float32)
+    idx = rs.randint(0, 50, size=37)
+    off = np.array([0, 3, 3, 10, 10, 20, 37 - 4], dtype=np.int64)
+    E = torch.nn.EmbeddingBag(50, 8, mode="sum", sparse=True, _weight=torch.tensor(W.copy()))
+    out = E(torch.tensor(idx), torch.tensor(off))
+    np.testing.assert_allclose(ops.embedding_bag_sum(W, idx, off), out.detach().numpy(), rtol=1e-6, atol=1e-6)
+    gout = rs.randn(len(off), 8).astype(np.float32)
+    out.backward(torch.tensor(gout))
+    torch.optim.SGD(E.parameters(), lr=0.3).step()
+    W2 = ops.sparse_sgd_update(W.copy(), idx, off, gout, 0.3)
+    np.testing.assert_allclose(W2, E.weight.detach().numpy(), rtol=1e-6, atol=1e-6)
+
+
+def test_adagrad_matches_torch():
+    rs = np.random.RandomState(6)
+    W = rs.randn(30, 4).astype(np.float32)
+    E = torch.nn.EmbeddingBag(30, 4, mode="sum", sparse=True, _weight=torch.tensor(W.copy()))
+    opt = torch.optim.Adagrad(E.parameters(), lr=0.01, eps=1e-10)
+    state = np.zeros_like(W)
+    Wn = W.copy()
+    for _ in range(3):
+        idx = rs.randint(0, 30, size=25)
+        off = np.arange(0, 25, 5, dtype=np.int64)
+        gout = rs.randn(5, 4).astype(np.float32)
+        opt.zero_grad()
+        E(torch.tensor(idx), torch.tensor(off)).backward(torch.tensor(gout))
+        opt.step()
+        ops.sparse_adagrad_update(Wn, state, idx, off, gout, 0.01, 1e-10)
+    np.testing.assert_allclose(Wn, E.weight.detach().numpy(), rtol=1e-5, atol=1e-6)
+
+
+def test_linearize():
+    idx = [np.array([1, 2, 0]), np.array([4, 4]), np.array([], dtype=np.int64)]
+    off = [np.array([0, 1]), np.array([0, 2]), np.array([0, 0])]
+    i, o, w = ops.linearize_indices_and_offsets(idx, off, [3, 5, 7])
+    np.testing.assert_array_equal(i, [1, 2, 0, 4, 4])
+    np.testing.assert_array_equal(o, [0, 1, 3, 5, 5, 5, 5])
+    np.testing.assert_array_equal(w, [1, 2, 0, 7, 7])
+
+
+def _port_from_fixture(g):
+    np.random.seed(int(g["seed"]))
+    torch.manual_seed(int(g["seed"]))
+    return DLRMPort(int(g["D"]), g["ln_emb"], g["ln_bot"], g["ln_top"])
+
+
+def test_port_small_model_bit_exact(golden):
+    g = golden("small_model")
+    net = _port_from_fixture(g)
+    for k, v in net.state_dict().items():
+        np.testing.assert_array_equal(v.numpy(), g["init/" + k])
+    opt = torch.optim.SGD(net.parameters(), lr=float(g["lr"]))
+    nt = len(g["ln_emb"])
+    losses = []
+    for s in range(int(g["steps"])):
+        lS_o = [torch.tensor(g[f"o{s}_{t}"]) for t in range(nt)]
+        lS_i = [torch.tensor(g[f"i{s}_{t}"]) for t in range(nt)]
+        losses.append(train_step(net, opt, torch.tensor(g[f"X{s}"]), lS_o, lS_i, torch.tensor(g[f"T{s}"])))
+    np.testing.assert_array_equal(np.array(losses), g["losses"])
+    for k, v in net.state_dict().items():
+        np.testing.assert_array_equal(v.numpy(), g["final/" + k])
+
+
+def test_port_kaggle_c1_losses(golden):
+    """BASELINE config 1 shape: loss trace of the reference, reproduced by the port."""
+    g = golden("kaggle_c1")
+    net = _port_from_fixture(g)
+    sums = np.array([net.emb_l[t].weight.detach().numpy().astype(np.float64).sum() for t in range(26)])
+    np.testing.assert_array_equal(sums, g["init_table_sums"])
+    opt = torch.optim.SGD(net.parameters(), lr=float(g["lr"]))
+    losses = []
+    for s in range(int(g["steps"])):
+        lS_o = [torch.tensor(g["off"][s, t].astype(np.int64)) for t in range(26)]
+        lS_i = [torch.tensor(g["idx"][s, t].astype(np.int64)) for t in range(26)]
+        losses.append(train_step(net, opt, torch.tensor(g["X"][s]), lS_o, lS_i, torch.tensor(g["T"][s])))
+    np.testing.assert_allclose(np.array(losses), g["losses"], rtol=1e-6)
+    for t in (2, 23):
+        np.testing.assert_allclose(net.emb_l[t].weight.detach().numpy()[g[f"rows_t{t}"]],
+                                   g[f"final_rows_t{t}"], rtol=1e-6, atol=1e-8)
+    np.testing.assert_allclose(net.top_l[0].weight.detach().numpy()[:8], g["final_top0_w"], rtol=1e-5, atol=1e-7)
