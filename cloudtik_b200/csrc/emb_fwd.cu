@@ -1,0 +1,289 @@
+// Sum-pooled EmbeddingBag forward, all tables in one launch (sm_100a).
+//
+// Replaces the 26-iteration Python loop over nn.EmbeddingBag in DLRM_Net.apply_emb
+// (reference P/dlrm_s_pytorch.py:290-305) -- see include/b200dlrm.h.
+//
+// Mapping: grid = (tiles of `tile` consecutive bags, T tables).  A CTA stages its tile of
+// CSR offsets and (when it fits) the tile's window of indices into shared memory with 1-D
+// bulk async copies (TMA engine, mbarrier completion), then sub-warp groups of G lanes own
+// one bag at a time: lane l of a group moves the 16-byte vectors l, l+G, ... of each row
+// (G*16 bytes coalesced per row).  Four bags are in flight per group; one-hot bags take a
+// copy-through path, pooled bags accumulate in fp32 in index order.
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int FWD_THREADS = 256;
+constexpr int FWD_MAX_TILE = 128;  // bags per CTA (upper bound; host picks <= this)
+constexpr int FWD_IDX_CAP = 2048;  // staged index window, int64 entries (16 KB)
+
+struct EmbFwdParams {
+  const void* const* weights;
+  const int64_t* rows;
+  const int64_t* indices;
+  const int64_t* offsets;
+  void* out;
+  int64_t nnz;
+  int64_t B;
+  int64_t out_stride_table;
+  int64_t out_stride_bag;
+  int32_t* error;
+  int D;
+  int V;     // 16-byte vectors per row
+  int tile;  // bags per CTA
+};
+
+template <typename WT, typename OT, int G, int NV>
+__global__ void __launch_bounds__(FWD_THREADS) emb_fwd_kernel(const EmbFwdParams p) {
+  constexpr int VE = Vec16<WT>::VE;
+  constexpr int NG = FWD_THREADS / G;
+  __shared__ __align__(16) int64_t s_off[FWD_MAX_TILE + 2];
+  __shared__ __align__(16) int64_t s_idx[FWD_IDX_CAP + 2];
+  __shared__ __align__(8) uint64_t s_bar;
+
+  const int tid = threadIdx.x;
+  const int t = blockIdx.y;
+  const int64_t b0 = (int64_t)blockIdx.x * p.tile;
+  const int nb = (int)min((int64_t)p.tile, p.B - b0);
+  const int64_t* offp = p.offsets + (int64_t)t * p.B + b0;
+  const int n_off = nb + 1;
+
+  // ---- stage the offsets tile (bulk copy when 16-byte aligned)
+  const bool off_al = (reinterpret_cast<uintptr_t>(offp) & 15) == 0;
+  if (tid == 0) {
+    mbar_init(&s_bar, 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+  if (off_al) {
+    const int nbulk = n_off & ~1;
+    if (tid == 0) {
+      mbar_expect_tx(&s_bar, nbulk * 8);
+      bulk_g2s(s_off, offp, nbulk * 8, &s_bar);
+    }
+    if (tid == 32 && (n_off & 1)) s_off[n_off - 1] = offp[n_off - 1];
+    mbar_wait(&s_bar, 0);
+  } else {
+    for (int i = tid; i < n_off; i += FWD_THREADS) s_off[i] = offp[i];
+  }
+  __syncthreads();
+
+  // ---- stage the index window of this tile
+  const int64_t i0 = s_off[0], i1 = s_off[nb];
+  const int64_t a0 = i0 & ~(int64_t)1;
+  const int64_t a1 = min((i1 + 1) & ~(int64_t)1, p.nnz);
+  const bool idx_al = (reinterpret_cast<uintptr_t>(p.indices) & 15) == 0;
+  const bool staged = idx_al && i1 > i0 && (a1 - a0) <= FWD_IDX_CAP && i0 >= 0 && i1 <= p.nnz;
+  if (staged) {
+    const int cnt = (int)(a1 - a0);
+    const int nbulk = cnt & ~1;
+    if (tid == 0 && nbulk > 0) {
+      mbar_expect_tx(&s_bar, nbulk * 8);
+      bulk_g2s(s_idx, p.indices + a0, nbulk * 8, &s_bar);
+    }
+    if (tid == 32 && (cnt & 1)) s_idx[cnt - 1] = p.indices[a0 + cnt - 1];
+    if (nbulk > 0) mbar_wait(&s_bar, off_al ? 1 : 0);
+    __syncthreads();
+  }
+
+  const int gid = tid / G;
+  const int lane = tid % G;
+  const int64_t nrows = p.rows[t];
+  const char* W = static_cast<const char*>(p.weights[t]);
+  const size_t row_bytes = (size_t)p.D * sizeof(WT);
+  OT* out_t = static_cast<OT*>(p.out) + (int64_t)t * p.out_stride_table + b0 * p.out_stride_bag;
+
+  auto get_idx = [&](int64_t j) -> int64_t {
+    return staged ? s_idx[j - a0] : __ldg(p.indices + j);
+  };
+  auto row_ptr = [&](int64_t idx, bool& ok) -> const char* {
+    ok = (uint64_t)idx < (uint64_t)nrows;
+    if (!ok && p.error) *p.error = 1;
+    return W + (ok ? (size_t)idx : 0) * row_bytes;
+  };
+
+  for (int r = gid; r < nb; r += 4 * NG) {
+    int64_t s[4], e[4];
+    bool onehot = true;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int bag = r + u * NG;
+      const bool valid = bag < nb;
+      s[u] = valid ? s_off[bag] : 0;
+      e[u] = valid ? s_off[bag + 1] : 0;
+      onehot = onehot && (e[u] - s[u] <= 1);
+    }
+    if (onehot) {
+      uint4 v[4][NV];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        bool ok = false;
+        const char* src = nullptr;
+        if (e[u] > s[u]) src = row_ptr(get_idx(s[u]), ok);
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+          const int vi = lane + k * G;
+          v[u][k] = (ok && vi < p.V) ? ld_nc_v4(src + (size_t)vi * 16) : make_uint4(0, 0, 0, 0);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int bag = r + u * NG;
+        if (bag < nb) {
+          OT* dst = out_t + (int64_t)bag * p.out_stride_bag;
+#pragma unroll
+          for (int k = 0; k < NV; ++k) {
+            const int vi = lane + k * G;
+            if (vi < p.V) {
+              float f[VE];
+              Vec16<WT>::unpack(f, v[u][k]);
+              store_vec<OT, VE, true>(dst + vi * VE, f);
+            }
+          }
+        }
+      }
+    } else {
+#pragma unroll 1
+      for (int u = 0; u < 4; ++u) {
+        const int bag = r + u * NG;
+        if (bag >= nb) break;
+        float acc[NV][VE];
+#pragma unroll
+        for (int k = 0; k < NV; ++k)
+#pragma unroll
+          for (int x = 0; x < VE; ++x) acc[k][x] = 0.f;
+        for (int64_t j = s[u]; j < e[u]; j += 4) {
+          uint4 v[4][NV];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            bool ok = false;
+            const char* src = nullptr;
+            if (j + q < e[u]) src = row_ptr(get_idx(j + q), ok);
+#pragma unroll
+            for (int k = 0; k < NV; ++k) {
+              const int vi = lane + k * G;
+              v[q][k] = (ok && vi < p.V) ? ld_nc_v4(src + (size_t)vi * 16) : make_uint4(0, 0, 0, 0);
+            }
+          }
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int k = 0; k < NV; ++k) Vec16<WT>::accum(acc[k], v[q][k]);
+        }
+        OT* dst = out_t + (int64_t)bag * p.out_stride_bag;
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+          const int vi = lane + k * G;
+          if (vi < p.V) store_vec<OT, VE, true>(dst + vi * VE, acc[k]);
+        }
+      }
+    }
+  }
+}
+
+// Fallback for rows that are not a whole number of 16-byte vectors (tiny D in tests).
+template <typename WT, typename OT>
+__global__ void emb_fwd_scalar_kernel(const EmbFwdParams p, int64_t T) {
+  const int64_t n = T * p.B * p.D;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int d = (int)(i % p.D);
+    const int64_t g = i / p.D;
+    const int64_t t = g / p.B, b = g % p.B;
+    const WT* W = static_cast<const WT*>(p.weights[t]);
+    const int64_t nrows = p.rows[t];
+    float acc = 0.f;
+    for (int64_t j = p.offsets[g]; j < p.offsets[g + 1]; ++j) {
+      const int64_t idx = p.indices[j];
+      if ((uint64_t)idx < (uint64_t)nrows) {
+        acc += to_f32<WT>(W[idx * p.D + d]);
+      } else if (p.error) {
+        *p.error = 1;
+      }
+    }
+    static_cast<OT*>(p.out)[t * p.out_stride_table + b * p.out_stride_bag + d] = from_f32<OT>(acc);
+  }
+}
+
+template <typename WT, typename OT>
+static int launch_fwd(const EmbFwdParams& p, int64_t T, cudaStream_t st) {
+  const int V = p.V;
+  dim3 grid((unsigned)ceil_div(p.B, p.tile), (unsigned)T);
+#define B200_FWD_CASE(G, NV) emb_fwd_kernel<WT, OT, G, NV><<<grid, FWD_THREADS, 0, st>>>(p)
+  if (V <= 1) B200_FWD_CASE(1, 1);
+  else if (V <= 2) B200_FWD_CASE(2, 1);
+  else if (V <= 4) B200_FWD_CASE(4, 1);
+  else if (V <= 8) B200_FWD_CASE(8, 1);
+  else if (V <= 16) B200_FWD_CASE(16, 1);
+  else if (V <= 32) B200_FWD_CASE(32, 1);
+  else if (V <= 64) B200_FWD_CASE(32, 2);
+  else B200_FWD_CASE(32, 4);
+#undef B200_FWD_CASE
+  B200_CHECK_LAUNCH("emb_fwd");
+  return B200_OK;
+}
+
+template <typename WT, typename OT>
+static int launch_fwd_scalar(const EmbFwdParams& p, int64_t T, cudaStream_t st) {
+  const int64_t n = T * p.B * p.D;
+  const int blocks = (int)std::min<int64_t>(ceil_div(n, 256), 148 * 16);
+  emb_fwd_scalar_kernel<WT, OT><<<blocks, 256, 0, st>>>(p, T);
+  B200_CHECK_LAUNCH("emb_fwd_scalar");
+  return B200_OK;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_emb_fwd(const void* const* d_weights, const int64_t* d_rows,
+                            const int64_t* d_indices, const int64_t* d_offsets, void* d_out,
+                            int64_t nnz, int64_t T, int64_t B, int64_t D, int64_t out_stride_table,
+                            int64_t out_stride_bag, int w_dtype, int out_dtype, int32_t* d_error,
+                            b200_stream_t stream) {
+  B200_REQUIRE(T >= 0 && B >= 0 && D > 0 && nnz >= 0, B200_EINVAL, "emb_fwd: negative size");
+  if (T == 0 || B == 0) return B200_OK;
+  B200_REQUIRE(d_weights && d_rows && d_offsets && d_out && (d_indices || nnz == 0), B200_EINVAL,
+               "emb_fwd: null pointer");
+  B200_REQUIRE(T <= 65535, B200_EUNSUPPORTED, "emb_fwd: more than 65535 tables");
+  B200_REQUIRE((w_dtype == B200_F32 || w_dtype == B200_BF16) &&
+                   (out_dtype == B200_F32 || out_dtype == B200_BF16),
+               B200_EINVAL, "emb_fwd: bad dtype");
+  EmbFwdParams p;
+  p.weights = d_weights;
+  p.rows = d_rows;
+  p.indices = d_indices;
+  p.offsets = d_offsets;
+  p.out = d_out;
+  p.nnz = nnz;
+  p.B = B;
+  p.out_stride_table = out_stride_table;
+  p.out_stride_bag = out_stride_bag;
+  p.error = d_error;
+  p.D = (int)D;
+  const int ws = dtype_size(w_dtype), os = dtype_size(out_dtype);
+  const int64_t row_bytes = D * ws;
+  p.V = (int)(row_bytes / 16);
+  // bags per CTA: keep the tile's index window inside the staged capacity on average
+  const int64_t avg_pool = (nnz + T * B - 1) / (T * B);
+  int tile = FWD_MAX_TILE;
+  while (tile > 8 && (int64_t)tile * (avg_pool > 0 ? avg_pool : 1) > FWD_IDX_CAP - 2) tile >>= 1;
+  p.tile = tile;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const bool vec_ok = row_bytes % 16 == 0 && p.V <= 128 &&
+                      (reinterpret_cast<uintptr_t>(d_out) & 15) == 0 &&
+                      (out_stride_table * os) % 16 == 0 && (out_stride_bag * os) % 16 == 0;
+  // (table base pointers are 16-byte aligned by construction of any CUDA allocation; a
+  //  misaligned view would fault, so the host wrapper checks it.)
+#define B200_DISPATCH(FN)                                                          \
+  (w_dtype == B200_F32                                                             \
+       ? (out_dtype == B200_F32 ? FN<float, float>(p, T, st)                       \
+                                : FN<float, __nv_bfloat16>(p, T, st))              \
+       : (out_dtype == B200_F32 ? FN<__nv_bfloat16, float>(p, T, st)               \
+                                : FN<__nv_bfloat16, __nv_bfloat16>(p, T, st)))
+  if (vec_ok) return B200_DISPATCH(launch_fwd);
+  return B200_DISPATCH(launch_fwd_scalar);
+#undef B200_DISPATCH
+}

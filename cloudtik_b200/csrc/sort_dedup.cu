@@ -1,0 +1,284 @@
+// Stable LSD radix sort of (key32, val32) pairs + run-length de-duplication (sm_100a).
+//
+// The index stage of the sparse embedding backward: equals torch.sort(stable=True) /
+// torch.unique(return_counts=True) on the global row ids, which is what the reference's
+// `param.add_(sparse_grad)` (optimizer.step, P/dlrm_s_pytorch.py:1059) relies on.
+//
+// Per 8-bit digit pass: (1) per-block digit histogram, (2) exclusive scan of the
+// digit-major [256][nblk] table, (3) stable scatter (warp match-any ranking, no atomics on
+// the data path).  Pure integer work, HBM/L2-bound; tiles are sized so that the whole
+// (key,val) working set of a DLRM batch stays in the 126 MB L2 between passes.
+#include "common.cuh"
+#include "sort_dedup.cuh"
+
+namespace b200 {
+
+// ------------------------------------------------------------------ histogram
+__global__ void __launch_bounds__(SORT_THREADS) radix_hist_kernel(const uint32_t* __restrict__ keys,
+                                                                  int64_t n, int shift,
+                                                                  uint32_t* __restrict__ counts,
+                                                                  int nblk) {
+  __shared__ uint32_t h[256];
+  h[threadIdx.x] = 0;
+  __syncthreads();
+  const int64_t base = (int64_t)blockIdx.x * SORT_CHUNK;
+#pragma unroll 4
+  for (int i = 0; i < SORT_ITEMS; ++i) {
+    const int64_t j = base + i * SORT_THREADS + threadIdx.x;
+    if (j < n) atomicAdd(&h[(keys[j] >> shift) & 255u], 1u);
+  }
+  __syncthreads();
+  counts[(int64_t)threadIdx.x * nblk + blockIdx.x] = h[threadIdx.x];
+}
+
+// ------------------------------------------------------------------ single-block exclusive scan
+// In-place exclusive scan of `total` uint32 values; optionally writes the grand total.
+__global__ void __launch_bounds__(1024) scan_exclusive_kernel(uint32_t* __restrict__ data,
+                                                              int64_t total,
+                                                              int32_t* __restrict__ grand_total) {
+  __shared__ uint32_t warp_sums[32];
+  __shared__ uint32_t carry_s;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) carry_s = 0;
+  __syncthreads();
+  const int64_t per = (total + 1023) / 1024;
+  const int64_t lo = min(total, (int64_t)tid * per), hi = min(total, lo + per);
+  uint32_t sum = 0;
+  for (int64_t i = lo; i < hi; ++i) sum += data[i];
+  // block exclusive scan of per-thread sums
+  uint32_t incl = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  if (lane == 31) warp_sums[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    uint32_t w = warp_sums[lane];
+    uint32_t wi = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t v = __shfl_up_sync(0xffffffffu, wi, o);
+      if (lane >= o) wi += v;
+    }
+    warp_sums[lane] = wi - w;  // exclusive
+    if (lane == 31 && grand_total) *grand_total = (int32_t)wi;
+  }
+  __syncthreads();
+  uint32_t run = warp_sums[warp] + incl - sum;
+  for (int64_t i = lo; i < hi; ++i) {
+    const uint32_t v = data[i];
+    data[i] = run;
+    run += v;
+  }
+}
+
+// ------------------------------------------------------------------ stable scatter
+__global__ void __launch_bounds__(SORT_THREADS)
+    radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                         uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int64_t n,
+                         int shift, const uint32_t* __restrict__ counts, int nblk) {
+  constexpr int NW = SORT_THREADS / 32;
+  constexpr int WCHUNK = SORT_CHUNK / NW;  // keys per warp, contiguous
+  __shared__ uint32_t whist[NW][256];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int i = tid; i < NW * 256; i += SORT_THREADS) (&whist[0][0])[i] = 0;
+  __syncthreads();
+
+  const int64_t wbase = (int64_t)blockIdx.x * SORT_CHUNK + (int64_t)warp * WCHUNK;
+  uint32_t key[SORT_ITEMS], val[SORT_ITEMS], rank[SORT_ITEMS];
+#pragma unroll
+  for (int i = 0; i < SORT_ITEMS; ++i) {
+    const int64_t j = wbase + i * 32 + lane;
+    const bool ok = j < n;
+    key[i] = ok ? keys_in[j] : 0u;
+    val[i] = ok ? vals_in[j] : 0u;
+  }
+  const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+  for (int i = 0; i < SORT_ITEMS; ++i) {
+    const int64_t j = wbase + i * 32 + lane;
+    const bool ok = j < n;
+    const uint32_t d = ok ? ((key[i] >> shift) & 255u) : 0xffffffffu;
+    const uint32_t m = __match_any_sync(0xffffffffu, d);
+    const int leader = __ffs(m) - 1;
+    uint32_t pre = 0;
+    if (ok && lane == leader) {
+      pre = whist[warp][d];
+      whist[warp][d] = pre + __popc(m);
+    }
+    pre = __shfl_sync(0xffffffffu, pre, leader);
+    rank[i] = pre + __popc(m & lt);
+    __syncwarp();
+  }
+  __syncthreads();
+  {  // thread `tid` owns digit `tid`: turn per-warp counts into global start positions
+    uint32_t run = counts[(int64_t)tid * nblk + blockIdx.x];
+#pragma unroll
+    for (int w = 0; w < NW; ++w) {
+      const uint32_t c = whist[w][tid];
+      whist[w][tid] = run;
+      run += c;
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < SORT_ITEMS; ++i) {
+    const int64_t j = wbase + i * 32 + lane;
+    if (j < n) {
+      const uint32_t pos = whist[warp][(key[i] >> shift) & 255u] + rank[i];
+      keys_out[pos] = key[i];
+      vals_out[pos] = val[i];
+    }
+  }
+}
+
+// ------------------------------------------------------------------ run-length dedup
+__device__ __forceinline__ bool is_head(const uint32_t* __restrict__ k, int64_t j) {
+  return j == 0 || k[j] != k[j - 1];
+}
+
+__global__ void __launch_bounds__(DEDUP_THREADS) head_count_kernel(const uint32_t* __restrict__ skeys,
+                                                                   int64_t n,
+                                                                   uint32_t* __restrict__ blk_counts) {
+  __shared__ uint32_t wsum[DEDUP_THREADS / 32];
+  const int64_t base = (int64_t)blockIdx.x * DEDUP_CHUNK;
+  uint32_t c = 0;
+#pragma unroll
+  for (int i = 0; i < DEDUP_ITEMS; ++i) {
+    const int64_t j = base + i * DEDUP_THREADS + threadIdx.x;
+    if (j < n) c += is_head(skeys, j) ? 1u : 0u;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = c;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t s = 0;
+    for (int w = 0; w < DEDUP_THREADS / 32; ++w) s += wsum[w];
+    blk_counts[blockIdx.x] = s;
+  }
+}
+
+__global__ void __launch_bounds__(DEDUP_THREADS)
+    compact_kernel(const uint32_t* __restrict__ skeys, int64_t n, const uint32_t* __restrict__ blk_offsets,
+                   const int32_t* __restrict__ num_unique, uint32_t* __restrict__ unique,
+                   uint32_t* __restrict__ seg) {
+  __shared__ uint32_t wsum[DEDUP_THREADS / 32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int64_t base = (int64_t)blockIdx.x * DEDUP_CHUNK;
+  uint32_t run = blk_offsets[blockIdx.x];
+  if (blockIdx.x == 0 && tid == 0) seg[*num_unique] = (uint32_t)n;
+#pragma unroll 1
+  for (int i = 0; i < DEDUP_ITEMS; ++i) {
+    const int64_t j = base + i * DEDUP_THREADS + tid;
+    const bool h = j < n && is_head(skeys, j);
+    const uint32_t b = __ballot_sync(0xffffffffu, h);
+    if (lane == 0) wsum[warp] = __popc(b);
+    __syncthreads();
+    uint32_t before = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < DEDUP_THREADS / 32; ++w) {
+      const uint32_t c = wsum[w];
+      before += (w < warp) ? c : 0u;
+      total += c;
+    }
+    if (h) {
+      const uint32_t pos = run + before + __popc(b & ((1u << lane) - 1u));
+      unique[pos] = skeys[j];
+      seg[pos] = (uint32_t)j;
+    }
+    run += total;
+    __syncthreads();
+  }
+}
+
+__global__ void empty_result_kernel(uint32_t* seg, int32_t* num_unique) {
+  seg[0] = 0;
+  *num_unique = 0;
+}
+
+// ------------------------------------------------------------------ host drivers
+size_t sort_ws_bytes(int64_t n) {
+  const int64_t nblk = ceil_div(n > 0 ? n : 1, SORT_CHUNK);
+  const int64_t nblk2 = ceil_div(n > 0 ? n : 1, DEDUP_CHUNK);
+  size_t b = 0;
+  b += 4 * align_up((size_t)n * 4, 256);              // keys A/B, vals A/B
+  b += align_up((size_t)256 * nblk * 4, 256);         // digit-major histograms
+  b += align_up((size_t)(nblk2 + 1) * 4, 256);        // dedup block counts
+  return b + 256;
+}
+
+int sort_pairs(const uint32_t* keys, const uint32_t* vals, int64_t n, uint64_t key_bound,
+               uint32_t* out_keys, uint32_t* out_vals, void* ws, cudaStream_t st) {
+  const int nblk = (int)ceil_div(n, SORT_CHUNK);
+  char* w = static_cast<char*>(ws);
+  const size_t stride = align_up((size_t)n * 4, 256);
+  uint32_t* kbuf[2] = {reinterpret_cast<uint32_t*>(w), reinterpret_cast<uint32_t*>(w + stride)};
+  uint32_t* vbuf[2] = {reinterpret_cast<uint32_t*>(w + 2 * stride),
+                       reinterpret_cast<uint32_t*>(w + 3 * stride)};
+  uint32_t* counts = reinterpret_cast<uint32_t*>(w + 4 * stride);
+  int bits = 1;
+  while (bits < 32 && (key_bound - 1) >> bits) ++bits;
+  const int passes = (bits + 7) / 8;
+  const uint32_t* ksrc = keys;
+  const uint32_t* vsrc = vals;
+  for (int pass = 0; pass < passes; ++pass) {
+    uint32_t* kdst = (pass == passes - 1) ? out_keys : kbuf[pass & 1];
+    uint32_t* vdst = (pass == passes - 1) ? out_vals : vbuf[pass & 1];
+    const int shift = pass * 8;
+    radix_hist_kernel<<<nblk, SORT_THREADS, 0, st>>>(ksrc, n, shift, counts, nblk);
+    scan_exclusive_kernel<<<1, 1024, 0, st>>>(counts, (int64_t)256 * nblk, nullptr);
+    radix_scatter_kernel<<<nblk, SORT_THREADS, 0, st>>>(ksrc, vsrc, kdst, vdst, n, shift, counts, nblk);
+    ksrc = kdst;
+    vsrc = vdst;
+  }
+  B200_CHECK_LAUNCH("radix sort");
+  return B200_OK;
+}
+
+int dedup_runs(const uint32_t* skeys, int64_t n, uint32_t* unique, uint32_t* seg, int32_t* num_unique,
+               void* ws, cudaStream_t st) {
+  char* w = static_cast<char*>(ws);
+  const size_t stride = align_up((size_t)n * 4, 256);
+  const int64_t nblk = ceil_div(n, SORT_CHUNK);
+  uint32_t* blk = reinterpret_cast<uint32_t*>(w + 4 * stride + align_up((size_t)256 * nblk * 4, 256));
+  const int nblk2 = (int)ceil_div(n, DEDUP_CHUNK);
+  head_count_kernel<<<nblk2, DEDUP_THREADS, 0, st>>>(skeys, n, blk);
+  scan_exclusive_kernel<<<1, 1024, 0, st>>>(blk, nblk2, num_unique);
+  compact_kernel<<<nblk2, DEDUP_THREADS, 0, st>>>(skeys, n, blk, num_unique, unique, seg);
+  B200_CHECK_LAUNCH("dedup");
+  return B200_OK;
+}
+
+int empty_result(uint32_t* seg, int32_t* num_unique, cudaStream_t st) {
+  empty_result_kernel<<<1, 1, 0, st>>>(seg, num_unique);
+  B200_CHECK_LAUNCH("empty_result");
+  return B200_OK;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" size_t b200_sort_workspace_bytes(int64_t n) { return sort_ws_bytes(n < 0 ? 0 : n); }
+
+extern "C" int b200_sort_dedup(const uint32_t* d_keys, const uint32_t* d_vals, int64_t n,
+                               uint64_t key_bound, uint32_t* d_sorted_keys, uint32_t* d_sorted_vals,
+                               uint32_t* d_unique, uint32_t* d_seg_offsets, int32_t* d_num_unique,
+                               void* ws, size_t ws_bytes, b200_stream_t stream) {
+  B200_REQUIRE(n >= 0, B200_EINVAL, "sort_dedup: negative n");
+  B200_REQUIRE(n < ((int64_t)1 << 31), B200_EUNSUPPORTED, "sort_dedup: n >= 2^31");
+  B200_REQUIRE(key_bound >= 1 && key_bound <= ((uint64_t)1 << 32), B200_EUNSUPPORTED,
+               "sort_dedup: key_bound must be in [1, 2^32]");
+  B200_REQUIRE(d_seg_offsets && d_num_unique, B200_EINVAL, "sort_dedup: null output");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (n == 0) return empty_result(d_seg_offsets, d_num_unique, st);
+  B200_REQUIRE(d_keys && d_vals && d_sorted_keys && d_sorted_vals && d_unique && ws, B200_EINVAL,
+               "sort_dedup: null pointer");
+  B200_REQUIRE(ws_bytes >= sort_ws_bytes(n), B200_EWORKSPACE, "sort_dedup: workspace too small");
+  int rc = sort_pairs(d_keys, d_vals, n, key_bound, d_sorted_keys, d_sorted_vals, ws, st);
+  if (rc) return rc;
+  return dedup_runs(d_sorted_keys, n, d_unique, d_seg_offsets, d_num_unique, ws, st);
+}

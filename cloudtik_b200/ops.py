@@ -1,0 +1,166 @@
+"""Functional wrappers: torch CUDA tensors -> C-ABI calls (pointers, sizes, current stream).
+
+torch is used here only for device memory and streams.  Every function raises
+``B200Error`` on a non-zero status; nothing falls back to torch or to the CPU.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+from ._lib import BF16, F32, OPT_ADAGRAD, OPT_SGD, check, lib
+
+
+def _dt(t: torch.dtype) -> int:
+    if t == torch.float32:
+        return F32
+    if t == torch.bfloat16:
+        return BF16
+    raise _lib.B200Error(f"unsupported dtype {t} (float32 / bfloat16 only)")
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _cuda(t: torch.Tensor, name: str, dtype=None):
+    if not t.is_cuda:
+        raise _lib.B200Error(f"{name} must be a CUDA tensor (no CPU path)")
+    if dtype is not None and t.dtype != dtype:
+        raise _lib.B200Error(f"{name} must be {dtype}, got {t.dtype}")
+    return t
+
+
+class TableSet:
+    """Device-side description of a list of embedding tables [rows_t, D] (same D, same dtype)."""
+
+    def __init__(self, weights, states=None):
+        assert len(weights) > 0
+        w0 = weights[0]
+        self.weights = list(weights)
+        self.D = int(w0.shape[1])
+        self.dtype = w0.dtype
+        self.device = w0.device
+        for w in weights:
+            _cuda(w, "weight")
+            if w.dtype != self.dtype or w.shape[1] != self.D or not w.is_contiguous():
+                raise _lib.B200Error("all tables must be contiguous with the same dim and dtype")
+            if w.data_ptr() % 16:
+                raise _lib.B200Error("table base pointers must be 16-byte aligned")
+        rows = [int(w.shape[0]) for w in weights]
+        self.rows = rows
+        self.total_rows = sum(rows)
+        base = [0]
+        for r in rows:
+            base.append(base[-1] + r)
+        self.d_ptrs = torch.tensor([w.data_ptr() for w in weights], dtype=torch.int64, device=self.device)
+        self.d_rows = torch.tensor(rows, dtype=torch.int64, device=self.device)
+        self.d_row_base = torch.tensor(base, dtype=torch.int64, device=self.device)
+        self.states = None
+        self.d_state_ptrs = None
+        if states is not None:
+            self.set_states(states)
+
+    def set_states(self, states):
+        for s, w in zip(states, self.weights):
+            _cuda(s, "state", torch.float32)
+            assert s.shape == w.shape and s.is_contiguous()
+        self.states = list(states)
+        self.d_state_ptrs = torch.tensor([s.data_ptr() for s in states], dtype=torch.int64, device=self.device)
+
+    def __len__(self):
+        return len(self.weights)
+
+
+def emb_fwd(tables: TableSet, indices, offsets, B: int, out: torch.Tensor, stride_table: int,
+            stride_bag: int, error: torch.Tensor | None = None):
+    """out[t*stride_table + b*stride_bag + :D] = sum of rows of bag (t, b).  See b200_emb_fwd."""
+    _cuda(indices, "indices", torch.int64)
+    _cuda(offsets, "offsets", torch.int64)
+    _cuda(out, "out")
+    T = len(tables)
+    if offsets.numel() != T * B + 1:
+        raise _lib.B200Error(f"offsets must have T*B+1 = {T * B + 1} entries, got {offsets.numel()}")
+    check(lib.b200_emb_fwd(tables.d_ptrs.data_ptr(), tables.d_rows.data_ptr(), indices.data_ptr(),
+                           offsets.data_ptr(), out.data_ptr(), indices.numel(), T, B, tables.D,
+                           stride_table, stride_bag, _dt(tables.dtype), _dt(out.dtype),
+                           error.data_ptr() if error is not None else None, _stream()), "b200_emb_fwd")
+    return out
+
+
+def sort_workspace_bytes(n: int) -> int:
+    return int(lib.b200_sort_workspace_bytes(n))
+
+
+def sort_dedup(keys: torch.Tensor, vals: torch.Tensor, key_bound: int):
+    """Stable sort of (key, val) uint32 pairs (given as int32/uint32-bit-pattern tensors) and
+    run-length dedup.  Returns (sorted_keys, sorted_vals, unique, seg_offsets, num_unique) with
+    unique / seg_offsets trimmed on the host (this helper synchronises; the fused backward does not)."""
+    n = keys.numel()
+    dev = keys.device
+    _cuda(keys, "keys", torch.int32)
+    _cuda(vals, "vals", torch.int32)
+    skeys = torch.empty(n, dtype=torch.int32, device=dev)
+    svals = torch.empty(n, dtype=torch.int32, device=dev)
+    uniq = torch.empty(n, dtype=torch.int32, device=dev)
+    seg = torch.empty(n + 1, dtype=torch.int32, device=dev)
+    nu = torch.zeros(1, dtype=torch.int32, device=dev)
+    ws_bytes = sort_workspace_bytes(n)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+    check(lib.b200_sort_dedup(keys.data_ptr(), vals.data_ptr(), n, key_bound, skeys.data_ptr(),
+                              svals.data_ptr(), uniq.data_ptr(), seg.data_ptr(), nu.data_ptr(),
+                              ws.data_ptr(), ws_bytes, _stream()), "b200_sort_dedup")
+    U = int(nu.item())
+    return skeys, svals, uniq[:U], seg[:U + 1], U
+
+
+def emb_bwd_workspace_bytes(nnz: int) -> int:
+    return int(lib.b200_emb_bwd_workspace_bytes(nnz))
+
+
+def emb_bwd_update(tables: TableSet, indices, offsets, B: int, grad: torch.Tensor, stride_table: int,
+                   stride_bag: int, lr: float, ws: torch.Tensor, optimizer: int = OPT_SGD,
+                   eps: float = 1e-10, lr_tensor: torch.Tensor | None = None,
+                   error: torch.Tensor | None = None):
+    """Fused sparse backward + row update.  See b200_emb_bwd_update."""
+    _cuda(indices, "indices", torch.int64)
+    _cuda(offsets, "offsets", torch.int64)
+    _cuda(grad, "grad")
+    T = len(tables)
+    if optimizer == OPT_ADAGRAD and tables.d_state_ptrs is None:
+        raise _lib.B200Error("Adagrad needs per-table fp32 state (TableSet.set_states)")
+    check(lib.b200_emb_bwd_update(
+        tables.d_ptrs.data_ptr(),
+        tables.d_state_ptrs.data_ptr() if tables.d_state_ptrs is not None else None,
+        tables.d_rows.data_ptr(), tables.d_row_base.data_ptr(), indices.data_ptr(), offsets.data_ptr(),
+        indices.numel(), grad.data_ptr(), T, B, tables.D, stride_table, stride_bag, _dt(tables.dtype),
+        _dt(grad.dtype), optimizer, float(lr), lr_tensor.data_ptr() if lr_tensor is not None else None,
+        float(eps), tables.total_rows, ws.data_ptr(), ws.numel() * ws.element_size(),
+        error.data_ptr() if error is not None else None, _stream()), "b200_emb_bwd_update")
+
+
+def interact_fwd(T: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+    """T [B, F, D] contiguous -> R [B, D + F(F-1)/2].  See b200_interact_fwd."""
+    _cuda(T, "T")
+    if T.dim() != 3 or not T.is_contiguous():
+        raise _lib.B200Error("interact_fwd: T must be a contiguous [B, F, D] tensor")
+    B, F, D = T.shape
+    if out is None:
+        out = torch.empty(B, D + F * (F - 1) // 2, dtype=T.dtype, device=T.device)
+    check(lib.b200_interact_fwd(T.data_ptr(), out.data_ptr(), B, F, D, _dt(T.dtype), _stream()),
+          "b200_interact_fwd")
+    return out
+
+
+def interact_bwd(T: torch.Tensor, dR: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+    """dT [B, F, D] from T and dR [B, D + F(F-1)/2].  See b200_interact_bwd."""
+    _cuda(T, "T")
+    _cuda(dR, "dR", T.dtype)
+    B, F, D = T.shape
+    if not T.is_contiguous() or not dR.is_contiguous() or tuple(dR.shape) != (B, D + F * (F - 1) // 2):
+        raise _lib.B200Error("interact_bwd: bad shapes / non-contiguous input")
+    if out is None:
+        out = torch.empty_like(T)
+    check(lib.b200_interact_bwd(T.data_ptr(), dR.data_ptr(), out.data_ptr(), B, F, D, _dt(T.dtype), _stream()),
+          "b200_interact_bwd")
+    return out

@@ -1,0 +1,125 @@
+/*
+ * b200dlrm.h -- C ABI of the B200-native DLRM training hot path.
+ *
+ * Drop-in boundary: these entry points are what a binding for the
+ * reference's DLRM step would call in place of the ATen / IPEX operators it uses today.
+ * Reference paths: P/ = applications/ai/quickstart/models/recommendation/pytorch/dlrm/product,
+ * T/ = .../dlrm/training/bfloat16.
+ *
+ * Conventions
+ *   - plain C: raw DEVICE pointers, int64_t sizes, dtype enum, a CUDA stream handle.
+ *   - every function returns an int status (0 = ok); no exception crosses the ABI.
+ *     b200_last_error() returns a thread-local message for the last non-zero status.
+ *   - the caller owns every buffer, including workspace (sizes from *_workspace_bytes).
+ *   - calls are stream-ordered, never synchronise, never allocate: they may be captured
+ *     in a CUDA graph.  The library keeps no global device state.
+ *   - element strides are in ELEMENTS of the buffer's dtype.
+ */
+#ifndef B200DLRM_H_
+#define B200DLRM_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct CUstream_st* b200_stream_t; /* == cudaStream_t */
+
+enum { B200_F32 = 0, B200_BF16 = 1 };
+
+enum {
+  B200_OK = 0,
+  B200_EINVAL = 1,       /* bad argument (null pointer, negative size, misaligned buffer) */
+  B200_EUNSUPPORTED = 2, /* valid but not implemented shape / dtype */
+  B200_EWORKSPACE = 3,   /* workspace too small */
+  B200_ELAUNCH = 4       /* CUDA launch error */
+};
+
+/* optimiser selector for b200_emb_bwd_update */
+enum { B200_OPT_SGD = 0, B200_OPT_ADAGRAD = 1 };
+
+const char* b200_last_error(void);
+int b200_version(void);
+
+/*
+ * Sum-pooled EmbeddingBag forward over ALL tables in one launch.
+ * Replaces the per-table loop `V = E(sparse_index_group_batch, sparse_offset_group_batch)` of
+ * DLRM_Net.apply_emb (P/dlrm_s_pytorch.py:290-305, T/dlrm_s_pytorch.py:383-405) and the forward
+ * half of ipex MergedEmbeddingBagWithSGD (call site P/dlrm_s_pytorch.py:288-289).
+ *
+ *   d_weights   device array [T] of table base pointers, table t is [rows_t, D] row-major
+ *   d_rows      device array [T] of row counts (for the optional bounds check)
+ *   d_indices   int64 [nnz]  table-local row ids, tables concatenated in order
+ *   d_offsets   int64 [T*B+1] CSR row pointers over all T*B bags (bag g = t*B + b)
+ *   d_out       out[t*out_stride_table + b*out_stride_bag + d]; an empty bag gives zeros
+ *   d_error     optional int32[1]; set to 1 if an index is out of range (the row is then
+ *               skipped). May be NULL.
+ */
+int b200_emb_fwd(const void* const* d_weights, const int64_t* d_rows, const int64_t* d_indices,
+                 const int64_t* d_offsets, void* d_out, int64_t nnz, int64_t T, int64_t B, int64_t D,
+                 int64_t out_stride_table, int64_t out_stride_bag, int w_dtype, int out_dtype,
+                 int32_t* d_error, b200_stream_t stream);
+
+/*
+ * Stable sort + run-length de-duplication of global row ids: the index stage of the sparse
+ * backward.  Equals torch.sort(stable=True) / torch.unique(return_counts=True) /
+ * sparse.coalesce().indices() which the reference reaches through
+ * `optimizer.step()` -> `param.add_(sparse_grad)` (P/dlrm_s_pytorch.py:1059).
+ *
+ *   d_keys        uint32 [n] keys (global row ids < key_bound)
+ *   d_vals        uint32 [n] payload carried through the sort (position or bag id)
+ *   outputs       d_sorted_keys[n], d_sorted_vals[n], d_unique[n], d_seg_offsets[n+1]
+ *                 (first *d_num_unique(+1) entries valid), d_num_unique int32[1]
+ *   ws            workspace of b200_sort_workspace_bytes(n) bytes
+ */
+size_t b200_sort_workspace_bytes(int64_t n);
+int b200_sort_dedup(const uint32_t* d_keys, const uint32_t* d_vals, int64_t n, uint64_t key_bound,
+                    uint32_t* d_sorted_keys, uint32_t* d_sorted_vals, uint32_t* d_unique,
+                    uint32_t* d_seg_offsets, int32_t* d_num_unique, void* ws, size_t ws_bytes,
+                    b200_stream_t stream);
+
+/*
+ * EmbeddingBag backward fused with the optimiser row update; never materialises the
+ * [nnz, D] COO gradient.  Replaces autograd's _embedding_bag_sparse_backward (triggered by
+ * E.backward(), P/dlrm_s_pytorch.py:1055) + torch.optim.SGD.step on the sparse grads
+ * (P/dlrm_s_pytorch.py:805,1059; lr/world for sharded tables T/dlrm_s_pytorch.py:1020-1031)
+ * and the backward half of ipex MergedEmbeddingBagWithSGD (P/dlrm_s_pytorch.py:801,1027).
+ * Adagrad follows torch.optim.Adagrad's sparse branch (no call site in the reference).
+ *
+ *   d_row_base  int64 [T+1] exclusive prefix sum of table row counts
+ *   d_grad      grad of the pooled output, addressed like d_out of b200_emb_fwd
+ *   d_state     Adagrad: device array [T] of fp32 state_sum tables; SGD: NULL
+ *   lr / d_lr   learning rate by value, or (if d_lr != NULL) read from device memory at
+ *               kernel time so a captured graph follows the LR schedule
+ *   ws          b200_emb_bwd_workspace_bytes(nnz) bytes
+ */
+size_t b200_emb_bwd_workspace_bytes(int64_t nnz);
+int b200_emb_bwd_update(void* const* d_weights, float* const* d_state, const int64_t* d_rows,
+                        const int64_t* d_row_base, const int64_t* d_indices,
+                        const int64_t* d_offsets, int64_t nnz, const void* d_grad, int64_t T,
+                        int64_t B, int64_t D, int64_t grad_stride_table, int64_t grad_stride_bag,
+                        int w_dtype, int grad_dtype, int optimizer, float lr, const float* d_lr,
+                        float eps, int64_t total_rows, void* ws, size_t ws_bytes, int32_t* d_error,
+                        b200_stream_t stream);
+
+/*
+ * Pairwise dot-product feature interaction, forward and backward.
+ * Replaces DLRM_Net.interact_features (P/dlrm_s_pytorch.py:309-334, T/dlrm_s_pytorch.py:407-444;
+ * cat + bmm + tril gather + cat) and ipex.nn.functional.interaction(*T) (P/dlrm_s_pytorch.py:312).
+ *
+ *   d_T   [B, F, D] contiguous: feature 0 is the bottom-MLP output x, 1..F-1 the pooled rows
+ *   d_R   [B, D + F(F-1)/2]: R[b] = [x_b, <T_i,T_j> for i in 1..F-1 for j in 0..i-1]
+ *   bwd:  d_dT[B, F, D] = (dZ + dZ^t) T with dZ scattered from d_dR[:, D:], plus d_dR[:, :D]
+ *         added into feature 0.
+ */
+int b200_interact_fwd(const void* d_T, void* d_R, int64_t B, int64_t F, int64_t D, int dtype,
+                      b200_stream_t stream);
+int b200_interact_bwd(const void* d_T, const void* d_dR, void* d_dT, int64_t B, int64_t F,
+                      int64_t D, int dtype, b200_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200DLRM_H_ */

@@ -1,0 +1,222 @@
+"""GPU parity tests of the C-ABI kernels against the CPU oracle (oracle/ops_numpy.py).
+
+Tolerances (BASELINE.json north_star): bit-exact for index sort / dedup / bucketing;
+<= 1e-5 relative for fp32 sums / updates, <= 1e-2 for bf16.
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import ops_numpy as ref
+
+pytestmark = pytest.mark.gpu
+
+RTOL32, ATOL32 = 1e-5, 1e-6
+RTOL16, ATOL16 = 1e-2, 1e-2
+
+
+def _ops():
+    from cloudtik_b200 import ops
+    return ops
+
+
+def _make_bags(rs, rows, B, pooling, ragged):
+    """Per-table (indices, offsets) lists; ragged => random lengths in [0, 2*pooling]."""
+    idx_l, off_l = [], []
+    for n in rows:
+        if ragged:
+            lens = rs.randint(0, 2 * pooling + 1, size=B)
+        else:
+            lens = np.full(B, pooling)
+        off = np.concatenate([[0], np.cumsum(lens)[:-1]]).astype(np.int64)
+        idx_l.append(rs.randint(0, n, size=int(lens.sum())).astype(np.int64))
+        off_l.append(off)
+    return idx_l, off_l
+
+
+def _tables(rs, rows, D, dtype):
+    Ws = [rs.uniform(-1, 1, size=(n, D)).astype(np.float32) for n in rows]
+    tw = [torch.tensor(W).to(dtype).cuda() for W in Ws]
+    Wr = [t.float().cpu().numpy() for t in tw]  # the values actually stored (bf16-rounded)
+    return Wr, tw
+
+
+FWD_CASES = [
+    # rows, B, D, pooling, ragged, wdtype, odtype
+    ([1000, 37, 5000], 257, 128, 1, False, torch.float32, torch.float32),
+    ([1000, 37, 5000], 300, 128, 6, True, torch.float32, torch.float32),
+    ([64, 64], 130, 16, 1, False, torch.float32, torch.float32),
+    ([64, 64], 33, 8, 3, True, torch.float32, torch.float32),
+    ([50, 20, 10], 7, 2, 2, True, torch.float32, torch.float32),      # scalar path
+    ([500, 700], 129, 64, 1, False, torch.bfloat16, torch.bfloat16),
+    ([500, 700], 64, 128, 40, True, torch.bfloat16, torch.float32),
+    ([500], 100, 128, 4, True, torch.float32, torch.bfloat16),
+    ([300, 200], 50, 256, 2, True, torch.float32, torch.float32),      # NV=2
+    ([300], 40, 512, 1, False, torch.float32, torch.float32),          # NV=4
+    ([2000], 64, 128, 200, False, torch.float32, torch.float32),       # long bags, unstaged indices
+    ([100, 100], 5, 24, 2, True, torch.float32, torch.float32),        # V=6 (non power of two)
+]
+
+
+@pytest.mark.parametrize("rows,B,D,pooling,ragged,wdt,odt", FWD_CASES)
+def test_emb_fwd(rows, B, D, pooling, ragged, wdt, odt):
+    ops = _ops()
+    rs = np.random.RandomState(len(rows) * 1000 + B + D)
+    Wr, tw = _tables(rs, rows, D, wdt)
+    idx_l, off_l = _make_bags(rs, rows, B, pooling, ragged)
+    indices, offsets, _ = ref.linearize_indices_and_offsets(idx_l, off_l, rows)
+    ts = ops.TableSet(tw)
+    T = len(rows)
+    F = T + 1
+    # strided [B, F, D] layout (slot 0 reserved for the dense feature) ...
+    buf = torch.full((B, F, D), 7.0, dtype=odt, device="cuda")
+    err = torch.zeros(1, dtype=torch.int32, device="cuda")
+    ops.emb_fwd(ts, torch.tensor(indices).cuda(), torch.tensor(offsets).cuda(), B, buf[:, 1:], D, F * D, err)
+    # ... and table-major contiguous [T, B, D]
+    out2 = torch.empty((T, B, D), dtype=odt, device="cuda")
+    ops.emb_fwd(ts, torch.tensor(indices).cuda(), torch.tensor(offsets).cuda(), B, out2, B * D, D, err)
+    torch.cuda.synchronize()
+    assert int(err.item()) == 0
+    got = buf.float().cpu().numpy()
+    got2 = out2.float().cpu().numpy()
+    assert (got[:, 0] == 7.0).all(), "slot 0 must be untouched"
+    rtol, atol = (RTOL32, ATOL32) if odt == torch.float32 else (RTOL16, ATOL16)
+    for t in range(T):
+        want = ref.embedding_bag_sum(Wr[t], idx_l[t], off_l[t])
+        np.testing.assert_allclose(got[:, 1 + t], want, rtol=rtol, atol=atol * pooling)
+        np.testing.assert_array_equal(got[:, 1 + t], got2[t])
+
+
+def test_emb_fwd_flags_bad_index():
+    ops = _ops()
+    tw = [torch.ones(10, 128, device="cuda")]
+    ts = ops.TableSet(tw)
+    idx = torch.tensor([1, 99, 2], device="cuda")
+    off = torch.tensor([0, 1, 2, 3], device="cuda")
+    err = torch.zeros(1, dtype=torch.int32, device="cuda")
+    out = torch.empty(3, 128, device="cuda")
+    ops.emb_fwd(ts, idx, off, 3, out, 3 * 128, 128, err)
+    torch.cuda.synchronize()
+    assert int(err.item()) == 1
+    assert out[0].eq(1).all() and out[1].eq(0).all() and out[2].eq(1).all()
+
+
+def _i32(a):
+    return torch.tensor(np.asarray(a, dtype=np.uint32).view(np.int32)).cuda()
+
+
+def _u32(t):
+    return t.cpu().numpy().view(np.uint32).astype(np.int64)
+
+
+@pytest.mark.parametrize("n,bound", [(0, 10), (1, 1), (31, 7), (4096, 200), (4097, 70000), (100003, 1 << 20),
+                                     (50000, 187_000_000), (70000, 1 << 32), (300000, 1000)])
+def test_sort_dedup_bit_exact(n, bound):
+    ops = _ops()
+    rs = np.random.RandomState(n % 9973 + 1)
+    keys = rs.randint(0, bound, size=n, dtype=np.int64)
+    vals = np.arange(n, dtype=np.int64)
+    sk, sv, uq, seg, U = ops.sort_dedup(_i32(keys), _i32(vals), bound)
+    wk, wperm, wuq, wcnt, wseg = ref.sort_dedup(keys)
+    np.testing.assert_array_equal(_u32(sk), wk)
+    np.testing.assert_array_equal(_u32(sv), wperm)   # payload = position => the stable permutation
+    assert U == len(wuq)
+    np.testing.assert_array_equal(_u32(uq), wuq)
+    np.testing.assert_array_equal(_u32(seg), wseg)
+    np.testing.assert_array_equal(np.diff(_u32(seg)), wcnt)
+
+
+def test_sort_dedup_golden_kat(golden):
+    ops = _ops()
+    g = golden("index_kats")
+    keys = g["idx"]
+    sk, sv, uq, seg, U = ops.sort_dedup(_i32(keys), _i32(np.arange(len(keys))), 10)
+    np.testing.assert_array_equal(_u32(sk), g["sorted"])
+    np.testing.assert_array_equal(_u32(sv), g["perm"])
+    np.testing.assert_array_equal(_u32(uq), g["coalesced_indices"])
+    np.testing.assert_array_equal(np.diff(_u32(seg)), g["counts"])
+
+
+BWD_CASES = [
+    # rows, B, D, pooling, ragged, wdtype, gdtype, opt
+    ([1000, 37, 5000], 257, 128, 1, False, torch.float32, torch.float32, "sgd"),
+    ([50, 37, 20], 300, 128, 6, True, torch.float32, torch.float32, "sgd"),       # heavy duplicates
+    ([64, 64], 130, 16, 1, False, torch.float32, torch.float32, "sgd"),
+    ([50, 20, 10], 7, 2, 2, True, torch.float32, torch.float32, "sgd"),           # scalar path
+    ([500, 700], 129, 64, 2, True, torch.bfloat16, torch.bfloat16, "sgd"),
+    ([500, 700], 129, 128, 2, True, torch.float32, torch.bfloat16, "sgd"),
+    ([500], 100, 128, 3, True, torch.bfloat16, torch.float32, "sgd"),
+    ([300, 200], 50, 256, 2, True, torch.float32, torch.float32, "sgd"),
+    ([1000, 37, 5000], 257, 128, 4, True, torch.float32, torch.float32, "adagrad"),
+    ([40, 30], 64, 8, 3, True, torch.float32, torch.float32, "adagrad"),
+    ([50, 20, 10], 7, 2, 2, True, torch.float32, torch.float32, "adagrad"),
+]
+
+
+@pytest.mark.parametrize("rows,B,D,pooling,ragged,wdt,gdt,opt", BWD_CASES)
+def test_emb_bwd_update(rows, B, D, pooling, ragged, wdt, gdt, opt):
+    ops = _ops()
+    rs = np.random.RandomState(len(rows) * 77 + B + D)
+    Wr, tw = _tables(rs, rows, D, wdt)
+    idx_l, off_l = _make_bags(rs, rows, B, pooling, ragged)
+    indices, offsets, _ = ref.linearize_indices_and_offsets(idx_l, off_l, rows)
+    T = len(rows)
+    F = T + 1
+    g = torch.tensor(rs.randn(B, F, D).astype(np.float32)).to(gdt).cuda()
+    gr = g.float().cpu().numpy()
+    ts = ops.TableSet(tw)
+    lr = 0.3
+    states_np = None
+    if opt == "adagrad":
+        st = [torch.tensor(rs.rand(n, D).astype(np.float32)).cuda() for n in rows]
+        states_np = [s.cpu().numpy().copy() for s in st]
+        ts.set_states(st)
+    ws = torch.empty(ops.emb_bwd_workspace_bytes(len(indices)), dtype=torch.uint8, device="cuda")
+    err = torch.zeros(1, dtype=torch.int32, device="cuda")
+    lr_t = torch.tensor([lr], device="cuda")
+    ops.emb_bwd_update(ts, torch.tensor(indices).cuda(), torch.tensor(offsets).cuda(), B, g[:, 1:], D, F * D,
+                       lr=123.0, ws=ws, optimizer=ops.OPT_ADAGRAD if opt == "adagrad" else ops.OPT_SGD,
+                       eps=1e-10, lr_tensor=lr_t, error=err)  # device lr must win over the by-value one
+    torch.cuda.synchronize()
+    assert int(err.item()) == 0
+    rtol, atol = (RTOL32, ATOL32 * 10) if wdt == torch.float32 else (RTOL16, ATOL16)
+    for t in range(T):
+        W = Wr[t].copy()
+        if opt == "adagrad":
+            ref.sparse_adagrad_update(W, states_np[t], idx_l[t], off_l[t], gr[:, 1 + t], lr, 1e-10)
+            np.testing.assert_allclose(ts.states[t].cpu().numpy(), states_np[t], rtol=1e-5, atol=1e-6)
+        else:
+            ref.sparse_sgd_update(W, idx_l[t], off_l[t], gr[:, 1 + t], lr)
+        np.testing.assert_allclose(tw[t].float().cpu().numpy(), W, rtol=rtol, atol=atol)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_interaction_golden(golden, dtype):
+    ops = _ops()
+    g = golden("interaction")
+    for tag in "abc":
+        x, ly = g[f"{tag}_x"], g[f"{tag}_ly"]
+        T = torch.tensor(np.concatenate([x[:, None], ly.transpose(1, 0, 2)], axis=1)).to(dtype).cuda().contiguous()
+        R = ops.interact_fwd(T)
+        dR = torch.tensor(g[f"{tag}_dR"]).to(dtype).cuda()
+        dT = ops.interact_bwd(T, dR)
+        torch.cuda.synchronize()
+        if dtype == torch.float32:
+            np.testing.assert_allclose(R.cpu().numpy(), g[f"{tag}_R"], rtol=1e-5, atol=1e-5)
+            np.testing.assert_allclose(dT[:, 0].cpu().numpy(), g[f"{tag}_dx"], rtol=1e-5, atol=5e-5)
+            np.testing.assert_allclose(dT[:, 1:].cpu().numpy().transpose(1, 0, 2), g[f"{tag}_dly"], rtol=1e-5, atol=5e-5)
+        else:
+            Tf = T.float().cpu().numpy()
+            want = ref.interact_fwd(Tf[:, 0], [Tf[:, k] for k in range(1, Tf.shape[1])])
+            scale = np.abs(want).max()
+            np.testing.assert_allclose(R.float().cpu().numpy(), want, rtol=1e-2, atol=1e-2 * scale)
+            dx, dly = ref.interact_bwd(Tf[:, 0], [Tf[:, k] for k in range(1, Tf.shape[1])], dR.float().cpu().numpy())
+            wdT = np.stack([dx] + dly, axis=1)
+            np.testing.assert_allclose(dT.float().cpu().numpy(), wdT, rtol=1e-2, atol=1e-2 * np.abs(wdT).max())
+
+
+def test_interaction_kat():
+    ops = _ops()
+    T = torch.tensor([[[1.0, 2.0], [3.0, 4.0], [5.0, 6.0]]], device="cuda")
+    R = ops.interact_fwd(T)
+    assert R.cpu().tolist() == [[1.0, 2.0, 11.0, 17.0, 39.0]]
