@@ -1,0 +1,342 @@
+#!/usr/bin/env python
+"""DLRM training-step benchmark (BASELINE.json metric: DLRM train samples/sec; EmbeddingBag HBM GB/s).
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--dtype bf16|fp32]
+
+Workload at N=1: BASELINE config 3 -- DLRM Criteo-Terabyte shape: 26 tables (MLPerf cardinalities
+under the 40M cap, 187.8M rows, 96 GB fp32), D=128, bottom 13-512-256-128, top 479-1024-1024-512-256-1,
+batch 32768, one-hot, SGD, BCE; synthetic uniform indices, random-init weights.
+At N>1 (config 4 family): tables sharded table-wise over ranks (ext_dist.get_my_slice), pooled
+all-to-all + DDP allreduce over NCCL, 32768 samples PER GPU (weak scaling; N=2 is exactly the
+64K global batch of config 4).
+
+A "step" = forward + BCE loss + backward + update (fused sparse SGD on the tables inside backward,
+torch SGD on the MLPs).  `value` = samples/s with inputs resident in HBM; `e2e` = the same through
+the public module API with inputs in pinned HOST memory (H2D every step) and the loss read back
+(D2H) every step.  Rank 0 prints ONE JSON line.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+# MLPerf Criteo-1TB cardinalities under --max-ind-range=40000000
+C3_ROWS = [39884406, 39043, 17289, 7420, 20263, 3, 7120, 1543, 63, 38532951, 2953546, 403346, 10, 2208,
+           11938, 155, 4, 976, 14, 39979771, 25641295, 39664984, 585935, 12972, 108, 36]
+D = 128
+LN_BOT = [13, 512, 256, D]
+LN_TOP = [D + 27 * 26 // 2, 1024, 1024, 512, 256, 1]
+LR = 1.0  # QS/scripts/recommendation/pytorch/dlrm/training/cpu/training.sh:83-93
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--batch", type=int, default=32768, help="samples per GPU")
+    ap.add_argument("--rows-cap", type=int, default=0, help="debug: cap table rows (0 = full config 3)")
+    ap.add_argument("--sets", type=int, default=4, help="distinct synthetic batches rotated")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-rows-cap", type=int, default=200000)
+    ap.add_argument("--cpu-steps", type=int, default=3)
+    return ap.parse_args()
+
+
+def table_rows(cap):
+    return [min(r, cap) if cap else r for r in C3_ROWS]
+
+
+# ------------------------------------------------------------------ CPU reference arm / baseline
+def cpu_reference_run(batch, rows_cap, steps, warmup, bf16, threads=None):
+    """The reference's own CPU implementation of the step, as restated in oracle/dlrm_port.py
+    (the reference tree itself is not on the GPU box).  All host threads torch can use."""
+    from oracle.dlrm_port import DLRMPort, train_step, uniform_batch
+    if threads:
+        torch.set_num_threads(threads)
+    rows = table_rows(rows_cap)
+    np.random.seed(727)
+    net = DLRMPort(D, rows, LN_BOT, LN_TOP)
+    opt = torch.optim.SGD(net.parameters(), lr=LR)
+    rs = np.random.RandomState(727)
+    X, lS_o, lS_i, T = uniform_batch(rs, batch, rows, pooling=1)
+    X, T = torch.tensor(X), torch.tensor(T)
+    lS_o = [torch.tensor(o) for o in lS_o]
+    lS_i = [torch.tensor(i) for i in lS_i]
+    for _ in range(warmup):
+        train_step(net, opt, X, lS_o, lS_i, T, bf16=bf16)
+    t0 = time.time()
+    for _ in range(steps):
+        train_step(net, opt, X, lS_o, lS_i, T, bf16=bf16)
+    dt = (time.time() - t0) / max(steps, 1)
+    return {"value": batch / dt, "unit": "samples/s", "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"config-3 architecture, batch {batch}, table rows capped at {rows_cap}, "
+                      f"{steps} steps after {warmup} warm-up, torch {torch.__version__} CPU, "
+                      f"{'bf16 autocast' if bf16 else 'fp32'}",
+            "ms_per_step": dt * 1e3}
+
+
+def run_reference_arm(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps, warm = max(1, min(a.steps, 5)), max(1, min(a.warmup, 2))
+    r = cpu_reference_run(a.batch, a.cpu_rows_cap, steps, warm, a.dtype == "bf16")
+    line = {"impl": "reference", "metric": "dlrm_train_samples_per_sec", "value": r["value"], "unit": "samples/s",
+            "n_gpus": a.gpus, "steps": steps, "warmup": warm, "ms_per_step": r["ms_per_step"],
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": a.dtype, "data": "synthetic",
+            "config": {"workload": "dlrm_criteo_terabyte_c3", "batch_per_gpu": a.batch, "dim": D,
+                       "tables": len(C3_ROWS), "cpu_table_rows_cap": a.cpu_rows_cap},
+            "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": r["value"], "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------ clocks
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                       "-lms", "100", "-i", str(index)], stdout=subprocess.PIPE,
+                                      stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        try:
+            out, _ = self.p.communicate(timeout=5)
+        except Exception:
+            self.p.kill()
+            out = ""
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in out.strip().splitlines():
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------ B200 arm
+def peak_hbm():
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def ncu_traffic(kernel):
+    """dram bytes per launch from the committed ncu capture (profiles/roofline_traffic.json), or None."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json"))).get(kernel)
+    except Exception:
+        return None
+
+
+def make_batches(a, rows_local, B_loc, B_glob, dev, rank):
+    """Synthetic Criteo-shaped inputs: dense U[0,1), targets round(U), one index per
+    (sample, table) uniform over the table's rows.  Generated on the host with numpy, kept both in
+    pinned host memory (e2e leg) and on the device (HBM-resident leg)."""
+    rs = np.random.RandomState(727 + 1000 * rank)
+    T = len(rows_local)
+    sets = []
+    for _ in range(a.sets):
+        X = rs.rand(B_loc, 13).astype(np.float32)
+        Y = np.round(rs.rand(B_loc, 1)).astype(np.float32)
+        idx = np.empty((T, B_glob), dtype=np.int64)
+        for t, n in enumerate(rows_local):
+            idx[t] = np.floor(rs.rand(B_glob) * n).astype(np.int64)
+        off = np.arange(T * B_glob + 1, dtype=np.int64)
+        host = [torch.from_numpy(v).pin_memory() for v in (X, Y, idx.reshape(-1), off)]
+        devt = [h.to(dev, non_blocking=True) for h in host]
+        uniq = [int(np.unique(idx[t]).size) for t in range(T)]
+        sets.append({"host": host, "dev": devt, "uniq": uniq})
+    torch.cuda.synchronize()
+    return sets
+
+
+def run_b200_arm(a):
+    from cloudtik_b200 import ext_dist
+    from cloudtik_b200.dlrm import DLRM_Net
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        ext_dist.init_distributed(rank=rank, size=world, backend="nccl")
+    bf16 = a.dtype == "bf16"
+    rows = table_rows(a.rows_cap)
+    B_loc, B_glob = a.batch, a.batch * world
+
+    np.random.seed(727)
+    torch.manual_seed(727 + rank)
+    # sharded tables see the sum of every rank's local-mean gradient: lr/world (T/dlrm_s_pytorch.py:1020-1031)
+    net = DLRM_Net(D, np.array(rows), np.array(LN_BOT), np.array(LN_TOP), sigmoid_top=len(LN_TOP) - 2,
+                   np_init_emb_weight=False, device=dev, lr=LR / world, bf16=bf16)
+    local_ids = list(range(len(rows))) if world == 1 else net.local_ln_emb
+    rows_local = [rows[i] for i in local_ids]
+    if world > 1:
+        net.bot_l = ext_dist.DDP(net.bot_l, device_ids=[local_rank])
+        net.top_l = ext_dist.DDP(net.top_l, device_ids=[local_rank])
+    dense_params = [p for p in net.parameters() if p.requires_grad]
+    opt = torch.optim.SGD(dense_params, lr=LR)
+    sets = make_batches(a, rows_local, B_loc, B_glob, dev, rank)
+    emb = net.emb_l
+
+    def step_dev(i):
+        X, Y, idx, off = sets[i % len(sets)]["dev"]
+        Z = net(X, idx, off, None).float()
+        E = net.loss_fn(Z, Y)
+        opt.zero_grad(set_to_none=True)
+        E.backward()
+        opt.step()
+        return E.detach()
+
+    stage = [torch.empty_like(t) for t in sets[0]["dev"]]
+
+    def step_e2e(i):
+        host = sets[i % len(sets)]["host"]
+        for d, h in zip(stage, host):
+            d.copy_(h, non_blocking=True)
+        X, Y, idx, off = stage
+        Z = net(X, idx, off, None).float()
+        E = net.loss_fn(Z, Y)
+        opt.zero_grad(set_to_none=True)
+        E.backward()
+        opt.step()
+        return float(E.detach().cpu())  # D2H read of the step's loss (reference: P/dlrm_s_pytorch.py:1048)
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        last = None
+        for i in range(steps):
+            last = fn(i)
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            torch.distributed.all_reduce(ms, op=torch.distributed.ReduceOp.MAX)
+        return float(ms.item()), last
+
+    for i in range(max(a.warmup, 3)):
+        step_dev(i)
+    clocks = ClockSampler(local_rank) if rank == 0 else None
+    emb.profile = {}
+    ms_total, last_loss = timed(step_dev, a.steps)
+    prof = emb.profile
+    emb.profile = None
+    clk = clocks.stop() if clocks else None
+    loss_val = float(last_loss.cpu())
+
+    for i in range(2):
+        step_e2e(i)
+    ms_e2e, _ = timed(step_e2e, a.steps)
+
+    if rank != 0:
+        return
+    ms_step = ms_total / a.steps
+    value = B_glob * a.steps / (ms_total / 1e3)
+    e2e_value = B_glob * a.steps / (ms_e2e / 1e3)
+    h2d = sum(t.numel() * t.element_size() for t in sets[0]["host"])
+
+    # ---- roofline of the dominant hand-written kernel (CUDA events around single launches)
+    ew, ea = 4, (2 if bf16 else 4)
+    T_loc = len(rows_local)
+    nnz = T_loc * B_glob
+    U = statistics.mean(sum(s["uniq"]) for s in sets)
+    common = nnz * 8 + (T_loc * B_glob + 1) * 8
+    alg = {"emb_fwd": U * D * ew + common + T_loc * B_glob * D * ea,
+           "emb_bwd_apply": T_loc * B_glob * D * ea + common + 2 * U * D * ew}
+    kt = {}
+    for k, evs in prof.items():
+        if k in alg and evs:
+            kt[k] = statistics.mean(x.elapsed_time(y) for x, y in evs)
+    peak, pk = peak_hbm()
+    roof = None
+    if kt:
+        dom = max(kt, key=kt.get)
+        ach = alg[dom] / (kt[dom] * 1e-3) / 1e9
+        roof = {"kernel": dom, "bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
+                "frac": round(ach / peak, 4), "frac_of_8TBps_nominal": round(ach / 8000.0, 4),
+                "peak_source": pk, "traffic": ncu_traffic(dom), "algorithmic_bytes": int(alg[dom]),
+                "kernel_ms": round(kt[dom], 4),
+                "others": {k: {"ms": round(v, 4), "GBps": round(alg[k] / (v * 1e-3) / 1e9, 1)}
+                           for k, v in kt.items() if k != dom}}
+
+    bits = max(1, int(sum(rows_local) - 1).bit_length())
+    launches = 1 + 1 + 3 * ((bits + 7) // 8) + 3 + 1 + 2  # fwd, keys, radix passes, dedup, update, interaction f/b
+    line = {"metric": "dlrm_train_samples_per_sec", "value": round(value, 1), "unit": "samples/s", "n_gpus": world,
+            "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": round(ms_step, 4), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": a.dtype, "data": "synthetic",
+            "config": {"workload": "dlrm_criteo_terabyte_c3", "batch_per_gpu": B_loc, "global_batch": B_glob,
+                       "dim": D, "tables": len(rows), "total_rows": int(sum(rows)), "pooling": 1,
+                       "table_dtype": "fp32", "mlp": "bot 13-512-256-128 / top 479-1024-1024-512-256-1",
+                       "optimizer": "SGD lr 1.0 (fused sparse update + torch SGD on MLPs)",
+                       "parallelism": "single" if world == 1 else f"table-wise x{world} + DDP MLPs",
+                       "l2": "inputs larger than L2 (96 GB of tables, uniform random rows)",
+                       "rows_cap": a.rows_cap or None},
+            "e2e": {"value": round(e2e_value, 1), "unit": "samples/s", "h2d_bytes_per_step": int(h2d),
+                    "d2h_bytes_per_step": 4, "ms_per_step": round(ms_e2e / a.steps, 4)},
+            "gpu_launches": launches * a.steps, "gpu_launches_per_step": launches,
+            "roofline": roof, "clocks": clk, "final_loss": loss_val}
+    if world == 1 and not a.no_cpu_baseline:
+        r = cpu_reference_run(a.batch, a.cpu_rows_cap, a.cpu_steps, 1, bf16)
+        line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
+    else:
+        line["cpu_baseline"] = None
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    a = parse()
+    if a.impl == "reference":
+        run_reference_arm(a)
+    else:
+        run_b200_arm(a)
+        if torch.distributed.is_available() and torch.distributed.is_initialized():
+            torch.distributed.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -319,24 +319,48 @@ extern "C" size_t b200_emb_bwd_workspace_bytes(int64_t nnz) {
   return bwd_layout(nullptr, nnz < 0 ? 0 : nnz).total;
 }
 
-extern "C" int b200_emb_bwd_update(void* const* d_weights, float* const* d_state,
-                                   const int64_t* d_rows, const int64_t* d_row_base,
-                                   const int64_t* d_indices, const int64_t* d_offsets, int64_t nnz,
-                                   const void* d_grad, int64_t T, int64_t B, int64_t D,
-                                   int64_t grad_stride_table, int64_t grad_stride_bag, int w_dtype,
-                                   int grad_dtype, int optimizer, float lr, const float* d_lr,
-                                   float eps, int64_t total_rows, void* ws, size_t ws_bytes,
-                                   int32_t* d_error, b200_stream_t stream) {
+static int check_bwd_common(int64_t T, int64_t B, int64_t D, int64_t nnz, int64_t total_rows) {
   B200_REQUIRE(T >= 0 && B >= 0 && D > 0 && nnz >= 0, B200_EINVAL, "emb_bwd: negative size");
-  if (T == 0 || B == 0 || nnz == 0) return B200_OK;
-  B200_REQUIRE(d_weights && d_rows && d_row_base && d_indices && d_offsets && d_grad && ws,
-               B200_EINVAL, "emb_bwd: null pointer");
-  B200_REQUIRE(optimizer == B200_OPT_SGD || (optimizer == B200_OPT_ADAGRAD && d_state), B200_EINVAL,
-               "emb_bwd: bad optimizer / missing state");
   B200_REQUIRE(total_rows > 0 && (uint64_t)total_rows <= ((uint64_t)1 << 32), B200_EUNSUPPORTED,
                "emb_bwd: total rows over all tables must be <= 2^32 (32-bit sort keys)");
   B200_REQUIRE(T * B < ((int64_t)1 << 32) && nnz < ((int64_t)1 << 31) && T <= 65535,
                B200_EUNSUPPORTED, "emb_bwd: T*B must be < 2^32 and nnz < 2^31");
+  return B200_OK;
+}
+
+extern "C" int b200_emb_bwd_prepare(const int64_t* d_rows, const int64_t* d_row_base,
+                                    const int64_t* d_indices, const int64_t* d_offsets, int64_t nnz,
+                                    int64_t T, int64_t B, int64_t total_rows, void* ws, size_t ws_bytes,
+                                    int32_t* d_error, b200_stream_t stream) {
+  int rc = check_bwd_common(T, B, 1, nnz, total_rows);
+  if (rc) return rc;
+  if (T == 0 || B == 0 || nnz == 0) return B200_OK;
+  B200_REQUIRE(d_rows && d_row_base && d_indices && d_offsets && ws, B200_EINVAL,
+               "emb_bwd_prepare: null pointer");
+  B200_REQUIRE(ws_bytes >= b200_emb_bwd_workspace_bytes(nnz), B200_EWORKSPACE,
+               "emb_bwd: workspace too small");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  BwdLayout L = bwd_layout(ws, nnz);
+  dim3 kgrid((unsigned)ceil_div(B, KEYS_THREADS), (unsigned)T);
+  build_keys_kernel<<<kgrid, KEYS_THREADS, 0, st>>>(d_indices, d_offsets, d_rows, d_row_base, B, L.keys,
+                                                    L.vals, d_error);
+  B200_CHECK_LAUNCH("build_keys");
+  rc = sort_pairs(L.keys, L.vals, nnz, (uint64_t)total_rows, L.skeys, L.svals, L.sort_ws, st);
+  if (rc) return rc;
+  return dedup_runs(L.skeys, nnz, L.unique, L.seg, L.num_unique, L.sort_ws, st);
+}
+
+extern "C" int b200_emb_bwd_apply(void* const* d_weights, float* const* d_state,
+                                  const int64_t* d_row_base, int64_t nnz, const void* d_grad, int64_t T,
+                                  int64_t B, int64_t D, int64_t grad_stride_table,
+                                  int64_t grad_stride_bag, int w_dtype, int grad_dtype, int optimizer,
+                                  float lr, const float* d_lr, float eps, void* ws, size_t ws_bytes,
+                                  b200_stream_t stream) {
+  B200_REQUIRE(T >= 0 && B >= 0 && D > 0 && nnz >= 0, B200_EINVAL, "emb_bwd: negative size");
+  if (T == 0 || B == 0 || nnz == 0) return B200_OK;
+  B200_REQUIRE(d_weights && d_row_base && d_grad && ws, B200_EINVAL, "emb_bwd_apply: null pointer");
+  B200_REQUIRE(optimizer == B200_OPT_SGD || (optimizer == B200_OPT_ADAGRAD && d_state), B200_EINVAL,
+               "emb_bwd: bad optimizer / missing state");
   B200_REQUIRE((w_dtype == B200_F32 || w_dtype == B200_BF16) &&
                    (grad_dtype == B200_F32 || grad_dtype == B200_BF16),
                B200_EINVAL, "emb_bwd: bad dtype");
@@ -344,16 +368,6 @@ extern "C" int b200_emb_bwd_update(void* const* d_weights, float* const* d_state
                "emb_bwd: workspace too small");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   BwdLayout L = bwd_layout(ws, nnz);
-
-  dim3 kgrid((unsigned)ceil_div(B, KEYS_THREADS), (unsigned)T);
-  build_keys_kernel<<<kgrid, KEYS_THREADS, 0, st>>>(d_indices, d_offsets, d_rows, d_row_base, B, L.keys,
-                                                    L.vals, d_error);
-  B200_CHECK_LAUNCH("build_keys");
-  int rc = sort_pairs(L.keys, L.vals, nnz, (uint64_t)total_rows, L.skeys, L.svals, L.sort_ws, st);
-  if (rc) return rc;
-  rc = dedup_runs(L.skeys, nnz, L.unique, L.seg, L.num_unique, L.sort_ws, st);
-  if (rc) return rc;
-
   UpdParams p;
   p.weights = d_weights;
   p.state = d_state;
@@ -387,4 +401,20 @@ extern "C" int b200_emb_bwd_update(void* const* d_weights, float* const* d_state
   if (optimizer == B200_OPT_ADAGRAD) return B200_UPD_DISPATCH(B200_OPT_ADAGRAD);
   return B200_UPD_DISPATCH(B200_OPT_SGD);
 #undef B200_UPD_DISPATCH
+}
+
+extern "C" int b200_emb_bwd_update(void* const* d_weights, float* const* d_state,
+                                   const int64_t* d_rows, const int64_t* d_row_base,
+                                   const int64_t* d_indices, const int64_t* d_offsets, int64_t nnz,
+                                   const void* d_grad, int64_t T, int64_t B, int64_t D,
+                                   int64_t grad_stride_table, int64_t grad_stride_bag, int w_dtype,
+                                   int grad_dtype, int optimizer, float lr, const float* d_lr,
+                                   float eps, int64_t total_rows, void* ws, size_t ws_bytes,
+                                   int32_t* d_error, b200_stream_t stream) {
+  int rc = b200_emb_bwd_prepare(d_rows, d_row_base, d_indices, d_offsets, nnz, T, B, total_rows, ws,
+                                ws_bytes, d_error, stream);
+  if (rc) return rc;
+  return b200_emb_bwd_apply(d_weights, d_state, d_row_base, nnz, d_grad, T, B, D, grad_stride_table,
+                            grad_stride_bag, w_dtype, grad_dtype, optimizer, lr, d_lr, eps, ws, ws_bytes,
+                            stream);
 }

@@ -1,0 +1,151 @@
+"""DLRM model wired to the B200 kernels.
+
+Mirror of the reference ``DLRM_Net`` (``P/dlrm_s_pytorch.py:171-397``): same constructor
+arguments, same weight initialisation order from the numpy stream (so a seed gives the same
+model as the reference), same ``forward(dense_x, *emb_args)`` dispatch.  The dense MLPs stay
+``torch.nn`` (cuBLAS); the embedding tables are a ``MergedEmbeddingBagWithSGD`` (pool + fused
+sparse update) and the interaction is ``cloudtik_b200.interaction`` -- the two seams the
+reference itself switches on with ``--ipex-merged-emb`` / ``--ipex-interaction``.
+"""
+from __future__ import annotations
+
+import sys
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from . import ext_dist
+from .interaction import interaction
+from .merged_embedding import MergedEmbeddingBagWithSGD
+
+
+class DLRM_Net(nn.Module):
+    def create_mlp(self, ln, sigmoid_layer):
+        # P/dlrm_s_pytorch.py:172-211
+        layers = nn.ModuleList()
+        for i in range(0, ln.size - 1):
+            n, m = int(ln[i]), int(ln[i + 1])
+            LL = nn.Linear(n, m, bias=True)
+            W = np.random.normal(0.0, np.sqrt(2 / (m + n)), size=(m, n)).astype(np.float32)
+            bt = np.random.normal(0.0, np.sqrt(1 / m), size=m).astype(np.float32)
+            LL.weight.data = torch.tensor(W, requires_grad=True)
+            LL.bias.data = torch.tensor(bt, requires_grad=True)
+            layers.append(LL)
+            layers.append(nn.Sigmoid() if i == sigmoid_layer else nn.ReLU())
+        return torch.nn.Sequential(*layers)
+
+    def create_emb(self, m, ln, local_ln_emb=None, np_init_emb_weight=False, device="cuda", lr=0.01,
+                   optimizer="sgd"):
+        # P/dlrm_s_pytorch.py:213-238; np_init_emb_weight=True draws every table from the numpy
+        # stream on the host (parity runs); otherwise rows are drawn on the device with the same
+        # U(-sqrt(1/n), sqrt(1/n)) law (Terabyte-size tables never exist on the host).
+        weights = []
+        ids = range(ln.size) if local_ln_emb is None else local_ln_emb
+        for i in ids:
+            n = int(ln[i])
+            if np_init_emb_weight:
+                W = np.random.uniform(low=-np.sqrt(1 / n), high=np.sqrt(1 / n), size=(n, m)).astype(np.float32)
+                weights.append(torch.from_numpy(W).to(device))
+            else:
+                w = torch.empty(n, m, dtype=torch.float32, device=device)
+                w.uniform_(-float(np.sqrt(1 / n)), float(np.sqrt(1 / n)))
+                weights.append(w)
+        return MergedEmbeddingBagWithSGD(weights, lr=lr, optimizer=optimizer)
+
+    def __init__(self, m_spa=None, ln_emb=None, ln_bot=None, ln_top=None, sigmoid_bot=-1, sigmoid_top=-1,
+                 weighted_pooling=None, loss_threshold=0.0, np_init_emb_weight=False, device="cuda",
+                 lr=0.01, emb_optimizer="sgd", bf16=False):
+        super().__init__()
+        if weighted_pooling is not None:
+            raise NotImplementedError("weighted pooling is not on the reference's product path")
+        self.loss_threshold = loss_threshold
+        self.bf16 = bf16
+        ln_emb = np.asarray(ln_emb)
+        if ext_dist.my_size > 1:
+            n_emb = len(ln_emb)
+            self.n_global_emb = n_emb
+            self.rank = ext_dist.dist.get_rank()
+            self.ln_emb = [i for i in range(n_emb)]
+            self.n_local_emb, self.n_emb_per_rank = ext_dist.get_split_lengths(n_emb)
+            self.local_ln_emb_slice = ext_dist.get_my_slice(n_emb)
+            self.local_ln_emb = self.ln_emb[self.local_ln_emb_slice]
+        else:
+            self.local_ln_emb = None
+        self.l_emb_seeds = np.random.randint(low=0, high=100000, size=len(ln_emb))
+        self.bot_l = self.create_mlp(np.asarray(ln_bot), sigmoid_bot).to(device)
+        self.top_l = self.create_mlp(np.asarray(ln_top), sigmoid_top).to(device)
+        self.emb_l = self.create_emb(m_spa, ln_emb, self.local_ln_emb, np_init_emb_weight, device, lr,
+                                     emb_optimizer)
+        if bf16:
+            self.emb_l.output_dtype = torch.bfloat16
+        if ext_dist.my_size > 1:
+            self.emb_l.reserve_dense_slot = False  # pooled rows go straight into the a2a send layout
+        self.need_linearize_indices_and_offsets = torch.BoolTensor([False])
+        self.loss_fn = torch.nn.BCELoss(reduction="mean")
+
+    def apply_mlp(self, x, layers):
+        return layers(x)
+
+    def apply_emb(self, emb_l, *emb_args):
+        # merged call style (P/dlrm_s_pytorch.py:288-289): (indices, offsets, indices_with_row_offsets)
+        if len(emb_args) == 3:
+            return emb_l(emb_args, self.need_linearize_indices_and_offsets)
+        # list style (P/dlrm_s_pytorch.py:290-305): (lS_o, lS_i) -> linearise on the fly
+        lS_o, lS_i = emb_args
+        return emb_l((list(lS_i), list(lS_o), [False] * len(lS_i)), torch.BoolTensor([True]))
+
+    def interact_features(self, x, ly):
+        return interaction(x, *ly)
+
+    def forward(self, dense_x, *emb_args):
+        if ext_dist.my_size > 1:
+            return self.distributed_forward(dense_x, *emb_args)
+        return self.sequential_forward(dense_x, *emb_args)
+
+    def _clamp(self, p):
+        if 0.0 < self.loss_threshold < 1.0:
+            return torch.clamp(p, min=self.loss_threshold, max=(1.0 - self.loss_threshold))
+        return p
+
+    def sequential_forward(self, dense_x, *emb_args):
+        # P/dlrm_s_pytorch.py:372-397
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.bf16):
+            x = self.apply_mlp(dense_x, self.bot_l)
+            ly = self.apply_emb(self.emb_l, *emb_args)
+            z = self.interact_features(x, ly)
+            p = self.apply_mlp(z, self.top_l)
+        return self._clamp(p)
+
+    def distributed_forward(self, dense_x, *emb_args):
+        # P/dlrm_s_pytorch.py:342-369: local tables on the GLOBAL batch -> all-to-all -> local batch
+        batch_size = dense_x.size()[0]
+        vector_lenght = self.emb_l.weights[0].size()[1]
+        if batch_size < ext_dist.my_size:
+            sys.exit("ERROR: batch_size (%d) must be larger than number of ranks (%d)"
+                     % (batch_size, ext_dist.my_size))
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.bf16):
+            ly = self.apply_emb(self.emb_l, *emb_args)
+            a2a_req = ext_dist.alltoall(ly, self.n_emb_per_rank)
+            x = self.apply_mlp(dense_x, self.bot_l)
+            ly = a2a_req.wait()
+            _ly = []
+            for r, item in enumerate(ly):
+                n_r = self.n_emb_per_rank[r] if self.n_emb_per_rank else self.emb_l.n_tables
+                _ly += [item[:, e * vector_lenght:(e + 1) * vector_lenght] for e in range(n_r)]
+            z = self.interact_features(x, _ly)
+            p = self.apply_mlp(z, self.top_l)
+        return self._clamp(p)
+
+
+def train_step(dlrm, optimizer, X, emb_args, T, lr=None):
+    """One iteration of the reference loop (P/dlrm_s_pytorch.py:1027-1059).  Returns the loss
+    TENSOR (no host sync here; the reference's per-step ``.cpu()`` is the caller's choice)."""
+    if lr is not None:
+        dlrm.emb_l.sgd_args = dlrm.emb_l.sgd_args._replace(lr=lr)
+    Z = dlrm(X, *emb_args).float()
+    E = dlrm.loss_fn(Z, T)
+    optimizer.zero_grad(set_to_none=True)
+    E.backward()
+    optimizer.step()
+    return E.detach()

@@ -1,0 +1,245 @@
+"""Table-wise model-parallel plumbing: one process per GPU over torch.distributed (NCCL).
+
+Mirror of the reference's ``extend_distributed`` module (``P/extend_distributed.py``): same
+public names and argument meaning -- ``init_distributed``, ``get_my_slice``,
+``get_split_lengths``, ``alltoall(inputs, per_rank_split_lengths) -> Request`` with
+``Request.wait()``, ``all_gather``, ``barrier``, ``DDP`` -- so the model code reads like the
+reference's.  Differences, on purpose:
+
+* rank/size come from ``torch.distributed`` (the reference's module-global ``my_rank`` is never
+  set: quirk q1 in SURVEY.md section 7.1);
+* one ``all_to_all_single`` implementation (NCCL, or gloo in the CPU tests); the scatter /
+  scatter-list fall-backs for back-ends without all-to-all (``P/extend_distributed.py:132-269``)
+  are not needed;
+* the forward all-to-all runs on a side stream so that it overlaps the bottom MLP, and the
+  send buffer is the pooled-embedding buffer itself when the embedding kernel wrote it in the
+  ``[N, lS*E]`` send layout (no ``torch.cat`` copy, ``P/extend_distributed.py:280``).
+"""
+from __future__ import annotations
+
+import os
+
+import torch
+import torch.distributed as dist
+from torch.autograd import Function
+from torch.nn.parallel import DistributedDataParallel as DDP  # noqa: F401  (re-exported)
+
+my_rank = -1
+my_size = -1
+my_local_rank = -1
+my_local_size = -1
+alltoall_supported = False
+myreq = None
+
+
+def env2int(env_list, default=-1):
+    # P/extend_distributed.py:27-31
+    for e in env_list:
+        val = int(os.environ.get(e, -1))
+        if val >= 0:
+            return val
+    return default
+
+
+def _world():
+    return dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+
+
+def _rank():
+    return dist.get_rank() if dist.is_available() and dist.is_initialized() else 0
+
+
+def get_my_slice(n):
+    # P/extend_distributed.py:33-37
+    size, rank = _world(), _rank()
+    k, m = divmod(n, size)
+    return slice(rank * k + min(rank, m), (rank + 1) * k + min(rank + 1, m), 1)
+
+
+def get_split_lengths(n):
+    # P/extend_distributed.py:39-49
+    size = _world()
+    k, m = divmod(n, size)
+    if m == 0:
+        return k, None
+    splits = [(k + 1) if i < m else k for i in range(size)]
+    return splits[_rank()], splits
+
+
+def init_distributed(rank=-1, size=-1, backend=""):
+    """P/extend_distributed.py:51-118, reduced to the launchers this build supports
+    (torchrun / cloudtik-run env: RANK, WORLD_SIZE, LOCAL_RANK, MASTER_ADDR, MASTER_PORT)."""
+    global myreq, my_rank, my_size, my_local_rank, my_local_size, alltoall_supported
+    if size == -1:
+        size = env2int(["PMI_SIZE", "OMPI_COMM_WORLD_SIZE", "MV2_COMM_WORLD_SIZE", "WORLD_SIZE"], 1)
+    if rank == -1:
+        rank = env2int(["PMI_RANK", "OMPI_COMM_WORLD_RANK", "MV2_COMM_WORLD_RANK", "RANK"], 0)
+    if backend == "":
+        backend = "nccl" if torch.cuda.is_available() else "gloo"
+    if size > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+        os.environ.setdefault("RANK", str(rank))
+        os.environ.setdefault("WORLD_SIZE", str(size))
+        my_local_rank = env2int(["MPI_LOCALRANKID", "OMPI_COMM_WORLD_LOCAL_RANK", "MV2_COMM_WORLD_LOCAL_RANK",
+                                 "LOCAL_RANK"], 0)
+        my_local_size = env2int(["MPI_LOCALNRANKS", "OMPI_COMM_WORLD_LOCAL_SIZE", "MV2_COMM_WORLD_LOCAL_SIZE",
+                                 "LOCAL_WORLD_SIZE"], 1)
+        if backend == "nccl":
+            torch.cuda.set_device(my_local_rank)
+        if not dist.is_initialized():
+            dist.init_process_group(backend, rank=rank, world_size=size)
+        my_rank = dist.get_rank()
+        my_size = dist.get_world_size()
+        alltoall_supported = True
+        if my_rank == 0:
+            print("Running on %d ranks using %s backend" % (my_size, backend))
+    else:
+        my_rank, my_size, my_local_rank, my_local_size = 0, 1, 0, 1
+    myreq = Request()
+
+
+class All2AllInfo(object):
+    pass
+
+
+class Request(object):
+    """One outstanding all-to-all (the reference keeps a module-global one too,
+    P/extend_distributed.py:25,120-130): not re-entrant, one per process."""
+
+    def __init__(self):
+        self.req = None
+        self.tensor = None
+        self.a2ai = None
+        self.event = None
+
+    def wait(self):
+        ret = All2All_Wait.apply(*self.tensor)
+        self.req = None
+        self.tensor = None
+        return ret
+
+
+def _finish(req_holder):
+    if req_holder.req is not None:
+        req_holder.req.wait()
+        req_holder.req = None
+
+
+def _send_view(inputs, N, E):
+    """[N, lS*E] send buffer: the tensors' common base if they are adjacent [N, E] column
+    blocks of one row-major buffer (what the merged embedding kernel writes), else a cat."""
+    t0 = inputs[0]
+    lS = len(inputs)
+    st = t0.untyped_storage().data_ptr()
+    ok = all(t.untyped_storage().data_ptr() == st and tuple(t.shape) == (N, E) and t.stride() == (lS * E, 1)
+             and t.storage_offset() == t0.storage_offset() + k * E for k, t in enumerate(inputs))
+    if ok:
+        return torch.as_strided(t0, (N * lS * E,), (1,), t0.storage_offset())
+    return torch.cat(inputs, dim=1).view([-1])
+
+
+class All2All_Req(Function):
+    # P/extend_distributed.py:271-305
+    @staticmethod
+    def forward(ctx, a2ai, *inputs):
+        global myreq
+        mb_split_lengths = a2ai.gNS
+        if mb_split_lengths:
+            mb_split_lengths = [m * a2ai.lS * a2ai.E for m in mb_split_lengths]
+        emb_split_lengths = a2ai.gSS
+        if emb_split_lengths:
+            emb_split_lengths = [a2ai.lN * e * a2ai.E for e in emb_split_lengths]
+        input = _send_view(inputs, a2ai.N, a2ai.E)
+        output = input.new_empty([a2ai.S * a2ai.lN * a2ai.E])
+        myreq.req = dist.all_to_all_single(output, input, emb_split_lengths, mb_split_lengths, async_op=True)
+        myreq.tensor = (output,)
+        a2ai.mb_split_lengths = mb_split_lengths
+        a2ai.emb_split_lengths = emb_split_lengths
+        myreq.a2ai = a2ai
+        ctx.a2ai = a2ai
+        return myreq.tensor
+
+    @staticmethod
+    def backward(ctx, *grad_output):
+        global myreq
+        a2ai = ctx.a2ai
+        _finish(myreq)
+        grad_input = myreq.tensor
+        myreq.tensor = None
+        # [N, lS*E] -> per-table [N, E] views (no copy: the fused embedding backward reads them
+        # in place through their common base)
+        gi = grad_input.view([a2ai.N, a2ai.lS, a2ai.E])
+        return (None, *[gi[:, k] for k in range(a2ai.lS)])
+
+
+class All2All_Wait(Function):
+    # P/extend_distributed.py:307-333
+    @staticmethod
+    def forward(ctx, *output):
+        global myreq
+        a2ai = myreq.a2ai
+        ctx.a2ai = a2ai
+        _finish(myreq)
+        myreq.tensor = None
+        emb_split_lengths = a2ai.emb_split_lengths if a2ai.emb_split_lengths else a2ai.lS * a2ai.lN * a2ai.E
+        outputs = output[0].split(emb_split_lengths)
+        return tuple(out.view([a2ai.lN, -1]) for out in outputs)
+
+    @staticmethod
+    def backward(ctx, *grad_outputs):
+        global myreq
+        a2ai = ctx.a2ai
+        grad_output = torch.cat([g.contiguous().view([-1]) for g in grad_outputs])
+        grad_input = grad_output.new_empty([a2ai.N * a2ai.lS * a2ai.E])
+        myreq.req = dist.all_to_all_single(grad_input, grad_output, a2ai.mb_split_lengths,
+                                           a2ai.emb_split_lengths, async_op=True)
+        myreq.tensor = grad_input
+        return (grad_output,)
+
+
+def alltoall(inputs, per_rank_split_lengths):
+    """P/extend_distributed.py:386-409.  ``inputs``: this rank's lS pooled tensors [N, E] for the
+    GLOBAL batch; returns the Request whose ``wait()`` yields one [lN, lS_r*E] tensor per rank."""
+    global myreq
+    N, E = inputs[0].size()
+    a2ai = All2AllInfo()
+    a2ai.lS = len(inputs)
+    a2ai.gSS = per_rank_split_lengths
+    a2ai.lN, a2ai.gNS = get_split_lengths(N)
+    a2ai.E = E
+    a2ai.N = N
+    a2ai.S = sum(per_rank_split_lengths) if per_rank_split_lengths else a2ai.lS * my_size
+    All2All_Req.apply(a2ai, *inputs)
+    return myreq
+
+
+class AllGather(Function):
+    # P/extend_distributed.py:335-381 (dim 0 only: the eval path gathers [B_local, 1] scores)
+    @staticmethod
+    def forward(ctx, input, global_lengths):
+        rank = dist.get_rank()
+        ctx.start = sum(global_lengths[:rank])
+        ctx.length = global_lengths[rank]
+        input = input.contiguous()
+        size = list(input.size())
+        size[0] = sum(global_lengths)
+        output = input.new_empty(size)
+        dist.all_gather(list(output.split(global_lengths, dim=0)), input)
+        return output
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        return grad_output.narrow(0, ctx.start, ctx.length), None
+
+
+def all_gather(input, lengths, dim=0):
+    assert dim == 0
+    if not lengths:
+        lengths = [input.size(0)] * my_size
+    return AllGather.apply(input, lengths)
+
+
+def barrier():
+    if my_size > 1:
+        dist.barrier()

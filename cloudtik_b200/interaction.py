@@ -1,0 +1,70 @@
+"""Pairwise dot-product feature interaction (differentiable).
+
+Host-side mirror of ``DLRM_Net.interact_features`` (reference ``P/dlrm_s_pytorch.py:309-334``,
+``T/dlrm_s_pytorch.py:407-444``) with the call shape of the reference's own fused seam
+``ipex.nn.functional.interaction(*T)`` (``P/dlrm_s_pytorch.py:310-312``): ``interaction(x, *ly)``
+returns ``[B, D + F(F-1)/2]`` = ``[x, <T_i, T_j> for i in 1..F-1 for j in 0..i-1]`` with
+``T = [x] + ly``.
+
+When ``ly`` are the views returned by ``MergedEmbeddingBagWithSGD`` the pooled rows already sit
+in a ``[B, F, D]`` buffer with slot 0 free: x is copied into slot 0 and the kernel reads the
+buffer in place (no ``torch.cat`` pass).  Backward writes ``dT [B, F, D]`` once and hands out
+views, which the merged embedding's backward consumes in place as well.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import ops
+from .merged_embedding import lookup_pooled
+
+
+def _pooled_base(x: torch.Tensor, ly):
+    base = lookup_pooled(ly[0])
+    if base is None:
+        return None
+    B, F, D = base.shape
+    if F != len(ly) + 1 or tuple(x.shape) != (B, D) or not base.is_contiguous():
+        return None
+    st = base.untyped_storage().data_ptr()
+    for k, t in enumerate(ly):
+        if (t.untyped_storage().data_ptr() != st or t.dtype != base.dtype or tuple(t.shape) != (B, D)
+                or t.stride() != (F * D, 1) or t.storage_offset() != base.storage_offset() + (1 + k) * D):
+            return None
+    return base
+
+
+class _InteractionFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, *ly):
+        base = _pooled_base(x, ly)
+        if base is not None:
+            T = base
+            T[:, 0].copy_(x)
+        else:
+            dt = ly[0].dtype if ly else x.dtype
+            T = torch.stack([x.to(dt)] + [t.to(dt) for t in ly], dim=1).contiguous()
+        ctx.save_for_backward(T)
+        ctx.x_dtype = x.dtype
+        ctx.ly_dtypes = [t.dtype for t in ly]
+        return ops.interact_fwd(T)
+
+    @staticmethod
+    def backward(ctx, dR):
+        (T,) = ctx.saved_tensors
+        dT = ops.interact_bwd(T, dR.contiguous().to(T.dtype))
+        dx = dT[:, 0]
+        if dx.dtype != ctx.x_dtype:
+            dx = dx.to(ctx.x_dtype)
+        dly = []
+        for k, dt in enumerate(ctx.ly_dtypes):
+            g = dT[:, 1 + k]
+            dly.append(g if g.dtype == dt else g.to(dt))
+        return (dx, *dly)
+
+
+def interaction(x: torch.Tensor, *ly: torch.Tensor) -> torch.Tensor:
+    """``interaction(x, *ly)`` -- see module docstring.  CUDA tensors only."""
+    if not x.is_cuda:
+        raise RuntimeError("cloudtik_b200.interaction needs CUDA tensors (no CPU fallback)")
+    return _InteractionFn.apply(x, *ly)

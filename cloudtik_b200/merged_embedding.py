@@ -1,0 +1,271 @@
+"""Merged sum-pooled EmbeddingBag with the optimiser step fused into backward.
+
+Host-side mirror of the seam the reference already has for its own fast path:
+``ipex.nn.modules.MergedEmbeddingBagWithSGD`` as used at reference
+``P/dlrm_s_pytorch.py:288-289`` (call), ``:801`` (``from_embeddingbag_list``), ``:908-915`` /
+``:1008-1014`` (``linearize_indices_and_offsets``), ``:1027`` (``sgd_args._replace(lr=)``),
+``:344,357`` (``.weights`` / ``.n_tables``), ``:931`` (``to_bfloat16_train``).
+Same names, same argument meaning; the arithmetic runs in libb200dlrm.so (no CPU path).
+
+Layout: the pooled output of all tables is written by ONE kernel launch straight into a
+``[B, T+1, D]`` buffer whose slot 0 is left free for the bottom-MLP output, so that the
+interaction kernel (``cloudtik_b200.interaction``) reads it without the reference's
+``torch.cat`` copy.  The returned list holds ``[B, D]`` views of that buffer.
+"""
+from __future__ import annotations
+
+import contextlib
+import weakref
+from collections import namedtuple
+from typing import List, Optional, Sequence
+
+import torch
+import torch.nn as nn
+
+from . import ops
+
+SGDArgs = namedtuple("SGDArgs", ["bf16_trail", "weight_decay", "lr"])
+AdagradArgs = namedtuple("AdagradArgs", ["lr", "eps"])
+
+# storage data_ptr -> weakref(pooled [B, F, D] buffer); lets interaction() recognise our layout
+_POOLED_BUFFERS = {}
+
+
+def _register_pooled(buf: torch.Tensor):
+    key = buf.untyped_storage().data_ptr()
+    _POOLED_BUFFERS[key] = weakref.ref(buf, lambda _r, k=key: _POOLED_BUFFERS.pop(k, None))
+
+
+def lookup_pooled(t: torch.Tensor) -> Optional[torch.Tensor]:
+    r = _POOLED_BUFFERS.get(t.untyped_storage().data_ptr())
+    return r() if r is not None else None
+
+
+class _TableHolder(nn.Module):
+    """Keeps ``emb_l.{k}.weight`` state_dict keys (checkpoint contract, T/dlrm_s_pytorch.py:1415)."""
+
+    def __init__(self, weight: torch.Tensor):
+        super().__init__()
+        self.weight = nn.Parameter(weight, requires_grad=False)  # updated inside backward
+
+
+def _common_layout(grads: Sequence[torch.Tensor], B: int, D: int):
+    """If the per-table gradients are [B, D] views at a constant element distance inside one
+    storage (what interaction backward returns), give (base tensor, stride_table, stride_bag)."""
+    g0 = grads[0]
+    if g0.dim() != 2 or tuple(g0.shape) != (B, D) or g0.stride(1) != 1:
+        return None
+    st = g0.untyped_storage().data_ptr()
+    sb = g0.stride(0)
+    stt = (grads[1].storage_offset() - g0.storage_offset()) if len(grads) > 1 else B * D
+    for k, g in enumerate(grads):
+        if (g.untyped_storage().data_ptr() != st or g.dtype != g0.dtype or tuple(g.shape) != (B, D)
+                or g.stride() != (sb, 1) or g.storage_offset() != g0.storage_offset() + k * stt):
+            return None
+    if stt <= 0 or sb <= 0:
+        return None
+    return g0, stt, sb
+
+
+class _MergedEmbFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, trigger, module, indices, offsets, B):
+        T, D = module.n_tables, module.dim
+        out_dtype = module.output_dtype or module.tables.dtype
+        s0 = 1 if module.reserve_dense_slot else 0
+        buf = torch.empty(B, T + s0, D, dtype=out_dtype, device=indices.device)
+        if s0:
+            _register_pooled(buf)
+        with module._timed("emb_fwd"):
+            ops.emb_fwd(module.tables, indices, offsets, B, buf[:, s0:], D, (T + s0) * D, module.error_flag)
+        module._launch_prepare(indices, offsets, B)
+        ctx.module, ctx.B = module, B
+        ctx.save_for_backward(indices, offsets)
+        ctx.set_materialize_grads(False)
+        return tuple(buf[:, s0 + k] for k in range(T))
+
+    @staticmethod
+    def backward(ctx, *grads):
+        module, B = ctx.module, ctx.B
+        indices, offsets = ctx.saved_tensors
+        T, D = module.n_tables, module.dim
+        if all(g is None for g in grads):
+            return (None,) * 5
+        if any(g is None for g in grads):
+            ref = next(g for g in grads if g is not None)
+            grads = tuple(torch.zeros_like(ref) if g is None else g for g in grads)
+        lay = _common_layout(grads, B, D)
+        if lay is None:  # generic autograd graph: pack once (the fused DLRM path never gets here)
+            packed = torch.stack([g.contiguous() for g in grads], dim=0)
+            base, stt, sb = packed, B * D, D
+        else:
+            base, stt, sb = lay
+        module._apply_update(indices, offsets, B, base, stt, sb)
+        return (None,) * 5
+
+
+class MergedEmbeddingBagWithSGD(nn.Module):
+    """All tables of a DLRM in one module; ``forward`` pools, ``backward`` updates the rows."""
+
+    def __init__(self, weights: List[torch.Tensor], lr: float = 0.01, weight_decay: float = 0.0,
+                 optimizer: str = "sgd", eps: float = 1e-10):
+        super().__init__()
+        if weight_decay != 0.0:
+            raise NotImplementedError("weight_decay != 0 is not supported by the fused update")
+        dev = weights[0].device
+        if dev.type != "cuda":
+            raise RuntimeError("MergedEmbeddingBagWithSGD needs CUDA tensors (no CPU fallback)")
+        self.n_tables = len(weights)
+        self.dim = int(weights[0].shape[1])
+        for k, w in enumerate(weights):
+            self.add_module(str(k), _TableHolder(w))
+        self.sgd_args = SGDArgs(bf16_trail=[None] * len(weights), weight_decay=0.0, lr=float(lr))
+        self.optimizer_kind = optimizer
+        self.eps = float(eps)
+        self.output_dtype = None  # None: same dtype as the tables
+        self.lr_tensor = None     # optional device scalar read at kernel time (CUDA-graph replay)
+        self.error_flag = None    # optional int32[1] device flag set on an out-of-range index
+        self.profile = None       # dict -> per-kernel CUDA-event pairs (see _timed)
+        self.overlap_prepare = True
+        # True: pooled buffer is [B, T+1, D] with slot 0 free for the dense feature (single-process
+        # interaction reads it in place); False: [B, T, D] = the all-to-all send layout.
+        self.reserve_dense_slot = True
+        self._trigger = torch.zeros((), device=dev, requires_grad=True)
+        self._ws = None
+        self._side_stream = None
+        self._prep_event = None
+        self._rebuild_tables()
+        if optimizer == "adagrad":
+            self.tables.set_states([torch.zeros_like(w, dtype=torch.float32) for w in self.weights])
+        elif optimizer != "sgd":
+            raise ValueError(f"unknown optimizer {optimizer!r}")
+
+    # ---- IPEX-shaped surface -------------------------------------------------------
+    @classmethod
+    def from_embeddingbag_list(cls, tables, lr: float = 0.01, weight_decay: float = 0.0, device=None,
+                               optimizer: str = "sgd", eps: float = 1e-10):
+        dev = torch.device(device) if device is not None else None
+        weights = []
+        for E in tables:
+            if getattr(E, "mode", "sum") != "sum":
+                raise NotImplementedError("only sum pooling is supported")
+            w = E.weight.detach()
+            if dev is None:
+                dev = w.device if w.is_cuda else torch.device("cuda", torch.cuda.current_device())
+            weights.append(w.to(dev).contiguous())
+        return cls(weights, lr=lr, weight_decay=weight_decay, optimizer=optimizer, eps=eps)
+
+    @property
+    def weights(self) -> List[torch.Tensor]:
+        return [getattr(self, str(k)).weight.data for k in range(self.n_tables)]
+
+    def linearize_indices_and_offsets(self, indices: List[torch.Tensor], offsets: List[torch.Tensor],
+                                      include_last_offsets: List[bool]):
+        """Per-table (indices, offsets) -> (indices, offsets, indices_with_row_offsets):
+        concatenated indices, one CSR array over all T*B bags with the trailing total, and
+        global row ids."""
+        dev = self.weights[0].device
+        idx = [i.to(dev, torch.int64) for i in indices]
+        offs = []
+        for o, inc in zip(offsets, include_last_offsets):
+            o = o.to(dev, torch.int64)
+            offs.append(o[:-1] if inc else o)
+        B = offs[0].numel()
+        if any(o.numel() != B for o in offs):
+            raise ValueError("all tables must be indexed with the same number of bags")
+        nnz = torch.tensor([0] + [i.numel() for i in idx], dtype=torch.int64).cumsum(0)
+        lin_idx = torch.cat(idx)
+        lin_off = torch.cat([o + int(nnz[t]) for t, o in enumerate(offs)]
+                            + [torch.tensor([int(nnz[-1])], dtype=torch.int64, device=dev)])
+        base = self.tables.d_row_base
+        iwro = torch.cat([i + base[t] for t, i in enumerate(idx)])
+        return lin_idx, lin_off, iwro
+
+    def to_bfloat16_train(self):
+        """Store the tables in bf16 (halves gather traffic).  NOTE: plain bf16 rows, the
+        reference's split hi/lo 'trail' storage (P/dlrm_s_pytorch.py:920-933) is not kept yet."""
+        for k in range(self.n_tables):
+            h = getattr(self, str(k))
+            h.weight = nn.Parameter(h.weight.data.to(torch.bfloat16), requires_grad=False)
+        self._rebuild_tables()
+        return self
+
+    def forward(self, input, need_linearize_indices_and_offsets=None):
+        need = True if need_linearize_indices_and_offsets is None else bool(need_linearize_indices_and_offsets)
+        if need:
+            idx_l, off_l = input[0], input[1]
+            inc = input[2] if len(input) > 2 else [False] * len(idx_l)
+            indices, offsets, _ = self.linearize_indices_and_offsets(idx_l, off_l, inc)
+        else:
+            indices, offsets = input[0], input[1]
+        B = (offsets.numel() - 1) // self.n_tables
+        if torch.is_grad_enabled() and self.training:
+            return list(_MergedEmbFn.apply(self._trigger, self, indices, offsets, B))
+        T, D = self.n_tables, self.dim
+        s0 = 1 if self.reserve_dense_slot else 0
+        buf = torch.empty(B, T + s0, D, dtype=self.output_dtype or self.tables.dtype, device=indices.device)
+        if s0:
+            _register_pooled(buf)
+        ops.emb_fwd(self.tables, indices, offsets, B, buf[:, s0:], D, (T + s0) * D, self.error_flag)
+        return [buf[:, s0 + k] for k in range(T)]
+
+    # ---- internals -----------------------------------------------------------------
+    def _rebuild_tables(self):
+        states = self.tables.states if getattr(self, "tables", None) is not None else None
+        self.tables = ops.TableSet(self.weights, states)
+
+    def _apply(self, fn, *a, **k):  # keep the device pointer table valid after .to()/.cuda()
+        r = super()._apply(fn, *a, **k)
+        if getattr(self, "tables", None) is not None:
+            self._rebuild_tables()
+        return r
+
+    def _workspace(self, nnz: int) -> torch.Tensor:
+        need = ops.emb_bwd_workspace_bytes(nnz)
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = torch.empty(need, dtype=torch.uint8, device=self.weights[0].device)
+        return self._ws
+
+    @contextlib.contextmanager
+    def _timed(self, name):
+        """CUDA-event bracket on the launching stream, active only when ``self.profile`` is a dict
+        (bench.py's roofline measurement); otherwise free."""
+        if self.profile is None:
+            yield
+            return
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        yield
+        b.record()
+        self.profile.setdefault(name, []).append((a, b))
+
+    def _launch_prepare(self, indices, offsets, B):
+        """Index stage of the backward (keys -> stable sort -> dedup).  It depends only on this
+        step's indices, so it is issued on a side stream right after the forward gather and
+        overlaps the interaction / MLP forward+backward; ``_apply_update`` joins it."""
+        ws = self._workspace(indices.numel())
+        if not self.overlap_prepare:
+            self._prep_event = None
+            return
+        main = torch.cuda.current_stream()
+        if self._side_stream is None:
+            self._side_stream = torch.cuda.Stream(device=indices.device)
+        self._side_stream.wait_stream(main)
+        with torch.cuda.stream(self._side_stream):
+            ops.emb_bwd_prepare(self.tables, indices, offsets, B, ws, self.error_flag)
+            ev = torch.cuda.Event()
+            ev.record(self._side_stream)
+        self._prep_event = ev
+
+    def _apply_update(self, indices, offsets, B, grad_base, stride_table, stride_bag):
+        opt = ops.OPT_ADAGRAD if self.optimizer_kind == "adagrad" else ops.OPT_SGD
+        ws = self._workspace(indices.numel())
+        if self._prep_event is not None:
+            torch.cuda.current_stream().wait_event(self._prep_event)
+            self._prep_event = None
+        else:
+            with self._timed("emb_bwd_prepare"):
+                ops.emb_bwd_prepare(self.tables, indices, offsets, B, ws, self.error_flag)
+        with self._timed("emb_bwd_apply"):
+            ops.emb_bwd_apply(self.tables, indices.numel(), B, grad_base, stride_table, stride_bag,
+                              self.sgd_args.lr, ws, optimizer=opt, eps=self.eps, lr_tensor=self.lr_tensor)

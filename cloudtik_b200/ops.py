@@ -139,6 +139,33 @@ def emb_bwd_update(tables: TableSet, indices, offsets, B: int, grad: torch.Tenso
         error.data_ptr() if error is not None else None, _stream()), "b200_emb_bwd_update")
 
 
+def emb_bwd_prepare(tables: TableSet, indices, offsets, B: int, ws: torch.Tensor,
+                    error: torch.Tensor | None = None):
+    """Index stage of the backward (keys, stable sort, dedup) into ``ws``.  See b200_emb_bwd_prepare."""
+    _cuda(indices, "indices", torch.int64)
+    _cuda(offsets, "offsets", torch.int64)
+    check(lib.b200_emb_bwd_prepare(tables.d_rows.data_ptr(), tables.d_row_base.data_ptr(), indices.data_ptr(),
+                                   offsets.data_ptr(), indices.numel(), len(tables), B, tables.total_rows,
+                                   ws.data_ptr(), ws.numel() * ws.element_size(),
+                                   error.data_ptr() if error is not None else None, _stream()),
+          "b200_emb_bwd_prepare")
+
+
+def emb_bwd_apply(tables: TableSet, nnz: int, B: int, grad: torch.Tensor, stride_table: int, stride_bag: int,
+                  lr: float, ws: torch.Tensor, optimizer: int = OPT_SGD, eps: float = 1e-10,
+                  lr_tensor: torch.Tensor | None = None):
+    """Segment-reduce + row update from a prepared ``ws``.  See b200_emb_bwd_apply."""
+    _cuda(grad, "grad")
+    if optimizer == OPT_ADAGRAD and tables.d_state_ptrs is None:
+        raise _lib.B200Error("Adagrad needs per-table fp32 state (TableSet.set_states)")
+    check(lib.b200_emb_bwd_apply(
+        tables.d_ptrs.data_ptr(), tables.d_state_ptrs.data_ptr() if tables.d_state_ptrs is not None else None,
+        tables.d_row_base.data_ptr(), nnz, grad.data_ptr(), len(tables), B, tables.D, stride_table, stride_bag,
+        _dt(tables.dtype), _dt(grad.dtype), optimizer, float(lr),
+        lr_tensor.data_ptr() if lr_tensor is not None else None, float(eps), ws.data_ptr(),
+        ws.numel() * ws.element_size(), _stream()), "b200_emb_bwd_apply")
+
+
 def interact_fwd(T: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
     """T [B, F, D] contiguous -> R [B, D + F(F-1)/2].  See b200_interact_fwd."""
     _cuda(T, "T")

@@ -105,6 +105,22 @@ int b200_emb_bwd_update(void* const* d_weights, float* const* d_state, const int
                         b200_stream_t stream);
 
 /*
+ * The two halves of b200_emb_bwd_update, callable separately (same workspace in between):
+ *   prepare: keys + stable sort + dedup.  Depends only on the step's indices, so a caller may
+ *            issue it on a side stream while the forward / dense backward runs.
+ *   apply:   segment-reduce the gradient rows of each unique row and update it.
+ */
+int b200_emb_bwd_prepare(const int64_t* d_rows, const int64_t* d_row_base, const int64_t* d_indices,
+                         const int64_t* d_offsets, int64_t nnz, int64_t T, int64_t B,
+                         int64_t total_rows, void* ws, size_t ws_bytes, int32_t* d_error,
+                         b200_stream_t stream);
+int b200_emb_bwd_apply(void* const* d_weights, float* const* d_state, const int64_t* d_row_base,
+                       int64_t nnz, const void* d_grad, int64_t T, int64_t B, int64_t D,
+                       int64_t grad_stride_table, int64_t grad_stride_bag, int w_dtype, int grad_dtype,
+                       int optimizer, float lr, const float* d_lr, float eps, void* ws, size_t ws_bytes,
+                       b200_stream_t stream);
+
+/*
  * Pairwise dot-product feature interaction, forward and backward.
  * Replaces DLRM_Net.interact_features (P/dlrm_s_pytorch.py:309-334, T/dlrm_s_pytorch.py:407-444;
  * cat + bmm + tril gather + cat) and ipex.nn.functional.interaction(*T) (P/dlrm_s_pytorch.py:312).

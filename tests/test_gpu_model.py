@@ -1,0 +1,98 @@
+"""End-to-end parity of the B200 DLRM step against the reference's loss traces
+(tests/golden/*.npz, generated from the reference code by oracle/gen_golden.py) and against
+the torch-CPU port run side by side.  fp32: <= 1e-5 relative; bf16: <= 1e-2."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _build(g, **kw):
+    from cloudtik_b200.dlrm import DLRM_Net
+    np.random.seed(int(g["seed"]))
+    torch.manual_seed(int(g["seed"]))
+    ln_top = g["ln_top"]
+    return DLRM_Net(int(g["D"]), g["ln_emb"], g["ln_bot"], ln_top, sigmoid_bot=-1, sigmoid_top=ln_top.size - 2,
+                    np_init_emb_weight=True, device="cuda", lr=float(g["lr"]), **kw)
+
+
+def _dense_sgd(net, lr):
+    return torch.optim.SGD([p for p in net.parameters() if p.requires_grad], lr=lr)
+
+
+def test_small_model_matches_reference(golden):
+    from cloudtik_b200.dlrm import train_step
+    g = golden("small_model")
+    net = _build(g)
+    sd = net.state_dict()
+    for k in sd:
+        if "emb_l" in k or "bot_l" in k or "top_l" in k:
+            np.testing.assert_array_equal(sd[k].cpu().numpy(), g["init/" + k])  # same keys, same init
+    opt = _dense_sgd(net, float(g["lr"]))
+    nt = len(g["ln_emb"])
+    losses = []
+    for s in range(int(g["steps"])):
+        lS_o = [torch.tensor(g[f"o{s}_{t}"]).cuda() for t in range(nt)]
+        lS_i = [torch.tensor(g[f"i{s}_{t}"]).cuda() for t in range(nt)]
+        L = train_step(net, opt, torch.tensor(g[f"X{s}"]).cuda(), (lS_o, lS_i), torch.tensor(g[f"T{s}"]).cuda())
+        losses.append(float(L.cpu()))
+    np.testing.assert_allclose(losses, g["losses"], rtol=1e-5)
+    for k, v in net.state_dict().items():
+        np.testing.assert_allclose(v.cpu().numpy(), g["final/" + k], rtol=1e-5, atol=1e-6)
+
+
+def test_kaggle_c1_loss_trace(golden):
+    """BASELINE config 1 (Kaggle shape, D=16, B=128, SGD lr 0.1): 8-step loss trace of the reference."""
+    from cloudtik_b200.dlrm import train_step
+    g = golden("kaggle_c1")
+    net = _build(g)
+    sums = np.array([w.double().sum().item() for w in net.emb_l.weights])
+    np.testing.assert_allclose(sums, g["init_table_sums"], rtol=1e-12, atol=1e-9)
+    opt = _dense_sgd(net, float(g["lr"]))
+    losses = []
+    for s in range(int(g["steps"])):
+        lS_o = [torch.tensor(g["off"][s, t].astype(np.int64)).cuda() for t in range(26)]
+        lS_i = [torch.tensor(g["idx"][s, t].astype(np.int64)).cuda() for t in range(26)]
+        indices, offsets, iwro = net.emb_l.linearize_indices_and_offsets(lS_i, lS_o, [False] * 26)
+        L = train_step(net, opt, torch.tensor(g["X"][s]).cuda(), (indices, offsets, iwro), torch.tensor(g["T"][s]).cuda())
+        losses.append(float(L.cpu()))
+    np.testing.assert_allclose(losses, g["losses"], rtol=1e-5)
+    for t in (2, 23):
+        rows = torch.tensor(g[f"rows_t{t}"]).cuda()
+        np.testing.assert_allclose(net.emb_l.weights[t][rows].cpu().numpy(), g[f"final_rows_t{t}"], rtol=1e-5, atol=1e-7)
+    np.testing.assert_allclose(net.top_l[0].weight[:8].detach().cpu().numpy(), g["final_top0_w"], rtol=1e-4, atol=1e-6)
+
+
+@pytest.mark.parametrize("bf16", [False, True])
+def test_terabyte_arch_vs_cpu_port(bf16):
+    """Config-3 architecture (D=128, bot 13-512-256-128, top 479-1024-1024-512-256-1) with small
+    tables, multi-hot ragged bags, 5 steps: GPU step vs the torch-CPU port on identical inputs."""
+    from cloudtik_b200.dlrm import DLRM_Net, train_step
+    from oracle.dlrm_port import DLRMPort, train_step as cpu_step, uniform_batch
+    D, rows = 128, [5000, 37, 20000, 3, 1200, 800, 64, 100000]
+    F = len(rows) + 1
+    ln_bot, ln_top = [13, 512, 256, D], [D + F * (F - 1) // 2, 1024, 1024, 512, 256, 1]
+    B, lr, steps = 512, 0.05, 5
+    np.random.seed(7)
+    port = DLRMPort(D, rows, ln_bot, ln_top)
+    np.random.seed(7)
+    net = DLRM_Net(D, np.array(rows), np.array(ln_bot), np.array(ln_top), sigmoid_top=len(ln_top) - 2,
+                   np_init_emb_weight=True, lr=lr, bf16=bf16)
+    copt = torch.optim.SGD(port.parameters(), lr=lr)
+    gopt = _dense_sgd(net, lr)
+    rs = np.random.RandomState(99)
+    cl, gl = [], []
+    for s in range(steps):
+        X, lS_o, lS_i, T = uniform_batch(rs, B, rows, pooling=4, unique_in_bag=(s % 2 == 0))
+        cl.append(cpu_step(port, copt, torch.tensor(X), [torch.tensor(o) for o in lS_o],
+                           [torch.tensor(i) for i in lS_i], torch.tensor(T), bf16=bf16))
+        L = train_step(net, gopt, torch.tensor(X).cuda(), ([torch.tensor(o).cuda() for o in lS_o],
+                                                          [torch.tensor(i).cuda() for i in lS_i]),
+                       torch.tensor(T).cuda())
+        gl.append(float(L.cpu()))
+    tol = 1e-2 if bf16 else 1e-5
+    np.testing.assert_allclose(gl, cl, rtol=tol)
+    for t in range(len(rows)):
+        np.testing.assert_allclose(net.emb_l.weights[t].cpu().numpy(), port.emb_l[t].weight.detach().numpy(),
+                                   rtol=tol, atol=tol * 1e-2 if not bf16 else 2e-3)
