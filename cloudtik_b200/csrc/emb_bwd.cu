@@ -19,14 +19,21 @@ namespace b200 {
 constexpr int KEYS_THREADS = 256;
 constexpr int UPD_THREADS = 256;
 
+// Runs longer than HOT_CH positions ("hot" rows: tiny tables, Zipf heads) are not summed by one
+// group serially: the sorted array is cut into windows of HOT_CH positions, every window
+// pre-reduces the (at most two) hot runs that cross it into fp32 partial rows, and the update
+// kernel adds the partials of a hot row in window order.  Deterministic, no atomics.
+constexpr int HOT_CH = 128;
+
 struct BwdLayout {
   uint32_t *keys, *vals, *skeys, *svals, *unique, *seg;
   int32_t* num_unique;
+  float* partial;  // [2 * ceil(n / HOT_CH)][D]
   void* sort_ws;
   size_t total;
 };
 
-static BwdLayout bwd_layout(void* ws, int64_t n) {
+static BwdLayout bwd_layout(void* ws, int64_t n, int64_t D) {
   BwdLayout L;
   char* w = static_cast<char*>(ws);
   const size_t s = align_up((size_t)n * 4, 256);
@@ -38,6 +45,7 @@ static BwdLayout bwd_layout(void* ws, int64_t n) {
   L.unique = reinterpret_cast<uint32_t*>(w + o), o += s;
   L.seg = reinterpret_cast<uint32_t*>(w + o), o += align_up((size_t)(n + 1) * 4, 256);
   L.num_unique = reinterpret_cast<int32_t*>(w + o), o += 256;
+  L.partial = reinterpret_cast<float*>(w + o), o += align_up((size_t)(2 * ceil_div(n, HOT_CH)) * D * 4, 256);
   L.sort_ws = w + o, o += sort_ws_bytes(n);
   L.total = o;
   return L;
@@ -102,6 +110,9 @@ struct UpdParams {
   float lr, eps;
   uint32_t B;
   int D, V;
+  const uint32_t* skeys;
+  float* partial;
+  int64_t n;
 };
 
 // load VE consecutive gradient elements (GT) as fp32
@@ -128,6 +139,82 @@ __device__ __forceinline__ void load_grad<__nv_bfloat16, 4>(const __nv_bfloat16*
   out[1] = bf16hi(v.x);
   out[2] = bf16lo(v.y);
   out[3] = bf16hi(v.y);
+}
+
+// One group per window of HOT_CH sorted positions: partial sums of the hot runs crossing it.
+// slot 0 = the run that contains the window's first position, slot 1 = a hot run that starts
+// inside the window (a window cannot hold a third: hot runs are longer than a window).
+template <typename GT, int VE, int G, int NV>
+__global__ void __launch_bounds__(UPD_THREADS) hot_window_kernel(const UpdParams p) {
+  constexpr int NG = UPD_THREADS / G;
+  const int gid = threadIdx.x / G, lane = threadIdx.x % G;
+  const int64_t w = (int64_t)blockIdx.x * NG + gid;
+  const int64_t a = w * HOT_CH;
+  if (a >= p.n) return;
+  const int64_t b = min(a + (int64_t)HOT_CH, p.n);
+  const bool cont_before = a > 0 && p.skeys[a - 1] == p.skeys[a];
+  const bool cont_after = b < p.n && p.skeys[b - 1] == p.skeys[b];
+  if (!cont_before && !cont_after) return;  // no run longer than a window can touch this one
+  const int64_t nU = *p.num_unique;
+  auto run_of = [&](int64_t pos) -> int64_t {  // largest u with seg[u] <= pos
+    int64_t lo = 0, hi = nU;                   // seg[lo] <= pos < seg[hi]
+    while (hi - lo > 1) {
+      const int64_t mid = (lo + hi) >> 1;
+      if ((int64_t)p.seg[mid] <= pos) lo = mid; else hi = mid;
+    }
+    return lo;
+  };
+  auto reduce_range = [&](int64_t lo, int64_t hi, int slot) {
+    float acc[NV][VE];
+#pragma unroll
+    for (int k = 0; k < NV; ++k)
+#pragma unroll
+      for (int x = 0; x < VE; ++x) acc[k][x] = 0.f;
+    const uint32_t tt = p.svals[lo] / p.B;
+    const GT* gt = static_cast<const GT*>(p.grad) + (int64_t)tt * p.grad_stride_table;
+    for (int64_t j = lo; j < hi; j += 8) {
+      float g8[8][NV][VE];
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        const bool ok = j + c < hi;
+        const uint32_t bb = ok ? p.svals[j + c] - tt * p.B : 0;
+        const GT* gp = gt + (int64_t)bb * p.grad_stride_bag;
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+          const int vi = lane + k * G;
+          if (ok && vi < p.V) {
+            load_grad<GT, VE>(gp + vi * VE, g8[c][k]);
+          } else {
+#pragma unroll
+            for (int x = 0; x < VE; ++x) g8[c][k][x] = 0.f;
+          }
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < 8; ++c)
+#pragma unroll
+        for (int k = 0; k < NV; ++k)
+#pragma unroll
+          for (int x = 0; x < VE; ++x) acc[k][x] += g8[c][k][x];
+    }
+    float* dst = p.partial + (size_t)(2 * w + slot) * p.D;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int vi = lane + k * G;
+      if (vi < p.V) {
+#pragma unroll
+        for (int h = 0; h < VE / 4; ++h) store_vec<float, 4, false>(dst + vi * VE + 4 * h, acc[k] + 4 * h);
+      }
+    }
+  };
+  const int64_t ua = run_of(a);
+  const int64_t sa = p.seg[ua], ea = p.seg[ua + 1];
+  if (ea - sa > HOT_CH) reduce_range(a, min(b, ea), 0);
+  if (ea < b) {
+    const int64_t ub = run_of(b - 1);
+    const int64_t sb = p.seg[ub], eb = p.seg[ub + 1];
+    if (eb - sb > HOT_CH) reduce_range(sb, b, 1);
+  }
 }
 
 template <typename WT, typename GT, int G, int NV, int OPT>
@@ -191,6 +278,28 @@ __global__ void __launch_bounds__(UPD_THREADS) emb_update_kernel(const UpdParams
 #pragma unroll 1
     for (int q = 0; q < R; ++q) {
       if (!valid[q]) continue;
+      if (e[q] - s[q] > (uint32_t)HOT_CH) {
+        // hot row: add the per-window partial sums (hot_window_kernel) in window order
+        const uint32_t w0 = s[q] / HOT_CH, w1 = (e[q] - 1) / HOT_CH;
+        for (uint32_t w = w0; w <= w1; ++w) {
+          const int slot = (s[q] > w * HOT_CH) ? 1 : 0;
+          const float* src = p.partial + (size_t)(2 * w + slot) * p.D;
+#pragma unroll
+          for (int k = 0; k < NV; ++k) {
+            const int vi = lane + k * G;
+            if (vi < p.V) {
+#pragma unroll
+              for (int h = 0; h < VE / 4; ++h) {
+                float f[4];
+                Vec16<float>::unpack(f, ld_v4(src + vi * VE + 4 * h));
+#pragma unroll
+                for (int x = 0; x < 4; ++x) acc[q][k][4 * h + x] += f[x];
+              }
+            }
+          }
+        }
+        continue;
+      }
       for (uint32_t j = s[q]; j < e[q]; j += 4) {
         float g4[4][NV][VE];
 #pragma unroll
@@ -295,17 +404,20 @@ static int launch_update(const UpdParams& p, int64_t n, bool vec_ok, cudaStream_
     return B200_OK;
   }
   const int V = p.V;
-#define B200_UPD_CASE(G, NV)                                                        \
-  emb_update_kernel<WT, GT, G, NV, OPT>                                             \
+  constexpr int VE = Vec16<WT>::VE;
+  const int64_t nwin = ceil_div(n, HOT_CH);
+#define B200_UPD_CASE(G, NV)                                                                       \
+  hot_window_kernel<GT, VE, G, NV><<<(unsigned)ceil_div(nwin, UPD_THREADS / G), UPD_THREADS, 0, st>>>(p); \
+  emb_update_kernel<WT, GT, G, NV, OPT>                                                            \
       <<<(unsigned)ceil_div(n, (UPD_THREADS / G) * 4), UPD_THREADS, 0, st>>>(p)
-  if (V <= 1) B200_UPD_CASE(1, 1);
-  else if (V <= 2) B200_UPD_CASE(2, 1);
-  else if (V <= 4) B200_UPD_CASE(4, 1);
-  else if (V <= 8) B200_UPD_CASE(8, 1);
-  else if (V <= 16) B200_UPD_CASE(16, 1);
-  else if (V <= 32) B200_UPD_CASE(32, 1);
-  else if (V <= 64) B200_UPD_CASE(32, 2);
-  else B200_UPD_CASE(32, 4);
+  if (V <= 1) { B200_UPD_CASE(1, 1); }
+  else if (V <= 2) { B200_UPD_CASE(2, 1); }
+  else if (V <= 4) { B200_UPD_CASE(4, 1); }
+  else if (V <= 8) { B200_UPD_CASE(8, 1); }
+  else if (V <= 16) { B200_UPD_CASE(16, 1); }
+  else if (V <= 32) { B200_UPD_CASE(32, 1); }
+  else if (V <= 64) { B200_UPD_CASE(32, 2); }
+  else { B200_UPD_CASE(32, 4); }
 #undef B200_UPD_CASE
   B200_CHECK_LAUNCH("emb_update");
   return B200_OK;
@@ -315,8 +427,8 @@ static int launch_update(const UpdParams& p, int64_t n, bool vec_ok, cudaStream_
 
 using namespace b200;
 
-extern "C" size_t b200_emb_bwd_workspace_bytes(int64_t nnz) {
-  return bwd_layout(nullptr, nnz < 0 ? 0 : nnz).total;
+extern "C" size_t b200_emb_bwd_workspace_bytes(int64_t nnz, int64_t D) {
+  return bwd_layout(nullptr, nnz < 0 ? 0 : nnz, D < 1 ? 1 : D).total;
 }
 
 static int check_bwd_common(int64_t T, int64_t B, int64_t D, int64_t nnz, int64_t total_rows) {
@@ -330,17 +442,17 @@ static int check_bwd_common(int64_t T, int64_t B, int64_t D, int64_t nnz, int64_
 
 extern "C" int b200_emb_bwd_prepare(const int64_t* d_rows, const int64_t* d_row_base,
                                     const int64_t* d_indices, const int64_t* d_offsets, int64_t nnz,
-                                    int64_t T, int64_t B, int64_t total_rows, void* ws, size_t ws_bytes,
+                                    int64_t T, int64_t B, int64_t D, int64_t total_rows, void* ws, size_t ws_bytes,
                                     int32_t* d_error, b200_stream_t stream) {
-  int rc = check_bwd_common(T, B, 1, nnz, total_rows);
+  int rc = check_bwd_common(T, B, D, nnz, total_rows);
   if (rc) return rc;
   if (T == 0 || B == 0 || nnz == 0) return B200_OK;
   B200_REQUIRE(d_rows && d_row_base && d_indices && d_offsets && ws, B200_EINVAL,
                "emb_bwd_prepare: null pointer");
-  B200_REQUIRE(ws_bytes >= b200_emb_bwd_workspace_bytes(nnz), B200_EWORKSPACE,
+  B200_REQUIRE(ws_bytes >= b200_emb_bwd_workspace_bytes(nnz, D), B200_EWORKSPACE,
                "emb_bwd: workspace too small");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  BwdLayout L = bwd_layout(ws, nnz);
+  BwdLayout L = bwd_layout(ws, nnz, D);
   dim3 kgrid((unsigned)ceil_div(B, KEYS_THREADS), (unsigned)T);
   build_keys_kernel<<<kgrid, KEYS_THREADS, 0, st>>>(d_indices, d_offsets, d_rows, d_row_base, B, L.keys,
                                                     L.vals, d_error);
@@ -364,10 +476,10 @@ extern "C" int b200_emb_bwd_apply(void* const* d_weights, float* const* d_state,
   B200_REQUIRE((w_dtype == B200_F32 || w_dtype == B200_BF16) &&
                    (grad_dtype == B200_F32 || grad_dtype == B200_BF16),
                B200_EINVAL, "emb_bwd: bad dtype");
-  B200_REQUIRE(ws_bytes >= b200_emb_bwd_workspace_bytes(nnz), B200_EWORKSPACE,
+  B200_REQUIRE(ws_bytes >= b200_emb_bwd_workspace_bytes(nnz, D), B200_EWORKSPACE,
                "emb_bwd: workspace too small");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  BwdLayout L = bwd_layout(ws, nnz);
+  BwdLayout L = bwd_layout(ws, nnz, D);
   UpdParams p;
   p.weights = d_weights;
   p.state = d_state;
@@ -384,6 +496,9 @@ extern "C" int b200_emb_bwd_apply(void* const* d_weights, float* const* d_state,
   p.eps = eps;
   p.B = (uint32_t)B;
   p.D = (int)D;
+  p.skeys = L.skeys;
+  p.partial = L.partial;
+  p.n = nnz;
   const int wsz = dtype_size(w_dtype), gsz = dtype_size(grad_dtype);
   p.V = (int)(D * wsz / 16);
   const int ve = 16 / wsz;  // elements per weight vector
@@ -411,7 +526,7 @@ extern "C" int b200_emb_bwd_update(void* const* d_weights, float* const* d_state
                                    int grad_dtype, int optimizer, float lr, const float* d_lr,
                                    float eps, int64_t total_rows, void* ws, size_t ws_bytes,
                                    int32_t* d_error, b200_stream_t stream) {
-  int rc = b200_emb_bwd_prepare(d_rows, d_row_base, d_indices, d_offsets, nnz, T, B, total_rows, ws,
+  int rc = b200_emb_bwd_prepare(d_rows, d_row_base, d_indices, d_offsets, nnz, T, B, D, total_rows, ws,
                                 ws_bytes, d_error, stream);
   if (rc) return rc;
   return b200_emb_bwd_apply(d_weights, d_state, d_row_base, nnz, d_grad, T, B, D, grad_stride_table,

@@ -221,7 +221,7 @@ class MergedEmbeddingBagWithSGD(nn.Module):
         return r
 
     def _workspace(self, nnz: int) -> torch.Tensor:
-        need = ops.emb_bwd_workspace_bytes(nnz)
+        need = ops.emb_bwd_workspace_bytes(nnz, self.dim)
         if self._ws is None or self._ws.numel() < need:
             self._ws = torch.empty(need, dtype=torch.uint8, device=self.weights[0].device)
         return self._ws

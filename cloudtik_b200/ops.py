@@ -114,8 +114,8 @@ def sort_dedup(keys: torch.Tensor, vals: torch.Tensor, key_bound: int):
     return skeys, svals, uniq[:U], seg[:U + 1], U
 
 
-def emb_bwd_workspace_bytes(nnz: int) -> int:
-    return int(lib.b200_emb_bwd_workspace_bytes(nnz))
+def emb_bwd_workspace_bytes(nnz: int, D: int) -> int:
+    return int(lib.b200_emb_bwd_workspace_bytes(nnz, D))
 
 
 def emb_bwd_update(tables: TableSet, indices, offsets, B: int, grad: torch.Tensor, stride_table: int,
@@ -145,8 +145,8 @@ def emb_bwd_prepare(tables: TableSet, indices, offsets, B: int, ws: torch.Tensor
     _cuda(indices, "indices", torch.int64)
     _cuda(offsets, "offsets", torch.int64)
     check(lib.b200_emb_bwd_prepare(tables.d_rows.data_ptr(), tables.d_row_base.data_ptr(), indices.data_ptr(),
-                                   offsets.data_ptr(), indices.numel(), len(tables), B, tables.total_rows,
-                                   ws.data_ptr(), ws.numel() * ws.element_size(),
+                                   offsets.data_ptr(), indices.numel(), len(tables), B, tables.D,
+                                   tables.total_rows, ws.data_ptr(), ws.numel() * ws.element_size(),
                                    error.data_ptr() if error is not None else None, _stream()),
           "b200_emb_bwd_prepare")
 

@@ -93,9 +93,9 @@ int b200_sort_dedup(const uint32_t* d_keys, const uint32_t* d_vals, int64_t n, u
  *   d_state     Adagrad: device array [T] of fp32 state_sum tables; SGD: NULL
  *   lr / d_lr   learning rate by value, or (if d_lr != NULL) read from device memory at
  *               kernel time so a captured graph follows the LR schedule
- *   ws          b200_emb_bwd_workspace_bytes(nnz) bytes
+ *   ws          b200_emb_bwd_workspace_bytes(nnz, D) bytes
  */
-size_t b200_emb_bwd_workspace_bytes(int64_t nnz);
+size_t b200_emb_bwd_workspace_bytes(int64_t nnz, int64_t D);
 int b200_emb_bwd_update(void* const* d_weights, float* const* d_state, const int64_t* d_rows,
                         const int64_t* d_row_base, const int64_t* d_indices,
                         const int64_t* d_offsets, int64_t nnz, const void* d_grad, int64_t T,
@@ -111,7 +111,7 @@ int b200_emb_bwd_update(void* const* d_weights, float* const* d_state, const int
  *   apply:   segment-reduce the gradient rows of each unique row and update it.
  */
 int b200_emb_bwd_prepare(const int64_t* d_rows, const int64_t* d_row_base, const int64_t* d_indices,
-                         const int64_t* d_offsets, int64_t nnz, int64_t T, int64_t B,
+                         const int64_t* d_offsets, int64_t nnz, int64_t T, int64_t B, int64_t D,
                          int64_t total_rows, void* ws, size_t ws_bytes, int32_t* d_error,
                          b200_stream_t stream);
 int b200_emb_bwd_apply(void* const* d_weights, float* const* d_state, const int64_t* d_row_base,

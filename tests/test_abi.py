@@ -35,4 +35,4 @@ def test_host_side_argument_checks_need_no_gpu():
     assert rc == 1 and b"negative" in _lib.lib.b200_last_error()
     rc = _lib.lib.b200_sort_dedup(None, None, 5, 0, None, None, None, None, None, None, 0, None)
     assert rc == 2
-    assert _lib.lib.b200_emb_bwd_workspace_bytes(1000) > 6 * 4000
+    assert _lib.lib.b200_emb_bwd_workspace_bytes(1000, 128) > 6 * 4000

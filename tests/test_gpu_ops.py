@@ -171,7 +171,7 @@ def test_emb_bwd_update(rows, B, D, pooling, ragged, wdt, gdt, opt):
         st = [torch.tensor(rs.rand(n, D).astype(np.float32)).cuda() for n in rows]
         states_np = [s.cpu().numpy().copy() for s in st]
         ts.set_states(st)
-    ws = torch.empty(ops.emb_bwd_workspace_bytes(len(indices)), dtype=torch.uint8, device="cuda")
+    ws = torch.empty(ops.emb_bwd_workspace_bytes(len(indices), D), dtype=torch.uint8, device="cuda")
     err = torch.zeros(1, dtype=torch.int32, device="cuda")
     lr_t = torch.tensor([lr], device="cuda")
     ops.emb_bwd_update(ts, torch.tensor(indices).cuda(), torch.tensor(offsets).cuda(), B, g[:, 1:], D, F * D,
@@ -188,6 +188,71 @@ def test_emb_bwd_update(rows, B, D, pooling, ragged, wdt, gdt, opt):
         else:
             ref.sparse_sgd_update(W, idx_l[t], off_l[t], gr[:, 1 + t], lr)
         np.testing.assert_allclose(tw[t].float().cpu().numpy(), W, rtol=rtol, atol=atol)
+
+
+HOT_CASES = [
+    # rows, B, D, pooling, wdtype, gdtype, opt  -- runs far longer than the 128-position hot window
+    ([3, 500, 7], 3000, 128, 1, torch.float32, torch.float32, "sgd"),
+    ([3, 40], 1500, 64, 2, torch.bfloat16, torch.bfloat16, "sgd"),
+    ([4, 100000], 700, 128, 1, torch.float32, torch.bfloat16, "sgd"),
+    ([4], 700, 128, 1, torch.float32, torch.float32, "adagrad"),
+    ([2, 9], 1111, 16, 3, torch.float32, torch.float32, "sgd"),
+]
+
+
+@pytest.mark.parametrize("rows,B,D,pooling,wdt,gdt,opt", HOT_CASES)
+def test_emb_bwd_hot_rows(rows, B, D, pooling, wdt, gdt, opt):
+    """Hot rows (thousands of duplicates: the tiny Criteo tables) go through the windowed
+    partial-sum path; checked against a float64 evaluation of the same update."""
+    ops = _ops()
+    rs = np.random.RandomState(B + D)
+    Wr, tw = _tables(rs, rows, D, wdt)
+    idx_l, off_l = _make_bags(rs, rows, B, pooling, False)
+    indices, offsets, _ = ref.linearize_indices_and_offsets(idx_l, off_l, rows)
+    T, F = len(rows), len(rows) + 1
+    g = torch.tensor(rs.randn(B, F, D).astype(np.float32)).to(gdt).cuda()
+    gr = g.float().cpu().numpy().astype(np.float64)
+    ts = ops.TableSet(tw)
+    lr = 0.01
+    if opt == "adagrad":
+        ts.set_states([torch.zeros(n, D, device="cuda") for n in rows])
+    ws = torch.empty(ops.emb_bwd_workspace_bytes(len(indices), D), dtype=torch.uint8, device="cuda")
+    ops.emb_bwd_update(ts, torch.tensor(indices).cuda(), torch.tensor(offsets).cuda(), B, g[:, 1:], D, F * D,
+                       lr=lr, ws=ws, optimizer=ops.OPT_ADAGRAD if opt == "adagrad" else ops.OPT_SGD)
+    torch.cuda.synchronize()
+    for t in range(T):
+        G = np.zeros((rows[t], D))
+        np.add.at(G, idx_l[t], gr[:, 1 + t][ref.offset2bag(off_l[t], len(idx_l[t]))])
+        if opt == "adagrad":
+            want = Wr[t] - lr * G / (np.sqrt(G * G) + 1e-10)
+        else:
+            want = Wr[t] - lr * G
+        got = tw[t].float().cpu().numpy()
+        if wdt == torch.float32:
+            np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-5 * np.abs(lr * G).max())
+        else:
+            np.testing.assert_allclose(got, want, rtol=1e-2, atol=1e-2)
+
+
+def test_emb_bwd_hot_window_boundaries():
+    """Crafted run lengths around the window size (127, 128, 129, 256, 257, 1, 640...) in one table."""
+    ops = _ops()
+    D, lens = 128, [127, 128, 129, 1, 256, 257, 1, 1, 640, 5, 383, 130]
+    rows = [len(lens) + 3]
+    idx = np.concatenate([np.full(n, r) for r, n in enumerate(lens)]).astype(np.int64)
+    rs = np.random.RandomState(0)
+    rs.shuffle(idx)
+    B = len(idx)
+    off = np.arange(B + 1, dtype=np.int64)
+    W = torch.zeros(rows[0], D, device="cuda")
+    g = torch.tensor(rs.randint(-3, 4, size=(B, D)).astype(np.float32)).cuda()  # integers: sums are exact
+    ts = ops.TableSet([W])
+    ws = torch.empty(ops.emb_bwd_workspace_bytes(B, D), dtype=torch.uint8, device="cuda")
+    ops.emb_bwd_update(ts, torch.tensor(idx).cuda(), torch.tensor(off).cuda(), B, g, B * D, D, lr=1.0, ws=ws)
+    torch.cuda.synchronize()
+    want = np.zeros((rows[0], D), np.float32)
+    np.add.at(want, idx, -g.cpu().numpy())
+    np.testing.assert_array_equal(W.cpu().numpy(), want)
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])

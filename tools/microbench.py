@@ -73,7 +73,7 @@ def main():
         off = torch.arange(0, T * B + 1, device=dev, dtype=torch.int64) * P
         buf = torch.empty(B, F, D, dtype=dt, device=dev)
         grad = torch.randn(B, F, D, device=dev).to(dt)
-        ws = torch.empty(ops.emb_bwd_workspace_bytes(T * nnz_t), dtype=torch.uint8, device=dev)
+        ws = torch.empty(ops.emb_bwd_workspace_bytes(T * nnz_t, D), dtype=torch.uint8, device=dev)
         Uavg = sum(s[1] for s in sets) / len(sets)
         common = T * nnz_t * 8 + (T * B + 1) * 8
         fwd_bytes = Uavg * D * es + common + T * B * D * es
