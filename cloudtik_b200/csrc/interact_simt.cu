@@ -22,7 +22,7 @@ __device__ __forceinline__ void pair_ij(int p, int& i, int& j) {
 
 template <typename ET>
 __global__ void __launch_bounds__(INT_THREADS)
-    interact_fwd_simt_kernel(const ET* __restrict__ T, ET* __restrict__ R, int64_t B, int F, int D) {
+    interact_fwd_simt_kernel(const ET* __restrict__ T, ET* __restrict__ R, int64_t B, int F, int D, int64_t ldr) {
   extern __shared__ float sT[];  // [F][D+1]
   const int ld = D + 1;
   const int npairs = F * (F - 1) / 2;
@@ -31,8 +31,9 @@ __global__ void __launch_bounds__(INT_THREADS)
     const ET* Tb = T + b * (int64_t)F * D;
     for (int i = threadIdx.x; i < F * D; i += INT_THREADS) sT[(i / D) * ld + (i % D)] = to_f32<ET>(Tb[i]);
     __syncthreads();
-    ET* Rb = R + b * (int64_t)rw;
+    ET* Rb = R + b * ldr;
     for (int d = threadIdx.x; d < D; d += INT_THREADS) Rb[d] = Tb[d];
+    for (int c = rw + threadIdx.x; c < ldr; c += INT_THREADS) Rb[c] = from_f32<ET>(0.f);
     for (int p = threadIdx.x; p < npairs; p += INT_THREADS) {
       int i, j;
       pair_ij(p, i, j);
@@ -49,15 +50,14 @@ __global__ void __launch_bounds__(INT_THREADS)
 template <typename ET>
 __global__ void __launch_bounds__(INT_THREADS)
     interact_bwd_simt_kernel(const ET* __restrict__ T, const ET* __restrict__ dR, ET* __restrict__ dT,
-                             int64_t B, int F, int D) {
+                             int64_t B, int F, int D, int64_t ldr) {
   extern __shared__ float sm[];  // sT [F][D] then sS [F][F]
   float* sT = sm;
   float* sS = sm + F * D;
   const int npairs = F * (F - 1) / 2;
-  const int rw = D + npairs;
   for (int64_t b = blockIdx.x; b < B; b += gridDim.x) {
     const ET* Tb = T + b * (int64_t)F * D;
-    const ET* dRb = dR + b * (int64_t)rw;
+    const ET* dRb = dR + b * ldr;
     for (int i = threadIdx.x; i < F * D; i += INT_THREADS) sT[i] = to_f32<ET>(Tb[i]);
     for (int i = threadIdx.x; i < F; i += INT_THREADS) sS[i * F + i] = 0.f;
     for (int p = threadIdx.x; p < npairs; p += INT_THREADS) {
@@ -80,35 +80,36 @@ __global__ void __launch_bounds__(INT_THREADS)
   }
 }
 
-int interact_fwd_simt(const void* T, void* R, int64_t B, int64_t F, int64_t D, int dtype, cudaStream_t st) {
+int interact_fwd_simt(const void* T, void* R, int64_t B, int64_t F, int64_t D, int64_t ldr, int dtype,
+                      cudaStream_t st) {
   const size_t smem = (size_t)F * (D + 1) * 4;
   B200_REQUIRE(smem <= 200 * 1024, B200_EUNSUPPORTED, "interact_fwd: F*D too large for shared memory");
   const int grid = (int)std::min<int64_t>(B, 148 * 16);
   if (dtype == B200_F32) {
     cudaFuncSetAttribute(interact_fwd_simt_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    interact_fwd_simt_kernel<float><<<grid, INT_THREADS, smem, st>>>((const float*)T, (float*)R, B, (int)F, (int)D);
+    interact_fwd_simt_kernel<float><<<grid, INT_THREADS, smem, st>>>((const float*)T, (float*)R, B, (int)F, (int)D, ldr);
   } else {
     cudaFuncSetAttribute(interact_fwd_simt_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     interact_fwd_simt_kernel<__nv_bfloat16>
-        <<<grid, INT_THREADS, smem, st>>>((const __nv_bfloat16*)T, (__nv_bfloat16*)R, B, (int)F, (int)D);
+        <<<grid, INT_THREADS, smem, st>>>((const __nv_bfloat16*)T, (__nv_bfloat16*)R, B, (int)F, (int)D, ldr);
   }
   B200_CHECK_LAUNCH("interact_fwd_simt");
   return B200_OK;
 }
 
-int interact_bwd_simt(const void* T, const void* dR, void* dT, int64_t B, int64_t F, int64_t D, int dtype,
-                      cudaStream_t st) {
+int interact_bwd_simt(const void* T, const void* dR, void* dT, int64_t B, int64_t F, int64_t D, int64_t ldr,
+                      int dtype, cudaStream_t st) {
   const size_t smem = ((size_t)F * D + (size_t)F * F) * 4;
   B200_REQUIRE(smem <= 200 * 1024, B200_EUNSUPPORTED, "interact_bwd: F*D too large for shared memory");
   const int grid = (int)std::min<int64_t>(B, 148 * 16);
   if (dtype == B200_F32) {
     cudaFuncSetAttribute(interact_bwd_simt_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     interact_bwd_simt_kernel<float>
-        <<<grid, INT_THREADS, smem, st>>>((const float*)T, (const float*)dR, (float*)dT, B, (int)F, (int)D);
+        <<<grid, INT_THREADS, smem, st>>>((const float*)T, (const float*)dR, (float*)dT, B, (int)F, (int)D, ldr);
   } else {
     cudaFuncSetAttribute(interact_bwd_simt_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     interact_bwd_simt_kernel<__nv_bfloat16><<<grid, INT_THREADS, smem, st>>>(
-        (const __nv_bfloat16*)T, (const __nv_bfloat16*)dR, (__nv_bfloat16*)dT, B, (int)F, (int)D);
+        (const __nv_bfloat16*)T, (const __nv_bfloat16*)dR, (__nv_bfloat16*)dT, B, (int)F, (int)D, ldr);
   }
   B200_CHECK_LAUNCH("interact_bwd_simt");
   return B200_OK;

@@ -1,15 +1,537 @@
-// tcgen05 interaction kernels (placeholder until the tensor-core path lands; the dispatcher
-// in api.cu falls through to interact_simt.cu while this reports "unsupported").
+// Pairwise dot-product interaction on tcgen05 tensor cores (sm_100a), bf16 in / fp32 accumulate.
+//
+// Replaces torch.cat + torch.bmm + tril gather + cat of DLRM_Net.interact_features
+// (reference P/dlrm_s_pytorch.py:309-334) and its autograd (two bmm + index_put).
+//
+// Shared structure of both kernels (persistent, one CTA per SM, warp-specialised):
+//   warp 0      TMA producer: 3-D tensor map over T[B, F, D]; one box = (64 d, 32 f, 4 samples),
+//               128-byte swizzle, rows f >= F and samples >= B zero-filled by the TMA unit.
+//               A stage holds D/64 boxes = the whole [4 x 32, D] tile of four samples.
+//   warp 1      MMA issuer (one elected lane): tcgen05.mma kind::f16, accumulators in TMEM.
+//   warps 2..5  epilogue: tcgen05.ld the accumulator quarter their warp may touch, write out.
+//   warps 6..9  (backward only) build the symmetric dZ tiles from dR in shared memory.
+// Forward:  Z = A A^t with A = the 128-row tile (4 samples x 32 padded features), K = D; the four
+//           32x32 diagonal blocks are the per-sample Gram matrices (the off-diagonal MMA work is
+//           free: the kernel is HBM-bound).
+// Backward: per sample dT^t[d, f] = sum_g T[g, d] * S[f, g]  (S = dZ + dZ^t): M = 128 d-values,
+//           N = 32, K = 32, A = the same smem tile read MN-major, B = S (K-major, no swizzle).
+#include <cuda.h>
+
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace b200 {
-bool interact_tc_supported(int64_t, int64_t, int64_t, int) { return false; }
-int interact_fwd_tc(const void*, void*, int64_t, int64_t, int64_t, int, cudaStream_t) {
-  set_error("interact_fwd_tc: not built");
-  return B200_EUNSUPPORTED;
+
+constexpr int TC_NS = 4;              // samples per tile
+constexpr int TC_FP = 32;             // padded features per sample
+constexpr int TC_BOX_BYTES = TC_NS * TC_FP * 128;  // 16 KB: (64 bf16) x 32 x 4
+constexpr int TC_EPI_WARPS = 4;
+constexpr uint32_t SPIN_LIMIT = 1u << 28;
+
+// ------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ void mbar_wait_bounded(uint64_t* bar, uint32_t parity) {
+  uint32_t n = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if (++n > SPIN_LIMIT) __trap();  // turn a protocol bug into an error instead of a hang
+  }
 }
-int interact_bwd_tc(const void*, const void*, void*, int64_t, int64_t, int64_t, int, cudaStream_t) {
-  set_error("interact_bwd_tc: not built");
-  return B200_EUNSUPPORTED;
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred P;\n\t"
+      "elect.sync _|P, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, P;\n\t"
+      "}"
+      : "=r"(pred));
+  return pred != 0;
 }
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, int c0, int c1, int c2,
+                                            uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t* slot, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)), "r"(ncols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// K-major / MN-major shared-memory matrix descriptors (cute::UMMA::SmemDescriptor bit layout):
+// [0,14) start>>4, [16,30) LBO>>4, [32,46) SBO>>4, [46,48) version=1, [61,64) layout type.
+__device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                              uint32_t layout_type) {
+  return (uint64_t)((saddr >> 4) & 0x3fff) | ((uint64_t)((lbo_bytes >> 4) & 0x3fff) << 16) |
+         ((uint64_t)((sbo_bytes >> 4) & 0x3fff) << 32) | (1ull << 46) | ((uint64_t)layout_type << 61);
+}
+constexpr uint32_t LAYOUT_SW128 = 2, LAYOUT_NONE = 0;
+// instruction descriptor (cute::UMMA::InstrDescriptor): c=F32 [4,6), a=BF16 [7,10), b=BF16 [10,13),
+// a_major bit 15, b_major bit 16 (1 = MN-major), N>>3 [17,23), M>>4 [24,29)
+__host__ __device__ constexpr uint32_t make_idesc(int M, int N, int a_mn, int b_mn) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) |
+         ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// strict-lower-triangle pair p -> (i, j), p = i(i-1)/2 + j
+__device__ __forceinline__ void tri_ij(int p, int& i, int& j) {
+  i = (int)((1.f + sqrtf(1.f + 8.f * (float)p)) * 0.5f);
+  while (i * (i - 1) / 2 > p) --i;
+  while ((i + 1) * i / 2 <= p) ++i;
+  j = p - i * (i - 1) / 2;
+}
+
+struct TcParams {
+  const __nv_bfloat16* T;
+  __nv_bfloat16* R;         // fwd out  [B, ldr]
+  const __nv_bfloat16* dR;  // bwd in   [B, ldr]
+  __nv_bfloat16* dT;        // bwd out  [B, F, D]
+  int64_t B;
+  int64_t ldr;
+  int F, D;
+  int n_tiles;
+  int stages;
+};
+
+// ================================================================== forward
+template <int KB>  // D / 64
+__global__ void __launch_bounds__(192, 1)
+    interact_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
+  constexpr int D = KB * 64;
+  constexpr int STAGE_BYTES = KB * TC_BOX_BYTES;
+  constexpr int ACC_COLS = 128;
+  constexpr int ACC_STAGES = 4;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int stages = p.stages;
+  uint8_t* tiles = smem;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)stages * STAGE_BYTES);
+  uint64_t* empty = full + stages;
+  uint64_t* acc_full = empty + stages;
+  uint64_t* acc_empty = acc_full + ACC_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + ACC_STAGES);
+  __nv_bfloat16* stg = reinterpret_cast<__nv_bfloat16*>(tmem_slot + 4);  // [4 warps][ldr_max]
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int s = 0; s < stages; ++s) {
+        mbar_init(&full[s], 1);
+        mbar_init(&empty[s], 1);
+      }
+      for (int s = 0; s < ACC_STAGES; ++s) {
+        mbar_init(&acc_full[s], 1);
+        mbar_init(&acc_empty[s], TC_EPI_WARPS);
+      }
+      fence_mbar_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, ACC_COLS * ACC_STAGES);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ---------------- TMA producer
+    if (elect_one()) {
+      int st = 0;
+      uint32_t ph = 0;
+      for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+        mbar_wait_bounded(&empty[st], ph ^ 1);
+        mbar_expect_tx(&full[st], STAGE_BYTES);
+        uint8_t* dst = tiles + (size_t)st * STAGE_BYTES;
+#pragma unroll
+        for (int kb = 0; kb < KB; ++kb) tma_load_3d(dst + kb * TC_BOX_BYTES, &tmap, kb * 64, 0, tile * TC_NS, &full[st]);
+        if (++st == stages) { st = 0; ph ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    // ---------------- MMA issuer
+    constexpr uint32_t idesc = make_idesc(128, 128, 0, 0);
+    int st = 0, as = 0;
+    uint32_t ph = 0, aph = 0;
+    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+      mbar_wait_bounded(&acc_empty[as], aph ^ 1);
+      mbar_wait_bounded(&full[st], ph);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t base = smem_u32(tiles + (size_t)st * STAGE_BYTES);
+#pragma unroll
+        for (int kb = 0; kb < KB; ++kb) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {  // UMMA_K = 16 bf16 = 32 bytes inside the 128-byte swizzle row
+            const uint64_t d = smem_desc(base + kb * TC_BOX_BYTES + k * 32, 16, 1024, LAYOUT_SW128);
+            umma_bf16(tmem_base + as * ACC_COLS, d, d, idesc, (kb | k) != 0);
+          }
+        }
+        umma_commit(&empty[st]);     // smem slot free once these MMAs have read it
+        umma_commit(&acc_full[as]);  // accumulator ready for the epilogue
+      }
+      __syncwarp();
+      if (++st == stages) { st = 0; ph ^= 1; }
+      if (++as == ACC_STAGES) { as = 0; aph ^= 1; }
+    }
+  } else {
+    // ---------------- epilogue: warp q owns TMEM lanes [32q, 32q+32) = sample q of the tile
+    const int q = warp & 3;
+    const int F = p.F;
+    const int npairs = F * (F - 1) / 2;
+    const int W = D + npairs;
+    __nv_bfloat16* my = stg + (size_t)(warp - 2) * ((p.ldr + 7) & ~7);
+    const bool vec_ok = (p.ldr % 8) == 0 && (reinterpret_cast<uintptr_t>(p.R) & 15) == 0;
+    int as = 0;
+    uint32_t aph = 0;
+    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+      const int64_t b = (int64_t)tile * TC_NS + q;
+      mbar_wait_bounded(&acc_full[as], aph);
+      tc_fence_after();
+      uint32_t v[32];
+      tmem_ld32(tmem_base + ((uint32_t)(32 * q) << 16) + as * ACC_COLS + 32 * q, v);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[as]);
+      if (b < p.B) {
+        // x pass-through (feature 0) straight from global (L2-resident: the TMA just read it)
+        const __nv_bfloat16* x = p.T + b * (int64_t)F * D;
+        for (int c = lane; c < D / 8; c += 32) reinterpret_cast<uint4*>(my)[c] = __ldg(reinterpret_cast<const uint4*>(x) + c);
+        // lane i holds Z[i][0..31]; keep j < i
+        if (lane < F) {
+          const int rowoff = D + lane * (lane - 1) / 2;
+#pragma unroll
+          for (int j = 0; j < 31; ++j)
+            if (j < lane) my[rowoff + j] = __float2bfloat16_rn(__uint_as_float(v[j]));
+        }
+        for (int c = W + lane; c < p.ldr; c += 32) my[c] = __float2bfloat16_rn(0.f);
+        __syncwarp();
+        __nv_bfloat16* out = p.R + b * p.ldr;
+        if (vec_ok) {
+          for (int c = lane; c < p.ldr / 8; c += 32) st_cs_v4(reinterpret_cast<uint4*>(out) + c, reinterpret_cast<uint4*>(my)[c]);
+        } else {
+          for (int c = lane; c < p.ldr; c += 32) out[c] = my[c];
+        }
+        __syncwarp();
+      }
+      if (++as == ACC_STAGES) { as = 0; aph ^= 1; }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_base, ACC_COLS * ACC_STAGES);
+}
+
+// ================================================================== backward
+// S tile of one sample: [32 f][32 g] bf16, K-major, no swizzle: core matrices of 8 rows x 16 bytes,
+// offset(f, g) = (f/8)*512 + (g/8)*128 + (f%8)*16 + (g%8)*2   (LBO = 128 B along K, SBO = 512 B along N)
+constexpr int S_BYTES = 2048;
+__device__ __forceinline__ uint32_t s_off(int f, int g) {
+  return (uint32_t)((f >> 3) * 512 + (g >> 3) * 128 + (f & 7) * 16 + (g & 7) * 2);
+}
+
+template <int KB>  // D / 64 (2 or 4)
+__global__ void __launch_bounds__(320, 1)
+    interact_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
+  constexpr int D = KB * 64;
+  constexpr int MB = D / 128;                    // 128-row accumulator blocks per sample
+  constexpr int STAGE_BYTES = KB * TC_BOX_BYTES;
+  constexpr int ACC_COLS = TC_NS * 32 * MB;      // TMEM columns per tile
+  constexpr int ACC_STAGES = 512 / ACC_COLS >= 4 ? 4 : 2;
+  constexpr int S_STAGE_BYTES = TC_NS * S_BYTES;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int stages = p.stages;
+  uint8_t* tiles = smem;
+  uint8_t* stiles = smem + (size_t)stages * STAGE_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(stiles + (size_t)stages * S_STAGE_BYTES);
+  uint64_t* empty = full + stages;
+  uint64_t* s_full = empty + stages;
+  uint64_t* s_empty = s_full + stages;
+  uint64_t* acc_full = s_empty + stages;
+  uint64_t* acc_empty = acc_full + ACC_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + ACC_STAGES);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // zero the S tiles once: the diagonal and the padding rows / columns stay zero for ever
+  for (int i = threadIdx.x; i < stages * S_STAGE_BYTES / 16; i += blockDim.x)
+    reinterpret_cast<uint4*>(stiles)[i] = make_uint4(0, 0, 0, 0);
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int s = 0; s < stages; ++s) {
+        mbar_init(&full[s], 1);
+        mbar_init(&empty[s], 1);
+        mbar_init(&s_full[s], 4);   // one arrive per S-builder warp
+        mbar_init(&s_empty[s], 1);
+      }
+      for (int s = 0; s < ACC_STAGES; ++s) {
+        mbar_init(&acc_full[s], 1);
+        mbar_init(&acc_empty[s], TC_EPI_WARPS);
+      }
+      fence_mbar_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, 512);
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int F = p.F;
+  const int npairs = F * (F - 1) / 2;
+
+  if (warp == 0) {
+    // ---------------- TMA producer (same tiles as the forward)
+    if (elect_one()) {
+      int st = 0;
+      uint32_t ph = 0;
+      for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+        mbar_wait_bounded(&empty[st], ph ^ 1);
+        mbar_expect_tx(&full[st], STAGE_BYTES);
+        uint8_t* dst = tiles + (size_t)st * STAGE_BYTES;
+#pragma unroll
+        for (int kb = 0; kb < KB; ++kb) tma_load_3d(dst + kb * TC_BOX_BYTES, &tmap, kb * 64, 0, tile * TC_NS, &full[st]);
+        if (++st == stages) { st = 0; ph ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    // ---------------- MMA issuer: per sample (and per 128-d block) D[128 d, 32 f] += A[d, g] B[f, g]
+    constexpr uint32_t idesc = make_idesc(128, 32, /*a MN-major*/ 1, 0);
+    int st = 0, as = 0;
+    uint32_t ph = 0, aph = 0;
+    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+      mbar_wait_bounded(&acc_empty[as], aph ^ 1);
+      mbar_wait_bounded(&full[st], ph);
+      mbar_wait_bounded(&s_full[st], ph);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t tbase = smem_u32(tiles + (size_t)st * STAGE_BYTES);
+        const uint32_t sbase = smem_u32(stiles + (size_t)st * S_STAGE_BYTES);
+#pragma unroll
+        for (int s = 0; s < TC_NS; ++s) {
+#pragma unroll
+          for (int mb = 0; mb < MB; ++mb) {
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {  // K = 32 g-rows = 2 x UMMA_K(16)
+              // A: element (d, g) at box(2mb + d/64) + s*4096 + g*128 + (d%64)*2 (128B-swizzled):
+              //    MN-major, LBO = one box (next 64 d), SBO = 1024 B (next 8 g rows)
+              const uint64_t ad = smem_desc(tbase + (2 * mb) * TC_BOX_BYTES + s * 4096 + k * 2048, TC_BOX_BYTES, 1024,
+                                            LAYOUT_SW128);
+              const uint64_t bd = smem_desc(sbase + s * S_BYTES + k * 256, 128, 512, LAYOUT_NONE);
+              umma_bf16(tmem_base + as * ACC_COLS + (s * MB + mb) * 32, ad, bd, idesc, k != 0);
+            }
+          }
+        }
+        umma_commit(&empty[st]);
+        umma_commit(&s_empty[st]);
+        umma_commit(&acc_full[as]);
+      }
+      __syncwarp();
+      if (++st == stages) { st = 0; ph ^= 1; }
+      if (++as == ACC_STAGES) { as = 0; aph ^= 1; }
+    }
+  } else if (warp < 6) {
+    // ---------------- epilogue: warp q reads TMEM lanes [32q, 32q+32) = d-values 32q + lane (+128 mb)
+    const int q = warp & 3;
+    int as = 0;
+    uint32_t aph = 0;
+    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+      mbar_wait_bounded(&acc_full[as], aph);
+      tc_fence_after();
+#pragma unroll 1
+      for (int s = 0; s < TC_NS; ++s) {
+        const int64_t b = (int64_t)tile * TC_NS + s;
+#pragma unroll
+        for (int mb = 0; mb < MB; ++mb) {
+          uint32_t v[32];
+          tmem_ld32(tmem_base + ((uint32_t)(32 * q) << 16) + as * ACC_COLS + (s * MB + mb) * 32, v);
+          if (b < p.B) {
+            const int d = mb * 128 + 32 * q + lane;
+            __nv_bfloat16* o = p.dT + b * (int64_t)F * D + d;
+            const float pass = __bfloat162float(p.dR[b * p.ldr + d]);  // dR[:, :D] flows into feature 0
+#pragma unroll
+            for (int f = 0; f < 32; ++f)
+              if (f < F) o[(int64_t)f * D] = __float2bfloat16_rn(__uint_as_float(v[f]) + (f == 0 ? pass : 0.f));
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[as]);
+      if (++as == ACC_STAGES) { as = 0; aph ^= 1; }
+    }
+  } else {
+    // ---------------- S builders (warps 6..9): S[i][j] = S[j][i] = dR[b, D + i(i-1)/2 + j]
+    const int t = threadIdx.x - 192;  // 0..127
+    int st = 0;
+    uint32_t ph = 0;
+    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+      mbar_wait_bounded(&s_empty[st], ph ^ 1);
+      uint8_t* sb = stiles + (size_t)st * S_STAGE_BYTES;
+#pragma unroll 1
+      for (int s = 0; s < TC_NS; ++s) {
+        const int64_t b = (int64_t)tile * TC_NS + s;
+        const bool live = b < p.B;
+        const __nv_bfloat16* src = p.dR + b * p.ldr + D;
+        for (int pi = t; pi < npairs; pi += 128) {
+          int i, j;
+          tri_ij(pi, i, j);
+          const __nv_bfloat16 val = live ? src[pi] : __float2bfloat16_rn(0.f);
+          *reinterpret_cast<__nv_bfloat16*>(sb + s * S_BYTES + s_off(i, j)) = val;
+          *reinterpret_cast<__nv_bfloat16*>(sb + s * S_BYTES + s_off(j, i)) = val;
+        }
+      }
+      fence_proxy_async();  // generic-proxy smem writes -> visible to the tensor-core (async) proxy
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&s_full[st]);
+      if (++st == stages) { st = 0; ph ^= 1; }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_base, 512);
+}
+
+// ================================================================== host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  }
+  return fn;
+}
+
+static int make_tmap(CUtensorMap* map, const void* T, int64_t B, int64_t F, int64_t D) {
+  EncodeTiledFn enc = get_encode();
+  B200_REQUIRE(enc != nullptr, B200_ELAUNCH, "interact_tc: cuTensorMapEncodeTiled entry point not available");
+  cuuint64_t dims[3] = {(cuuint64_t)D, (cuuint64_t)F, (cuuint64_t)B};
+  cuuint64_t strides[2] = {(cuuint64_t)D * 2, (cuuint64_t)F * D * 2};
+  cuuint32_t box[3] = {64, TC_FP, TC_NS};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(T), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  B200_REQUIRE(r == CUDA_SUCCESS, B200_ELAUNCH, "interact_tc: cuTensorMapEncodeTiled failed (%d)", (int)r);
+  return B200_OK;
+}
+
+static int sm_count() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+bool interact_tc_supported(int64_t B, int64_t F, int64_t D, int dtype, const void* T, int64_t ldr) {
+  return dtype == B200_BF16 && F >= 2 && F <= TC_FP && (D == 128 || D == 256) && B >= 1 &&
+         B < ((int64_t)1 << 31) - 8 && (reinterpret_cast<uintptr_t>(T) & 15) == 0 && ldr <= 2048;
+}
+
+int interact_fwd_tc(const void* T, void* R, int64_t B, int64_t F, int64_t D, int64_t ldr, cudaStream_t st) {
+  CUtensorMap map;
+  int rc = make_tmap(&map, T, B, F, D);
+  if (rc) return rc;
+  TcParams p{};
+  p.T = static_cast<const __nv_bfloat16*>(T);
+  p.R = static_cast<__nv_bfloat16*>(R);
+  p.B = B;
+  p.ldr = ldr;
+  p.F = (int)F;
+  p.D = (int)D;
+  p.n_tiles = (int)ceil_div(B, TC_NS);
+  const int KB = (int)(D / 64);
+  const size_t stage = (size_t)KB * TC_BOX_BYTES;
+  p.stages = (int)std::min<size_t>(4, (200 * 1024) / stage);
+  const size_t smem = 1024 + p.stages * stage + (2 * p.stages + 8) * 8 + 16 + 4 * (((size_t)ldr + 7) & ~7) * 2;
+  const int grid = std::min(p.n_tiles, sm_count());
+  if (KB == 2) {
+    cudaFuncSetAttribute(interact_fwd_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    interact_fwd_tc_kernel<2><<<grid, 192, smem, st>>>(map, p);
+  } else {
+    cudaFuncSetAttribute(interact_fwd_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    interact_fwd_tc_kernel<4><<<grid, 192, smem, st>>>(map, p);
+  }
+  B200_CHECK_LAUNCH("interact_fwd_tc");
+  return B200_OK;
+}
+
+int interact_bwd_tc(const void* T, const void* dR, void* dT, int64_t B, int64_t F, int64_t D, int64_t ldr,
+                    cudaStream_t st) {
+  CUtensorMap map;
+  int rc = make_tmap(&map, T, B, F, D);
+  if (rc) return rc;
+  TcParams p{};
+  p.T = static_cast<const __nv_bfloat16*>(T);
+  p.dR = static_cast<const __nv_bfloat16*>(dR);
+  p.dT = static_cast<__nv_bfloat16*>(dT);
+  p.B = B;
+  p.ldr = ldr;
+  p.F = (int)F;
+  p.D = (int)D;
+  p.n_tiles = (int)ceil_div(B, TC_NS);
+  const int KB = (int)(D / 64);
+  const size_t stage = (size_t)KB * TC_BOX_BYTES + TC_NS * S_BYTES;
+  p.stages = (int)std::min<size_t>(4, (200 * 1024) / stage);
+  const size_t smem = 1024 + p.stages * stage + (4 * p.stages + 8) * 8 + 16;
+  const int grid = std::min(p.n_tiles, sm_count());
+  if (KB == 2) {
+    cudaFuncSetAttribute(interact_bwd_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    interact_bwd_tc_kernel<2><<<grid, 320, smem, st>>>(map, p);
+  } else {
+    cudaFuncSetAttribute(interact_bwd_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    interact_bwd_tc_kernel<4><<<grid, 320, smem, st>>>(map, p);
+  }
+  B200_CHECK_LAUNCH("interact_bwd_tc");
+  return B200_OK;
+}
+
 }  // namespace b200

@@ -16,17 +16,17 @@ import torch
 import torch.nn as nn
 
 from . import ext_dist
-from .interaction import interaction
+from .interaction import PaddedLinear, interaction
 from .merged_embedding import MergedEmbeddingBagWithSGD
 
 
 class DLRM_Net(nn.Module):
-    def create_mlp(self, ln, sigmoid_layer):
-        # P/dlrm_s_pytorch.py:172-211
+    def create_mlp(self, ln, sigmoid_layer, pad_first=False):
+        # P/dlrm_s_pytorch.py:172-211 (pad_first: first layer tolerates zero-padded input columns)
         layers = nn.ModuleList()
         for i in range(0, ln.size - 1):
             n, m = int(ln[i]), int(ln[i + 1])
-            LL = nn.Linear(n, m, bias=True)
+            LL = PaddedLinear(n, m, bias=True) if (pad_first and i == 0) else nn.Linear(n, m, bias=True)
             W = np.random.normal(0.0, np.sqrt(2 / (m + n)), size=(m, n)).astype(np.float32)
             bt = np.random.normal(0.0, np.sqrt(1 / m), size=m).astype(np.float32)
             LL.weight.data = torch.tensor(W, requires_grad=True)
@@ -74,7 +74,8 @@ class DLRM_Net(nn.Module):
             self.local_ln_emb = None
         self.l_emb_seeds = np.random.randint(low=0, high=100000, size=len(ln_emb))
         self.bot_l = self.create_mlp(np.asarray(ln_bot), sigmoid_bot).to(device)
-        self.top_l = self.create_mlp(np.asarray(ln_top), sigmoid_top).to(device)
+        self.top_l = self.create_mlp(np.asarray(ln_top), sigmoid_top, pad_first=True).to(device)
+        self.interaction_pad = 8  # interaction output rounded up to a multiple of 8 columns
         self.emb_l = self.create_emb(m_spa, ln_emb, self.local_ln_emb, np_init_emb_weight, device, lr,
                                      emb_optimizer)
         if bf16:
@@ -96,7 +97,7 @@ class DLRM_Net(nn.Module):
         return emb_l((list(lS_i), list(lS_o), [False] * len(lS_i)), torch.BoolTensor([True]))
 
     def interact_features(self, x, ly):
-        return interaction(x, *ly)
+        return interaction(x, *ly, pad_to=self.interaction_pad)
 
     def forward(self, dense_x, *emb_args):
         if ext_dist.my_size > 1:

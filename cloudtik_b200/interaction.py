@@ -36,7 +36,7 @@ def _pooled_base(x: torch.Tensor, ly):
 
 class _InteractionFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, *ly):
+    def forward(ctx, pad_to, x, *ly):
         base = _pooled_base(x, ly)
         if base is not None:
             T = base
@@ -47,7 +47,7 @@ class _InteractionFn(torch.autograd.Function):
         ctx.save_for_backward(T)
         ctx.x_dtype = x.dtype
         ctx.ly_dtypes = [t.dtype for t in ly]
-        return ops.interact_fwd(T)
+        return ops.interact_fwd(T, pad_to=pad_to)
 
     @staticmethod
     def backward(ctx, dR):
@@ -60,11 +60,29 @@ class _InteractionFn(torch.autograd.Function):
         for k, dt in enumerate(ctx.ly_dtypes):
             g = dT[:, 1 + k]
             dly.append(g if g.dtype == dt else g.to(dt))
-        return (dx, *dly)
+        return (None, dx, *dly)
 
 
-def interaction(x: torch.Tensor, *ly: torch.Tensor) -> torch.Tensor:
-    """``interaction(x, *ly)`` -- see module docstring.  CUDA tensors only."""
+def interaction(x: torch.Tensor, *ly: torch.Tensor, pad_to: int = 1) -> torch.Tensor:
+    """``interaction(x, *ly)`` -- see module docstring.  CUDA tensors only.
+
+    ``pad_to`` > 1 rounds the output width up to a multiple of ``pad_to`` with zero columns (e.g.
+    479 -> 480) so that the GEMM consuming it gets an aligned K; ``PaddedLinear`` accepts that."""
     if not x.is_cuda:
         raise RuntimeError("cloudtik_b200.interaction needs CUDA tensors (no CPU fallback)")
-    return _InteractionFn.apply(x, *ly)
+    return _InteractionFn.apply(int(pad_to), x, *ly)
+
+
+class PaddedLinear(torch.nn.Linear):
+    """``nn.Linear`` (same parameters, same state_dict keys) that also accepts an input with extra
+    zero columns on the right: the weight is zero-padded on the fly.  Used for the first top-MLP
+    layer (reference P/dlrm_s_pytorch.py:172-211 builds a plain Linear(479, 1024)): K = 479 sends
+    cuBLAS to an unaligned legacy kernel ~6x slower than K = 480."""
+
+    def forward(self, input):
+        extra = input.shape[-1] - self.in_features
+        if extra == 0:
+            return torch.nn.functional.linear(input, self.weight, self.bias)
+        if extra < 0:
+            raise RuntimeError("PaddedLinear: input narrower than in_features")
+        return torch.nn.functional.linear(input, torch.nn.functional.pad(self.weight, (0, extra)), self.bias)

@@ -166,28 +166,33 @@ def emb_bwd_apply(tables: TableSet, nnz: int, B: int, grad: torch.Tensor, stride
         ws.numel() * ws.element_size(), _stream()), "b200_emb_bwd_apply")
 
 
-def interact_fwd(T: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
-    """T [B, F, D] contiguous -> R [B, D + F(F-1)/2].  See b200_interact_fwd."""
+def interact_fwd(T: torch.Tensor, out: torch.Tensor | None = None, pad_to: int = 1) -> torch.Tensor:
+    """T [B, F, D] contiguous -> R [B, ldr] with ldr = D + F(F-1)/2 rounded up to ``pad_to``
+    (padding columns are written as zeros).  See b200_interact_fwd."""
     _cuda(T, "T")
     if T.dim() != 3 or not T.is_contiguous():
         raise _lib.B200Error("interact_fwd: T must be a contiguous [B, F, D] tensor")
     B, F, D = T.shape
+    W = D + F * (F - 1) // 2
     if out is None:
-        out = torch.empty(B, D + F * (F - 1) // 2, dtype=T.dtype, device=T.device)
-    check(lib.b200_interact_fwd(T.data_ptr(), out.data_ptr(), B, F, D, _dt(T.dtype), _stream()),
+        out = torch.empty(B, (W + pad_to - 1) // pad_to * pad_to, dtype=T.dtype, device=T.device)
+    if out.dim() != 2 or out.shape[0] != B or out.shape[1] < W or out.stride(1) != 1 or out.dtype != T.dtype:
+        raise _lib.B200Error("interact_fwd: bad output tensor")
+    check(lib.b200_interact_fwd(T.data_ptr(), out.data_ptr(), B, F, D, out.stride(0), _dt(T.dtype), _stream()),
           "b200_interact_fwd")
     return out
 
 
 def interact_bwd(T: torch.Tensor, dR: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
-    """dT [B, F, D] from T and dR [B, D + F(F-1)/2].  See b200_interact_bwd."""
+    """dT [B, F, D] from T and dR [B, >= D + F(F-1)/2] (row stride = dR.stride(0)).  See b200_interact_bwd."""
     _cuda(T, "T")
     _cuda(dR, "dR", T.dtype)
     B, F, D = T.shape
-    if not T.is_contiguous() or not dR.is_contiguous() or tuple(dR.shape) != (B, D + F * (F - 1) // 2):
+    if (not T.is_contiguous() or dR.dim() != 2 or dR.shape[0] != B or dR.shape[1] < D + F * (F - 1) // 2
+            or dR.stride(1) != 1):
         raise _lib.B200Error("interact_bwd: bad shapes / non-contiguous input")
     if out is None:
         out = torch.empty_like(T)
-    check(lib.b200_interact_bwd(T.data_ptr(), dR.data_ptr(), out.data_ptr(), B, F, D, _dt(T.dtype), _stream()),
-          "b200_interact_bwd")
+    check(lib.b200_interact_bwd(T.data_ptr(), dR.data_ptr(), out.data_ptr(), B, F, D, dR.stride(0), _dt(T.dtype),
+                                _stream()), "b200_interact_bwd")
     return out

@@ -126,14 +126,18 @@ int b200_emb_bwd_apply(void* const* d_weights, float* const* d_state, const int6
  * cat + bmm + tril gather + cat) and ipex.nn.functional.interaction(*T) (P/dlrm_s_pytorch.py:312).
  *
  *   d_T   [B, F, D] contiguous: feature 0 is the bottom-MLP output x, 1..F-1 the pooled rows
- *   d_R   [B, D + F(F-1)/2]: R[b] = [x_b, <T_i,T_j> for i in 1..F-1 for j in 0..i-1]
- *   bwd:  d_dT[B, F, D] = (dZ + dZ^t) T with dZ scattered from d_dR[:, D:], plus d_dR[:, :D]
- *         added into feature 0.
+ *   d_R   [B, ldr], ldr >= W = D + F(F-1)/2 (row stride in elements):
+ *         R[b, :W] = [x_b, <T_i,T_j> for i in 1..F-1 for j in 0..i-1]; R[b, W:ldr] = 0 (padding a
+ *         caller may ask for so that the next GEMM sees a K that is a multiple of 8)
+ *   bwd:  d_dT[B, F, D] = (dZ + dZ^t) T with dZ scattered from d_dR[:, D:W], plus d_dR[:, :D]
+ *         added into feature 0.  d_dR has the same row stride ldr.
+ * bf16 with F <= 32 and D in {128, 256} runs on tcgen05 tensor cores (TMA-fed, TMEM
+ * accumulators); other shapes / fp32 run a CUDA-core kernel.
  */
-int b200_interact_fwd(const void* d_T, void* d_R, int64_t B, int64_t F, int64_t D, int dtype,
-                      b200_stream_t stream);
+int b200_interact_fwd(const void* d_T, void* d_R, int64_t B, int64_t F, int64_t D, int64_t ldr,
+                      int dtype, b200_stream_t stream);
 int b200_interact_bwd(const void* d_T, const void* d_dR, void* d_dT, int64_t B, int64_t F,
-                      int64_t D, int dtype, b200_stream_t stream);
+                      int64_t D, int64_t ldr, int dtype, b200_stream_t stream);
 
 #ifdef __cplusplus
 }

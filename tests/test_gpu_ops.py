@@ -280,6 +280,35 @@ def test_interaction_golden(golden, dtype):
             np.testing.assert_allclose(dT.float().cpu().numpy(), wdT, rtol=1e-2, atol=1e-2 * np.abs(wdT).max())
 
 
+@pytest.mark.parametrize("B,F,D,pad", [(1, 27, 128, 1), (3, 27, 128, 8), (4, 27, 128, 8), (5, 2, 128, 1),
+                                       (1000, 27, 128, 8), (613, 32, 128, 1), (77, 27, 256, 8), (2048, 9, 256, 1),
+                                       (4099, 27, 128, 8)])
+def test_interaction_tensor_core_path(B, F, D, pad):
+    """bf16, F <= 32, D in {128, 256}: the tcgen05 kernels.  Checked against a float64 evaluation of
+    the same bf16 inputs; outputs are bf16-rounded, so <= 1e-2 relative (north_star bf16 bound)."""
+    ops = _ops()
+    rs = np.random.RandomState(B + F + D)
+    T = torch.tensor(rs.randn(B, F, D).astype(np.float32)).bfloat16().cuda()
+    Tf = T.float().cpu().numpy().astype(np.float64)
+    W = D + F * (F - 1) // 2
+    R = ops.interact_fwd(T, pad_to=pad)
+    ldr = R.shape[1]
+    assert ldr % pad == 0 and ldr >= W
+    want = ref.interact_fwd(Tf[:, 0], [Tf[:, k] for k in range(1, F)])
+    got = R.float().cpu().numpy()
+    np.testing.assert_allclose(got[:, :W], want, rtol=1e-2, atol=1e-2 * np.sqrt(D))
+    np.testing.assert_array_equal(got[:, :D], Tf[:, 0])          # pass-through is exact
+    assert (got[:, W:] == 0).all()
+    dR = torch.zeros(B, ldr, dtype=torch.bfloat16, device="cuda")
+    dR[:, :W] = torch.tensor(rs.randn(B, W).astype(np.float32)).bfloat16().cuda()
+    dT = ops.interact_bwd(T, dR)
+    torch.cuda.synchronize()
+    dRf = dR.float().cpu().numpy().astype(np.float64)[:, :W]
+    dx, dly = ref.interact_bwd(Tf[:, 0], [Tf[:, k] for k in range(1, F)], dRf)
+    wdT = np.stack([dx] + dly, axis=1)
+    np.testing.assert_allclose(dT.float().cpu().numpy(), wdT, rtol=1e-2, atol=1e-2 * np.sqrt(F))
+
+
 def test_interaction_kat():
     ops = _ops()
     T = torch.tensor([[[1.0, 2.0], [3.0, 4.0], [5.0, 6.0]]], device="cuda")
