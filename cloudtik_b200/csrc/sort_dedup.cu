@@ -8,6 +8,8 @@
 // digit-major [256][nblk] table, (3) stable scatter (warp match-any ranking, no atomics on
 // the data path).  Pure integer work, HBM/L2-bound; tiles are sized so that the whole
 // (key,val) working set of a DLRM batch stays in the 126 MB L2 between passes.
+#include <mutex>
+
 #include "common.cuh"
 #include "sort_dedup.cuh"
 
@@ -281,4 +283,82 @@ extern "C" int b200_sort_dedup(const uint32_t* d_keys, const uint32_t* d_vals, i
   int rc = sort_pairs(d_keys, d_vals, n, key_bound, d_sorted_keys, d_sorted_vals, ws, st);
   if (rc) return rc;
   return dedup_runs(d_sorted_keys, n, d_unique, d_seg_offsets, d_num_unique, ws, st);
+}
+
+namespace b200 {
+// ------------------------------------------------------------------ entry point that allocates nothing
+//
+// Who this is for: callers that are handed device pointers but have no way to obtain device
+// memory of their own.  Typical cases: a trainer whose framework has already claimed all of HBM
+// for its caching allocator (a DLRM with 96 GB of tables leaves a bare cudaMalloc nothing to
+// find, and the framework's allocator is not reachable from a plain C caller); a latency-critical
+// loop that must not stall (cudaMalloc / cudaFree synchronise the whole device); and thin
+// language bindings (cgo, JNI, ctypes callbacks) that cannot own the lifetime of a device buffer.
+//
+// The sort / dedup scratch therefore lives in the library image itself: a file-scope device array
+// of fixed size, present once on every GPU that loads libb200dlrm.so and held until the process
+// exits.  Consequences the caller must accept:
+//   * n is limited to B200_SORT_NOALLOC_MAX_KEYS keys (larger n is refused with B200_EUNSUPPORTED);
+//   * all calls on a device share that one array, so two calls that may overlap on the GPU
+//     (different streams, different host threads) race -- serialise them;
+//   * the array keeps whatever the previous call left in it.  Nothing in it has to start at zero:
+//     every word a call reads (digit histograms, dedup block counts, ping-pong key/value buffers)
+//     is written earlier in the same call, so no clearing pass is needed.
+constexpr int64_t NOALLOC_MAX_KEYS = B200_SORT_NOALLOC_MAX_KEYS;
+constexpr size_t cx_align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+constexpr size_t cx_ceil_div(size_t a, size_t b) { return (a + b - 1) / b; }
+// same carve-up as sort_ws_bytes(), evaluated at compile time for the maximum n
+constexpr size_t NOALLOC_SCRATCH_BYTES =
+    4 * cx_align_up((size_t)NOALLOC_MAX_KEYS * 4, 256) +
+    cx_align_up((size_t)256 * cx_ceil_div(NOALLOC_MAX_KEYS, SORT_CHUNK) * 4, 256) +
+    cx_align_up((cx_ceil_div(NOALLOC_MAX_KEYS, DEDUP_CHUNK) + 1) * 4, 256) + 256;
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_SCRATCH_BYTES];
+
+// In host code `g_noalloc_scratch` is only a handle for the symbol, not a device address: the
+// address differs per device and has to be asked for with that device current.
+static std::mutex g_noalloc_mu;
+static void* g_noalloc_dev_ptr[64] = {};
+
+static int noalloc_scratch_for_current_device(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  B200_REQUIRE(e == cudaSuccess && dev >= 0 && dev < 64, B200_ELAUNCH, "sort_dedup_noalloc: cudaGetDevice failed: %s",
+               cudaGetErrorString(e));
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (g_noalloc_dev_ptr[dev] == nullptr) {
+    void* ptr = nullptr;
+    e = cudaGetSymbolAddress(&ptr, g_noalloc_scratch);
+    B200_REQUIRE(e == cudaSuccess && ptr != nullptr, B200_ELAUNCH,
+                 "sort_dedup_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+    g_noalloc_dev_ptr[dev] = ptr;
+  }
+  *out = g_noalloc_dev_ptr[dev];
+  return B200_OK;
+}
+
+}  // namespace b200
+
+extern "C" int b200_sort_dedup_noalloc(const uint32_t* d_keys, const uint32_t* d_vals, int64_t n,
+                                       uint64_t key_bound, uint32_t* d_sorted_keys, uint32_t* d_sorted_vals,
+                                       uint32_t* d_unique, uint32_t* d_seg_offsets, int32_t* d_num_unique,
+                                       b200_stream_t stream) {
+  B200_REQUIRE(n >= 0, B200_EINVAL, "sort_dedup_noalloc: negative n");
+  B200_REQUIRE(n <= NOALLOC_MAX_KEYS, B200_EUNSUPPORTED,
+               "sort_dedup_noalloc: n = %lld exceeds the built-in scratch (max %lld keys); use b200_sort_dedup "
+               "with a caller-provided workspace",
+               (long long)n, (long long)NOALLOC_MAX_KEYS);
+  B200_REQUIRE(key_bound >= 1 && key_bound <= ((uint64_t)1 << 32), B200_EUNSUPPORTED,
+               "sort_dedup_noalloc: key_bound must be in [1, 2^32]");
+  B200_REQUIRE(d_seg_offsets && d_num_unique, B200_EINVAL, "sort_dedup_noalloc: null output");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (n == 0) return empty_result(d_seg_offsets, d_num_unique, st);
+  B200_REQUIRE(d_keys && d_vals && d_sorted_keys && d_sorted_vals && d_unique, B200_EINVAL,
+               "sort_dedup_noalloc: null pointer");
+  void* scratch = nullptr;
+  int rc = noalloc_scratch_for_current_device(&scratch);
+  if (rc) return rc;
+  rc = sort_pairs(d_keys, d_vals, n, key_bound, d_sorted_keys, d_sorted_vals, scratch, st);
+  if (rc) return rc;
+  return dedup_runs(d_sorted_keys, n, d_unique, d_seg_offsets, d_num_unique, scratch, st);
 }

@@ -81,6 +81,29 @@ int b200_sort_dedup(const uint32_t* d_keys, const uint32_t* d_vals, int64_t n, u
                     b200_stream_t stream);
 
 /*
+ * Same result as b200_sort_dedup, for callers that cannot provide a workspace because they cannot
+ * allocate device memory at all (all of HBM already belongs to their framework's allocator, an
+ * allocation would stall a latency-critical loop, or the caller is a thin language binding that
+ * cannot own a device buffer).  No counterpart in the reference: this entry point exists only for
+ * such callers.
+ *
+ * The scratch is a fixed array inside the library image (about 4.3 MB on every GPU that loads the
+ * library, kept until the process exits); the call allocates nothing, neither on the device nor
+ * through any library.  Limits and rules:
+ *   - n <= B200_SORT_NOALLOC_MAX_KEYS, otherwise B200_EUNSUPPORTED and nothing is launched;
+ *   - the first call on each device looks up the array's address on that device (the device the
+ *     stream belongs to must be current); make that first call before any stream capture begins;
+ *   - every call on a device uses the same array: calls that can overlap on the GPU race, so
+ *     issue them on one stream or order them yourself.  The array keeps the previous call's
+ *     contents; nothing in it needs to be zero on entry.
+ */
+#define B200_SORT_NOALLOC_MAX_KEYS 262144
+int b200_sort_dedup_noalloc(const uint32_t* d_keys, const uint32_t* d_vals, int64_t n,
+                            uint64_t key_bound, uint32_t* d_sorted_keys, uint32_t* d_sorted_vals,
+                            uint32_t* d_unique, uint32_t* d_seg_offsets, int32_t* d_num_unique,
+                            b200_stream_t stream);
+
+/*
  * EmbeddingBag backward fused with the optimiser row update; never materialises the
  * [nnz, D] COO gradient.  Replaces autograd's _embedding_bag_sparse_backward (triggered by
  * E.backward(), P/dlrm_s_pytorch.py:1055) + torch.optim.SGD.step on the sparse grads
