@@ -218,8 +218,18 @@ __global__ void __launch_bounds__(192, 1)
     const bool vec_ok = (p.ldr % 8) == 0 && (reinterpret_cast<uintptr_t>(p.R) & 15) == 0;
     int as = 0;
     uint32_t aph = 0;
+    // x pass-through (feature 0) comes straight from global and is prefetched one tile ahead so its
+    // latency hides behind the current tile's epilogue (D/8 <= 32 16-byte chunks: one per lane)
+    auto load_x = [&](int tile) -> uint4 {
+      const int64_t b = (int64_t)tile * TC_NS + q;
+      if (tile < p.n_tiles && b < p.B && lane < D / 8)
+        return __ldg(reinterpret_cast<const uint4*>(p.T + b * (int64_t)F * D) + lane);
+      return make_uint4(0, 0, 0, 0);
+    };
+    uint4 xv = load_x(blockIdx.x);
     for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
       const int64_t b = (int64_t)tile * TC_NS + q;
+      const uint4 xn = load_x(tile + gridDim.x);
       mbar_wait_bounded(&acc_full[as], aph);
       tc_fence_after();
       uint32_t v[32];
@@ -228,9 +238,7 @@ __global__ void __launch_bounds__(192, 1)
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[as]);
       if (b < p.B) {
-        // x pass-through (feature 0) straight from global (L2-resident: the TMA just read it)
-        const __nv_bfloat16* x = p.T + b * (int64_t)F * D;
-        for (int c = lane; c < D / 8; c += 32) reinterpret_cast<uint4*>(my)[c] = __ldg(reinterpret_cast<const uint4*>(x) + c);
+        if (lane < D / 8) reinterpret_cast<uint4*>(my)[lane] = xv;
         // lane i holds Z[i][0..31]; keep j < i
         if (lane < F) {
           const int rowoff = D + lane * (lane - 1) / 2;
@@ -248,6 +256,7 @@ __global__ void __launch_bounds__(192, 1)
         }
         __syncwarp();
       }
+      xv = xn;
       if (++as == ACC_STAGES) { as = 0; aph ^= 1; }
     }
   }
@@ -370,10 +379,23 @@ __global__ void __launch_bounds__(320, 1)
     const int q = warp & 3;
     int as = 0;
     uint32_t aph = 0;
+    // dR[:, :D] flows into feature 0; prefetched one tile ahead (TC_NS x MB values per thread)
+    float pass_cur[TC_NS][MB], pass_nxt[TC_NS][MB];
+    auto load_pass = [&](int tile, float (*dst)[MB]) {
+#pragma unroll
+      for (int s = 0; s < TC_NS; ++s) {
+        const int64_t b = (int64_t)tile * TC_NS + s;
+#pragma unroll
+        for (int mb = 0; mb < MB; ++mb)
+          dst[s][mb] = (tile < p.n_tiles && b < p.B) ? __bfloat162float(p.dR[b * p.ldr + mb * 128 + 32 * q + lane]) : 0.f;
+      }
+    };
+    load_pass(blockIdx.x, pass_cur);
     for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+      load_pass(tile + gridDim.x, pass_nxt);
       mbar_wait_bounded(&acc_full[as], aph);
       tc_fence_after();
-#pragma unroll 1
+#pragma unroll
       for (int s = 0; s < TC_NS; ++s) {
         const int64_t b = (int64_t)tile * TC_NS + s;
 #pragma unroll
@@ -383,42 +405,82 @@ __global__ void __launch_bounds__(320, 1)
           if (b < p.B) {
             const int d = mb * 128 + 32 * q + lane;
             __nv_bfloat16* o = p.dT + b * (int64_t)F * D + d;
-            const float pass = __bfloat162float(p.dR[b * p.ldr + d]);  // dR[:, :D] flows into feature 0
+            // lanes 2k / 2k+1 hold adjacent d: swap so that each lane stores one packed bf16x2
+            // (even lanes take the even features, odd lanes the odd ones)
+            const bool odd = lane & 1;
 #pragma unroll
-            for (int f = 0; f < 32; ++f)
-              if (f < F) o[(int64_t)f * D] = __float2bfloat16_rn(__uint_as_float(v[f]) + (f == 0 ? pass : 0.f));
+            for (int f = 0; f < 32; f += 2) {
+              float a0 = __uint_as_float(v[f]) + (f == 0 ? pass_cur[s][mb] : 0.f);
+              float a1 = __uint_as_float(v[f + 1]);
+              const float send = odd ? a0 : a1;
+              const float recv = __shfl_xor_sync(0xffffffffu, send, 1);
+              const int fo = f + (odd ? 1 : 0);
+              const float lo = odd ? recv : a0, hi = odd ? a1 : recv;
+              if (fo < F) *reinterpret_cast<uint32_t*>(o - (odd ? 1 : 0) + (int64_t)fo * D) = pack_bf16x2(lo, hi);
+            }
           }
         }
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[as]);
+#pragma unroll
+      for (int s = 0; s < TC_NS; ++s)
+#pragma unroll
+        for (int mb = 0; mb < MB; ++mb) pass_cur[s][mb] = pass_nxt[s][mb];
       if (++as == ACC_STAGES) { as = 0; aph ^= 1; }
     }
   } else {
     // ---------------- S builders (warps 6..9): S[i][j] = S[j][i] = dR[b, D + i(i-1)/2 + j]
     const int t = threadIdx.x - 192;  // 0..127
+    constexpr int PPT = 4;            // pairs per thread: 4 * 128 >= 32 * 31 / 2
+    uint32_t off_ij[PPT], off_ji[PPT];
+#pragma unroll
+    for (int c = 0; c < PPT; ++c) {
+      const int pi = t + c * 128;
+      int i = 1, j = 0;
+      if (pi < npairs) tri_ij(pi, i, j);
+      off_ij[c] = s_off(i, j);
+      off_ji[c] = s_off(j, i);
+    }
+    const __nv_bfloat16 zero = __float2bfloat16_rn(0.f);
+    __nv_bfloat16 cur[TC_NS][PPT], nxt[TC_NS][PPT];
+    auto load_vals = [&](int tile, __nv_bfloat16 (*dst)[PPT]) {
+#pragma unroll
+      for (int s = 0; s < TC_NS; ++s) {
+        const int64_t b = (int64_t)tile * TC_NS + s;
+        const bool live = tile < p.n_tiles && b < p.B;
+#pragma unroll
+        for (int c = 0; c < PPT; ++c) {
+          const int pi = t + c * 128;
+          dst[s][c] = (live && pi < npairs) ? p.dR[b * p.ldr + D + pi] : zero;
+        }
+      }
+    };
+    load_vals(blockIdx.x, cur);
     int st = 0;
     uint32_t ph = 0;
     for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+      load_vals(tile + gridDim.x, nxt);  // in flight while this tile's S is written
       mbar_wait_bounded(&s_empty[st], ph ^ 1);
       uint8_t* sb = stiles + (size_t)st * S_STAGE_BYTES;
-#pragma unroll 1
+#pragma unroll
       for (int s = 0; s < TC_NS; ++s) {
-        const int64_t b = (int64_t)tile * TC_NS + s;
-        const bool live = b < p.B;
-        const __nv_bfloat16* src = p.dR + b * p.ldr + D;
-        for (int pi = t; pi < npairs; pi += 128) {
-          int i, j;
-          tri_ij(pi, i, j);
-          const __nv_bfloat16 val = live ? src[pi] : __float2bfloat16_rn(0.f);
-          *reinterpret_cast<__nv_bfloat16*>(sb + s * S_BYTES + s_off(i, j)) = val;
-          *reinterpret_cast<__nv_bfloat16*>(sb + s * S_BYTES + s_off(j, i)) = val;
+#pragma unroll
+        for (int c = 0; c < PPT; ++c) {
+          if (t + c * 128 < npairs) {
+            *reinterpret_cast<__nv_bfloat16*>(sb + s * S_BYTES + off_ij[c]) = cur[s][c];
+            *reinterpret_cast<__nv_bfloat16*>(sb + s * S_BYTES + off_ji[c]) = cur[s][c];
+          }
         }
       }
       fence_proxy_async();  // generic-proxy smem writes -> visible to the tensor-core (async) proxy
       __syncwarp();
       if (lane == 0) mbar_arrive(&s_full[st]);
+#pragma unroll
+      for (int s = 0; s < TC_NS; ++s)
+#pragma unroll
+        for (int c = 0; c < PPT; ++c) cur[s][c] = nxt[s][c];
       if (++st == stages) { st = 0; ph ^= 1; }
     }
   }
