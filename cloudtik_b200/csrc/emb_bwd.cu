@@ -23,10 +23,8 @@ constexpr int UPD_THREADS = 256;
 // group serially: the sorted array is cut into windows of HOT_CH positions, every window
 // pre-reduces the (at most two) hot runs that cross it into fp32 partial rows, and the update
 // kernel adds the partials of a hot row in window order.  Deterministic, no atomics.
-constexpr int HOT_CH = 128;
-
 struct BwdLayout {
-  uint32_t *keys, *vals, *skeys, *svals, *unique, *seg;
+  uint32_t *keys, *vals, *skeys, *svals, *unique, *seg, *win_run;
   int32_t* num_unique;
   float* partial;  // [2 * ceil(n / HOT_CH)][D]
   void* sort_ws;
@@ -45,6 +43,7 @@ static BwdLayout bwd_layout(void* ws, int64_t n, int64_t D) {
   L.unique = reinterpret_cast<uint32_t*>(w + o), o += s;
   L.seg = reinterpret_cast<uint32_t*>(w + o), o += align_up((size_t)(n + 1) * 4, 256);
   L.num_unique = reinterpret_cast<int32_t*>(w + o), o += 256;
+  L.win_run = reinterpret_cast<uint32_t*>(w + o), o += align_up((size_t)(ceil_div(n, HOT_CH) + 1) * 4, 256);
   L.partial = reinterpret_cast<float*>(w + o), o += align_up((size_t)(2 * ceil_div(n, HOT_CH)) * D * 4, 256);
   L.sort_ws = w + o, o += sort_ws_bytes(n);
   L.total = o;
@@ -111,6 +110,7 @@ struct UpdParams {
   uint32_t B;
   int D, V;
   const uint32_t* skeys;
+  const uint32_t* win_run;
   float* partial;
   int64_t n;
 };
@@ -144,9 +144,12 @@ __device__ __forceinline__ void load_grad<__nv_bfloat16, 4>(const __nv_bfloat16*
 // One group per window of HOT_CH sorted positions: partial sums of the hot runs crossing it.
 // slot 0 = the run that contains the window's first position, slot 1 = a hot run that starts
 // inside the window (a window cannot hold a third: hot runs are longer than a window).
+// The run containing each window start comes from the dedup stage (win_run), so no search.
 template <typename GT, int VE, int G, int NV>
 __global__ void __launch_bounds__(UPD_THREADS) hot_window_kernel(const UpdParams p) {
   constexpr int NG = UPD_THREADS / G;
+  constexpr int CH = 16;  // gradient rows in flight per lane
+  __shared__ uint32_t s_bag[NG][HOT_CH];
   const int gid = threadIdx.x / G, lane = threadIdx.x % G;
   const int64_t w = (int64_t)blockIdx.x * NG + gid;
   const int64_t a = w * HOT_CH;
@@ -155,47 +158,42 @@ __global__ void __launch_bounds__(UPD_THREADS) hot_window_kernel(const UpdParams
   const bool cont_before = a > 0 && p.skeys[a - 1] == p.skeys[a];
   const bool cont_after = b < p.n && p.skeys[b - 1] == p.skeys[b];
   if (!cont_before && !cont_after) return;  // no run longer than a window can touch this one
-  const int64_t nU = *p.num_unique;
-  auto run_of = [&](int64_t pos) -> int64_t {  // largest u with seg[u] <= pos
-    int64_t lo = 0, hi = nU;                   // seg[lo] <= pos < seg[hi]
-    while (hi - lo > 1) {
-      const int64_t mid = (lo + hi) >> 1;
-      if ((int64_t)p.seg[mid] <= pos) lo = mid; else hi = mid;
-    }
-    return lo;
-  };
+  const uint32_t gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << ((threadIdx.x & 31) & ~(G - 1)));
+
   auto reduce_range = [&](int64_t lo, int64_t hi, int slot) {
+    const int cnt = (int)(hi - lo);
+    for (int i = lane; i < cnt; i += G) s_bag[gid][i] = p.svals[lo + i];  // coalesced
+    __syncwarp(gmask);
+    const uint32_t tt = s_bag[gid][0] / p.B;
+    const GT* gt = static_cast<const GT*>(p.grad) + (int64_t)tt * p.grad_stride_table - (int64_t)(tt * p.B) * p.grad_stride_bag;
     float acc[NV][VE];
 #pragma unroll
     for (int k = 0; k < NV; ++k)
 #pragma unroll
       for (int x = 0; x < VE; ++x) acc[k][x] = 0.f;
-    const uint32_t tt = p.svals[lo] / p.B;
-    const GT* gt = static_cast<const GT*>(p.grad) + (int64_t)tt * p.grad_stride_table;
-    for (int64_t j = lo; j < hi; j += 8) {
-      float g8[8][NV][VE];
+    for (int j = 0; j < cnt; j += CH) {
+      float g[CH][NV][VE];
 #pragma unroll
-      for (int c = 0; c < 8; ++c) {
-        const bool ok = j + c < hi;
-        const uint32_t bb = ok ? p.svals[j + c] - tt * p.B : 0;
-        const GT* gp = gt + (int64_t)bb * p.grad_stride_bag;
+      for (int c = 0; c < CH; ++c) {
+        const bool ok = j + c < cnt;
+        const GT* gp = gt + (int64_t)(ok ? s_bag[gid][j + c] : tt * p.B) * p.grad_stride_bag;
 #pragma unroll
         for (int k = 0; k < NV; ++k) {
           const int vi = lane + k * G;
           if (ok && vi < p.V) {
-            load_grad<GT, VE>(gp + vi * VE, g8[c][k]);
+            load_grad<GT, VE>(gp + vi * VE, g[c][k]);
           } else {
 #pragma unroll
-            for (int x = 0; x < VE; ++x) g8[c][k][x] = 0.f;
+            for (int x = 0; x < VE; ++x) g[c][k][x] = 0.f;
           }
         }
       }
 #pragma unroll
-      for (int c = 0; c < 8; ++c)
+      for (int c = 0; c < CH; ++c)
 #pragma unroll
         for (int k = 0; k < NV; ++k)
 #pragma unroll
-          for (int x = 0; x < VE; ++x) acc[k][x] += g8[c][k][x];
+          for (int x = 0; x < VE; ++x) acc[k][x] += g[c][k][x];
     }
     float* dst = p.partial + (size_t)(2 * w + slot) * p.D;
 #pragma unroll
@@ -206,12 +204,14 @@ __global__ void __launch_bounds__(UPD_THREADS) hot_window_kernel(const UpdParams
         for (int h = 0; h < VE / 4; ++h) store_vec<float, 4, false>(dst + vi * VE + 4 * h, acc[k] + 4 * h);
       }
     }
+    __syncwarp(gmask);
   };
-  const int64_t ua = run_of(a);
+  const int64_t ua = p.win_run[w];
   const int64_t sa = p.seg[ua], ea = p.seg[ua + 1];
   if (ea - sa > HOT_CH) reduce_range(a, min(b, ea), 0);
   if (ea < b) {
-    const int64_t ub = run_of(b - 1);
+    const int64_t ub = (b < p.n) ? (int64_t)p.win_run[w + 1] - (p.skeys[b] != p.skeys[b - 1] ? 1 : 0)
+                                 : (int64_t)(*p.num_unique) - 1;
     const int64_t sb = p.seg[ub], eb = p.seg[ub + 1];
     if (eb - sb > HOT_CH) reduce_range(sb, b, 1);
   }
@@ -275,11 +275,14 @@ __global__ void __launch_bounds__(UPD_THREADS) emb_update_kernel(const UpdParams
       }
     }
   } else {
-#pragma unroll 1
+    // hot rows first: add their per-window partial sums (hot_window_kernel) in window order
+    uint32_t j[R], je[R];
+#pragma unroll
     for (int q = 0; q < R; ++q) {
-      if (!valid[q]) continue;
-      if (e[q] - s[q] > (uint32_t)HOT_CH) {
-        // hot row: add the per-window partial sums (hot_window_kernel) in window order
+      j[q] = s[q];
+      je[q] = valid[q] ? e[q] : s[q];
+      if (valid[q] && e[q] - s[q] > (uint32_t)HOT_CH) {
+        je[q] = s[q];  // nothing left for the walk below
         const uint32_t w0 = s[q] / HOT_CH, w1 = (e[q] - 1) / HOT_CH;
         for (uint32_t w = w0; w <= w1; ++w) {
           const int slot = (s[q] > w * HOT_CH) ? 1 : 0;
@@ -298,31 +301,44 @@ __global__ void __launch_bounds__(UPD_THREADS) emb_update_kernel(const UpdParams
             }
           }
         }
-        continue;
       }
-      for (uint32_t j = s[q]; j < e[q]; j += 4) {
-        float g4[4][NV][VE];
+    }
+    // the four runs advance together: R independent (bag id -> gradient row) chains in flight,
+    // each run still summed in sorted (= bag) order
+    while (true) {
+      bool act[R];
+      bool any = false;
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          const bool ok = j + c < e[q];
-          const GT* gp = ok ? grad_row(p.svals[j + c], t[q]) : nullptr;
+      for (int q = 0; q < R; ++q) {
+        act[q] = j[q] < je[q];
+        any = any || act[q];
+      }
+      if (!any) break;
+      uint32_t g[R];
 #pragma unroll
-          for (int k = 0; k < NV; ++k) {
-            const int vi = lane + k * G;
-            if (ok && vi < p.V) {
-              load_grad<GT, VE>(gp + vi * VE, g4[c][k]);
-            } else {
+      for (int q = 0; q < R; ++q) g[q] = act[q] ? p.svals[j[q]] : 0u;
+      float tmp[R][NV][VE];
 #pragma unroll
-              for (int x = 0; x < VE; ++x) g4[c][k][x] = 0.f;
-            }
+      for (int q = 0; q < R; ++q) {
+        const GT* gp = grad_row(g[q], t[q]);
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+          const int vi = lane + k * G;
+          if (act[q] && vi < p.V) {
+            load_grad<GT, VE>(gp + vi * VE, tmp[q][k]);
+          } else {
+#pragma unroll
+            for (int x = 0; x < VE; ++x) tmp[q][k][x] = 0.f;
           }
         }
+      }
 #pragma unroll
-        for (int c = 0; c < 4; ++c)
+      for (int q = 0; q < R; ++q) {
 #pragma unroll
-          for (int k = 0; k < NV; ++k)
+        for (int k = 0; k < NV; ++k)
 #pragma unroll
-            for (int x = 0; x < VE; ++x) acc[q][k][x] += g4[c][k][x];
+          for (int x = 0; x < VE; ++x) acc[q][k][x] += tmp[q][k][x];
+        j[q] += act[q] ? 1u : 0u;
       }
     }
   }
@@ -459,7 +475,7 @@ extern "C" int b200_emb_bwd_prepare(const int64_t* d_rows, const int64_t* d_row_
   B200_CHECK_LAUNCH("build_keys");
   rc = sort_pairs(L.keys, L.vals, nnz, (uint64_t)total_rows, L.skeys, L.svals, L.sort_ws, st);
   if (rc) return rc;
-  return dedup_runs(L.skeys, nnz, L.unique, L.seg, L.num_unique, L.sort_ws, st);
+  return dedup_runs(L.skeys, nnz, L.unique, L.seg, L.num_unique, L.sort_ws, st, L.win_run);
 }
 
 extern "C" int b200_emb_bwd_apply(void* const* d_weights, float* const* d_state,
@@ -497,6 +513,7 @@ extern "C" int b200_emb_bwd_apply(void* const* d_weights, float* const* d_state,
   p.B = (uint32_t)B;
   p.D = (int)D;
   p.skeys = L.skeys;
+  p.win_run = L.win_run;
   p.partial = L.partial;
   p.n = nnz;
   const int wsz = dtype_size(w_dtype), gsz = dtype_size(grad_dtype);

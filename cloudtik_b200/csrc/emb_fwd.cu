@@ -7,8 +7,9 @@
 // CSR offsets and (when it fits) the tile's window of indices into shared memory with 1-D
 // bulk async copies (TMA engine, mbarrier completion), then sub-warp groups of G lanes own
 // one bag at a time: lane l of a group moves the 16-byte vectors l, l+G, ... of each row
-// (G*16 bytes coalesced per row).  Four bags are in flight per group; one-hot bags take a
-// copy-through path, pooled bags accumulate in fp32 in index order.
+// (G*16 bytes coalesced per row).  The staged tile is first compacted to 32-bit offsets / row
+// ids (bounds check done once there).  One-hot tiles take a copy-through path with four bags in
+// flight per group; pooled bags accumulate in fp32 in index order, four rows in flight.
 #include <algorithm>
 
 #include "common.cuh"
@@ -95,91 +96,132 @@ __global__ void __launch_bounds__(FWD_THREADS) emb_fwd_kernel(const EmbFwdParams
   const size_t row_bytes = (size_t)p.D * sizeof(WT);
   OT* out_t = static_cast<OT*>(p.out) + (int64_t)t * p.out_stride_table + b0 * p.out_stride_bag;
 
-  auto get_idx = [&](int64_t j) -> int64_t {
-    return staged ? s_idx[j - a0] : __ldg(p.indices + j);
-  };
-  auto row_ptr = [&](int64_t idx, bool& ok) -> const char* {
-    ok = (uint64_t)idx < (uint64_t)nrows;
-    if (!ok && p.error) *p.error = 1;
-    return W + (ok ? (size_t)idx : 0) * row_bytes;
-  };
-
-  for (int r = gid; r < nb; r += 4 * NG) {
-    int64_t s[4], e[4];
-    bool onehot = true;
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int bag = r + u * NG;
-      const bool valid = bag < nb;
-      s[u] = valid ? s_off[bag] : 0;
-      e[u] = valid ? s_off[bag + 1] : 0;
-      onehot = onehot && (e[u] - s[u] <= 1);
+  // ---- compact the staged tile to 32 bits: bag offsets relative to i0, row ids (bounds-checked
+  //      once here, 0xffffffff = out of range) -- keeps 64-bit arithmetic out of the gather loop
+  __shared__ int s_rel[FWD_MAX_TILE + 1];
+  __shared__ uint32_t s_row[FWD_IDX_CAP + 2];
+  const bool staged32 = staged && nrows < 0xffffffffll;
+  bool all_one = true;
+  if (staged32) {
+    for (int i = tid; i <= nb; i += FWD_THREADS) s_rel[i] = (int)(s_off[i] - i0);
+    for (int i = tid; i < nb; i += FWD_THREADS) all_one = all_one && (s_off[i + 1] - s_off[i] == 1);
+    const int cnt = (int)(i1 - i0), shift = (int)(i0 - a0);
+    for (int k = tid; k < cnt; k += FWD_THREADS) {
+      const int64_t idx = s_idx[k + shift];
+      const bool ok = (uint64_t)idx < (uint64_t)nrows;
+      if (!ok && p.error) *p.error = 1;
+      s_row[k] = ok ? (uint32_t)idx : 0xffffffffu;
     }
-    if (onehot) {
+  }
+  const bool fast = __syncthreads_and(staged32 && all_one) != 0;
+
+  const char* Wl = W + (size_t)lane * 16;
+  OT* outl = out_t + lane * VE;
+
+  if (fast) {
+    // every bag of the tile holds exactly one index (Criteo one-hot): bag k reads row s_row[k]
+    for (int r = gid; r < nb; r += 4 * NG) {
+      uint32_t row[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) row[u] = (r + u * NG < nb) ? s_row[r + u * NG] : 0xffffffffu;
       uint4 v[4][NV];
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        bool ok = false;
-        const char* src = nullptr;
-        if (e[u] > s[u]) src = row_ptr(get_idx(s[u]), ok);
-#pragma unroll
-        for (int k = 0; k < NV; ++k) {
-          const int vi = lane + k * G;
-          v[u][k] = (ok && vi < p.V) ? ld_nc_v4(src + (size_t)vi * 16) : make_uint4(0, 0, 0, 0);
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int bag = r + u * NG;
-        if (bag < nb) {
-          OT* dst = out_t + (int64_t)bag * p.out_stride_bag;
-#pragma unroll
-          for (int k = 0; k < NV; ++k) {
-            const int vi = lane + k * G;
-            if (vi < p.V) {
-              float f[VE];
-              Vec16<WT>::unpack(f, v[u][k]);
-              store_vec<OT, VE, true>(dst + vi * VE, f);
-            }
-          }
-        }
-      }
-    } else {
-#pragma unroll 1
-      for (int u = 0; u < 4; ++u) {
-        const int bag = r + u * NG;
-        if (bag >= nb) break;
-        float acc[NV][VE];
+        const char* src = Wl + (size_t)row[u] * row_bytes;
 #pragma unroll
         for (int k = 0; k < NV; ++k)
+          v[u][k] = (row[u] != 0xffffffffu && lane + k * G < p.V) ? ld_nc_v4(src + (size_t)k * G * 16)
+                                                                 : make_uint4(0, 0, 0, 0);
+      }
 #pragma unroll
-          for (int x = 0; x < VE; ++x) acc[k][x] = 0.f;
-        for (int64_t j = s[u]; j < e[u]; j += 4) {
-          uint4 v[4][NV];
+      for (int u = 0; u < 4; ++u) {
+        if (r + u * NG < nb) {
+          OT* dst = outl + (int64_t)(r + u * NG) * p.out_stride_bag;
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            bool ok = false;
-            const char* src = nullptr;
-            if (j + q < e[u]) src = row_ptr(get_idx(j + q), ok);
-#pragma unroll
-            for (int k = 0; k < NV; ++k) {
-              const int vi = lane + k * G;
-              v[q][k] = (ok && vi < p.V) ? ld_nc_v4(src + (size_t)vi * 16) : make_uint4(0, 0, 0, 0);
+          for (int k = 0; k < NV; ++k) {
+            if (lane + k * G < p.V) {
+              if constexpr (sizeof(WT) == sizeof(OT)) {
+                st_cs_v4(dst + k * G * VE, v[u][k]);
+              } else {
+                float f[VE];
+                Vec16<WT>::unpack(f, v[u][k]);
+                store_vec<OT, VE, true>(dst + k * G * VE, f);
+              }
             }
           }
-#pragma unroll
-          for (int q = 0; q < 4; ++q)
-#pragma unroll
-            for (int k = 0; k < NV; ++k) Vec16<WT>::accum(acc[k], v[q][k]);
-        }
-        OT* dst = out_t + (int64_t)bag * p.out_stride_bag;
-#pragma unroll
-        for (int k = 0; k < NV; ++k) {
-          const int vi = lane + k * G;
-          if (vi < p.V) store_vec<OT, VE, true>(dst + vi * VE, acc[k]);
         }
       }
     }
+    return;
+  }
+
+  if (staged32) {
+    // pooled / ragged bags, indices staged: fp32 accumulation in index order, 4 rows in flight
+    for (int bag = gid; bag < nb; bag += NG) {
+      const int sb = s_rel[bag], eb = s_rel[bag + 1];
+      float acc[NV][VE];
+#pragma unroll
+      for (int k = 0; k < NV; ++k)
+#pragma unroll
+        for (int x = 0; x < VE; ++x) acc[k][x] = 0.f;
+      for (int j = sb; j < eb; j += 4) {
+        uint4 v[4][NV];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const uint32_t row = (j + q < eb) ? s_row[j + q] : 0xffffffffu;
+          const char* src = Wl + (size_t)row * row_bytes;
+#pragma unroll
+          for (int k = 0; k < NV; ++k)
+            v[q][k] = (row != 0xffffffffu && lane + k * G < p.V) ? ld_nc_v4(src + (size_t)k * G * 16)
+                                                               : make_uint4(0, 0, 0, 0);
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+#pragma unroll
+          for (int k = 0; k < NV; ++k) Vec16<WT>::accum(acc[k], v[q][k]);
+      }
+      OT* dst = outl + (int64_t)bag * p.out_stride_bag;
+#pragma unroll
+      for (int k = 0; k < NV; ++k)
+        if (lane + k * G < p.V) store_vec<OT, VE, true>(dst + k * G * VE, acc[k]);
+    }
+    return;
+  }
+
+  // tile's index window does not fit the staging buffer (very long bags) or is misaligned:
+  // indices come straight from global memory (one broadcast load per row)
+  for (int bag = gid; bag < nb; bag += NG) {
+    const int64_t sb = s_off[bag], eb = s_off[bag + 1];
+    float acc[NV][VE];
+#pragma unroll
+    for (int k = 0; k < NV; ++k)
+#pragma unroll
+      for (int x = 0; x < VE; ++x) acc[k][x] = 0.f;
+    for (int64_t j = sb; j < eb; j += 4) {
+      uint4 v[4][NV];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        bool ok = false;
+        int64_t idx = 0;
+        if (j + q < eb) {
+          idx = __ldg(p.indices + j + q);
+          ok = (uint64_t)idx < (uint64_t)nrows;
+          if (!ok && p.error) *p.error = 1;
+        }
+        const char* src = Wl + (ok ? (size_t)idx : 0) * row_bytes;
+#pragma unroll
+        for (int k = 0; k < NV; ++k)
+          v[q][k] = (ok && lane + k * G < p.V) ? ld_nc_v4(src + (size_t)k * G * 16) : make_uint4(0, 0, 0, 0);
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int k = 0; k < NV; ++k) Vec16<WT>::accum(acc[k], v[q][k]);
+    }
+    OT* dst = outl + (int64_t)bag * p.out_stride_bag;
+#pragma unroll
+    for (int k = 0; k < NV; ++k)
+      if (lane + k * G < p.V) store_vec<OT, VE, true>(dst + k * G * VE, acc[k]);
   }
 }
 

@@ -10,6 +10,8 @@ constexpr int SORT_CHUNK = SORT_THREADS * SORT_ITEMS;  // keys per block
 constexpr int DEDUP_THREADS = 256;
 constexpr int DEDUP_ITEMS = 8;
 constexpr int DEDUP_CHUNK = DEDUP_THREADS * DEDUP_ITEMS;
+// window size of the hot-run pre-reduction in emb_bwd.cu (DEDUP_THREADS must be a multiple of it)
+constexpr int HOT_CH = 128;
 
 // workspace: [keysA | keysB | valsA | valsB | digit histograms | dedup block counts]
 size_t sort_ws_bytes(int64_t n);
@@ -21,8 +23,10 @@ int sort_pairs(const uint32_t* keys, const uint32_t* vals, int64_t n, uint64_t k
 
 // run-length de-duplication of sorted keys: unique[u], seg[u] (start of run u), seg[U] = n,
 // *num_unique = U.  n > 0.  Uses the tail of the same workspace.
+// win_run (optional, may be null): win_run[w] = index of the run that contains sorted position
+// w * HOT_CH, for every window start below n.
 int dedup_runs(const uint32_t* skeys, int64_t n, uint32_t* unique, uint32_t* seg, int32_t* num_unique,
-               void* ws, cudaStream_t st);
+               void* ws, cudaStream_t st, uint32_t* win_run = nullptr);
 
 int empty_result(uint32_t* seg, int32_t* num_unique, cudaStream_t st);
 

@@ -1,0 +1,79 @@
+"""world_size-2 gloo tests (CPU) of the table-wise model-parallel plumbing in cloudtik_b200.ext_dist:
+partition helpers, pooled-embedding all-to-all forward and its mirrored backward, uneven table split
+(5 tables over 2 ranks) -- checked against the single-process global-batch computation, which is the
+multi-GPU parity oracle."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.multiprocessing as mp
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _global_problem(n_tables, N, E):
+    g = torch.Generator().manual_seed(1234)
+    tables = [torch.randn(11 + 3 * t, E, generator=g) for t in range(n_tables)]
+    idx = [torch.randint(0, 11 + 3 * t, (N,), generator=g) for t in range(n_tables)]
+    gout = torch.randn(N, n_tables * E, generator=g)  # gradient w.r.t. the per-sample concatenated features
+    return tables, idx, gout
+
+
+def _worker(rank, world, port, n_tables, N, E, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    from cloudtik_b200 import ext_dist
+    from oracle import ops_numpy as ref
+    ext_dist.init_distributed(rank=rank, size=world, backend="gloo")
+    try:
+        assert ext_dist.my_size == world and ext_dist.my_rank == rank
+        sl = ext_dist.get_my_slice(n_tables)
+        want_sl = ref.get_my_slice(n_tables, world, rank)
+        assert (sl.start, sl.stop) == (want_sl.start, want_sl.stop)
+        my_len, splits = ext_dist.get_split_lengths(n_tables)
+        assert (my_len, splits) == ref.get_split_lengths(n_tables, world, rank)
+
+        tables, idx, gout = _global_problem(n_tables, N, E)
+        local = list(range(n_tables))[sl]
+        lN = N // world
+        # local tables looked up for the GLOBAL batch (one-hot), written as adjacent column blocks of
+        # one [N, lS*E] buffer -- the layout the merged embedding kernel produces for the a2a
+        buf = torch.empty(N, len(local) * E)
+        for k, t in enumerate(local):
+            buf[:, k * E:(k + 1) * E] = tables[t][idx[t]]
+        buf.requires_grad_(True)
+        ly = [buf[:, k * E:(k + 1) * E] for k in range(len(local))]
+        req = ext_dist.alltoall(ly, splits)
+        outs = req.wait()
+        assert len(outs) == world
+        got = torch.cat([o for o in outs], dim=1)            # [lN, n_tables*E], tables in global order
+        want = torch.cat([tables[t][idx[t]] for t in range(n_tables)], dim=1)[rank * lN:(rank + 1) * lN]
+        assert torch.equal(got, want)
+        # backward: each rank feeds the gradient of ITS samples; the mirrored a2a must hand every rank the
+        # gradient of its tables for the global batch
+        got.backward(gout[rank * lN:(rank + 1) * lN])
+        gw = torch.cat([gout[:, t * E:(t + 1) * E] for t in local], dim=1)
+        assert torch.equal(buf.grad, gw)
+        # all_gather of per-rank scores (eval path)
+        scores = torch.full((lN, 1), float(rank))
+        allg = ext_dist.all_gather(scores, None)
+        assert torch.equal(allg, torch.arange(world, dtype=torch.float32).repeat_interleave(lN).view(-1, 1))
+        ext_dist.barrier()
+        ret[rank] = "ok"
+    finally:
+        torch.distributed.destroy_process_group()
+
+
+@pytest.mark.parametrize("n_tables,N", [(5, 6), (4, 8)])
+def test_alltoall_two_ranks_gloo(n_tables, N):
+    world = 2
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    port = _free_port()
+    mp.spawn(_worker, args=(world, port, n_tables, N, 3, ret), nprocs=world, join=True)
+    assert dict(ret) == {0: "ok", 1: "ok"}
