@@ -16,7 +16,7 @@ import torch
 import torch.nn as nn
 
 from . import ext_dist
-from .interaction import PaddedLinear, interaction
+from .interaction import PaddedLinear, interaction, interaction_sharded
 from .merged_embedding import MergedEmbeddingBagWithSGD
 
 
@@ -73,7 +73,8 @@ class DLRM_Net(nn.Module):
         else:
             self.local_ln_emb = None
         self.l_emb_seeds = np.random.randint(low=0, high=100000, size=len(ln_emb))
-        self.bot_l = self.create_mlp(np.asarray(ln_bot), sigmoid_bot).to(device)
+        self.bot_l = self.create_mlp(np.asarray(ln_bot), sigmoid_bot, pad_first=True).to(device)
+        self.dense_pad = (-int(ln_bot[0])) % 8  # 13 dense features -> 16 zero-padded columns (aligned GEMM K)
         self.top_l = self.create_mlp(np.asarray(ln_top), sigmoid_top, pad_first=True).to(device)
         self.interaction_pad = 8  # interaction output rounded up to a multiple of 8 columns
         self.emb_l = self.create_emb(m_spa, ln_emb, self.local_ln_emb, np_init_emb_weight, device, lr,
@@ -87,6 +88,9 @@ class DLRM_Net(nn.Module):
 
     def apply_mlp(self, x, layers):
         return layers(x)
+
+    def _pad_dense(self, dense_x):
+        return torch.nn.functional.pad(dense_x, (0, self.dense_pad)) if self.dense_pad else dense_x
 
     def apply_emb(self, emb_l, *emb_args):
         # merged call style (P/dlrm_s_pytorch.py:288-289): (indices, offsets, indices_with_row_offsets)
@@ -112,7 +116,7 @@ class DLRM_Net(nn.Module):
     def sequential_forward(self, dense_x, *emb_args):
         # P/dlrm_s_pytorch.py:372-397
         with torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.bf16):
-            x = self.apply_mlp(dense_x, self.bot_l)
+            x = self.apply_mlp(self._pad_dense(dense_x), self.bot_l)
             ly = self.apply_emb(self.emb_l, *emb_args)
             z = self.interact_features(x, ly)
             p = self.apply_mlp(z, self.top_l)
@@ -128,13 +132,11 @@ class DLRM_Net(nn.Module):
         with torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.bf16):
             ly = self.apply_emb(self.emb_l, *emb_args)
             a2a_req = ext_dist.alltoall(ly, self.n_emb_per_rank)
-            x = self.apply_mlp(dense_x, self.bot_l)
+            x = self.apply_mlp(self._pad_dense(dense_x), self.bot_l)
             ly = a2a_req.wait()
-            _ly = []
-            for r, item in enumerate(ly):
-                n_r = self.n_emb_per_rank[r] if self.n_emb_per_rank else self.emb_l.n_tables
-                _ly += [item[:, e * vector_lenght:(e + 1) * vector_lenght] for e in range(n_r)]
-            z = self.interact_features(x, _ly)
+            # the reference re-slices every rank's block into per-table [lN, D] views
+            # (P/dlrm_s_pytorch.py:355-357); here the blocks go to the interaction as they are
+            z = interaction_sharded(x, ly, pad_to=self.interaction_pad)
             p = self.apply_mlp(z, self.top_l)
         return self._clamp(p)
 

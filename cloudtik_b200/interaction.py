@@ -63,6 +63,49 @@ class _InteractionFn(torch.autograd.Function):
         return (None, dx, *dly)
 
 
+class _InteractionShardedFn(torch.autograd.Function):
+    """Distributed variant: ``chunks[r]`` is what the pooled-embedding all-to-all delivered from rank r,
+    a contiguous ``[lN, lS_r * D]`` block.  Forward packs x and the chunks into ``T [lN, F, D]`` with one
+    strided copy per source rank (instead of F slices + stack), backward unpacks ``dT`` the same way, so
+    autograd never materialises per-feature slices."""
+
+    @staticmethod
+    def forward(ctx, pad_to, x, *chunks):
+        lN, D = x.shape
+        counts = [c.shape[1] // D for c in chunks]
+        F = 1 + sum(counts)
+        dt = chunks[0].dtype
+        T = torch.empty(lN, F, D, dtype=dt, device=x.device)
+        T[:, 0].copy_(x)
+        f0 = 1
+        for c, n in zip(chunks, counts):
+            T[:, f0:f0 + n].copy_(c.view(lN, n, D))
+            f0 += n
+        ctx.save_for_backward(T)
+        ctx.counts = counts
+        ctx.x_dtype = x.dtype
+        return ops.interact_fwd(T, pad_to=pad_to)
+
+    @staticmethod
+    def backward(ctx, dR):
+        (T,) = ctx.saved_tensors
+        lN, F, D = T.shape
+        dT = ops.interact_bwd(T, dR.contiguous().to(T.dtype))
+        dx = dT[:, 0].to(ctx.x_dtype)
+        grads, f0 = [], 1
+        for n in ctx.counts:
+            grads.append(dT[:, f0:f0 + n].reshape(lN, n * D))  # one contiguous copy per destination rank
+            f0 += n
+        return (None, dx, *grads)
+
+
+def interaction_sharded(x: torch.Tensor, chunks, pad_to: int = 1) -> torch.Tensor:
+    """Interaction of the local-batch dense feature ``x [lN, D]`` with the per-source-rank pooled
+    chunks ``[lN, lS_r * D]`` returned by ``ext_dist.alltoall(...).wait()`` (features in rank order =
+    global table order for the contiguous table partition)."""
+    return _InteractionShardedFn.apply(int(pad_to), x, *chunks)
+
+
 def interaction(x: torch.Tensor, *ly: torch.Tensor, pad_to: int = 1) -> torch.Tensor:
     """``interaction(x, *ly)`` -- see module docstring.  CUDA tensors only.
 
