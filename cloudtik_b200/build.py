@@ -62,4 +62,9 @@ def build(force=False, verbose=False):
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv))
+    try:
+        print("BUILD OK:", build(force="--force" in sys.argv, verbose="--verbose" in sys.argv))
+    except Exception as e:  # keep the failure impossible to miss behind a pipe
+        print(str(e)[-6000:])
+        print("BUILD FAILED")
+        sys.exit(1)

@@ -41,33 +41,40 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
-// 128-bit global load that bypasses L1 allocation (rows are touched once per kernel).
-__device__ __forceinline__ uint4 ld_nc_v4(const void* p) {
+// 128-bit accesses.  Loads are volatile asm so that a batch of them stays in program order, and
+// keep() pins a loaded value as "used" by an (empty) volatile asm: issuing every load of a batch
+// and only then keep()-ing them forces all the loads in flight together.  Left to itself the
+// compiler interleaves load / use pairs to save registers, which serialises the memory latency
+// these HBM-bound kernels depend on hiding.
+__device__ __forceinline__ uint4 ld_nc_v4(const void* p) {  // read-only data, no L1 allocation
   uint4 r;
   asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
                : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
                : "l"(p));
   return r;
 }
-// plain (coherent) 128-bit load for read-modify-write rows
-__device__ __forceinline__ uint4 ld_v4(const void* p) {
-  uint4 r;
-  asm volatile("ld.global.v4.u32 {%0,%1,%2,%3}, [%4];"
-               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-               : "l"(p));
+__device__ __forceinline__ uint2 ld_nc_v2(const void* p) {
+  uint2 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
   return r;
 }
-__device__ __forceinline__ void st_cs_v4(void* p, uint4 v) {
-  asm volatile("st.global.cs.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z),
-               "r"(v.w)
-               : "memory");
+__device__ __forceinline__ uint4 ld_v4(const void* p) {  // coherent load for read-modify-write rows
+  uint4 r;
+  asm volatile("ld.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
 }
-__device__ __forceinline__ void st_cs_v2(void* p, uint2 v) {
-  asm volatile("st.global.cs.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
+__device__ __forceinline__ void keep(uint4& v) { asm volatile("" : "+r"(v.x), "+r"(v.y), "+r"(v.z), "+r"(v.w)); }
+__device__ __forceinline__ void keep(uint2& v) { asm volatile("" : "+r"(v.x), "+r"(v.y)); }
+__device__ __forceinline__ void st_cs_v4(void* p, uint4 v) { __stcs(reinterpret_cast<uint4*>(p), v); }
+__device__ __forceinline__ void st_cs_v2(void* p, uint2 v) { __stcs(reinterpret_cast<uint2*>(p), v); }
+__device__ __forceinline__ void st_v4(void* p, uint4 v) { *reinterpret_cast<uint4*>(p) = v; }
+
+// fire-and-forget vector reductions performed by the L2 atomic unit (no value returns to the SM)
+__device__ __forceinline__ void red_add_v4_f32(float* p, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
-__device__ __forceinline__ void st_v4(void* p, uint4 v) {
-  asm volatile("st.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z),
-               "r"(v.w)
+__device__ __forceinline__ void red_add_v4_bf16x2(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("red.global.add.noftz.v4.bf16x2 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d)
                : "memory");
 }
 

@@ -9,6 +9,8 @@
 //   3. update     : one sub-warp group per unique row: sum grad rows of the run (fp32, in
 //                   bag order), then ONE read-modify-write of the weight row (and of the
 //                   Adagrad state row).  The [nnz, D] COO gradient is never materialised.
+#include <stdlib.h>
+
 #include <algorithm>
 
 #include "common.cuh"
@@ -24,7 +26,7 @@ constexpr int UPD_THREADS = 256;
 // pre-reduces the (at most two) hot runs that cross it into fp32 partial rows, and the update
 // kernel adds the partials of a hot row in window order.  Deterministic, no atomics.
 struct BwdLayout {
-  uint32_t *keys, *vals, *skeys, *svals, *unique, *seg, *win_run;
+  uint32_t *keys, *vals, *skeys, *svals, *unique, *seg, *win_run, *first_val;
   int32_t* num_unique;
   float* partial;  // [2 * ceil(n / HOT_CH)][D]
   void* sort_ws;
@@ -41,6 +43,7 @@ static BwdLayout bwd_layout(void* ws, int64_t n, int64_t D) {
   L.skeys = reinterpret_cast<uint32_t*>(w + o), o += s;
   L.svals = reinterpret_cast<uint32_t*>(w + o), o += s;
   L.unique = reinterpret_cast<uint32_t*>(w + o), o += s;
+  L.first_val = reinterpret_cast<uint32_t*>(w + o), o += s;
   L.seg = reinterpret_cast<uint32_t*>(w + o), o += align_up((size_t)(n + 1) * 4, 256);
   L.num_unique = reinterpret_cast<int32_t*>(w + o), o += 256;
   L.win_run = reinterpret_cast<uint32_t*>(w + o), o += align_up((size_t)(ceil_div(n, HOT_CH) + 1) * 4, 256);
@@ -111,6 +114,8 @@ struct UpdParams {
   int D, V;
   const uint32_t* skeys;
   const uint32_t* win_run;
+  const uint32_t* first_val;
+  int T;
   float* partial;
   int64_t n;
 };
@@ -133,248 +138,321 @@ __device__ __forceinline__ void load_grad<__nv_bfloat16, 8>(const __nv_bfloat16*
 }
 template <>
 __device__ __forceinline__ void load_grad<__nv_bfloat16, 4>(const __nv_bfloat16* p, float* out) {
-  uint2 v;
-  asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+  const uint2 v = ld_nc_v2(p);
   out[0] = bf16lo(v.x);
   out[1] = bf16hi(v.x);
   out[2] = bf16lo(v.y);
   out[3] = bf16hi(v.y);
 }
 
-// One group per window of HOT_CH sorted positions: partial sums of the hot runs crossing it.
-// slot 0 = the run that contains the window's first position, slot 1 = a hot run that starts
-// inside the window (a window cannot hold a third: hot runs are longer than a window).
-// The run containing each window start comes from the dedup stage (win_run), so no search.
-template <typename GT, int VE, int G, int NV>
-__global__ void __launch_bounds__(UPD_THREADS) hot_window_kernel(const UpdParams p) {
-  constexpr int NG = UPD_THREADS / G;
-  constexpr int CH = 16;  // gradient rows in flight per lane
-  __shared__ uint32_t s_bag[NG][HOT_CH];
-  const int gid = threadIdx.x / G, lane = threadIdx.x % G;
-  const int64_t w = (int64_t)blockIdx.x * NG + gid;
-  const int64_t a = w * HOT_CH;
-  if (a >= p.n) return;
-  const int64_t b = min(a + (int64_t)HOT_CH, p.n);
-  const bool cont_before = a > 0 && p.skeys[a - 1] == p.skeys[a];
-  const bool cont_after = b < p.n && p.skeys[b - 1] == p.skeys[b];
-  if (!cont_before && !cont_after) return;  // no run longer than a window can touch this one
-  const uint32_t gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << ((threadIdx.x & 31) & ~(G - 1)));
-
-  auto reduce_range = [&](int64_t lo, int64_t hi, int slot) {
-    const int cnt = (int)(hi - lo);
-    for (int i = lane; i < cnt; i += G) s_bag[gid][i] = p.svals[lo + i];  // coalesced
-    __syncwarp(gmask);
-    const uint32_t tt = s_bag[gid][0] / p.B;
-    const GT* gt = static_cast<const GT*>(p.grad) + (int64_t)tt * p.grad_stride_table - (int64_t)(tt * p.B) * p.grad_stride_bag;
-    float acc[NV][VE];
-#pragma unroll
-    for (int k = 0; k < NV; ++k)
-#pragma unroll
-      for (int x = 0; x < VE; ++x) acc[k][x] = 0.f;
-    for (int j = 0; j < cnt; j += CH) {
-      float g[CH][NV][VE];
-#pragma unroll
-      for (int c = 0; c < CH; ++c) {
-        const bool ok = j + c < cnt;
-        const GT* gp = gt + (int64_t)(ok ? s_bag[gid][j + c] : tt * p.B) * p.grad_stride_bag;
-#pragma unroll
-        for (int k = 0; k < NV; ++k) {
-          const int vi = lane + k * G;
-          if (ok && vi < p.V) {
-            load_grad<GT, VE>(gp + vi * VE, g[c][k]);
-          } else {
-#pragma unroll
-            for (int x = 0; x < VE; ++x) g[c][k][x] = 0.f;
-          }
-        }
-      }
-#pragma unroll
-      for (int c = 0; c < CH; ++c)
-#pragma unroll
-        for (int k = 0; k < NV; ++k)
-#pragma unroll
-          for (int x = 0; x < VE; ++x) acc[k][x] += g[c][k][x];
-    }
-    float* dst = p.partial + (size_t)(2 * w + slot) * p.D;
-#pragma unroll
-    for (int k = 0; k < NV; ++k) {
-      const int vi = lane + k * G;
-      if (vi < p.V) {
-#pragma unroll
-        for (int h = 0; h < VE / 4; ++h) store_vec<float, 4, false>(dst + vi * VE + 4 * h, acc[k] + 4 * h);
-      }
-    }
-    __syncwarp(gmask);
-  };
-  const int64_t ua = p.win_run[w];
-  const int64_t sa = p.seg[ua], ea = p.seg[ua + 1];
-  if (ea - sa > HOT_CH) reduce_range(a, min(b, ea), 0);
-  if (ea < b) {
-    const int64_t ub = (b < p.n) ? (int64_t)p.win_run[w + 1] - (p.skeys[b] != p.skeys[b - 1] ? 1 : 0)
-                                 : (int64_t)(*p.num_unique) - 1;
-    const int64_t sb = p.seg[ub], eb = p.seg[ub + 1];
-    if (eb - sb > HOT_CH) reduce_range(sb, b, 1);
+// raw (still packed) gradient vector of VE elements: kept packed while in flight, unpacked when added
+template <typename GT, int VE>
+struct GradVec;
+template <>
+struct GradVec<float, 4> {
+  uint4 v;
+  __device__ __forceinline__ void load(const float* p) { v = ld_nc_v4(p); }
+  __device__ __forceinline__ void zero() { v = make_uint4(0, 0, 0, 0); }
+  __device__ __forceinline__ void pin() { keep(v); }
+  __device__ __forceinline__ void add_to(float* a) const { Vec16<float>::accum(a, v); }
+};
+template <>
+struct GradVec<float, 8> {
+  uint4 v0, v1;
+  __device__ __forceinline__ void load(const float* p) { v0 = ld_nc_v4(p); v1 = ld_nc_v4(p + 4); }
+  __device__ __forceinline__ void zero() { v0 = v1 = make_uint4(0, 0, 0, 0); }
+  __device__ __forceinline__ void pin() { keep(v0); keep(v1); }
+  __device__ __forceinline__ void add_to(float* a) const { Vec16<float>::accum(a, v0); Vec16<float>::accum(a + 4, v1); }
+};
+template <>
+struct GradVec<__nv_bfloat16, 8> {
+  uint4 v;
+  __device__ __forceinline__ void load(const __nv_bfloat16* p) { v = ld_nc_v4(p); }
+  __device__ __forceinline__ void zero() { v = make_uint4(0, 0, 0, 0); }
+  __device__ __forceinline__ void pin() { keep(v); }
+  __device__ __forceinline__ void add_to(float* a) const { Vec16<__nv_bfloat16>::accum(a, v); }
+};
+template <>
+struct GradVec<__nv_bfloat16, 4> {
+  uint2 v;
+  __device__ __forceinline__ void load(const __nv_bfloat16* p) { v = ld_nc_v2(p); }
+  __device__ __forceinline__ void zero() { v = make_uint2(0, 0); }
+  __device__ __forceinline__ void pin() { keep(v); }
+  __device__ __forceinline__ void add_to(float* a) const {
+    a[0] += bf16lo(v.x);
+    a[1] += bf16hi(v.x);
+    a[2] += bf16lo(v.y);
+    a[3] += bf16hi(v.y);
   }
-}
+};
 
-template <typename WT, typename GT, int G, int NV, int OPT>
-__global__ void __launch_bounds__(UPD_THREADS) emb_update_kernel(const UpdParams p) {
+// ---- 3a. window kernel: uniform work per group, independent of the duplicate structure ----
+// One group of G lanes owns a window of HOT_CH consecutive SORTED positions.  It stages the
+// window's keys / gradient-row offsets in shared memory (coalesced), then streams the gradient
+// rows in batches (BS rows in flight per lane, plus the weight rows of the runs that end in the
+// batch) and sums run by run, in position (= bag) order:
+//   * a run that lies entirely inside the window is finished here: ONE read-modify-write of its
+//     weight row (and Adagrad state row);
+//   * a run that crosses a window border leaves an fp32 partial row: slot 0 if it began at or
+//     before the window's first position, slot 1 if it began inside;  window_join_kernel adds the
+//     partials of such a run in window order and updates the row.
+// Every weight row is written by exactly one group: deterministic, no atomics.
+template <int OPT, typename WT>
+__device__ __forceinline__ void apply_row(char* wp, float* sp, const float* acc, const float* w_in, float lr,
+                                          float eps) {
   constexpr int VE = Vec16<WT>::VE;
-  constexpr int NG = UPD_THREADS / G;
-  constexpr int R = 4;  // unique rows in flight per group
-  const int gid = threadIdx.x / G, lane = threadIdx.x % G;
-  const int64_t nU = *p.num_unique;
-  const int64_t u0 = (int64_t)blockIdx.x * (NG * R);
-  if (u0 >= nU) return;
-  const float lr = p.d_lr ? *p.d_lr : p.lr;
-
-  uint32_t s[R], e[R], t[R];
-  char* wrow[R];
-  float* srow[R];
-  bool valid[R];
-  bool single = true;
+  float w[VE];
 #pragma unroll
-  for (int q = 0; q < R; ++q) {
-    const int64_t u = u0 + q * NG + gid;
-    valid[q] = u < nU;
-    s[q] = valid[q] ? p.seg[u] : 0;
-    e[q] = valid[q] ? p.seg[u + 1] : 0;
-    const uint32_t key = valid[q] ? p.unique[u] : 0;
-    const uint32_t g0 = valid[q] ? p.svals[s[q]] : 0;
-    t[q] = g0 / p.B;
-    const int64_t row = valid[q] ? (int64_t)key - p.row_base[t[q]] : 0;
-    wrow[q] = valid[q] ? static_cast<char*>(p.weights[t[q]]) + (size_t)row * p.D * sizeof(WT) : nullptr;
-    if (OPT == B200_OPT_ADAGRAD) srow[q] = valid[q] ? p.state[t[q]] + (size_t)row * p.D : nullptr;
-    single = single && (e[q] - s[q] <= 1);
-  }
-
-  float acc[R][NV][VE];
+  for (int x = 0; x < VE; ++x) w[x] = w_in[x];
+  if (OPT == B200_OPT_ADAGRAD) {
 #pragma unroll
-  for (int q = 0; q < R; ++q)
+    for (int h = 0; h < VE / 4; ++h) {
+      float st[4];
+      Vec16<float>::unpack(st, ld_v4(sp + 4 * h));
 #pragma unroll
-    for (int k = 0; k < NV; ++k)
-#pragma unroll
-      for (int x = 0; x < VE; ++x) acc[q][k][x] = 0.f;
-
-  auto grad_row = [&](uint32_t g, uint32_t tt) -> const GT* {
-    const uint32_t b = g - tt * p.B;
-    return static_cast<const GT*>(p.grad) + (int64_t)tt * p.grad_stride_table + (int64_t)b * p.grad_stride_bag;
-  };
-
-  if (single) {
-    // every run has one element (the common one-hot, mostly-unique case): all loads first
-#pragma unroll
-    for (int q = 0; q < R; ++q) {
-      if (valid[q]) {
-        const GT* gp = grad_row(p.svals[s[q]], t[q]);
-#pragma unroll
-        for (int k = 0; k < NV; ++k) {
-          const int vi = lane + k * G;
-          if (vi < p.V) load_grad<GT, VE>(gp + vi * VE, acc[q][k]);
-        }
+      for (int x = 0; x < 4; ++x) {
+        const float g = acc[4 * h + x];
+        st[x] += g * g;
+        w[4 * h + x] -= lr * g / (sqrtf(st[x]) + eps);
       }
+      store_vec<float, 4, false>(sp + 4 * h, st);
     }
   } else {
-    // hot rows first: add their per-window partial sums (hot_window_kernel) in window order
-    uint32_t j[R], je[R];
 #pragma unroll
-    for (int q = 0; q < R; ++q) {
-      j[q] = s[q];
-      je[q] = valid[q] ? e[q] : s[q];
-      if (valid[q] && e[q] - s[q] > (uint32_t)HOT_CH) {
-        je[q] = s[q];  // nothing left for the walk below
-        const uint32_t w0 = s[q] / HOT_CH, w1 = (e[q] - 1) / HOT_CH;
-        for (uint32_t w = w0; w <= w1; ++w) {
-          const int slot = (s[q] > w * HOT_CH) ? 1 : 0;
-          const float* src = p.partial + (size_t)(2 * w + slot) * p.D;
+    for (int x = 0; x < VE; ++x) w[x] -= lr * acc[x];
+  }
+  store_vec<WT, VE, false>(reinterpret_cast<WT*>(wp), w);
+}
+
+constexpr int UPD_TMAX = 256;  // tables whose base pointers / row bases are cached in shared memory
+
+// RED (fp32 SGD only): the row update W += -lr * sum is linear, so it is issued as ONE vector
+// reduction per 16 bytes (REDG.ADD.F32x4, executed by the L2 atomic unit) instead of a load +
+// store: no weight row ever travels to the SM, no registers wait for it.  Each row still gets
+// exactly one update per step from exactly one group, so the result stays deterministic.
+template <typename WT, typename GT, int G, int NV, int OPT, bool RED>
+__global__ void __launch_bounds__(UPD_THREADS) window_update_kernel(const UpdParams p) {
+  static_assert(!RED || (OPT == B200_OPT_SGD && sizeof(WT) == 4), "RED path is fp32 SGD only");
+  constexpr int VE = Vec16<WT>::VE;
+  constexpr int NG = UPD_THREADS / G;
+  constexpr int C = HOT_CH;
+  constexpr int BS0 = (NV * VE >= 32) ? 1 : (NV * VE >= 16 ? 2 : (NV * VE >= 8 ? 4 : 8));
+  constexpr int BS = RED ? 2 * BS0 : BS0;  // gradient rows in flight per lane
+  __shared__ int64_t s_base[UPD_TMAX];
+  __shared__ char* s_wptr[UPD_TMAX];
+  __shared__ float* s_sptr[UPD_TMAX];
+  __shared__ uint32_t s_key[NG][C + 2];  // [0] = key before the window, [C+1] = key after it
+  __shared__ int64_t s_goff[NG][C];      // element offset of the gradient row of each position
+  __shared__ uint16_t s_tab[NG][C];
+  const int gid = threadIdx.x / G, lane = threadIdx.x % G;
+  const bool cached = p.T <= UPD_TMAX;
+  if (cached) {
+    for (int i = threadIdx.x; i < p.T; i += UPD_THREADS) {
+      s_base[i] = p.row_base[i];
+      s_wptr[i] = static_cast<char*>(p.weights[i]);
+      s_sptr[i] = (OPT == B200_OPT_ADAGRAD) ? p.state[i] : nullptr;
+    }
+  }
+  const int64_t w = (int64_t)blockIdx.x * NG + gid;
+  const int64_t a = w * C;
+  const int cnt = a < p.n ? (int)min((int64_t)C, p.n - a) : 0;
+  for (int i = lane; i < cnt; i += G) {
+    const uint32_t g = p.svals[a + i];
+    const uint32_t tt = g / p.B;
+    s_key[gid][i + 1] = p.skeys[a + i];
+    s_tab[gid][i] = (uint16_t)tt;
+    s_goff[gid][i] = (int64_t)tt * p.grad_stride_table + (int64_t)(g - tt * p.B) * p.grad_stride_bag;
+  }
+  if (lane == 0 && cnt > 0) {
+    // sentinels: a key that differs from its neighbour when there is no neighbour
+    s_key[gid][0] = a > 0 ? p.skeys[a - 1] : ~p.skeys[a];
+    s_key[gid][cnt + 1] = a + cnt < p.n ? p.skeys[a + cnt] : ~p.skeys[a + cnt - 1];
+  }
+  const float lr = p.d_lr ? *p.d_lr : p.lr;
+  __syncthreads();
+  if (cnt == 0) return;
+
+  const GT* gbase = static_cast<const GT*>(p.grad) + lane * VE;
+  float acc[NV][VE];
+#pragma unroll
+  for (int k = 0; k < NV; ++k)
+#pragma unroll
+    for (int x = 0; x < VE; ++x) acc[k][x] = 0.f;
+  // is the run being summed a continuation from the previous window, and where is its head?
+  bool cont = s_key[gid][0] == s_key[gid][1];
+  int cur_head = cont ? -1 : 0;
+
+  for (int c0 = 0; c0 < cnt; c0 += BS) {
+    GradVec<GT, VE> g[BS][NV];
+    uint4 wv[RED ? 1 : BS][NV];
+    char* wp[RED ? 1 : BS];
+    float* sp[RED ? 1 : BS];
+    bool ends[BS], closed[BS];
+#pragma unroll
+    for (int c = 0; c < BS; ++c) {
+      const int pos = c0 + c;
+      const bool ok = pos < cnt;
+      const uint32_t key = ok ? s_key[gid][pos + 1] : 0u;
+      if (ok && pos > 0 && s_key[gid][pos] != key) {  // a run begins here, inside the window
+        cont = false;
+        cur_head = pos;
+      }
+      ends[c] = ok && s_key[gid][pos + 2] != key;
+      closed[c] = ends[c] && !cont;  // began and ends inside this window: finished here
+      const GT* gp = gbase + (ok ? s_goff[gid][pos] : 0);
+#pragma unroll
+      for (int k = 0; k < NV; ++k) {
+        if (ok && lane + k * G < p.V) {
+          g[c][k].load(gp + k * G * VE);
+        } else {
+          g[c][k].zero();
+        }
+      }
+      if constexpr (!RED) {
+        wp[c] = nullptr;
+        sp[c] = nullptr;
+#pragma unroll
+        for (int k = 0; k < NV; ++k) wv[c][k] = make_uint4(0, 0, 0, 0);
+        if (closed[c]) {
+          const int tt = s_tab[gid][pos];
+          const int64_t row = (int64_t)key - (cached ? s_base[tt] : p.row_base[tt]);
+          wp[c] = (cached ? s_wptr[tt] : static_cast<char*>(p.weights[tt])) + ((size_t)row * p.D + lane * VE) * sizeof(WT);
+          if (OPT == B200_OPT_ADAGRAD) sp[c] = (cached ? s_sptr[tt] : p.state[tt]) + (size_t)row * p.D + lane * VE;
+#pragma unroll
+          for (int k = 0; k < NV; ++k)
+            if (lane + k * G < p.V) wv[c][k] = ld_v4(wp[c] + (size_t)k * G * 16);
+        }
+      }
+    }
+    // every load of the batch is issued by now; pin them so they stay in flight together
+#pragma unroll
+    for (int c = 0; c < BS; ++c)
+#pragma unroll
+      for (int k = 0; k < NV; ++k) {
+        g[c][k].pin();
+        if constexpr (!RED) keep(wv[c][k]);
+      }
+#pragma unroll
+    for (int c = 0; c < BS; ++c) {
+#pragma unroll
+      for (int k = 0; k < NV; ++k) g[c][k].add_to(acc[k]);
+      if (ends[c]) {
+        if (closed[c]) {
 #pragma unroll
           for (int k = 0; k < NV; ++k) {
-            const int vi = lane + k * G;
-            if (vi < p.V) {
-#pragma unroll
-              for (int h = 0; h < VE / 4; ++h) {
-                float f[4];
-                Vec16<float>::unpack(f, ld_v4(src + vi * VE + 4 * h));
-#pragma unroll
-                for (int x = 0; x < 4; ++x) acc[q][k][4 * h + x] += f[x];
+            if (lane + k * G < p.V) {
+              if constexpr (RED) {
+                const int pos = c0 + c;
+                const int tt = s_tab[gid][pos];
+                const int64_t row = (int64_t)s_key[gid][pos + 1] - (cached ? s_base[tt] : p.row_base[tt]);
+                float* dstw = reinterpret_cast<float*>(cached ? s_wptr[tt] : static_cast<char*>(p.weights[tt])) +
+                              (size_t)row * p.D + lane * VE + k * G * VE;
+                red_add_v4_f32(dstw, -lr * acc[k][0], -lr * acc[k][1], -lr * acc[k][2], -lr * acc[k][3]);
+              } else {
+                float wf[VE];
+                Vec16<WT>::unpack(wf, wv[c][k]);
+                apply_row<OPT, WT>(wp[c] + (size_t)k * G * 16, sp[c] ? sp[c] + k * G * VE : nullptr, acc[k], wf, lr,
+                                   p.eps);
               }
             }
           }
+        } else {  // continuation from the previous window that ends here: slot 0
+          float* dst = p.partial + (size_t)(2 * w) * p.D + lane * VE;
+#pragma unroll
+          for (int k = 0; k < NV; ++k)
+            if (lane + k * G < p.V) {
+#pragma unroll
+              for (int h = 0; h < VE / 4; ++h) store_vec<float, 4, false>(dst + k * G * VE + 4 * h, acc[k] + 4 * h);
+            }
         }
-      }
-    }
-    // the four runs advance together: R independent (bag id -> gradient row) chains in flight,
-    // each run still summed in sorted (= bag) order
-    while (true) {
-      bool act[R];
-      bool any = false;
-#pragma unroll
-      for (int q = 0; q < R; ++q) {
-        act[q] = j[q] < je[q];
-        any = any || act[q];
-      }
-      if (!any) break;
-      uint32_t g[R];
-#pragma unroll
-      for (int q = 0; q < R; ++q) g[q] = act[q] ? p.svals[j[q]] : 0u;
-      float tmp[R][NV][VE];
-#pragma unroll
-      for (int q = 0; q < R; ++q) {
-        const GT* gp = grad_row(g[q], t[q]);
-#pragma unroll
-        for (int k = 0; k < NV; ++k) {
-          const int vi = lane + k * G;
-          if (act[q] && vi < p.V) {
-            load_grad<GT, VE>(gp + vi * VE, tmp[q][k]);
-          } else {
-#pragma unroll
-            for (int x = 0; x < VE; ++x) tmp[q][k][x] = 0.f;
-          }
-        }
-      }
-#pragma unroll
-      for (int q = 0; q < R; ++q) {
 #pragma unroll
         for (int k = 0; k < NV; ++k)
 #pragma unroll
-          for (int x = 0; x < VE; ++x) acc[q][k][x] += tmp[q][k][x];
-        j[q] += act[q] ? 1u : 0u;
+          for (int x = 0; x < VE; ++x) acc[k][x] = 0.f;
       }
     }
   }
+  // a run still open at the right border: slot 0 if it began at or before the first position
+  if (s_key[gid][cnt] == s_key[gid][cnt + 1]) {
+    float* dst = p.partial + (size_t)(2 * w + (cur_head <= 0 ? 0 : 1)) * p.D + lane * VE;
+#pragma unroll
+    for (int k = 0; k < NV; ++k)
+      if (lane + k * G < p.V) {
+#pragma unroll
+        for (int h = 0; h < VE / 4; ++h) store_vec<float, 4, false>(dst + k * G * VE + 4 * h, acc[k] + 4 * h);
+      }
+  }
+}
 
-  // one read-modify-write per unique row
+// ---- 3b. join kernel: one group per window border; the border that a run crosses FIRST owns it
+template <typename WT, int G, int NV, int OPT, bool RED>
+__global__ void __launch_bounds__(UPD_THREADS) window_join_kernel(const UpdParams p) {
+  constexpr int VE = Vec16<WT>::VE;
+  constexpr int NG = UPD_THREADS / G;
+  constexpr int C = HOT_CH;
+  constexpr int PB = (NV * VE >= 32) ? 2 : (NV * VE >= 16 ? 4 : (NV * VE >= 8 ? 8 : 16));  // partial rows in flight
+  const int gid = threadIdx.x / G, lane = threadIdx.x % G;
+  const int64_t k = (int64_t)blockIdx.x * NG + gid + 1;  // border between positions kC-1 and kC
+  if (k * C >= p.n) return;
+  if (p.skeys[k * C - 1] != p.skeys[k * C]) return;  // nothing crosses this border
+  const int64_t u = p.win_run[k];
+  const int64_t s = p.seg[u], e = p.seg[u + 1];
+  if (s / C + 1 != k) return;  // an earlier border owns this run
+  const float lr = p.d_lr ? *p.d_lr : p.lr;
+  const uint32_t tt = p.first_val[u] / p.B;
+  const int64_t row = (int64_t)p.unique[u] - p.row_base[tt];
+  char* wp = static_cast<char*>(p.weights[tt]) + ((size_t)row * p.D + lane * VE) * sizeof(WT);
+  float* sp = (OPT == B200_OPT_ADAGRAD) ? p.state[tt] + (size_t)row * p.D + lane * VE : nullptr;
+  uint4 wv[NV];
+  if constexpr (!RED) {
 #pragma unroll
-  for (int q = 0; q < R; ++q) {
-    if (!valid[q]) continue;
-#pragma unroll
-    for (int k = 0; k < NV; ++k) {
-      const int vi = lane + k * G;
-      if (vi >= p.V) continue;
-      float w[VE];
-      char* wp = wrow[q] + (size_t)vi * 16;
-      Vec16<WT>::unpack(w, ld_v4(wp));
-      if (OPT == B200_OPT_ADAGRAD) {
-        float* sp = srow[q] + vi * VE;
-#pragma unroll
-        for (int h = 0; h < VE / 4; ++h) {
-          float st[4];
-          Vec16<float>::unpack(st, ld_v4(sp + 4 * h));
-#pragma unroll
-          for (int x = 0; x < 4; ++x) {
-            const float g = acc[q][k][4 * h + x];
-            st[x] += g * g;
-            w[4 * h + x] -= lr * g / (sqrtf(st[x]) + p.eps);
-          }
-          store_vec<float, 4, false>(sp + 4 * h, st);
-        }
-      } else {
-#pragma unroll
-        for (int x = 0; x < VE; ++x) w[x] -= lr * acc[q][k][x];
-      }
-      store_vec<WT, VE, false>(reinterpret_cast<WT*>(wp), w);
-    }
+    for (int kk = 0; kk < NV; ++kk)
+      if (lane + kk * G < p.V) wv[kk] = ld_v4(wp + (size_t)kk * G * 16);
   }
+  float acc[NV][VE];
+#pragma unroll
+  for (int kk = 0; kk < NV; ++kk)
+#pragma unroll
+    for (int x = 0; x < VE; ++x) acc[kk][x] = 0.f;
+  const int64_t w0 = s / C, w1 = (e - 1) / C;
+  for (int64_t wb = w0; wb <= w1; wb += PB) {
+    uint4 f[PB][NV][VE / 4];
+#pragma unroll
+    for (int c = 0; c < PB; ++c) {
+      const int64_t ww = wb + c;
+      const bool ok = ww <= w1;
+      const float* src = p.partial + (size_t)(2 * ww + ((ok && s > ww * C) ? 1 : 0)) * p.D + lane * VE;
+#pragma unroll
+      for (int kk = 0; kk < NV; ++kk)
+#pragma unroll
+        for (int h = 0; h < VE / 4; ++h)
+          f[c][kk][h] = (ok && lane + kk * G < p.V) ? ld_v4(src + kk * G * VE + 4 * h) : make_uint4(0, 0, 0, 0);
+    }
+#pragma unroll
+    for (int c = 0; c < PB; ++c)
+#pragma unroll
+      for (int kk = 0; kk < NV; ++kk)
+#pragma unroll
+        for (int h = 0; h < VE / 4; ++h) keep(f[c][kk][h]);
+#pragma unroll
+    for (int c = 0; c < PB; ++c)
+#pragma unroll
+      for (int kk = 0; kk < NV; ++kk)
+#pragma unroll
+        for (int h = 0; h < VE / 4; ++h) Vec16<float>::accum(acc[kk] + 4 * h, f[c][kk][h]);
+  }
+#pragma unroll
+  for (int kk = 0; kk < NV; ++kk)
+    if (lane + kk * G < p.V) {
+      if constexpr (RED) {
+        red_add_v4_f32(reinterpret_cast<float*>(wp + (size_t)kk * G * 16), -lr * acc[kk][0], -lr * acc[kk][1],
+                       -lr * acc[kk][2], -lr * acc[kk][3]);
+      } else {
+        float wf[VE];
+        Vec16<WT>::unpack(wf, wv[kk]);
+        apply_row<OPT, WT>(wp + (size_t)kk * G * 16, sp ? sp + kk * G * VE : nullptr, acc[kk], wf, lr, p.eps);
+      }
+    }
 }
 
 // scalar fallback (rows not a whole number of 16-byte vectors): thread per (unique row, d)
@@ -420,21 +498,34 @@ static int launch_update(const UpdParams& p, int64_t n, bool vec_ok, cudaStream_
     return B200_OK;
   }
   const int V = p.V;
-  constexpr int VE = Vec16<WT>::VE;
   const int64_t nwin = ceil_div(n, HOT_CH);
-#define B200_UPD_CASE(G, NV)                                                                       \
-  hot_window_kernel<GT, VE, G, NV><<<(unsigned)ceil_div(nwin, UPD_THREADS / G), UPD_THREADS, 0, st>>>(p); \
-  emb_update_kernel<WT, GT, G, NV, OPT>                                                            \
-      <<<(unsigned)ceil_div(n, (UPD_THREADS / G) * 4), UPD_THREADS, 0, st>>>(p)
-  if (V <= 1) { B200_UPD_CASE(1, 1); }
-  else if (V <= 2) { B200_UPD_CASE(2, 1); }
-  else if (V <= 4) { B200_UPD_CASE(4, 1); }
+  constexpr bool CAN_RED = OPT == B200_OPT_SGD && sizeof(WT) == 4;
+  static const bool use_red = []() {
+    const char* e = getenv("B200_SGD_RED");
+    return e == nullptr || e[0] != '0';
+  }();
+#define B200_UPD_LAUNCH(G, NV, RED)                                                                                  \
+  window_update_kernel<WT, GT, G, NV, OPT, RED><<<(unsigned)ceil_div(nwin, UPD_THREADS / G), UPD_THREADS, 0, st>>>(p); \
+  if (nwin > 1)                                                                                                      \
+  window_join_kernel<WT, G, NV, OPT, RED><<<(unsigned)ceil_div(nwin - 1, UPD_THREADS / G), UPD_THREADS, 0, st>>>(p)
+#define B200_UPD_CASE(G, NV)                 \
+  if constexpr (CAN_RED) {                   \
+    if (use_red) {                           \
+      B200_UPD_LAUNCH(G, NV, true);          \
+    } else {                                 \
+      B200_UPD_LAUNCH(G, NV, false);         \
+    }                                        \
+  } else {                                   \
+    B200_UPD_LAUNCH(G, NV, false);           \
+  }
+  if (V <= 4) { B200_UPD_CASE(4, 1); }
   else if (V <= 8) { B200_UPD_CASE(8, 1); }
   else if (V <= 16) { B200_UPD_CASE(16, 1); }
   else if (V <= 32) { B200_UPD_CASE(32, 1); }
   else if (V <= 64) { B200_UPD_CASE(32, 2); }
   else { B200_UPD_CASE(32, 4); }
 #undef B200_UPD_CASE
+#undef B200_UPD_LAUNCH
   B200_CHECK_LAUNCH("emb_update");
   return B200_OK;
 }
@@ -475,7 +566,7 @@ extern "C" int b200_emb_bwd_prepare(const int64_t* d_rows, const int64_t* d_row_
   B200_CHECK_LAUNCH("build_keys");
   rc = sort_pairs(L.keys, L.vals, nnz, (uint64_t)total_rows, L.skeys, L.svals, L.sort_ws, st);
   if (rc) return rc;
-  return dedup_runs(L.skeys, nnz, L.unique, L.seg, L.num_unique, L.sort_ws, st, L.win_run);
+  return dedup_runs(L.skeys, nnz, L.unique, L.seg, L.num_unique, L.sort_ws, st, L.win_run, L.svals, L.first_val);
 }
 
 extern "C" int b200_emb_bwd_apply(void* const* d_weights, float* const* d_state,
@@ -514,6 +605,8 @@ extern "C" int b200_emb_bwd_apply(void* const* d_weights, float* const* d_state,
   p.D = (int)D;
   p.skeys = L.skeys;
   p.win_run = L.win_run;
+  p.first_val = L.first_val;
+  p.T = (int)T;
   p.partial = L.partial;
   p.n = nnz;
   const int wsz = dtype_size(w_dtype), gsz = dtype_size(grad_dtype);

@@ -166,7 +166,8 @@ __global__ void __launch_bounds__(DEDUP_THREADS) head_count_kernel(const uint32_
 __global__ void __launch_bounds__(DEDUP_THREADS)
     compact_kernel(const uint32_t* __restrict__ skeys, int64_t n, const uint32_t* __restrict__ blk_offsets,
                    const int32_t* __restrict__ num_unique, uint32_t* __restrict__ unique,
-                   uint32_t* __restrict__ seg, uint32_t* __restrict__ win_run) {
+                   uint32_t* __restrict__ seg, uint32_t* __restrict__ win_run,
+                   const uint32_t* __restrict__ svals, uint32_t* __restrict__ first_val) {
   __shared__ uint32_t wsum[DEDUP_THREADS / 32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int64_t base = (int64_t)blockIdx.x * DEDUP_CHUNK;
@@ -190,6 +191,7 @@ __global__ void __launch_bounds__(DEDUP_THREADS)
       const uint32_t pos = run + before + __popc(b & ((1u << lane) - 1u));
       unique[pos] = skeys[j];
       seg[pos] = (uint32_t)j;
+      if (first_val != nullptr) first_val[pos] = svals[j];  // payload of the run's first element
     }
     if (win_run != nullptr && j < n && (tid % HOT_CH) == 0)  // run containing this window start
       win_run[j / HOT_CH] = run + before + __popc(b & (0xffffffffu >> (31 - lane))) - 1u;
@@ -243,7 +245,7 @@ int sort_pairs(const uint32_t* keys, const uint32_t* vals, int64_t n, uint64_t k
 }
 
 int dedup_runs(const uint32_t* skeys, int64_t n, uint32_t* unique, uint32_t* seg, int32_t* num_unique,
-               void* ws, cudaStream_t st, uint32_t* win_run) {
+               void* ws, cudaStream_t st, uint32_t* win_run, const uint32_t* svals, uint32_t* first_val) {
   char* w = static_cast<char*>(ws);
   const size_t stride = align_up((size_t)n * 4, 256);
   const int64_t nblk = ceil_div(n, SORT_CHUNK);
@@ -251,7 +253,7 @@ int dedup_runs(const uint32_t* skeys, int64_t n, uint32_t* unique, uint32_t* seg
   const int nblk2 = (int)ceil_div(n, DEDUP_CHUNK);
   head_count_kernel<<<nblk2, DEDUP_THREADS, 0, st>>>(skeys, n, blk);
   scan_exclusive_kernel<<<1, 1024, 0, st>>>(blk, nblk2, num_unique);
-  compact_kernel<<<nblk2, DEDUP_THREADS, 0, st>>>(skeys, n, blk, num_unique, unique, seg, win_run);
+  compact_kernel<<<nblk2, DEDUP_THREADS, 0, st>>>(skeys, n, blk, num_unique, unique, seg, win_run, svals, first_val);
   B200_CHECK_LAUNCH("dedup");
   return B200_OK;
 }

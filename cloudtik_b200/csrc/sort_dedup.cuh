@@ -10,8 +10,8 @@ constexpr int SORT_CHUNK = SORT_THREADS * SORT_ITEMS;  // keys per block
 constexpr int DEDUP_THREADS = 256;
 constexpr int DEDUP_ITEMS = 8;
 constexpr int DEDUP_CHUNK = DEDUP_THREADS * DEDUP_ITEMS;
-// window size of the hot-run pre-reduction in emb_bwd.cu (DEDUP_THREADS must be a multiple of it)
-constexpr int HOT_CH = 128;
+// window of sorted positions one group of emb_bwd.cu's update kernel owns (divides DEDUP_THREADS)
+constexpr int HOT_CH = 32;
 
 // workspace: [keysA | keysB | valsA | valsB | digit histograms | dedup block counts]
 size_t sort_ws_bytes(int64_t n);
@@ -25,8 +25,10 @@ int sort_pairs(const uint32_t* keys, const uint32_t* vals, int64_t n, uint64_t k
 // *num_unique = U.  n > 0.  Uses the tail of the same workspace.
 // win_run (optional, may be null): win_run[w] = index of the run that contains sorted position
 // w * HOT_CH, for every window start below n.
+// svals / first_val (optional): first_val[u] = svals[seg[u]], the payload of run u's first element.
 int dedup_runs(const uint32_t* skeys, int64_t n, uint32_t* unique, uint32_t* seg, int32_t* num_unique,
-               void* ws, cudaStream_t st, uint32_t* win_run = nullptr);
+               void* ws, cudaStream_t st, uint32_t* win_run = nullptr, const uint32_t* svals = nullptr,
+               uint32_t* first_val = nullptr);
 
 int empty_result(uint32_t* seg, int32_t* num_unique, cudaStream_t st);
 

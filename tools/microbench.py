@@ -51,6 +51,10 @@ def main():
     ap.add_argument("--cases", default="262144:1,8192:32,2048:128,32768:1")
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--sets", type=int, default=4)
+    ap.add_argument("--c3", action="store_true", help="use the config-3 (Criteo-Terabyte) table sizes; fp32 tables")
+    ap.add_argument("--c3-cap", type=int, default=0, help="cap config-3 table rows (0 = full, 96 GB)")
+    ap.add_argument("--act", default="", help="activation / gradient dtype (default: same as --dtype)")
+    ap.add_argument("--no-interact", action="store_true")
     a = ap.parse_args()
     dt = torch.float32 if a.dtype == "fp32" else torch.bfloat16
     es = 4 if a.dtype == "fp32" else 2
@@ -58,8 +62,20 @@ def main():
     F = T + 1
     dev = "cuda"
     peak, pk = peak_hbm()
-    tw = [(torch.rand(n, D, device=dev) - 0.5).to(dt) for _ in range(T)]
+    C3 = [39884406, 39043, 17289, 7420, 20263, 3, 7120, 1543, 63, 38532951, 2953546, 403346, 10, 2208, 11938, 155, 4,
+          976, 14, 39979771, 25641295, 39664984, 585935, 12972, 108, 36]
+    rows = [min(r, a.c3_cap) if a.c3_cap else r for r in C3] if a.c3 else [n] * T
+    T = len(rows)
+    F = T + 1
+    adt = dt if not a.act else (torch.float32 if a.act == "fp32" else torch.bfloat16)
+    ea = 4 if adt == torch.float32 else 2
+    tw = []
+    for r in rows:
+        w = torch.empty(r, D, dtype=dt, device=dev)
+        w.uniform_(-0.5, 0.5)
+        tw.append(w)
     ts = ops.TableSet(tw)
+    rows_t = torch.tensor(rows, device=dev, dtype=torch.float64)
     g = torch.Generator(device=dev)
     g.manual_seed(1234)
     for case in a.cases.split(","):
@@ -67,17 +83,18 @@ def main():
         nnz_t = B * P
         sets = []
         for _ in range(a.sets):
-            idx = torch.randint(0, n, (T * nnz_t,), device=dev, generator=g, dtype=torch.int64)
+            u01 = torch.rand(T, nnz_t, device=dev, generator=g, dtype=torch.float64)
+            idx = torch.floor(u01 * rows_t[:, None]).to(torch.int64).reshape(-1)
             U = sum(int(torch.unique(idx[t * nnz_t:(t + 1) * nnz_t]).numel()) for t in range(T))
             sets.append((idx, U))
         off = torch.arange(0, T * B + 1, device=dev, dtype=torch.int64) * P
-        buf = torch.empty(B, F, D, dtype=dt, device=dev)
-        grad = torch.randn(B, F, D, device=dev).to(dt)
+        buf = torch.empty(B, F, D, dtype=adt, device=dev)
+        grad = torch.randn(B, F, D, device=dev).to(adt)
         ws = torch.empty(ops.emb_bwd_workspace_bytes(T * nnz_t, D), dtype=torch.uint8, device=dev)
         Uavg = sum(s[1] for s in sets) / len(sets)
         common = T * nnz_t * 8 + (T * B + 1) * 8
-        fwd_bytes = Uavg * D * es + common + T * B * D * es
-        bwd_bytes = T * B * D * es + common + 2 * Uavg * D * es
+        fwd_bytes = Uavg * D * es + common + T * B * D * ea
+        bwd_bytes = T * B * D * ea + common + 2 * Uavg * D * es
 
         def f_fwd(i):
             ops.emb_fwd(ts, sets[i % len(sets)][0], off, B, buf[:, 1:], D, F * D)
@@ -85,7 +102,14 @@ def main():
         def f_bwd(i):
             ops.emb_bwd_update(ts, sets[i % len(sets)][0], off, B, grad[:, 1:], D, F * D, lr=1e-6, ws=ws)
 
-        for name, fn, nbytes in (("emb_fwd", f_fwd, fwd_bytes), ("emb_bwd_sgd", f_bwd, bwd_bytes)):
+        def f_prep(i):
+            ops.emb_bwd_prepare(ts, sets[i % len(sets)][0], off, B, ws)
+
+        def f_apply(i):  # re-applies the last prepared index set (tiny lr keeps the weights sane)
+            ops.emb_bwd_apply(ts, T * nnz_t, B, grad[:, 1:], D, F * D, 1e-6, ws)
+
+        for name, fn, nbytes in (("emb_fwd", f_fwd, fwd_bytes), ("emb_bwd_sgd", f_bwd, bwd_bytes),
+                                 ("emb_bwd_prepare", f_prep, common), ("emb_bwd_apply", f_apply, bwd_bytes)):
             med, best = time_ms(fn, a.iters)
             gbs = nbytes / med / 1e6
             print(json.dumps({"kernel": name, "B": B, "P": P, "T": T, "D": D, "dtype": a.dtype, "ms": round(med, 4),
@@ -94,7 +118,7 @@ def main():
                               "unique_rows": int(Uavg)}), flush=True)
         del buf, grad, ws, sets
     # interaction at the training shape
-    for B in (32768,):
+    for B in (() if a.no_interact else (32768,)):
         Tt = torch.randn(B, F, D, device=dev).to(dt)
         R = torch.empty(B, D + F * (F - 1) // 2, dtype=dt, device=dev)
         dR = torch.randn_like(R)
