@@ -76,16 +76,68 @@ __global__ void __launch_bounds__(1024) scan_exclusive_kernel(uint32_t* __restri
   }
 }
 
+// ------------------------------------------------------------------ per-digit row scan
+// grid = 256 blocks: block d turns row d of the digit-major table counts[256][nblk] into exclusive
+// prefixes (in place) and writes the row total; the scatter kernel scans the 256 totals itself.
+__global__ void __launch_bounds__(256) radix_rowscan_kernel(uint32_t* __restrict__ counts, int nblk,
+                                                            uint32_t* __restrict__ totals) {
+  __shared__ uint32_t wsum[8];
+  __shared__ uint32_t carry;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  uint32_t* row = counts + (int64_t)blockIdx.x * nblk;
+  if (tid == 0) carry = 0;
+  __syncthreads();
+  for (int base = 0; base < nblk; base += 256) {
+    const int i = base + tid;
+    const uint32_t v = i < nblk ? row[i] : 0u;
+    uint32_t incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t u = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += u;
+    }
+    if (lane == 31) wsum[warp] = incl;
+    __syncthreads();
+    uint32_t before = carry;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) before += (w < warp) ? wsum[w] : 0u;
+    if (i < nblk) row[i] = before + incl - v;
+    __syncthreads();
+    if (tid == 255) carry = before + incl;
+    __syncthreads();
+  }
+  if (tid == 0) totals[blockIdx.x] = carry;
+}
+
 // ------------------------------------------------------------------ stable scatter
 __global__ void __launch_bounds__(SORT_THREADS)
     radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                          uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int64_t n,
-                         int shift, const uint32_t* __restrict__ counts, int nblk) {
+                         int shift, const uint32_t* __restrict__ counts, int nblk,
+                         const uint32_t* __restrict__ totals) {
   constexpr int NW = SORT_THREADS / 32;
   constexpr int WCHUNK = SORT_CHUNK / NW;  // keys per warp, contiguous
   __shared__ uint32_t whist[NW][256];
+  __shared__ uint32_t dsum[NW];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   for (int i = tid; i < NW * 256; i += SORT_THREADS) (&whist[0][0])[i] = 0;
+  // global start of digit `tid` = exclusive scan of the 256 digit totals (every block redoes it)
+  uint32_t dbase;
+  {
+    const uint32_t v = totals[tid];
+    uint32_t incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t u = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += u;
+    }
+    if (lane == 31) dsum[warp] = incl;
+    __syncthreads();
+    uint32_t before = 0;
+#pragma unroll
+    for (int w = 0; w < NW; ++w) before += (w < warp) ? dsum[w] : 0u;
+    dbase = before + incl - v;
+  }
   __syncthreads();
 
   const int64_t wbase = (int64_t)blockIdx.x * SORT_CHUNK + (int64_t)warp * WCHUNK;
@@ -116,7 +168,7 @@ __global__ void __launch_bounds__(SORT_THREADS)
   }
   __syncthreads();
   {  // thread `tid` owns digit `tid`: turn per-warp counts into global start positions
-    uint32_t run = counts[(int64_t)tid * nblk + blockIdx.x];
+    uint32_t run = dbase + counts[(int64_t)tid * nblk + blockIdx.x];
 #pragma unroll
     for (int w = 0; w < NW; ++w) {
       const uint32_t c = whist[w][tid];
@@ -213,6 +265,7 @@ size_t sort_ws_bytes(int64_t n) {
   b += 4 * align_up((size_t)n * 4, 256);              // keys A/B, vals A/B
   b += align_up((size_t)256 * nblk * 4, 256);         // digit-major histograms
   b += align_up((size_t)(nblk2 + 1) * 4, 256);        // dedup block counts
+  b += 1024;                                          // 256 digit totals
   return b + 256;
 }
 
@@ -225,6 +278,9 @@ int sort_pairs(const uint32_t* keys, const uint32_t* vals, int64_t n, uint64_t k
   uint32_t* vbuf[2] = {reinterpret_cast<uint32_t*>(w + 2 * stride),
                        reinterpret_cast<uint32_t*>(w + 3 * stride)};
   uint32_t* counts = reinterpret_cast<uint32_t*>(w + 4 * stride);
+  // 256 digit totals: own 1 KB slot behind the dedup block counts (see sort_ws_bytes)
+  uint32_t* totals = reinterpret_cast<uint32_t*>(w + 4 * stride + align_up((size_t)256 * nblk * 4, 256) +
+                                                 align_up((size_t)(ceil_div(n, DEDUP_CHUNK) + 1) * 4, 256));
   int bits = 1;
   while (bits < 32 && (key_bound - 1) >> bits) ++bits;
   const int passes = (bits + 7) / 8;
@@ -235,8 +291,8 @@ int sort_pairs(const uint32_t* keys, const uint32_t* vals, int64_t n, uint64_t k
     uint32_t* vdst = (pass == passes - 1) ? out_vals : vbuf[pass & 1];
     const int shift = pass * 8;
     radix_hist_kernel<<<nblk, SORT_THREADS, 0, st>>>(ksrc, n, shift, counts, nblk);
-    scan_exclusive_kernel<<<1, 1024, 0, st>>>(counts, (int64_t)256 * nblk, nullptr);
-    radix_scatter_kernel<<<nblk, SORT_THREADS, 0, st>>>(ksrc, vsrc, kdst, vdst, n, shift, counts, nblk);
+    radix_rowscan_kernel<<<256, 256, 0, st>>>(counts, nblk, totals);
+    radix_scatter_kernel<<<nblk, SORT_THREADS, 0, st>>>(ksrc, vsrc, kdst, vdst, n, shift, counts, nblk, totals);
     ksrc = kdst;
     vsrc = vdst;
   }
@@ -315,7 +371,7 @@ constexpr size_t cx_ceil_div(size_t a, size_t b) { return (a + b - 1) / b; }
 constexpr size_t NOALLOC_SCRATCH_BYTES =
     4 * cx_align_up((size_t)NOALLOC_MAX_KEYS * 4, 256) +
     cx_align_up((size_t)256 * cx_ceil_div(NOALLOC_MAX_KEYS, SORT_CHUNK) * 4, 256) +
-    cx_align_up((cx_ceil_div(NOALLOC_MAX_KEYS, DEDUP_CHUNK) + 1) * 4, 256) + 256;
+    cx_align_up((cx_ceil_div(NOALLOC_MAX_KEYS, DEDUP_CHUNK) + 1) * 4, 256) + 1024 + 256;
 
 static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_SCRATCH_BYTES];
 

@@ -1,0 +1,55 @@
+"""Whole-step CUDA graph: forward + loss + backward (incl. the fused sparse update) + dense SGD.
+
+The step launches ~110 small kernels (torch MLP pieces) around the hand-written ones; replaying
+them as one graph removes the launch gaps ("CUDA streams and graphs instead of a tracing
+compiler").  Every C-ABI call is stream-ordered, allocation-free and sync-free, so it is captured
+like any other kernel; the side-stream sort joins the capture through event fork/join.
+
+Static input buffers are owned by this object: ``step(X, Y, indices, offsets)`` copies the batch
+into them (device or pinned-host sources both work, non-blocking) and replays.
+"""
+from __future__ import annotations
+
+import torch
+
+
+class GraphedTrainStep:
+    def __init__(self, net, optimizer, example, warmup: int = 3):
+        """``example`` = (X, Y, indices, offsets) device tensors with the shapes of every later batch."""
+        self.net, self.opt = net, optimizer
+        self.static = [torch.empty_like(t) for t in example]
+        for d, s in zip(self.static, example):
+            d.copy_(s)
+        emb = net.emb_l
+        if emb.profile is not None:
+            raise RuntimeError("disable MergedEmbeddingBagWithSGD.profile before capturing a graph")
+        # warm up on a side stream (allocator pools, cuBLAS handles / workspaces, the embedding
+        # workspace, the tensor-map entry point) -- nothing may allocate lazily during capture
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            for _ in range(warmup):
+                self._eager()
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.loss = self._eager()
+        torch.cuda.synchronize()
+
+    def _eager(self):
+        X, Y, idx, off = self.static
+        Z = self.net(X, idx, off, None).float()
+        E = self.net.loss_fn(Z, Y)
+        self.opt.zero_grad(set_to_none=True)
+        E.backward()
+        self.opt.step()
+        return E.detach()
+
+    def step(self, X, Y, indices, offsets):
+        """Copy one batch into the static buffers and replay; returns the (device) loss tensor."""
+        for d, s in zip(self.static, (X, Y, indices, offsets)):
+            if d.data_ptr() != s.data_ptr():
+                d.copy_(s, non_blocking=True)
+        self.graph.replay()
+        return self.loss
