@@ -46,6 +46,40 @@ class GraphedTrainStep:
         self.opt.step()
         return E.detach()
 
+    # ---- host-fed operation: pinned-host batches are staged by a copy stream one step ahead ----
+    def prefetch(self, host_batch):
+        """Start the H2D copy of a pinned-host batch (X, Y, indices, offsets) into the staging
+        buffers on the copy stream; ``step_prefetched()`` consumes it."""
+        if not hasattr(self, "_copy_stream"):
+            self._copy_stream = torch.cuda.Stream()
+            self._stage = [[torch.empty_like(t) for t in self.static] for _ in range(2)]
+            self._stage_ready = [None, None]
+            self._stage_free = [None, None]
+            self._slot = 0
+        k = self._slot
+        with torch.cuda.stream(self._copy_stream):
+            if self._stage_free[k] is not None:
+                self._copy_stream.wait_event(self._stage_free[k])  # previous consumer of this slot is done
+            for d, s in zip(self._stage[k], host_batch):
+                d.copy_(s, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(self._copy_stream)
+        self._stage_ready[k] = ev
+        self._slot ^= 1
+        return k
+
+    def step_prefetched(self, k):
+        """Replay on the batch staged in slot ``k`` (device-to-device hop into the static buffers)."""
+        main = torch.cuda.current_stream()
+        main.wait_event(self._stage_ready[k])
+        for d, s in zip(self.static, self._stage[k]):
+            d.copy_(s, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record(main)
+        self._stage_free[k] = ev
+        self.graph.replay()
+        return self.loss
+
     def step(self, X, Y, indices, offsets):
         """Copy one batch into the static buffers and replay; returns the (device) loss tensor."""
         for d, s in zip(self.static, (X, Y, indices, offsets)):
