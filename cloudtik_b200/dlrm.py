@@ -18,6 +18,7 @@ import torch.nn as nn
 from . import ext_dist
 from .interaction import PaddedLinear, interaction, interaction_sharded
 from .merged_embedding import MergedEmbeddingBagWithSGD
+from .mlp import mlp_forward
 
 
 class DLRM_Net(nn.Module):
@@ -61,6 +62,7 @@ class DLRM_Net(nn.Module):
             raise NotImplementedError("weighted pooling is not on the reference's product path")
         self.loss_threshold = loss_threshold
         self.bf16 = bf16
+        self.fused_mlp = True
         ln_emb = np.asarray(ln_emb)
         if ext_dist.my_size > 1:
             n_emb = len(ln_emb)
@@ -87,6 +89,10 @@ class DLRM_Net(nn.Module):
         self.loss_fn = torch.nn.BCELoss(reduction="mean")
 
     def apply_mlp(self, x, layers):
+        # bf16: fused Linear+ReLU path over the same modules (cloudtik_b200/mlp.py); a DDP-wrapped MLP
+        # must go through its own forward (gradient hooks), fp32 stays plain torch
+        if self.bf16 and self.fused_mlp and isinstance(layers, nn.Sequential) and x.is_cuda:
+            return mlp_forward(layers, x)
         return layers(x)
 
     def _pad_dense(self, dense_x):

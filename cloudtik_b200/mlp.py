@@ -1,0 +1,87 @@
+"""bf16 fast path for the dense MLPs (they stay on torch / cuBLAS, north_star).
+
+The reference builds ``nn.Sequential(Linear, ReLU, ..., Linear, Sigmoid)`` (``P/dlrm_s_pytorch.py:172-211``)
+and runs it under autocast.  On a B200 the GEMMs are a minor part of that: per layer autocast also
+launches a ReLU kernel, two cast/copy kernels and -- the expensive one -- a column reduction of the
+bf16 ``[B, N]`` output gradient for the bias gradient (48 us for 32768 x 1024, as much as the GEMM).
+
+``mlp_forward`` walks the SAME modules (same parameters, same state_dict keys) but calls, per
+(Linear, ReLU) pair, one autograd function that
+  * fuses bias + ReLU into the GEMM epilogue (``torch._addmm_activation``),
+  * computes the bias gradient as a skinny tensor-core GEMM ``ones[8, B] @ dY`` instead of a reduction,
+  * casts each weight to bf16 once per step.
+Numerically it is the autocast path (bf16 operands, fp32 accumulation, bf16 activations / gradients).
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+
+from .interaction import PaddedLinear
+
+_ONES = {}
+
+
+def _ones(rows: int, device) -> torch.Tensor:
+    key = (rows, device)
+    t = _ONES.get(key)
+    if t is None:
+        t = _ONES[key] = torch.ones(8, rows, dtype=torch.bfloat16, device=device)
+    return t
+
+
+class _LinearReLU(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, relu: bool):
+        x16 = x if x.dtype == torch.bfloat16 else x.to(torch.bfloat16)
+        w16 = weight.to(torch.bfloat16)
+        extra = x16.shape[1] - w16.shape[1]
+        if extra > 0:  # PaddedLinear: input carries zero columns beyond in_features
+            w16 = torch.nn.functional.pad(w16, (0, extra))
+        b16 = bias.to(torch.bfloat16)
+        if relu:
+            y = torch._addmm_activation(b16, x16, w16.t())  # bias + ReLU in the GEMM epilogue
+        else:
+            y = torch.addmm(b16, x16, w16.t())
+        ctx.save_for_backward(x16, w16, y)
+        ctx.relu = relu
+        ctx.extra = extra
+        ctx.x_dtype = x.dtype
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x16, w16, y = ctx.saved_tensors
+        dy = dy.contiguous()
+        if ctx.relu:
+            dy = torch.ops.aten.threshold_backward(dy, y, 0)
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx = dy @ w16
+            if dx.dtype != ctx.x_dtype:
+                dx = dx.to(ctx.x_dtype)
+        if ctx.needs_input_grad[1]:
+            dw = dy.t() @ x16
+            if ctx.extra > 0:
+                dw = dw[:, :dw.shape[1] - ctx.extra]
+            dw = dw.float()
+        if ctx.needs_input_grad[2]:
+            db = (_ones(dy.shape[0], dy.device) @ dy)[0].float()  # column sums on the tensor cores
+        return dx, dw, db, None
+
+
+def mlp_forward(layers: nn.Sequential, x: torch.Tensor) -> torch.Tensor:
+    """Apply ``layers`` (Linear/ReLU/Sigmoid modules of the reference MLP) through the fused bf16 path."""
+    mods = list(layers)
+    i = 0
+    while i < len(mods):
+        m = mods[i]
+        if isinstance(m, (nn.Linear, PaddedLinear)):
+            nxt = mods[i + 1] if i + 1 < len(mods) else None
+            relu = isinstance(nxt, nn.ReLU)
+            x = _LinearReLU.apply(x, m.weight, m.bias, relu)
+            i += 2 if relu else 1
+        else:
+            x = m(x)
+            i += 1
+    return x
