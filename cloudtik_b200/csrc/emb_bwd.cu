@@ -25,10 +25,13 @@ constexpr int UPD_THREADS = 256;
 // group serially: the sorted array is cut into windows of HOT_CH positions, every window
 // pre-reduces the (at most two) hot runs that cross it into fp32 partial rows, and the update
 // kernel adds the partials of a hot row in window order.  Deterministic, no atomics.
+constexpr int HOT_SW = 16;  // windows per super-window (second reduction level for very long runs)
+
 struct BwdLayout {
   uint32_t *keys, *vals, *skeys, *svals, *unique, *seg, *win_run, *first_val;
   int32_t* num_unique;
-  float* partial;  // [2 * ceil(n / HOT_CH)][D]
+  float* partial;   // [2 * nwin][D], nwin = ceil(n / HOT_CH)
+  float* partial2;  // [2 * ceil(nwin / HOT_SW)][D]: per super-window sums for very long runs
   void* sort_ws;
   size_t total;
 };
@@ -48,6 +51,8 @@ static BwdLayout bwd_layout(void* ws, int64_t n, int64_t D) {
   L.num_unique = reinterpret_cast<int32_t*>(w + o), o += 256;
   L.win_run = reinterpret_cast<uint32_t*>(w + o), o += align_up((size_t)(ceil_div(n, HOT_CH) + 1) * 4, 256);
   L.partial = reinterpret_cast<float*>(w + o), o += align_up((size_t)(2 * ceil_div(n, HOT_CH)) * D * 4, 256);
+  L.partial2 = reinterpret_cast<float*>(w + o),
+  o += align_up((size_t)(2 * ceil_div(ceil_div(n, HOT_CH), HOT_SW)) * D * 4, 256);
   L.sort_ws = w + o, o += sort_ws_bytes(n);
   L.total = o;
   return L;
@@ -115,6 +120,7 @@ struct UpdParams {
   const uint32_t* skeys;
   const uint32_t* win_run;
   const uint32_t* first_val;
+  float* partial2;
   int T;
   float* partial;
   int64_t n;
@@ -384,8 +390,47 @@ __global__ void __launch_bounds__(UPD_THREADS) window_update_kernel(const UpdPar
   }
 }
 
-// ---- 3b. join kernel: one group per window border; the border that a run crosses FIRST owns it
-template <typename WT, int G, int NV, int OPT, bool RED>
+// ---- 3b. join: runs that cross window borders.  Two levels so that no group ever adds more than
+// a few dozen partial rows in sequence (the hottest Criteo rows collect > 10^4 gradients per step):
+//   level 1  window_join_kernel<..., 1>: one group per window border; the border a run crosses
+//            FIRST owns it; runs of at most HOT_SW windows are finished here;
+//            super_window_kernel: one group per super-window (HOT_SW windows) pre-adds the window
+//            partials of the longer runs (at most two per super-window: the one covering its first
+//            position -> slot 0, one beginning inside -> slot 1);
+//   level 2  window_join_kernel<..., 2>: the owner adds the super-window sums and updates the row.
+template <int G, int NV, int VE, int PB>
+__device__ __forceinline__ void add_partial_rows(float (*acc)[VE], const float* base, int64_t first, int64_t last,
+                                                 int64_t s_pos, int64_t unit, int D, int V, int lane) {
+  // adds rows base[2 * i + slot(i)] for i in [first, last], slot = (s_pos > i * unit), PB rows in flight
+  for (int64_t ib = first; ib <= last; ib += PB) {
+    uint4 f[PB][NV][VE / 4];
+#pragma unroll
+    for (int c = 0; c < PB; ++c) {
+      const int64_t i = ib + c;
+      const bool ok = i <= last;
+      const float* src = base + (size_t)(2 * i + ((ok && s_pos > i * unit) ? 1 : 0)) * D + lane * VE;
+#pragma unroll
+      for (int kk = 0; kk < NV; ++kk)
+#pragma unroll
+        for (int h = 0; h < VE / 4; ++h)
+          f[c][kk][h] = (ok && lane + kk * G < V) ? ld_v4(src + kk * G * VE + 4 * h) : make_uint4(0, 0, 0, 0);
+    }
+#pragma unroll
+    for (int c = 0; c < PB; ++c)
+#pragma unroll
+      for (int kk = 0; kk < NV; ++kk)
+#pragma unroll
+        for (int h = 0; h < VE / 4; ++h) keep(f[c][kk][h]);
+#pragma unroll
+    for (int c = 0; c < PB; ++c)
+#pragma unroll
+      for (int kk = 0; kk < NV; ++kk)
+#pragma unroll
+        for (int h = 0; h < VE / 4; ++h) Vec16<float>::accum(acc[kk] + 4 * h, f[c][kk][h]);
+  }
+}
+
+template <typename WT, int G, int NV, int OPT, bool RED, int LEVEL>
 __global__ void __launch_bounds__(UPD_THREADS) window_join_kernel(const UpdParams p) {
   constexpr int VE = Vec16<WT>::VE;
   constexpr int NG = UPD_THREADS / G;
@@ -398,6 +443,9 @@ __global__ void __launch_bounds__(UPD_THREADS) window_join_kernel(const UpdParam
   const int64_t u = p.win_run[k];
   const int64_t s = p.seg[u], e = p.seg[u + 1];
   if (s / C + 1 != k) return;  // an earlier border owns this run
+  const int64_t w0 = s / C, w1 = (e - 1) / C;
+  const bool is_long = w1 - w0 + 1 > HOT_SW;
+  if (is_long != (LEVEL == 2)) return;
   const float lr = p.d_lr ? *p.d_lr : p.lr;
   const uint32_t tt = p.first_val[u] / p.B;
   const int64_t row = (int64_t)p.unique[u] - p.row_base[tt];
@@ -414,33 +462,10 @@ __global__ void __launch_bounds__(UPD_THREADS) window_join_kernel(const UpdParam
   for (int kk = 0; kk < NV; ++kk)
 #pragma unroll
     for (int x = 0; x < VE; ++x) acc[kk][x] = 0.f;
-  const int64_t w0 = s / C, w1 = (e - 1) / C;
-  for (int64_t wb = w0; wb <= w1; wb += PB) {
-    uint4 f[PB][NV][VE / 4];
-#pragma unroll
-    for (int c = 0; c < PB; ++c) {
-      const int64_t ww = wb + c;
-      const bool ok = ww <= w1;
-      const float* src = p.partial + (size_t)(2 * ww + ((ok && s > ww * C) ? 1 : 0)) * p.D + lane * VE;
-#pragma unroll
-      for (int kk = 0; kk < NV; ++kk)
-#pragma unroll
-        for (int h = 0; h < VE / 4; ++h)
-          f[c][kk][h] = (ok && lane + kk * G < p.V) ? ld_v4(src + kk * G * VE + 4 * h) : make_uint4(0, 0, 0, 0);
-    }
-#pragma unroll
-    for (int c = 0; c < PB; ++c)
-#pragma unroll
-      for (int kk = 0; kk < NV; ++kk)
-#pragma unroll
-        for (int h = 0; h < VE / 4; ++h) keep(f[c][kk][h]);
-#pragma unroll
-    for (int c = 0; c < PB; ++c)
-#pragma unroll
-      for (int kk = 0; kk < NV; ++kk)
-#pragma unroll
-        for (int h = 0; h < VE / 4; ++h) Vec16<float>::accum(acc[kk] + 4 * h, f[c][kk][h]);
-  }
+  if (LEVEL == 1)
+    add_partial_rows<G, NV, VE, PB>(acc, p.partial, w0, w1, s, C, p.D, p.V, lane);
+  else
+    add_partial_rows<G, NV, VE, PB>(acc, p.partial2, w0 / HOT_SW, w1 / HOT_SW, s, (int64_t)C * HOT_SW, p.D, p.V, lane);
 #pragma unroll
   for (int kk = 0; kk < NV; ++kk)
     if (lane + kk * G < p.V) {
@@ -453,6 +478,44 @@ __global__ void __launch_bounds__(UPD_THREADS) window_join_kernel(const UpdParam
         apply_row<OPT, WT>(wp + (size_t)kk * G * 16, sp ? sp + kk * G * VE : nullptr, acc[kk], wf, lr, p.eps);
       }
     }
+}
+
+template <typename WT, int G, int NV>
+__global__ void __launch_bounds__(UPD_THREADS) super_window_kernel(const UpdParams p) {
+  constexpr int VE = Vec16<WT>::VE;
+  constexpr int NG = UPD_THREADS / G;
+  constexpr int C = HOT_CH;
+  constexpr int PB = (NV * VE >= 32) ? 2 : (NV * VE >= 16 ? 4 : (NV * VE >= 8 ? 8 : 16));
+  const int gid = threadIdx.x / G, lane = threadIdx.x % G;
+  const int64_t S = (int64_t)blockIdx.x * NG + gid;
+  const int64_t nwin = (p.n + C - 1) / C;
+  const int64_t a = S * HOT_SW;
+  if (a >= nwin) return;
+  const int64_t last = min(a + HOT_SW, nwin) - 1;
+  auto reduce_run = [&](int64_t u, int slot) {
+    const int64_t s = p.seg[u], e = p.seg[u + 1];
+    const int64_t w0 = s / C, w1 = (e - 1) / C;
+    if (w1 - w0 + 1 <= HOT_SW) return;  // short runs are finished by the level-1 join
+    float acc[NV][VE];
+#pragma unroll
+    for (int kk = 0; kk < NV; ++kk)
+#pragma unroll
+      for (int x = 0; x < VE; ++x) acc[kk][x] = 0.f;
+    add_partial_rows<G, NV, VE, PB>(acc, p.partial, max(a, w0), min(last, w1), s, C, p.D, p.V, lane);
+    float* dst = p.partial2 + (size_t)(2 * S + slot) * p.D + lane * VE;
+#pragma unroll
+    for (int kk = 0; kk < NV; ++kk)
+      if (lane + kk * G < p.V) {
+#pragma unroll
+        for (int h = 0; h < VE / 4; ++h) store_vec<float, 4, false>(dst + kk * G * VE + 4 * h, acc[kk] + 4 * h);
+      }
+  };
+  const int64_t uA = p.win_run[a];  // run covering the super-window's first position
+  reduce_run(uA, 0);
+  const int64_t endpos = min((last + 1) * C, p.n);  // one past the super-window's last position
+  const int64_t uB = endpos < p.n ? (int64_t)p.win_run[last + 1] - (p.skeys[endpos] != p.skeys[endpos - 1] ? 1 : 0)
+                                  : (int64_t)(*p.num_unique) - 1;
+  if (uB != uA) reduce_run(uB, 1);
 }
 
 // scalar fallback (rows not a whole number of 16-byte vectors): thread per (unique row, d)
@@ -506,8 +569,16 @@ static int launch_update(const UpdParams& p, int64_t n, bool vec_ok, cudaStream_
   }();
 #define B200_UPD_LAUNCH(G, NV, RED)                                                                                  \
   window_update_kernel<WT, GT, G, NV, OPT, RED><<<(unsigned)ceil_div(nwin, UPD_THREADS / G), UPD_THREADS, 0, st>>>(p); \
-  if (nwin > 1)                                                                                                      \
-  window_join_kernel<WT, G, NV, OPT, RED><<<(unsigned)ceil_div(nwin - 1, UPD_THREADS / G), UPD_THREADS, 0, st>>>(p)
+  if (nwin > 1) {                                                                                                    \
+    window_join_kernel<WT, G, NV, OPT, RED, 1>                                                                       \
+        <<<(unsigned)ceil_div(nwin - 1, UPD_THREADS / G), UPD_THREADS, 0, st>>>(p);                                  \
+    if (nwin > HOT_SW) {                                                                                             \
+      super_window_kernel<WT, G, NV>                                                                                 \
+          <<<(unsigned)ceil_div(ceil_div(nwin, HOT_SW), UPD_THREADS / G), UPD_THREADS, 0, st>>>(p);                  \
+      window_join_kernel<WT, G, NV, OPT, RED, 2>                                                                     \
+          <<<(unsigned)ceil_div(nwin - 1, UPD_THREADS / G), UPD_THREADS, 0, st>>>(p);                                \
+    }                                                                                                                \
+  }
 #define B200_UPD_CASE(G, NV)                 \
   if constexpr (CAN_RED) {                   \
     if (use_red) {                           \
@@ -608,6 +679,7 @@ extern "C" int b200_emb_bwd_apply(void* const* d_weights, float* const* d_state,
   p.first_val = L.first_val;
   p.T = (int)T;
   p.partial = L.partial;
+  p.partial2 = L.partial2;
   p.n = nnz;
   const int wsz = dtype_size(w_dtype), gsz = dtype_size(grad_dtype);
   p.V = (int)(D * wsz / 16);
