@@ -25,6 +25,7 @@ constexpr int UPD_THREADS = 256;
 // group serially: the sorted array is cut into windows of HOT_CH positions, every window
 // pre-reduces the (at most two) hot runs that cross it into fp32 partial rows, and the update
 // kernel adds the partials of a hot row in window order.  Deterministic, no atomics.
+constexpr int OPT_STORE = 2;  // internal "optimizer": write the per-row gradient sums to values[run index]
 constexpr int HOT_SW = 16;  // windows per super-window (second reduction level for very long runs)
 
 struct BwdLayout {
@@ -121,6 +122,7 @@ struct UpdParams {
   const uint32_t* win_run;
   const uint32_t* first_val;
   float* partial2;
+  float* values;  // OPT_STORE: [n, D] fp32 coalesced gradient rows, row u = sum of run u
   int T;
   float* partial;
   int64_t n;
@@ -210,7 +212,10 @@ __device__ __forceinline__ void apply_row(char* wp, float* sp, const float* acc,
   float w[VE];
 #pragma unroll
   for (int x = 0; x < VE; ++x) w[x] = w_in[x];
-  if (OPT == B200_OPT_ADAGRAD) {
+  if (OPT == OPT_STORE) {
+#pragma unroll
+    for (int x = 0; x < VE; ++x) w[x] = acc[x];
+  } else if (OPT == B200_OPT_ADAGRAD) {
 #pragma unroll
     for (int h = 0; h < VE / 4; ++h) {
       float st[4];
@@ -251,7 +256,7 @@ __global__ void __launch_bounds__(UPD_THREADS) window_update_kernel(const UpdPar
   __shared__ int64_t s_goff[NG][C];      // element offset of the gradient row of each position
   __shared__ uint16_t s_tab[NG][C];
   const int gid = threadIdx.x / G, lane = threadIdx.x % G;
-  const bool cached = p.T <= UPD_TMAX;
+  const bool cached = p.T <= UPD_TMAX && OPT != OPT_STORE;
   if (cached) {
     for (int i = threadIdx.x; i < p.T; i += UPD_THREADS) {
       s_base[i] = p.row_base[i];
@@ -287,6 +292,7 @@ __global__ void __launch_bounds__(UPD_THREADS) window_update_kernel(const UpdPar
   // is the run being summed a continuation from the previous window, and where is its head?
   bool cont = s_key[gid][0] == s_key[gid][1];
   int cur_head = cont ? -1 : 0;
+  int64_t uidx = (OPT == OPT_STORE) ? (int64_t)p.win_run[w] : 0;  // index of the run being summed
 
   for (int c0 = 0; c0 < cnt; c0 += BS) {
     GradVec<GT, VE> g[BS][NV];
@@ -302,6 +308,7 @@ __global__ void __launch_bounds__(UPD_THREADS) window_update_kernel(const UpdPar
       if (ok && pos > 0 && s_key[gid][pos] != key) {  // a run begins here, inside the window
         cont = false;
         cur_head = pos;
+        if (OPT == OPT_STORE) ++uidx;
       }
       ends[c] = ok && s_key[gid][pos + 2] != key;
       closed[c] = ends[c] && !cont;  // began and ends inside this window: finished here
@@ -320,13 +327,17 @@ __global__ void __launch_bounds__(UPD_THREADS) window_update_kernel(const UpdPar
 #pragma unroll
         for (int k = 0; k < NV; ++k) wv[c][k] = make_uint4(0, 0, 0, 0);
         if (closed[c]) {
-          const int tt = s_tab[gid][pos];
-          const int64_t row = (int64_t)key - (cached ? s_base[tt] : p.row_base[tt]);
-          wp[c] = (cached ? s_wptr[tt] : static_cast<char*>(p.weights[tt])) + ((size_t)row * p.D + lane * VE) * sizeof(WT);
-          if (OPT == B200_OPT_ADAGRAD) sp[c] = (cached ? s_sptr[tt] : p.state[tt]) + (size_t)row * p.D + lane * VE;
+          if (OPT == OPT_STORE) {
+            wp[c] = reinterpret_cast<char*>(p.values) + ((size_t)uidx * p.D + lane * VE) * sizeof(WT);
+          } else {
+            const int tt = s_tab[gid][pos];
+            const int64_t row = (int64_t)key - (cached ? s_base[tt] : p.row_base[tt]);
+            wp[c] = (cached ? s_wptr[tt] : static_cast<char*>(p.weights[tt])) + ((size_t)row * p.D + lane * VE) * sizeof(WT);
+            if (OPT == B200_OPT_ADAGRAD) sp[c] = (cached ? s_sptr[tt] : p.state[tt]) + (size_t)row * p.D + lane * VE;
 #pragma unroll
-          for (int k = 0; k < NV; ++k)
-            if (lane + k * G < p.V) wv[c][k] = ld_v4(wp[c] + (size_t)k * G * 16);
+            for (int k = 0; k < NV; ++k)
+              if (lane + k * G < p.V) wv[c][k] = ld_v4(wp[c] + (size_t)k * G * 16);
+          }
         }
       }
     }
@@ -447,12 +458,20 @@ __global__ void __launch_bounds__(UPD_THREADS) window_join_kernel(const UpdParam
   const bool is_long = w1 - w0 + 1 > HOT_SW;
   if (is_long != (LEVEL == 2)) return;
   const float lr = p.d_lr ? *p.d_lr : p.lr;
-  const uint32_t tt = p.first_val[u] / p.B;
-  const int64_t row = (int64_t)p.unique[u] - p.row_base[tt];
-  char* wp = static_cast<char*>(p.weights[tt]) + ((size_t)row * p.D + lane * VE) * sizeof(WT);
-  float* sp = (OPT == B200_OPT_ADAGRAD) ? p.state[tt] + (size_t)row * p.D + lane * VE : nullptr;
+  char* wp;
+  float* sp = nullptr;
+  if (OPT == OPT_STORE) {
+    wp = reinterpret_cast<char*>(p.values) + ((size_t)u * p.D + lane * VE) * sizeof(WT);
+  } else {
+    const uint32_t tt = p.first_val[u] / p.B;
+    const int64_t row = (int64_t)p.unique[u] - p.row_base[tt];
+    wp = static_cast<char*>(p.weights[tt]) + ((size_t)row * p.D + lane * VE) * sizeof(WT);
+    if (OPT == B200_OPT_ADAGRAD) sp = p.state[tt] + (size_t)row * p.D + lane * VE;
+  }
   uint4 wv[NV];
-  if constexpr (!RED) {
+#pragma unroll
+  for (int kk = 0; kk < NV; ++kk) wv[kk] = make_uint4(0, 0, 0, 0);
+  if constexpr (!RED && OPT != OPT_STORE) {
 #pragma unroll
     for (int kk = 0; kk < NV; ++kk)
       if (lane + kk * G < p.V) wv[kk] = ld_v4(wp + (size_t)kk * G * 16);
@@ -538,6 +557,10 @@ __global__ void emb_update_scalar_kernel(const UpdParams p, int64_t n_max) {
       acc += to_f32<GT>(static_cast<const GT*>(p.grad)[(int64_t)t * p.grad_stride_table +
                                                       (int64_t)b * p.grad_stride_bag + d]);
     }
+    if (OPT == OPT_STORE) {
+      p.values[u * p.D + d] = acc;
+      continue;
+    }
     WT* w = static_cast<WT*>(p.weights[t]) + row * p.D + d;
     float wv = to_f32<WT>(*w);
     if (OPT == B200_OPT_ADAGRAD) {
@@ -550,6 +573,12 @@ __global__ void emb_update_scalar_kernel(const UpdParams p, int64_t n_max) {
     }
     *w = from_f32<WT>(wv);
   }
+}
+
+__global__ void unique_to_i64_kernel(const uint32_t* __restrict__ unique, const int32_t* __restrict__ num_unique,
+                                     int64_t* __restrict__ out, int64_t n) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n && i < *num_unique) out[i] = (int64_t)unique[i];
 }
 
 template <typename WT, typename GT, int OPT>
@@ -714,4 +743,55 @@ extern "C" int b200_emb_bwd_update(void* const* d_weights, float* const* d_state
   return b200_emb_bwd_apply(d_weights, d_state, d_row_base, nnz, d_grad, T, B, D, grad_stride_table,
                             grad_stride_bag, w_dtype, grad_dtype, optimizer, lr, d_lr, eps, ws, ws_bytes,
                             stream);
+}
+
+extern "C" int b200_emb_bwd_coalesce(const int64_t* d_rows, const int64_t* d_row_base, const int64_t* d_indices,
+                                     const int64_t* d_offsets, int64_t nnz, const void* d_grad, int64_t T,
+                                     int64_t B, int64_t D, int64_t grad_stride_table, int64_t grad_stride_bag,
+                                     int grad_dtype, int64_t total_rows, int64_t* d_unique_rows, float* d_values,
+                                     int32_t* d_num_unique, void* ws, size_t ws_bytes, int32_t* d_error,
+                                     b200_stream_t stream) {
+  B200_REQUIRE(d_num_unique, B200_EINVAL, "emb_bwd_coalesce: null output");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (T == 0 || B == 0 || nnz == 0) {
+    cudaMemsetAsync(d_num_unique, 0, sizeof(int32_t), st);
+    return B200_OK;
+  }
+  B200_REQUIRE(d_unique_rows && d_values && d_grad, B200_EINVAL, "emb_bwd_coalesce: null pointer");
+  B200_REQUIRE(grad_dtype == B200_F32 || grad_dtype == B200_BF16, B200_EINVAL, "emb_bwd_coalesce: bad dtype");
+  int rc = b200_emb_bwd_prepare(d_rows, d_row_base, d_indices, d_offsets, nnz, T, B, D, total_rows, ws, ws_bytes,
+                                d_error, stream);
+  if (rc) return rc;
+  BwdLayout L = bwd_layout(ws, nnz, D);
+  UpdParams p{};
+  p.row_base = d_row_base;
+  p.unique = L.unique;
+  p.seg = L.seg;
+  p.svals = L.svals;
+  p.num_unique = L.num_unique;
+  p.grad = d_grad;
+  p.grad_stride_table = grad_stride_table;
+  p.grad_stride_bag = grad_stride_bag;
+  p.B = (uint32_t)B;
+  p.D = (int)D;
+  p.V = (int)(D * 4 / 16);
+  p.skeys = L.skeys;
+  p.win_run = L.win_run;
+  p.first_val = L.first_val;
+  p.partial = L.partial;
+  p.partial2 = L.partial2;
+  p.values = d_values;
+  p.n = nnz;
+  p.T = (int)T;
+  const int gsz = dtype_size(grad_dtype);
+  const bool vec_ok = (D * 4) % 16 == 0 && p.V <= 128 && (reinterpret_cast<uintptr_t>(d_grad) % 16) == 0 &&
+                      (reinterpret_cast<uintptr_t>(d_values) % 16) == 0 && (grad_stride_table * gsz) % 16 == 0 &&
+                      (grad_stride_bag * gsz) % 16 == 0;
+  rc = grad_dtype == B200_F32 ? launch_update<float, float, OPT_STORE>(p, nnz, vec_ok, st)
+                              : launch_update<float, __nv_bfloat16, OPT_STORE>(p, nnz, vec_ok, st);
+  if (rc) return rc;
+  unique_to_i64_kernel<<<(unsigned)ceil_div(nnz, 256), 256, 0, st>>>(L.unique, L.num_unique, d_unique_rows, nnz);
+  cudaMemcpyAsync(d_num_unique, L.num_unique, sizeof(int32_t), cudaMemcpyDeviceToDevice, st);
+  B200_CHECK_LAUNCH("emb_bwd_coalesce");
+  return B200_OK;
 }

@@ -166,6 +166,29 @@ def emb_bwd_apply(tables: TableSet, nnz: int, B: int, grad: torch.Tensor, stride
         ws.numel() * ws.element_size(), _stream()), "b200_emb_bwd_apply")
 
 
+def emb_bwd_coalesce(tables: TableSet, indices, offsets, B: int, grad: torch.Tensor, stride_table: int,
+                     stride_bag: int, ws: torch.Tensor, error: torch.Tensor | None = None):
+    """Coalesced sparse gradient of the pooled lookup: returns (unique_rows int64[U] global row ids ascending,
+    values fp32[U, D]).  Synchronises once to read U (a sparse tensor needs a concrete nnz).
+    See b200_emb_bwd_coalesce."""
+    _cuda(indices, "indices", torch.int64)
+    _cuda(offsets, "offsets", torch.int64)
+    _cuda(grad, "grad")
+    nnz = indices.numel()
+    dev = indices.device
+    rows = torch.empty(nnz, dtype=torch.int64, device=dev)
+    vals = torch.empty(nnz, tables.D, dtype=torch.float32, device=dev)
+    nu = torch.zeros(1, dtype=torch.int32, device=dev)
+    check(lib.b200_emb_bwd_coalesce(tables.d_rows.data_ptr(), tables.d_row_base.data_ptr(), indices.data_ptr(),
+                                    offsets.data_ptr(), nnz, grad.data_ptr(), len(tables), B, tables.D,
+                                    stride_table, stride_bag, _dt(grad.dtype), tables.total_rows, rows.data_ptr(),
+                                    vals.data_ptr(), nu.data_ptr(), ws.data_ptr(), ws.numel() * ws.element_size(),
+                                    error.data_ptr() if error is not None else None, _stream()),
+          "b200_emb_bwd_coalesce")
+    U = int(nu.item())
+    return rows[:U], vals[:U]
+
+
 def interact_fwd(T: torch.Tensor, out: torch.Tensor | None = None, pad_to: int = 1) -> torch.Tensor:
     """T [B, F, D] contiguous -> R [B, ldr] with ldr = D + F(F-1)/2 rounded up to ``pad_to``
     (padding columns are written as zeros).  See b200_interact_fwd."""

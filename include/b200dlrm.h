@@ -144,6 +144,22 @@ int b200_emb_bwd_apply(void* const* d_weights, float* const* d_state, const int6
                        b200_stream_t stream);
 
 /*
+ * EmbeddingBag backward as a COALESCED sparse gradient (no optimiser fused): for callers that keep
+ * the per-table `nn.EmbeddingBag(sparse=True)` seam of DLRM_Net.apply_emb (P/dlrm_s_pytorch.py:299-305)
+ * and let torch.optim.SGD / Adagrad consume the sparse gradient (P/dlrm_s_pytorch.py:805,1059).
+ * Equals `weight.grad.coalesce()` of the reference: d_unique_rows[u] = u-th distinct global row id
+ * (ascending), d_values[u, :] = sum of the gradient rows of all bags that looked it up (fp32),
+ * *d_num_unique = number of distinct rows.  Outputs must hold nnz rows.  Same workspace as
+ * b200_emb_bwd_update.
+ */
+int b200_emb_bwd_coalesce(const int64_t* d_rows, const int64_t* d_row_base, const int64_t* d_indices,
+                          const int64_t* d_offsets, int64_t nnz, const void* d_grad, int64_t T, int64_t B,
+                          int64_t D, int64_t grad_stride_table, int64_t grad_stride_bag, int grad_dtype,
+                          int64_t total_rows, int64_t* d_unique_rows, float* d_values,
+                          int32_t* d_num_unique, void* ws, size_t ws_bytes, int32_t* d_error,
+                          b200_stream_t stream);
+
+/*
  * Pairwise dot-product feature interaction, forward and backward.
  * Replaces DLRM_Net.interact_features (P/dlrm_s_pytorch.py:309-334, T/dlrm_s_pytorch.py:407-444;
  * cat + bmm + tril gather + cat) and ipex.nn.functional.interaction(*T) (P/dlrm_s_pytorch.py:312).

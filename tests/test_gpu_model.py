@@ -96,3 +96,35 @@ def test_terabyte_arch_vs_cpu_port(bf16):
     for t in range(len(rows)):
         np.testing.assert_allclose(net.emb_l.weights[t].cpu().numpy(), port.emb_l[t].weight.detach().numpy(),
                                    rtol=tol, atol=tol * 1e-2 if not bf16 else 2e-3)
+
+
+@pytest.mark.parametrize("opt_name", ["sgd", "adagrad"])
+def test_per_table_embedding_bag_seam(opt_name):
+    """The per-table seam: E(indices, offsets) with a sparse gradient consumed by torch.optim, against
+    nn.EmbeddingBag(sparse=True) on the CPU (what DLRM_Net.create_emb builds)."""
+    from cloudtik_b200.embedding_bag import EmbeddingBag
+    rs = np.random.RandomState(3)
+    n, D, B = 700, 128, 300
+    W = rs.randn(n, D).astype(np.float32)
+    ref = torch.nn.EmbeddingBag(n, D, mode="sum", sparse=True, _weight=torch.tensor(W.copy()))
+    mine = EmbeddingBag(n, D, _weight=torch.tensor(W.copy()))
+    mk = (lambda ps: torch.optim.SGD(ps, lr=0.1)) if opt_name == "sgd" else (lambda ps: torch.optim.Adagrad(ps, lr=0.05))
+    o_ref, o_mine = mk(ref.parameters()), mk(mine.parameters())
+    for step in range(3):
+        lens = rs.randint(0, 7, size=B)
+        off = np.concatenate([[0], np.cumsum(lens)[:-1]]).astype(np.int64)
+        idx = rs.randint(0, n if step else 40, size=int(lens.sum())).astype(np.int64)  # step 0: heavy duplicates
+        gout = rs.randn(B, D).astype(np.float32)
+        y_ref = ref(torch.tensor(idx), torch.tensor(off))
+        y = mine(torch.tensor(idx).cuda(), torch.tensor(off).cuda())
+        np.testing.assert_allclose(y.detach().cpu().numpy(), y_ref.detach().numpy(), rtol=1e-5, atol=1e-5)
+        o_ref.zero_grad(), o_mine.zero_grad()
+        y_ref.backward(torch.tensor(gout))
+        y.backward(torch.tensor(gout).cuda())
+        g, gr = mine.weight.grad, ref.weight.grad.coalesce()
+        assert g.is_sparse
+        # the raw (not re-coalesced) indices are already the sorted distinct rows: bit-exact dedup
+        np.testing.assert_array_equal(g._indices().cpu().numpy(), gr.indices().numpy())
+        np.testing.assert_allclose(g._values().cpu().numpy(), gr.values().numpy(), rtol=1e-5, atol=1e-5)
+        o_ref.step(), o_mine.step()
+        np.testing.assert_allclose(mine.weight.detach().cpu().numpy(), ref.weight.detach().numpy(), rtol=1e-5, atol=1e-6)
