@@ -243,3 +243,30 @@ def all_gather(input, lengths, dim=0):
 def barrier():
     if my_size > 1:
         dist.barrier()
+
+
+class DenseGradAllreduce(object):
+    """Data-parallel gradient averaging for the (small, 2.4 M-parameter) MLPs without wrapping them in
+    DDP: one flat fp32 buffer, ONE all-reduce after backward.  Same result as the reference's
+    ``ext_dist.DDP(bot_l) / DDP(top_l)`` (``P/dlrm_s_pytorch.py:955-957``: mean over ranks); used when the
+    MLPs run through the fused bf16 path, whose autograd functions bypass ``DDP.forward``."""
+
+    def __init__(self, params):
+        self.params = [p for p in params if p.requires_grad]
+        n = sum(p.numel() for p in self.params)
+        self.flat = torch.zeros(n, dtype=torch.float32, device=self.params[0].device)
+        self.views = []
+        o = 0
+        for p in self.params:
+            self.views.append(self.flat[o:o + p.numel()].view_as(p))
+            o += p.numel()
+
+    def __call__(self):
+        if my_size <= 1:
+            return
+        grads = [p.grad if p.grad is not None else torch.zeros_like(p) for p in self.params]
+        torch._foreach_copy_(self.views, grads)
+        dist.all_reduce(self.flat)
+        self.flat.mul_(1.0 / my_size)
+        for p, v in zip(self.params, self.views):
+            p.grad = v  # the optimizer reads the averaged gradient straight from the flat buffer

@@ -14,9 +14,12 @@ import torch
 
 
 class GraphedTrainStep:
-    def __init__(self, net, optimizer, example, warmup: int = 3):
-        """``example`` = (X, Y, indices, offsets) device tensors with the shapes of every later batch."""
+    def __init__(self, net, optimizer, example, warmup: int = 3, post_backward=None):
+        """``example`` = (X, Y, indices, offsets) device tensors with the shapes of every later batch.
+        ``post_backward``: optional callable run between backward and the optimizer step (the flat
+        all-reduce of the MLP gradients in the multi-GPU case; NCCL collectives are captured too)."""
         self.net, self.opt = net, optimizer
+        self.post_backward = post_backward
         self.static = [torch.empty_like(t) for t in example]
         for d, s in zip(self.static, example):
             d.copy_(s)
@@ -43,6 +46,8 @@ class GraphedTrainStep:
         E = self.net.loss_fn(Z, Y)
         self.opt.zero_grad(set_to_none=True)
         E.backward()
+        if self.post_backward is not None:
+            self.post_backward()
         self.opt.step()
         return E.detach()
 

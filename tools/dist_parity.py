@@ -27,6 +27,7 @@ def main():
     ap.add_argument("--tables", type=int, default=8)
     ap.add_argument("--steps", type=int, default=4)
     ap.add_argument("--batch", type=int, default=512, help="GLOBAL batch")
+    ap.add_argument("--ddp", action="store_true", help="wrap the MLPs in DDP instead of the flat all-reduce")
     a = ap.parse_args()
 
     from cloudtik_b200 import ext_dist
@@ -53,10 +54,13 @@ def main():
         for dst, src in ((net.bot_l, port.bot_l), (net.top_l, port.top_l)):
             for pd, ps in zip(dst.parameters(), src.parameters()):
                 pd.copy_(ps)
-    net.bot_l = ext_dist.DDP(net.bot_l, device_ids=[dev.index])
-    net.top_l = ext_dist.DDP(net.top_l, device_ids=[dev.index])
+    if a.ddp:
+        net.bot_l = ext_dist.DDP(net.bot_l, device_ids=[dev.index])
+        net.top_l = ext_dist.DDP(net.top_l, device_ids=[dev.index])
     copt = torch.optim.SGD(port.parameters(), lr=lr)
-    gopt = torch.optim.SGD([p for p in net.parameters() if p.requires_grad], lr=lr)
+    dense = [p for p in net.parameters() if p.requires_grad]
+    gopt = torch.optim.SGD(dense, lr=lr)
+    sync_dense = (lambda: None) if a.ddp else ext_dist.DenseGradAllreduce(dense)
     rs = np.random.RandomState(5)
     N, lN = a.batch, a.batch // world
     tol = 1e-2 if a.bf16 else 1e-5
@@ -72,6 +76,7 @@ def main():
         E = net.loss_fn(Z, Tl)
         gopt.zero_grad(set_to_none=True)
         E.backward()
+        sync_dense()
         gopt.step()
         Lm = E.detach().clone()
         torch.distributed.all_reduce(Lm)
@@ -81,7 +86,8 @@ def main():
         w = net.emb_l.weights[k].float().cpu().numpy()
         np.testing.assert_allclose(w, port.emb_l[t].weight.detach().numpy(), rtol=tol,
                                    atol=2e-3 if a.bf16 else 1e-7, err_msg=f"table {t}")
-    for (n1, p1), p2 in zip(net.top_l.module.named_parameters(), port.top_l.parameters()):
+    top = net.top_l.module if a.ddp else net.top_l
+    for (n1, p1), p2 in zip(top.named_parameters(), port.top_l.parameters()):
         np.testing.assert_allclose(p1.detach().cpu().numpy(), p2.detach().numpy(), rtol=10 * tol,
                                    atol=2e-3 if a.bf16 else 1e-6, err_msg=n1)
     ext_dist.barrier()
