@@ -52,7 +52,7 @@ def parse():
     ap.add_argument("--sets", type=int, default=4, help="distinct synthetic batches rotated")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="run the step eagerly instead of as one CUDA graph")
-    ap.add_argument("--graph-multi", action="store_true", help="capture the multi-GPU step (NCCL collectives included) too")
+    ap.add_argument("--no-p2p", action="store_true", help="multi-GPU: NCCL all-to-all instead of the fused peer-memory exchange")
     ap.add_argument("--cpu-rows-cap", type=int, default=200000)
     ap.add_argument("--cpu-steps", type=int, default=3)
     return ap.parse_args()
@@ -191,7 +191,7 @@ def make_batches(a, rows_local, B_loc, B_glob, dev, rank):
 
 def run_b200_arm(a):
     from cloudtik_b200 import ext_dist
-    from cloudtik_b200.dlrm import DLRM_Net
+    from cloudtik_b200.dlrm import DLRM_Net, enable_peer_exchange
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -211,6 +211,9 @@ def run_b200_arm(a):
                    np_init_emb_weight=False, device=dev, lr=LR / world, bf16=bf16)
     local_ids = list(range(len(rows))) if world == 1 else net.local_ln_emb
     rows_local = [rows[i] for i in local_ids]
+    use_p2p = world > 1 and not a.no_p2p
+    if use_p2p:
+        enable_peer_exchange(net, B_loc)
     dense_params = [p for p in net.parameters() if p.requires_grad]
     opt = torch.optim.SGD(dense_params, lr=LR)
     # MLPs are data-parallel: one flat all-reduce of their 2.4 M gradients per step (the fused bf16 MLP
@@ -272,7 +275,7 @@ def run_b200_arm(a):
     prof = emb.profile
     emb.profile = None
 
-    use_graph = not a.no_graph and (world == 1 or a.graph_multi)
+    use_graph = not a.no_graph
     step_fn, e2e_fn = step_dev, step_e2e
     if use_graph:
         from cloudtik_b200.graph import GraphedTrainStep
@@ -343,7 +346,8 @@ def run_b200_arm(a):
                        "dim": D, "tables": len(rows), "total_rows": int(sum(rows)), "pooling": 1,
                        "table_dtype": "fp32", "mlp": "bot 13-512-256-128 / top 479-1024-1024-512-256-1",
                        "optimizer": "SGD lr 1.0 (fused sparse update + torch SGD on MLPs)",
-                       "parallelism": "single" if world == 1 else f"table-wise x{world} + DDP MLPs",
+                       "parallelism": "single" if world == 1 else
+                       f"table-wise x{world} ({'fused peer-memory exchange' if use_p2p else 'NCCL all-to-all'}) + data-parallel MLPs",
                        "l2": "inputs larger than L2 (96 GB of tables, uniform random rows)",
                        "rows_cap": a.rows_cap or None,
                        "launch": "whole step replayed as one CUDA graph" if use_graph else "eager"},

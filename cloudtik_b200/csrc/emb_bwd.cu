@@ -123,6 +123,10 @@ struct UpdParams {
   const uint32_t* first_val;
   float* partial2;
   float* values;  // OPT_STORE: [n, D] fp32 coalesced gradient rows, row u = sum of run u
+  // sharded gradients (fused mirror all-to-all over peer memory): the gradient row of bag b of local
+  // table t lives on rank r = b / lN at grad_ptrs[r] + ((b - r*lN) * F + feat0 + t) * D
+  const void* const* grad_ptrs;
+  int64_t lN, F, feat0;
   int T;
   float* partial;
   int64_t n;
@@ -253,7 +257,7 @@ __global__ void __launch_bounds__(UPD_THREADS) window_update_kernel(const UpdPar
   __shared__ char* s_wptr[UPD_TMAX];
   __shared__ float* s_sptr[UPD_TMAX];
   __shared__ uint32_t s_key[NG][C + 2];  // [0] = key before the window, [C+1] = key after it
-  __shared__ int64_t s_goff[NG][C];      // element offset of the gradient row of each position
+  __shared__ int64_t s_goff[NG][C];      // address of the gradient row of each position
   __shared__ uint16_t s_tab[NG][C];
   const int gid = threadIdx.x / G, lane = threadIdx.x % G;
   const bool cached = p.T <= UPD_TMAX && OPT != OPT_STORE;
@@ -272,7 +276,15 @@ __global__ void __launch_bounds__(UPD_THREADS) window_update_kernel(const UpdPar
     const uint32_t tt = g / p.B;
     s_key[gid][i + 1] = p.skeys[a + i];
     s_tab[gid][i] = (uint16_t)tt;
-    s_goff[gid][i] = (int64_t)tt * p.grad_stride_table + (int64_t)(g - tt * p.B) * p.grad_stride_bag;
+    const int64_t bb = g - tt * p.B;
+    const GT* gaddr;
+    if (p.grad_ptrs != nullptr) {
+      const int64_t r = bb / p.lN;
+      gaddr = static_cast<const GT*>(p.grad_ptrs[r]) + ((bb - r * p.lN) * p.F + p.feat0 + tt) * p.D;
+    } else {
+      gaddr = static_cast<const GT*>(p.grad) + (int64_t)tt * p.grad_stride_table + bb * p.grad_stride_bag;
+    }
+    s_goff[gid][i] = reinterpret_cast<int64_t>(gaddr);  // absolute address of the gradient row
   }
   if (lane == 0 && cnt > 0) {
     // sentinels: a key that differs from its neighbour when there is no neighbour
@@ -283,7 +295,6 @@ __global__ void __launch_bounds__(UPD_THREADS) window_update_kernel(const UpdPar
   __syncthreads();
   if (cnt == 0) return;
 
-  const GT* gbase = static_cast<const GT*>(p.grad) + lane * VE;
   float acc[NV][VE];
 #pragma unroll
   for (int k = 0; k < NV; ++k)
@@ -312,7 +323,7 @@ __global__ void __launch_bounds__(UPD_THREADS) window_update_kernel(const UpdPar
       }
       ends[c] = ok && s_key[gid][pos + 2] != key;
       closed[c] = ends[c] && !cont;  // began and ends inside this window: finished here
-      const GT* gp = gbase + (ok ? s_goff[gid][pos] : 0);
+      const GT* gp = reinterpret_cast<const GT*>(ok ? s_goff[gid][pos] : s_goff[gid][0]) + lane * VE;
 #pragma unroll
       for (int k = 0; k < NV; ++k) {
         if (ok && lane + k * G < p.V) {
@@ -669,15 +680,17 @@ extern "C" int b200_emb_bwd_prepare(const int64_t* d_rows, const int64_t* d_row_
   return dedup_runs(L.skeys, nnz, L.unique, L.seg, L.num_unique, L.sort_ws, st, L.win_run, L.svals, L.first_val);
 }
 
-extern "C" int b200_emb_bwd_apply(void* const* d_weights, float* const* d_state,
-                                  const int64_t* d_row_base, int64_t nnz, const void* d_grad, int64_t T,
-                                  int64_t B, int64_t D, int64_t grad_stride_table,
-                                  int64_t grad_stride_bag, int w_dtype, int grad_dtype, int optimizer,
-                                  float lr, const float* d_lr, float eps, void* ws, size_t ws_bytes,
-                                  b200_stream_t stream) {
+static int emb_bwd_apply_impl(void* const* d_weights, float* const* d_state, const int64_t* d_row_base,
+                              int64_t nnz, const void* d_grad, int64_t T, int64_t B, int64_t D,
+                              int64_t grad_stride_table, int64_t grad_stride_bag, int w_dtype, int grad_dtype,
+                              int optimizer, float lr, const float* d_lr, float eps, void* ws, size_t ws_bytes,
+                              b200_stream_t stream, const void* const* d_grad_ptrs, int64_t lN, int64_t F,
+                              int64_t feat0) {
   B200_REQUIRE(T >= 0 && B >= 0 && D > 0 && nnz >= 0, B200_EINVAL, "emb_bwd: negative size");
   if (T == 0 || B == 0 || nnz == 0) return B200_OK;
-  B200_REQUIRE(d_weights && d_row_base && d_grad && ws, B200_EINVAL, "emb_bwd_apply: null pointer");
+  B200_REQUIRE(d_weights && d_row_base && (d_grad || d_grad_ptrs) && ws, B200_EINVAL, "emb_bwd_apply: null pointer");
+  B200_REQUIRE(!d_grad_ptrs || (lN > 0 && B % lN == 0 && F > 0), B200_EINVAL,
+               "emb_bwd_apply_sharded: B must be a multiple of lN");
   B200_REQUIRE(optimizer == B200_OPT_SGD || (optimizer == B200_OPT_ADAGRAD && d_state), B200_EINVAL,
                "emb_bwd: bad optimizer / missing state");
   B200_REQUIRE((w_dtype == B200_F32 || w_dtype == B200_BF16) &&
@@ -710,13 +723,20 @@ extern "C" int b200_emb_bwd_apply(void* const* d_weights, float* const* d_state,
   p.partial = L.partial;
   p.partial2 = L.partial2;
   p.n = nnz;
+  p.values = nullptr;
+  p.grad_ptrs = d_grad_ptrs;
+  p.lN = lN;
+  p.F = F;
+  p.feat0 = feat0;
   const int wsz = dtype_size(w_dtype), gsz = dtype_size(grad_dtype);
   p.V = (int)(D * wsz / 16);
   const int ve = 16 / wsz;  // elements per weight vector
   const bool vec_ok = (D * wsz) % 16 == 0 && p.V <= 128 &&
                       (reinterpret_cast<uintptr_t>(d_grad) % 16) == 0 &&
                       (grad_stride_table * gsz) % 16 == 0 && (grad_stride_bag * gsz) % 16 == 0 &&
-                      (ve * gsz) % 8 == 0;
+                      (ve * gsz) % 8 == 0 && (!d_grad_ptrs || (D * gsz) % 16 == 0);
+  B200_REQUIRE(vec_ok || !d_grad_ptrs, B200_EUNSUPPORTED,
+               "emb_bwd_apply_sharded: row size must be a multiple of 16 bytes");
 #define B200_UPD_DISPATCH(OPT)                                                                  \
   (w_dtype == B200_F32                                                                          \
        ? (grad_dtype == B200_F32 ? launch_update<float, float, OPT>(p, nnz, vec_ok, st)         \
@@ -727,6 +747,29 @@ extern "C" int b200_emb_bwd_apply(void* const* d_weights, float* const* d_state,
   if (optimizer == B200_OPT_ADAGRAD) return B200_UPD_DISPATCH(B200_OPT_ADAGRAD);
   return B200_UPD_DISPATCH(B200_OPT_SGD);
 #undef B200_UPD_DISPATCH
+}
+
+extern "C" int b200_emb_bwd_apply(void* const* d_weights, float* const* d_state,
+                                  const int64_t* d_row_base, int64_t nnz, const void* d_grad, int64_t T,
+                                  int64_t B, int64_t D, int64_t grad_stride_table,
+                                  int64_t grad_stride_bag, int w_dtype, int grad_dtype, int optimizer,
+                                  float lr, const float* d_lr, float eps, void* ws, size_t ws_bytes,
+                                  b200_stream_t stream) {
+  B200_REQUIRE(d_grad != nullptr || nnz == 0, B200_EINVAL, "emb_bwd_apply: null gradient");
+  return emb_bwd_apply_impl(d_weights, d_state, d_row_base, nnz, d_grad, T, B, D, grad_stride_table,
+                            grad_stride_bag, w_dtype, grad_dtype, optimizer, lr, d_lr, eps, ws, ws_bytes, stream,
+                            nullptr, 0, 0, 0);
+}
+
+extern "C" int b200_emb_bwd_apply_sharded(void* const* d_weights, float* const* d_state,
+                                          const int64_t* d_row_base, int64_t nnz,
+                                          const void* const* d_grad_ptrs, int64_t T, int64_t B, int64_t D,
+                                          int64_t lN, int64_t F, int64_t feat0, int w_dtype, int grad_dtype,
+                                          int optimizer, float lr, const float* d_lr, float eps, void* ws,
+                                          size_t ws_bytes, b200_stream_t stream) {
+  B200_REQUIRE(d_grad_ptrs != nullptr, B200_EINVAL, "emb_bwd_apply_sharded: null pointer table");
+  return emb_bwd_apply_impl(d_weights, d_state, d_row_base, nnz, nullptr, T, B, D, 0, 0, w_dtype, grad_dtype,
+                            optimizer, lr, d_lr, eps, ws, ws_bytes, stream, d_grad_ptrs, lN, F, feat0);
 }
 
 extern "C" int b200_emb_bwd_update(void* const* d_weights, float* const* d_state,

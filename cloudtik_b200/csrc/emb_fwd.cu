@@ -34,6 +34,12 @@ struct EmbFwdParams {
   int D;
   int V;     // 16-byte vectors per row
   int tile;  // bags per CTA
+  // sharded output (fused pooled-embedding all-to-all over peer memory): bag b of local table t is
+  // written to rank r = b / lN at out_ptrs[r] + ((b - r*lN) * F + feat0 + t) * D.  lN % tile == 0.
+  void* const* out_ptrs;
+  int64_t lN;
+  int64_t F;
+  int64_t feat0;
 };
 
 template <typename WT, typename OT, int G, int NV>
@@ -94,7 +100,13 @@ __global__ void __launch_bounds__(FWD_THREADS) emb_fwd_kernel(const EmbFwdParams
   const int64_t nrows = p.rows[t];
   const char* W = static_cast<const char*>(p.weights[t]);
   const size_t row_bytes = (size_t)p.D * sizeof(WT);
-  OT* out_t = static_cast<OT*>(p.out) + (int64_t)t * p.out_stride_table + b0 * p.out_stride_bag;
+  OT* out_t;
+  if (p.out_ptrs != nullptr) {  // this tile's bags all belong to one destination rank
+    const int64_t r = b0 / p.lN;
+    out_t = static_cast<OT*>(p.out_ptrs[r]) + ((b0 - r * p.lN) * p.F + p.feat0 + t) * p.D;
+  } else {
+    out_t = static_cast<OT*>(p.out) + (int64_t)t * p.out_stride_table + b0 * p.out_stride_bag;
+  }
 
   // ---- compact the staged tile to 32 bits: bag offsets relative to i0, row ids (bounds-checked
   //      once here, 0xffffffff = out of range) -- keeps 64-bit arithmetic out of the gather loop
@@ -280,14 +292,14 @@ static int launch_fwd_scalar(const EmbFwdParams& p, int64_t T, cudaStream_t st) 
 
 using namespace b200;
 
-extern "C" int b200_emb_fwd(const void* const* d_weights, const int64_t* d_rows,
-                            const int64_t* d_indices, const int64_t* d_offsets, void* d_out,
-                            int64_t nnz, int64_t T, int64_t B, int64_t D, int64_t out_stride_table,
-                            int64_t out_stride_bag, int w_dtype, int out_dtype, int32_t* d_error,
-                            b200_stream_t stream) {
+static int emb_fwd_impl(const void* const* d_weights, const int64_t* d_rows, const int64_t* d_indices,
+                        const int64_t* d_offsets, void* d_out, int64_t nnz, int64_t T, int64_t B, int64_t D,
+                        int64_t out_stride_table, int64_t out_stride_bag, int w_dtype, int out_dtype,
+                        int32_t* d_error, b200_stream_t stream, void* const* d_out_ptrs, int64_t lN, int64_t F,
+                        int64_t feat0) {
   B200_REQUIRE(T >= 0 && B >= 0 && D > 0 && nnz >= 0, B200_EINVAL, "emb_fwd: negative size");
   if (T == 0 || B == 0) return B200_OK;
-  B200_REQUIRE(d_weights && d_rows && d_offsets && d_out && (d_indices || nnz == 0), B200_EINVAL,
+  B200_REQUIRE(d_weights && d_rows && d_offsets && (d_out || d_out_ptrs) && (d_indices || nnz == 0), B200_EINVAL,
                "emb_fwd: null pointer");
   B200_REQUIRE(T <= 65535, B200_EUNSUPPORTED, "emb_fwd: more than 65535 tables");
   B200_REQUIRE((w_dtype == B200_F32 || w_dtype == B200_BF16) &&
@@ -305,6 +317,10 @@ extern "C" int b200_emb_fwd(const void* const* d_weights, const int64_t* d_rows,
   p.out_stride_bag = out_stride_bag;
   p.error = d_error;
   p.D = (int)D;
+  p.out_ptrs = d_out_ptrs;
+  p.lN = lN;
+  p.F = F;
+  p.feat0 = feat0;
   const int ws = dtype_size(w_dtype), os = dtype_size(out_dtype);
   const int64_t row_bytes = D * ws;
   p.V = (int)(row_bytes / 16);
@@ -312,13 +328,18 @@ extern "C" int b200_emb_fwd(const void* const* d_weights, const int64_t* d_rows,
   const int64_t avg_pool = (nnz + T * B - 1) / (T * B);
   int tile = FWD_MAX_TILE;
   while (tile > 8 && (int64_t)tile * (avg_pool > 0 ? avg_pool : 1) > FWD_IDX_CAP - 2) tile >>= 1;
+  if (d_out_ptrs) {
+    B200_REQUIRE(lN > 0 && B % lN == 0 && F > 0, B200_EINVAL, "emb_fwd_sharded: B must be a multiple of lN");
+    while (tile > 1 && lN % tile != 0) tile >>= 1;  // a tile never straddles two destination ranks
+    p.out_stride_bag = F * D;
+  }
   p.tile = tile;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const bool vec_ok = row_bytes % 16 == 0 && p.V <= 128 &&
-                      (reinterpret_cast<uintptr_t>(d_out) & 15) == 0 &&
-                      (out_stride_table * os) % 16 == 0 && (out_stride_bag * os) % 16 == 0;
-  // (table base pointers are 16-byte aligned by construction of any CUDA allocation; a
-  //  misaligned view would fault, so the host wrapper checks it.)
+                      (d_out_ptrs ? (D * os) % 16 == 0
+                                  : ((reinterpret_cast<uintptr_t>(d_out) & 15) == 0 &&
+                                     (out_stride_table * os) % 16 == 0 && (out_stride_bag * os) % 16 == 0));
+  B200_REQUIRE(vec_ok || !d_out_ptrs, B200_EUNSUPPORTED, "emb_fwd_sharded: row size must be a multiple of 16 bytes");
 #define B200_DISPATCH(FN)                                                          \
   (w_dtype == B200_F32                                                             \
        ? (out_dtype == B200_F32 ? FN<float, float>(p, T, st)                       \
@@ -328,4 +349,23 @@ extern "C" int b200_emb_fwd(const void* const* d_weights, const int64_t* d_rows,
   if (vec_ok) return B200_DISPATCH(launch_fwd);
   return B200_DISPATCH(launch_fwd_scalar);
 #undef B200_DISPATCH
+}
+
+extern "C" int b200_emb_fwd(const void* const* d_weights, const int64_t* d_rows,
+                            const int64_t* d_indices, const int64_t* d_offsets, void* d_out,
+                            int64_t nnz, int64_t T, int64_t B, int64_t D, int64_t out_stride_table,
+                            int64_t out_stride_bag, int w_dtype, int out_dtype, int32_t* d_error,
+                            b200_stream_t stream) {
+  return emb_fwd_impl(d_weights, d_rows, d_indices, d_offsets, d_out, nnz, T, B, D, out_stride_table,
+                      out_stride_bag, w_dtype, out_dtype, d_error, stream, nullptr, 0, 0, 0);
+}
+
+extern "C" int b200_emb_fwd_sharded(const void* const* d_weights, const int64_t* d_rows,
+                                    const int64_t* d_indices, const int64_t* d_offsets,
+                                    void* const* d_out_ptrs, int64_t nnz, int64_t T, int64_t B, int64_t D,
+                                    int64_t lN, int64_t F, int64_t feat0, int w_dtype, int out_dtype,
+                                    int32_t* d_error, b200_stream_t stream) {
+  B200_REQUIRE(d_out_ptrs, B200_EINVAL, "emb_fwd_sharded: null pointer table");
+  return emb_fwd_impl(d_weights, d_rows, d_indices, d_offsets, nullptr, nnz, T, B, D, 0, 0, w_dtype, out_dtype,
+                      d_error, stream, d_out_ptrs, lN, F, feat0);
 }

@@ -63,6 +63,7 @@ class DLRM_Net(nn.Module):
         self.loss_threshold = loss_threshold
         self.bf16 = bf16
         self.fused_mlp = True
+        self.peer_exchange = None  # set by enable_peer_exchange(): fused a2a over NVLink peer memory
         ln_emb = np.asarray(ln_emb)
         if ext_dist.my_size > 1:
             n_emb = len(ln_emb)
@@ -135,6 +136,8 @@ class DLRM_Net(nn.Module):
         if batch_size < ext_dist.my_size:
             sys.exit("ERROR: batch_size (%d) must be larger than number of ranks (%d)"
                      % (batch_size, ext_dist.my_size))
+        if self.peer_exchange is not None:
+            return self._p2p_forward(dense_x, *emb_args)
         with torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.bf16):
             ly = self.apply_emb(self.emb_l, *emb_args)
             a2a_req = ext_dist.alltoall(ly, self.n_emb_per_rank)
@@ -145,6 +148,35 @@ class DLRM_Net(nn.Module):
             z = interaction_sharded(x, ly, pad_to=self.interaction_pad)
             p = self.apply_mlp(z, self.top_l)
         return self._clamp(p)
+
+
+def _p2p_forward(self, dense_x, *emb_args):
+    """distributed_forward with the all-to-all fused into the embedding kernels (cloudtik_b200.p2p)."""
+    from .p2p import sharded_emb_interact
+    if len(emb_args) == 3:
+        indices, offsets = emb_args[0], emb_args[1]
+    else:
+        lS_o, lS_i = emb_args
+        indices, offsets, _ = self.emb_l.linearize_indices_and_offsets(list(lS_i), list(lS_o), [False] * len(lS_i))
+    with torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.bf16):
+        x = self.apply_mlp(self._pad_dense(dense_x), self.bot_l)
+        z = sharded_emb_interact(x, self.emb_l, self.peer_exchange, indices, offsets,
+                                 1 + self.local_ln_emb_slice.start, pad_to=self.interaction_pad)
+        p = self.apply_mlp(z, self.top_l)
+    return self._clamp(p)
+
+
+DLRM_Net._p2p_forward = _p2p_forward
+
+
+def enable_peer_exchange(dlrm, local_batch: int):
+    """Switch a table-wise sharded DLRM_Net (one process per GPU on one NVLink box) to the fused
+    peer-memory exchange; ``local_batch`` = samples per rank (fixed: the buffers are symmetric)."""
+    from .p2p import PeerExchange
+    n_feat = 1 + dlrm.n_global_emb
+    dt = torch.bfloat16 if dlrm.bf16 else dlrm.emb_l.tables.dtype
+    dlrm.peer_exchange = PeerExchange(local_batch, n_feat, dlrm.emb_l.dim, dt, dlrm.emb_l.weights[0].device)
+    return dlrm.peer_exchange
 
 
 def train_step(dlrm, optimizer, X, emb_args, T, lr=None):

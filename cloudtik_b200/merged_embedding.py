@@ -257,6 +257,20 @@ class MergedEmbeddingBagWithSGD(nn.Module):
             ev.record(self._side_stream)
         self._prep_event = ev
 
+    def _apply_update_sharded(self, indices, offsets, B, exch, feat0):
+        """Backward of the peer-memory path (cloudtik_b200.p2p): gradients are read from every rank's dT."""
+        opt = ops.OPT_ADAGRAD if self.optimizer_kind == "adagrad" else ops.OPT_SGD
+        ws = self._workspace(indices.numel())
+        if self._prep_event is not None:
+            torch.cuda.current_stream().wait_event(self._prep_event)
+            self._prep_event = None
+        else:
+            ops.emb_bwd_prepare(self.tables, indices, offsets, B, ws, self.error_flag)
+        with self._timed("emb_bwd_apply"):
+            ops.emb_bwd_apply_sharded(self.tables, indices.numel(), B, exch.dT_ptrs_dev, exch.lN, exch.F, feat0,
+                                      exch.dtype, self.sgd_args.lr, ws, optimizer=opt, eps=self.eps,
+                                      lr_tensor=self.lr_tensor)
+
     def _apply_update(self, indices, offsets, B, grad_base, stride_table, stride_bag):
         opt = ops.OPT_ADAGRAD if self.optimizer_kind == "adagrad" else ops.OPT_SGD
         ws = self._workspace(indices.numel())

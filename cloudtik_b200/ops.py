@@ -166,6 +166,35 @@ def emb_bwd_apply(tables: TableSet, nnz: int, B: int, grad: torch.Tensor, stride
         ws.numel() * ws.element_size(), _stream()), "b200_emb_bwd_apply")
 
 
+def emb_fwd_sharded(tables: TableSet, indices, offsets, B: int, out_ptrs_dev: int, lN: int, F: int, feat0: int,
+                    out_dtype: torch.dtype, error: torch.Tensor | None = None):
+    """Pooled lookup of this rank's tables for the GLOBAL batch, written straight into every rank's
+    interaction input over peer memory.  ``out_ptrs_dev``: device address of the [world] pointer table.
+    See b200_emb_fwd_sharded."""
+    _cuda(indices, "indices", torch.int64)
+    _cuda(offsets, "offsets", torch.int64)
+    check(lib.b200_emb_fwd_sharded(tables.d_ptrs.data_ptr(), tables.d_rows.data_ptr(), indices.data_ptr(),
+                                   offsets.data_ptr(), out_ptrs_dev, indices.numel(), len(tables), B, tables.D,
+                                   lN, F, feat0, _dt(tables.dtype), _dt(out_dtype),
+                                   error.data_ptr() if error is not None else None, _stream()),
+          "b200_emb_fwd_sharded")
+
+
+def emb_bwd_apply_sharded(tables: TableSet, nnz: int, B: int, grad_ptrs_dev: int, lN: int, F: int, feat0: int,
+                          grad_dtype: torch.dtype, lr: float, ws: torch.Tensor, optimizer: int = OPT_SGD,
+                          eps: float = 1e-10, lr_tensor: torch.Tensor | None = None):
+    """Row update from a prepared ``ws`` with the gradient rows read from every rank's dT over peer memory.
+    See b200_emb_bwd_apply_sharded."""
+    if optimizer == OPT_ADAGRAD and tables.d_state_ptrs is None:
+        raise _lib.B200Error("Adagrad needs per-table fp32 state (TableSet.set_states)")
+    check(lib.b200_emb_bwd_apply_sharded(
+        tables.d_ptrs.data_ptr(), tables.d_state_ptrs.data_ptr() if tables.d_state_ptrs is not None else None,
+        tables.d_row_base.data_ptr(), nnz, grad_ptrs_dev, len(tables), B, tables.D, lN, F, feat0,
+        _dt(tables.dtype), _dt(grad_dtype), optimizer, float(lr),
+        lr_tensor.data_ptr() if lr_tensor is not None else None, float(eps), ws.data_ptr(),
+        ws.numel() * ws.element_size(), _stream()), "b200_emb_bwd_apply_sharded")
+
+
 def emb_bwd_coalesce(tables: TableSet, indices, offsets, B: int, grad: torch.Tensor, stride_table: int,
                      stride_bag: int, ws: torch.Tensor, error: torch.Tensor | None = None):
     """Coalesced sparse gradient of the pooled lookup: returns (unique_rows int64[U] global row ids ascending,

@@ -1,0 +1,82 @@
+"""Fused embedding + pooled all-to-all over NVLink peer memory (table-wise sharding, one process per GPU).
+
+The reference's ``distributed_forward`` (``P/dlrm_s_pytorch.py:342-369``) pools the local tables for the
+global batch, then ``ext_dist.alltoall`` (``P/extend_distributed.py:271-333``) converts table-sharded /
+global-batch into batch-sharded / all-tables, and autograd mirrors it for the gradients.  Here both
+exchanges disappear into the embedding kernels:
+
+* forward: ``b200_emb_fwd_sharded`` writes every pooled row directly into the DESTINATION rank's
+  interaction input ``T[lN, F, D]`` (a symmetric-memory buffer every rank maps), so after one
+  cross-rank barrier the tcgen05 interaction kernel reads its tile in place -- no send buffer, no
+  NCCL all-to-all, no re-packing copy;
+* backward: the interaction backward writes ``dT[lN, F, D]`` locally; after a barrier
+  ``b200_emb_bwd_apply_sharded`` gathers the gradient rows it needs from the owning ranks' ``dT`` while
+  it reduces and updates.
+
+Two barriers per step order everything (kernels are stream-ordered on each rank):
+  B1 after emb_fwd_sharded  : all rows of T have landed           (also: peers finished reading my dT)
+  B2 after interact_bwd     : all dT are complete                 (also: nobody still needs last T)
+Single box only (NVLink / NVSwitch peers); uses ``torch.distributed._symmetric_memory`` for the mapping.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+from . import ops
+
+
+class PeerExchange:
+    """Symmetric T / dT buffers of one model replica plus their per-rank pointer tables."""
+
+    def __init__(self, lN: int, F: int, D: int, dtype: torch.dtype, device):
+        import torch.distributed._symmetric_memory as symm
+        self.lN, self.F, self.D, self.dtype = lN, F, D, dtype
+        self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        group = dist.group.WORLD.group_name
+        self.T = symm.empty((lN, F, D), dtype=dtype, device=device)
+        self.dT = symm.empty((lN, F, D), dtype=dtype, device=device)
+        self.hT = symm.rendezvous(self.T, group)
+        self.hdT = symm.rendezvous(self.dT, group)
+        self.T_ptrs_dev = int(self.hT.buffer_ptrs_dev)
+        self.dT_ptrs_dev = int(self.hdT.buffer_ptrs_dev)
+        self.T.zero_()
+        self.dT.zero_()
+        torch.cuda.synchronize()
+        dist.barrier()
+
+    def barrier(self, channel: int = 0):
+        self.hT.barrier(channel=channel)
+
+
+class _ShardedEmbInteractFn(torch.autograd.Function):
+    """x [lN, D] (+ this rank's tables, global-batch indices) -> interaction output R [lN, ldr]."""
+
+    @staticmethod
+    def forward(ctx, x, trigger, emb, exch, indices, offsets, feat0, pad_to):
+        B_glob = exch.lN * exch.world
+        ops.emb_fwd_sharded(emb.tables, indices, offsets, B_glob, exch.T_ptrs_dev, exch.lN, exch.F, feat0, exch.dtype,
+                            emb.error_flag)
+        emb._launch_prepare(indices, offsets, B_glob)  # sort / dedup on the side stream
+        exch.T[:, 0].copy_(x)
+        exch.barrier(0)  # B1
+        R = ops.interact_fwd(exch.T, pad_to=pad_to)
+        ctx.emb, ctx.exch, ctx.feat0 = emb, exch, feat0
+        ctx.save_for_backward(indices, offsets)
+        ctx.x_dtype = x.dtype
+        return R
+
+    @staticmethod
+    def backward(ctx, dR):
+        emb, exch = ctx.emb, ctx.exch
+        indices, offsets = ctx.saved_tensors
+        B_glob = exch.lN * exch.world
+        ops.interact_bwd(exch.T, dR.contiguous().to(exch.dtype), out=exch.dT)
+        exch.barrier(1)  # B2
+        emb._apply_update_sharded(indices, offsets, B_glob, exch, ctx.feat0)
+        dx = exch.dT[:, 0].clone()  # dT is overwritten by the next step; the bottom MLP backward runs now
+        return dx.to(ctx.x_dtype), None, None, None, None, None, None, None
+
+
+def sharded_emb_interact(x, emb, exch: PeerExchange, indices, offsets, feat0: int, pad_to: int = 1):
+    return _ShardedEmbInteractFn.apply(x, emb._trigger, emb, exch, indices, offsets, feat0, pad_to)

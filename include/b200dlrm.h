@@ -144,6 +144,30 @@ int b200_emb_bwd_apply(void* const* d_weights, float* const* d_state, const int6
                        b200_stream_t stream);
 
 /*
+ * Table-wise sharded variants: the pooled-embedding all-to-all of the reference's distributed_forward
+ * (ext_dist.alltoall, P/dlrm_s_pytorch.py:351,354 -> P/extend_distributed.py:271-333) fused into the
+ * two embedding kernels over NVLink peer memory (one process per GPU, every rank maps every rank's
+ * buffers, e.g. torch symmetric memory / CUDA IPC):
+ *   fwd:   bag b (index in the GLOBAL batch) of local table t is written straight to its destination
+ *          rank r = b / lN:  d_out_ptrs[r] + ((b - r*lN) * F + feat0 + t) * D, i.e. into that rank's
+ *          interaction input T[lN, F, D] (feat0 = 1 + global id of this rank's first table);
+ *   apply: the gradient row of that bag is read from d_grad_ptrs[r] at the same offset of rank r's
+ *          dT[lN, F, D] (the mirror all-to-all of P/extend_distributed.py:323-333).
+ * The caller provides the cross-rank ordering: a barrier after every rank's fwd kernel before T is
+ * read, and one after every rank's interaction backward before apply reads the gradients.
+ * B (global batch) must be a multiple of lN; rows must be a multiple of 16 bytes.
+ */
+int b200_emb_fwd_sharded(const void* const* d_weights, const int64_t* d_rows, const int64_t* d_indices,
+                         const int64_t* d_offsets, void* const* d_out_ptrs, int64_t nnz, int64_t T,
+                         int64_t B, int64_t D, int64_t lN, int64_t F, int64_t feat0, int w_dtype,
+                         int out_dtype, int32_t* d_error, b200_stream_t stream);
+int b200_emb_bwd_apply_sharded(void* const* d_weights, float* const* d_state, const int64_t* d_row_base,
+                               int64_t nnz, const void* const* d_grad_ptrs, int64_t T, int64_t B,
+                               int64_t D, int64_t lN, int64_t F, int64_t feat0, int w_dtype,
+                               int grad_dtype, int optimizer, float lr, const float* d_lr, float eps,
+                               void* ws, size_t ws_bytes, b200_stream_t stream);
+
+/*
  * EmbeddingBag backward as a COALESCED sparse gradient (no optimiser fused): for callers that keep
  * the per-table `nn.EmbeddingBag(sparse=True)` seam of DLRM_Net.apply_emb (P/dlrm_s_pytorch.py:299-305)
  * and let torch.optim.SGD / Adagrad consume the sparse gradient (P/dlrm_s_pytorch.py:805,1059).

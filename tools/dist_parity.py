@@ -28,10 +28,11 @@ def main():
     ap.add_argument("--steps", type=int, default=4)
     ap.add_argument("--batch", type=int, default=512, help="GLOBAL batch")
     ap.add_argument("--ddp", action="store_true", help="wrap the MLPs in DDP instead of the flat all-reduce")
+    ap.add_argument("--p2p", action="store_true", help="fused embedding + all-to-all over NVLink peer memory")
     a = ap.parse_args()
 
     from cloudtik_b200 import ext_dist
-    from cloudtik_b200.dlrm import DLRM_Net
+    from cloudtik_b200.dlrm import DLRM_Net, enable_peer_exchange
     from oracle.dlrm_port import DLRMPort, train_step as cpu_step, uniform_batch
 
     ext_dist.init_distributed(backend="nccl")
@@ -54,6 +55,8 @@ def main():
         for dst, src in ((net.bot_l, port.bot_l), (net.top_l, port.top_l)):
             for pd, ps in zip(dst.parameters(), src.parameters()):
                 pd.copy_(ps)
+    if a.p2p:
+        enable_peer_exchange(net, a.batch // world)
     if a.ddp:
         net.bot_l = ext_dist.DDP(net.bot_l, device_ids=[dev.index])
         net.top_l = ext_dist.DDP(net.top_l, device_ids=[dev.index])
@@ -92,7 +95,7 @@ def main():
                                    atol=2e-3 if a.bf16 else 1e-6, err_msg=n1)
     ext_dist.barrier()
     if rank == 0:
-        print(f"dist parity ok: world={world} tables={len(rows)} bf16={a.bf16} steps={a.steps} "
+        print(f"dist parity ok: world={world} tables={len(rows)} bf16={a.bf16} p2p={a.p2p} steps={a.steps} "
               f"(losses and weights match the single-process oracle)")
     torch.distributed.destroy_process_group()
 
