@@ -88,7 +88,7 @@ def main():
     for k, t in enumerate(local):
         w = net.emb_l.weights[k].float().cpu().numpy()
         np.testing.assert_allclose(w, port.emb_l[t].weight.detach().numpy(), rtol=tol,
-                                   atol=2e-3 if a.bf16 else 1e-7, err_msg=f"table {t}")
+                                   atol=2e-3 if a.bf16 else 1e-6, err_msg=f"table {t}")  # abs: rows near zero
     top = net.top_l.module if a.ddp else net.top_l
     for (n1, p1), p2 in zip(top.named_parameters(), port.top_l.parameters()):
         np.testing.assert_allclose(p1.detach().cpu().numpy(), p2.detach().numpy(), rtol=10 * tol,
