@@ -12,7 +12,8 @@
  *     b200_last_error() returns a thread-local message for the last non-zero status.
  *   - the caller owns every buffer, including workspace (sizes from *_workspace_bytes).
  *   - calls are stream-ordered, never synchronise, never allocate: they may be captured
- *     in a CUDA graph.  The library keeps no global device state.
+ *     in a CUDA graph.  The library keeps no global device state (b200_sort_dedup_noalloc's
+ *     built-in scratch excepted).
  *   - element strides are in ELEMENTS of the buffer's dtype.
  */
 #ifndef B200DLRM_H_
