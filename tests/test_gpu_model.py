@@ -128,3 +128,29 @@ def test_per_table_embedding_bag_seam(opt_name):
         np.testing.assert_allclose(g._values().cpu().numpy(), gr.values().numpy(), rtol=1e-5, atol=1e-5)
         o_ref.step(), o_mine.step()
         np.testing.assert_allclose(mine.weight.detach().cpu().numpy(), ref.weight.detach().numpy(), rtol=1e-5, atol=1e-6)
+
+
+def test_train_entry_point_logs_and_checkpoint(tmp_path, capsys):
+    """python -m cloudtik_b200.train with the reference's flag names: progress / throughput lines in the
+    reference's format, checkpoint with the reference's state_dict keys, and a reload that continues."""
+    import re
+    from cloudtik_b200 import train
+    ck = str(tmp_path / "dlrm.pt")
+    flags = ["--arch-sparse-feature-size=16", "--arch-mlp-bot=13-64-16", "--arch-mlp-top=64-1",
+             "--arch-embedding-size=1000-37-5000-3", "--mini-batch-size=256", "--num-batches=6",
+             "--learning-rate=0.1", "--num-indices-per-lookup=3", "--print-freq=2", "--print-time",
+             "--lr-num-warmup-steps=2", "--lr-decay-start-step=4", "--lr-num-decay-steps=2", "--round-targets=True"]
+    net = train.run(flags + ["--save-model=" + ck])
+    out = capsys.readouterr().out
+    lines = re.findall(r"Finished training it (\d+)/6 of epoch 0, ([\d.]+) ms/it, loss ([\d.]+)", out)
+    assert [int(l[0]) for l in lines] == [2, 4, 6]
+    assert all(0.3 < float(l[2]) < 1.5 for l in lines)
+    assert re.search(r"Throughput: [\d.]+ fps", out) and "Saving model to" in out
+    sd = torch.load(ck, map_location="cpu")["state_dict"]
+    for k in ("emb_l.0.weight", "emb_l.3.weight", "bot_l.0.weight", "bot_l.2.bias", "top_l.0.weight", "top_l.2.bias"):
+        assert k in sd, k
+    assert tuple(sd["emb_l.2.weight"].shape) == (5000, 16) and tuple(sd["top_l.0.weight"].shape) == (64, 16 + 10)
+    net2 = train.run(flags + ["--load-model=" + ck, "--num-batches=8"])
+    out2 = capsys.readouterr().out
+    assert "Loaded model" in out2 and "it 8/8" in out2
+    assert not torch.equal(net2.emb_l.weights[0], net.emb_l.weights[0])  # kept training from the checkpoint

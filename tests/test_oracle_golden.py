@@ -150,3 +150,20 @@ def test_port_kaggle_c1_losses(golden):
         np.testing.assert_allclose(net.emb_l[t].weight.detach().numpy()[g[f"rows_t{t}"]],
                                    g[f"final_rows_t{t}"], rtol=1e-6, atol=1e-8)
     np.testing.assert_allclose(net.top_l[0].weight.detach().numpy()[:8], g["final_top0_w"], rtol=1e-5, atol=1e-7)
+
+
+def test_lr_scheduler_mirror_matches_reference_traces(golden):
+    """cloudtik_b200.lr.LRPolicyScheduler (the product's host-side mirror) against the traces the
+    reference's scheduler produced (tests/golden/lr_policy.npz)."""
+    from cloudtik_b200.lr import LRPolicyScheduler
+    g = golden("lr_policy")
+    p = torch.nn.Parameter(torch.zeros(1))
+    for c, (base, warm, start, nsteps) in enumerate(g["cfgs"]):
+        opt = torch.optim.SGD([p], lr=float(base))
+        sch = LRPolicyScheduler(opt, int(warm), int(start), int(nsteps))
+        got = []
+        for _ in range(20):
+            got.append(sch.get_last_lr()[0])
+            opt.step()
+            sch.step()
+        np.testing.assert_allclose(got, g[f"trace{c}"], rtol=1e-12)
