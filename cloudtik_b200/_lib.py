@@ -28,14 +28,14 @@ SIGNATURES = {
     "b200_sort_dedup": (_int, [_p, _p, _i64, _c.c_uint64, _p, _p, _p, _p, _p, _p, _c.c_size_t, _p]),
     "b200_sort_dedup_noalloc": (_int, [_p, _p, _i64, _c.c_uint64, _p, _p, _p, _p, _p, _p]),
     "b200_emb_bwd_workspace_bytes": (_c.c_size_t, [_i64, _i64]),
-    "b200_emb_bwd_update": (_int, [_p, _p, _p, _p, _p, _p, _i64, _p, _i64, _i64, _i64, _i64, _i64,
+    "b200_emb_bwd_update": (_int, [_p, _p, _p, _p, _p, _p, _p, _i64, _p, _i64, _i64, _i64, _i64, _i64,
                                    _int, _int, _int, _c.c_float, _p, _c.c_float, _i64, _p,
                                    _c.c_size_t, _p, _p]),
     "b200_emb_bwd_prepare": (_int, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _p, _c.c_size_t, _p, _p]),
-    "b200_emb_bwd_apply": (_int, [_p, _p, _p, _i64, _p, _i64, _i64, _i64, _i64, _i64, _int, _int, _int,
+    "b200_emb_bwd_apply": (_int, [_p, _p, _p, _p, _i64, _p, _i64, _i64, _i64, _i64, _i64, _int, _int, _int,
                                   _c.c_float, _p, _c.c_float, _p, _c.c_size_t, _p]),
     "b200_emb_fwd_sharded": (_int, [_p, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i64, _i64, _int, _int, _p, _p]),
-    "b200_emb_bwd_apply_sharded": (_int, [_p, _p, _p, _i64, _p, _i64, _i64, _i64, _i64, _i64, _i64, _int, _int, _int,
+    "b200_emb_bwd_apply_sharded": (_int, [_p, _p, _p, _p, _i64, _p, _i64, _i64, _i64, _i64, _i64, _i64, _int, _int, _int,
                                           _c.c_float, _p, _c.c_float, _p, _c.c_size_t, _p]),
     "b200_emb_bwd_coalesce": (_int, [_p, _p, _p, _p, _i64, _p, _i64, _i64, _i64, _i64, _i64, _int, _i64, _p, _p, _p,
                                      _p, _c.c_size_t, _p, _p]),

@@ -109,6 +109,9 @@ __global__ void __launch_bounds__(KEYS_THREADS)
 struct UpdParams {
   void* const* weights;
   float* const* state;
+  // bf16 tables with a 16-bit "trail": weight = upper half, trail = lower half of the fp32 master value
+  // (the reference's IPEX split-SGD storage, P/dlrm_s_pytorch.py:920-933); same [rows, D] layout
+  uint16_t* const* trail;
   const int64_t* row_base;
   const uint32_t *unique, *seg, *svals;
   const int32_t* num_unique;
@@ -211,11 +214,19 @@ struct GradVec<__nv_bfloat16, 4> {
 // Every weight row is written by exactly one group: deterministic, no atomics.
 template <int OPT, typename WT>
 __device__ __forceinline__ void apply_row(char* wp, float* sp, const float* acc, const float* w_in, float lr,
-                                          float eps) {
+                                          float eps, char* tp = nullptr, uint4 tv = make_uint4(0, 0, 0, 0)) {
   constexpr int VE = Vec16<WT>::VE;
   float w[VE];
 #pragma unroll
   for (int x = 0; x < VE; ++x) w[x] = w_in[x];
+  if constexpr (sizeof(WT) == 2) {
+    if (tp != nullptr) {  // exact fp32 master = (bf16 bits << 16) | trail bits
+      const uint32_t t4[4] = {tv.x, tv.y, tv.z, tv.w};
+#pragma unroll
+      for (int x = 0; x < VE; ++x)
+        w[x] = __uint_as_float(__float_as_uint(w[x]) | ((x & 1) ? (t4[x >> 1] >> 16) : (t4[x >> 1] & 0xffffu)));
+    }
+  }
   if (OPT == OPT_STORE) {
 #pragma unroll
     for (int x = 0; x < VE; ++x) w[x] = acc[x];
@@ -235,6 +246,20 @@ __device__ __forceinline__ void apply_row(char* wp, float* sp, const float* acc,
   } else {
 #pragma unroll
     for (int x = 0; x < VE; ++x) w[x] -= lr * acc[x];
+  }
+  if constexpr (sizeof(WT) == 2) {
+    if (tp != nullptr) {  // split back: upper half -> bf16 table (truncation keeps hi|lo exact), lower -> trail
+      uint32_t hi[4], lo[4];
+#pragma unroll
+      for (int x = 0; x < 4; ++x) {
+        const uint32_t a = __float_as_uint(w[2 * x]), b = __float_as_uint(w[2 * x + 1]);
+        hi[x] = (a >> 16) | (b & 0xffff0000u);
+        lo[x] = (a & 0xffffu) | (b << 16);
+      }
+      st_v4(wp, make_uint4(hi[0], hi[1], hi[2], hi[3]));
+      st_v4(tp, make_uint4(lo[0], lo[1], lo[2], lo[3]));
+      return;
+    }
   }
   store_vec<WT, VE, false>(reinterpret_cast<WT*>(wp), w);
 }
@@ -256,6 +281,7 @@ __global__ void __launch_bounds__(UPD_THREADS) window_update_kernel(const UpdPar
   __shared__ int64_t s_base[UPD_TMAX];
   __shared__ char* s_wptr[UPD_TMAX];
   __shared__ float* s_sptr[UPD_TMAX];
+  __shared__ int64_t s_tdelta[UPD_TMAX];  // trail base - weight base (bytes), 0 = no trail
   __shared__ uint32_t s_key[NG][C + 2];  // [0] = key before the window, [C+1] = key after it
   __shared__ int64_t s_goff[NG][C];      // address of the gradient row of each position
   __shared__ uint16_t s_tab[NG][C];
@@ -266,8 +292,11 @@ __global__ void __launch_bounds__(UPD_THREADS) window_update_kernel(const UpdPar
       s_base[i] = p.row_base[i];
       s_wptr[i] = static_cast<char*>(p.weights[i]);
       s_sptr[i] = (OPT == B200_OPT_ADAGRAD) ? p.state[i] : nullptr;
+      s_tdelta[i] = (sizeof(WT) == 2 && p.trail != nullptr)
+                        ? reinterpret_cast<char*>(p.trail[i]) - static_cast<char*>(p.weights[i]) : 0;
     }
   }
+  const bool has_trail = sizeof(WT) == 2 && p.trail != nullptr;
   const int64_t w = (int64_t)blockIdx.x * NG + gid;
   const int64_t a = w * C;
   const int cnt = a < p.n ? (int)min((int64_t)C, p.n - a) : 0;
@@ -308,6 +337,8 @@ __global__ void __launch_bounds__(UPD_THREADS) window_update_kernel(const UpdPar
   for (int c0 = 0; c0 < cnt; c0 += BS) {
     GradVec<GT, VE> g[BS][NV];
     uint4 wv[RED ? 1 : BS][NV];
+    uint4 tv[(RED || sizeof(WT) != 2) ? 1 : BS][NV];  // trail halves of the rows in wv
+    int64_t tdel[(RED || sizeof(WT) != 2) ? 1 : BS];
     char* wp[RED ? 1 : BS];
     float* sp[RED ? 1 : BS];
     bool ends[BS], closed[BS];
@@ -348,6 +379,14 @@ __global__ void __launch_bounds__(UPD_THREADS) window_update_kernel(const UpdPar
 #pragma unroll
             for (int k = 0; k < NV; ++k)
               if (lane + k * G < p.V) wv[c][k] = ld_v4(wp[c] + (size_t)k * G * 16);
+            if constexpr (sizeof(WT) == 2) {
+              tdel[c] = !has_trail ? 0
+                        : (cached ? s_tdelta[tt] : reinterpret_cast<char*>(p.trail[tt]) - static_cast<char*>(p.weights[tt]));
+#pragma unroll
+              for (int k = 0; k < NV; ++k)
+                tv[c][k] = (has_trail && lane + k * G < p.V) ? ld_v4(wp[c] + tdel[c] + (size_t)k * G * 16)
+                                                             : make_uint4(0, 0, 0, 0);
+            }
           }
         }
       }
@@ -379,8 +418,13 @@ __global__ void __launch_bounds__(UPD_THREADS) window_update_kernel(const UpdPar
               } else {
                 float wf[VE];
                 Vec16<WT>::unpack(wf, wv[c][k]);
-                apply_row<OPT, WT>(wp[c] + (size_t)k * G * 16, sp[c] ? sp[c] + k * G * VE : nullptr, acc[k], wf, lr,
-                                   p.eps);
+                if constexpr (sizeof(WT) == 2) {
+                  apply_row<OPT, WT>(wp[c] + (size_t)k * G * 16, sp[c] ? sp[c] + k * G * VE : nullptr, acc[k], wf, lr,
+                                     p.eps, has_trail ? wp[c] + tdel[c] + (size_t)k * G * 16 : nullptr, tv[c][k]);
+                } else {
+                  apply_row<OPT, WT>(wp[c] + (size_t)k * G * 16, sp[c] ? sp[c] + k * G * VE : nullptr, acc[k], wf, lr,
+                                     p.eps);
+                }
               }
             }
           }
@@ -479,13 +523,23 @@ __global__ void __launch_bounds__(UPD_THREADS) window_join_kernel(const UpdParam
     wp = static_cast<char*>(p.weights[tt]) + ((size_t)row * p.D + lane * VE) * sizeof(WT);
     if (OPT == B200_OPT_ADAGRAD) sp = p.state[tt] + (size_t)row * p.D + lane * VE;
   }
-  uint4 wv[NV];
+  uint4 wv[NV], tv[NV];
+  char* tp = nullptr;
 #pragma unroll
-  for (int kk = 0; kk < NV; ++kk) wv[kk] = make_uint4(0, 0, 0, 0);
+  for (int kk = 0; kk < NV; ++kk) wv[kk] = tv[kk] = make_uint4(0, 0, 0, 0);
   if constexpr (!RED && OPT != OPT_STORE) {
 #pragma unroll
     for (int kk = 0; kk < NV; ++kk)
       if (lane + kk * G < p.V) wv[kk] = ld_v4(wp + (size_t)kk * G * 16);
+    if constexpr (sizeof(WT) == 2) {
+      if (p.trail != nullptr) {
+        const uint32_t tt2 = p.first_val[u] / p.B;
+        tp = wp + (reinterpret_cast<char*>(p.trail[tt2]) - static_cast<char*>(p.weights[tt2]));
+#pragma unroll
+        for (int kk = 0; kk < NV; ++kk)
+          if (lane + kk * G < p.V) tv[kk] = ld_v4(tp + (size_t)kk * G * 16);
+      }
+    }
   }
   float acc[NV][VE];
 #pragma unroll
@@ -505,7 +559,8 @@ __global__ void __launch_bounds__(UPD_THREADS) window_join_kernel(const UpdParam
       } else {
         float wf[VE];
         Vec16<WT>::unpack(wf, wv[kk]);
-        apply_row<OPT, WT>(wp + (size_t)kk * G * 16, sp ? sp + kk * G * VE : nullptr, acc[kk], wf, lr, p.eps);
+        apply_row<OPT, WT>(wp + (size_t)kk * G * 16, sp ? sp + kk * G * VE : nullptr, acc[kk], wf, lr, p.eps,
+                           tp ? tp + (size_t)kk * G * 16 : nullptr, tv[kk]);
       }
     }
 }
@@ -574,6 +629,8 @@ __global__ void emb_update_scalar_kernel(const UpdParams p, int64_t n_max) {
     }
     WT* w = static_cast<WT*>(p.weights[t]) + row * p.D + d;
     float wv = to_f32<WT>(*w);
+    uint16_t* tr = (sizeof(WT) == 2 && p.trail != nullptr) ? p.trail[t] + row * p.D + d : nullptr;
+    if (tr) wv = __uint_as_float(__float_as_uint(wv) | *tr);
     if (OPT == B200_OPT_ADAGRAD) {
       float* sp = p.state[t] + row * p.D + d;
       const float st = *sp + acc * acc;
@@ -582,7 +639,13 @@ __global__ void emb_update_scalar_kernel(const UpdParams p, int64_t n_max) {
     } else {
       wv -= lr * acc;
     }
-    *w = from_f32<WT>(wv);
+    if (tr) {
+      const uint32_t bits = __float_as_uint(wv);
+      *reinterpret_cast<uint16_t*>(w) = (uint16_t)(bits >> 16);
+      *tr = (uint16_t)(bits & 0xffffu);
+    } else {
+      *w = from_f32<WT>(wv);
+    }
   }
 }
 
@@ -680,7 +743,8 @@ extern "C" int b200_emb_bwd_prepare(const int64_t* d_rows, const int64_t* d_row_
   return dedup_runs(L.skeys, nnz, L.unique, L.seg, L.num_unique, L.sort_ws, st, L.win_run, L.svals, L.first_val);
 }
 
-static int emb_bwd_apply_impl(void* const* d_weights, float* const* d_state, const int64_t* d_row_base,
+static int emb_bwd_apply_impl(void* const* d_weights, float* const* d_state, uint16_t* const* d_trail,
+                              const int64_t* d_row_base,
                               int64_t nnz, const void* d_grad, int64_t T, int64_t B, int64_t D,
                               int64_t grad_stride_table, int64_t grad_stride_bag, int w_dtype, int grad_dtype,
                               int optimizer, float lr, const float* d_lr, float eps, void* ws, size_t ws_bytes,
@@ -703,6 +767,7 @@ static int emb_bwd_apply_impl(void* const* d_weights, float* const* d_state, con
   UpdParams p;
   p.weights = d_weights;
   p.state = d_state;
+  p.trail = (w_dtype == B200_BF16) ? d_trail : nullptr;
   p.row_base = d_row_base;
   p.unique = L.unique;
   p.seg = L.seg;
@@ -749,30 +814,30 @@ static int emb_bwd_apply_impl(void* const* d_weights, float* const* d_state, con
 #undef B200_UPD_DISPATCH
 }
 
-extern "C" int b200_emb_bwd_apply(void* const* d_weights, float* const* d_state,
+extern "C" int b200_emb_bwd_apply(void* const* d_weights, float* const* d_state, uint16_t* const* d_trail,
                                   const int64_t* d_row_base, int64_t nnz, const void* d_grad, int64_t T,
                                   int64_t B, int64_t D, int64_t grad_stride_table,
                                   int64_t grad_stride_bag, int w_dtype, int grad_dtype, int optimizer,
                                   float lr, const float* d_lr, float eps, void* ws, size_t ws_bytes,
                                   b200_stream_t stream) {
   B200_REQUIRE(d_grad != nullptr || nnz == 0, B200_EINVAL, "emb_bwd_apply: null gradient");
-  return emb_bwd_apply_impl(d_weights, d_state, d_row_base, nnz, d_grad, T, B, D, grad_stride_table,
+  return emb_bwd_apply_impl(d_weights, d_state, d_trail, d_row_base, nnz, d_grad, T, B, D, grad_stride_table,
                             grad_stride_bag, w_dtype, grad_dtype, optimizer, lr, d_lr, eps, ws, ws_bytes, stream,
                             nullptr, 0, 0, 0);
 }
 
 extern "C" int b200_emb_bwd_apply_sharded(void* const* d_weights, float* const* d_state,
-                                          const int64_t* d_row_base, int64_t nnz,
+                                          uint16_t* const* d_trail, const int64_t* d_row_base, int64_t nnz,
                                           const void* const* d_grad_ptrs, int64_t T, int64_t B, int64_t D,
                                           int64_t lN, int64_t F, int64_t feat0, int w_dtype, int grad_dtype,
                                           int optimizer, float lr, const float* d_lr, float eps, void* ws,
                                           size_t ws_bytes, b200_stream_t stream) {
   B200_REQUIRE(d_grad_ptrs != nullptr, B200_EINVAL, "emb_bwd_apply_sharded: null pointer table");
-  return emb_bwd_apply_impl(d_weights, d_state, d_row_base, nnz, nullptr, T, B, D, 0, 0, w_dtype, grad_dtype,
-                            optimizer, lr, d_lr, eps, ws, ws_bytes, stream, d_grad_ptrs, lN, F, feat0);
+  return emb_bwd_apply_impl(d_weights, d_state, d_trail, d_row_base, nnz, nullptr, T, B, D, 0, 0, w_dtype,
+                            grad_dtype, optimizer, lr, d_lr, eps, ws, ws_bytes, stream, d_grad_ptrs, lN, F, feat0);
 }
 
-extern "C" int b200_emb_bwd_update(void* const* d_weights, float* const* d_state,
+extern "C" int b200_emb_bwd_update(void* const* d_weights, float* const* d_state, uint16_t* const* d_trail,
                                    const int64_t* d_rows, const int64_t* d_row_base,
                                    const int64_t* d_indices, const int64_t* d_offsets, int64_t nnz,
                                    const void* d_grad, int64_t T, int64_t B, int64_t D,
@@ -783,7 +848,7 @@ extern "C" int b200_emb_bwd_update(void* const* d_weights, float* const* d_state
   int rc = b200_emb_bwd_prepare(d_rows, d_row_base, d_indices, d_offsets, nnz, T, B, D, total_rows, ws,
                                 ws_bytes, d_error, stream);
   if (rc) return rc;
-  return b200_emb_bwd_apply(d_weights, d_state, d_row_base, nnz, d_grad, T, B, D, grad_stride_table,
+  return b200_emb_bwd_apply(d_weights, d_state, d_trail, d_row_base, nnz, d_grad, T, B, D, grad_stride_table,
                             grad_stride_bag, w_dtype, grad_dtype, optimizer, lr, d_lr, eps, ws, ws_bytes,
                             stream);
 }

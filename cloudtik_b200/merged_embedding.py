@@ -181,14 +181,42 @@ class MergedEmbeddingBagWithSGD(nn.Module):
         iwro = torch.cat([i + base[t] for t, i in enumerate(idx)])
         return lin_idx, lin_off, iwro
 
-    def to_bfloat16_train(self):
-        """Store the tables in bf16 (halves gather traffic).  NOTE: plain bf16 rows, the
-        reference's split hi/lo 'trail' storage (P/dlrm_s_pytorch.py:920-933) is not kept yet."""
+    def to_bfloat16_train(self, keep_trail: bool = True):
+        """Store the tables in bf16: the forward gathers half the bytes.  With ``keep_trail`` (default,
+        the reference's split-SGD storage, P/dlrm_s_pytorch.py:920-933) every table keeps the LOWER 16 bits
+        of its fp32 master weights in a side tensor (``sgd_args.bf16_trail``): the fused update rebuilds the
+        fp32 value, updates it exactly and splits it again, so no small update is ever rounded away.
+        Without it the rows are plain bf16, rounded to nearest after each update."""
+        trails = []
         for k in range(self.n_tables):
             h = getattr(self, str(k))
-            h.weight = nn.Parameter(h.weight.data.to(torch.bfloat16), requires_grad=False)
+            w = h.weight.data
+            if w.dtype != torch.float32:
+                raise RuntimeError("to_bfloat16_train expects fp32 tables")
+            if keep_trail:
+                bits = w.view(torch.int32)
+                trails.append((bits & 0xFFFF).to(torch.int16))             # low half (bit pattern)
+                hi = (bits >> 16).to(torch.int16).view(torch.bfloat16)     # high half = truncated bf16
+            else:
+                hi = w.to(torch.bfloat16)
+            h.weight = nn.Parameter(hi.contiguous(), requires_grad=False)
         self._rebuild_tables()
+        if keep_trail:
+            self.tables.set_trails(trails)
+            self.sgd_args = self.sgd_args._replace(bf16_trail=trails)
         return self
+
+    def master_weights(self):
+        """fp32 view of the tables (exact when the trail is kept)."""
+        out = []
+        for k, w in enumerate(self.weights):
+            if w.dtype == torch.bfloat16 and self.tables.trails is not None:
+                hi = w.view(torch.int16).to(torch.int32) << 16
+                lo = self.tables.trails[k].to(torch.int32) & 0xFFFF
+                out.append((hi | lo).view(torch.float32))
+            else:
+                out.append(w.float())
+        return out
 
     def forward(self, input, need_linearize_indices_and_offsets=None):
         need = True if need_linearize_indices_and_offsets is None else bool(need_linearize_indices_and_offsets)
@@ -211,8 +239,12 @@ class MergedEmbeddingBagWithSGD(nn.Module):
 
     # ---- internals -----------------------------------------------------------------
     def _rebuild_tables(self):
-        states = self.tables.states if getattr(self, "tables", None) is not None else None
+        old = getattr(self, "tables", None)
+        states = old.states if old is not None else None
+        trails = old.trails if old is not None else None
         self.tables = ops.TableSet(self.weights, states)
+        if trails is not None and self.tables.dtype == torch.bfloat16:
+            self.tables.set_trails(trails)
 
     def _apply(self, fn, *a, **k):  # keep the device pointer table valid after .to()/.cuda()
         r = super()._apply(fn, *a, **k)

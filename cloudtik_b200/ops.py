@@ -58,8 +58,17 @@ class TableSet:
         self.d_row_base = torch.tensor(base, dtype=torch.int64, device=self.device)
         self.states = None
         self.d_state_ptrs = None
+        self.trails = None
+        self.d_trail_ptrs = None
         if states is not None:
             self.set_states(states)
+
+    def set_trails(self, trails):
+        """bf16 tables: int16/uint16-bit-pattern [rows, D] tensors holding the low halves of the fp32 masters."""
+        for t_, w in zip(trails, self.weights):
+            assert t_.is_cuda and t_.shape == w.shape and t_.is_contiguous() and t_.element_size() == 2
+        self.trails = list(trails)
+        self.d_trail_ptrs = torch.tensor([t_.data_ptr() for t_ in trails], dtype=torch.int64, device=self.device)
 
     def set_states(self, states):
         for s, w in zip(states, self.weights):
@@ -132,6 +141,7 @@ def emb_bwd_update(tables: TableSet, indices, offsets, B: int, grad: torch.Tenso
     check(lib.b200_emb_bwd_update(
         tables.d_ptrs.data_ptr(),
         tables.d_state_ptrs.data_ptr() if tables.d_state_ptrs is not None else None,
+        tables.d_trail_ptrs.data_ptr() if tables.d_trail_ptrs is not None else None,
         tables.d_rows.data_ptr(), tables.d_row_base.data_ptr(), indices.data_ptr(), offsets.data_ptr(),
         indices.numel(), grad.data_ptr(), T, B, tables.D, stride_table, stride_bag, _dt(tables.dtype),
         _dt(grad.dtype), optimizer, float(lr), lr_tensor.data_ptr() if lr_tensor is not None else None,
@@ -160,6 +170,7 @@ def emb_bwd_apply(tables: TableSet, nnz: int, B: int, grad: torch.Tensor, stride
         raise _lib.B200Error("Adagrad needs per-table fp32 state (TableSet.set_states)")
     check(lib.b200_emb_bwd_apply(
         tables.d_ptrs.data_ptr(), tables.d_state_ptrs.data_ptr() if tables.d_state_ptrs is not None else None,
+        tables.d_trail_ptrs.data_ptr() if tables.d_trail_ptrs is not None else None,
         tables.d_row_base.data_ptr(), nnz, grad.data_ptr(), len(tables), B, tables.D, stride_table, stride_bag,
         _dt(tables.dtype), _dt(grad.dtype), optimizer, float(lr),
         lr_tensor.data_ptr() if lr_tensor is not None else None, float(eps), ws.data_ptr(),
@@ -189,6 +200,7 @@ def emb_bwd_apply_sharded(tables: TableSet, nnz: int, B: int, grad_ptrs_dev: int
         raise _lib.B200Error("Adagrad needs per-table fp32 state (TableSet.set_states)")
     check(lib.b200_emb_bwd_apply_sharded(
         tables.d_ptrs.data_ptr(), tables.d_state_ptrs.data_ptr() if tables.d_state_ptrs is not None else None,
+        tables.d_trail_ptrs.data_ptr() if tables.d_trail_ptrs is not None else None,
         tables.d_row_base.data_ptr(), nnz, grad_ptrs_dev, len(tables), B, tables.D, lN, F, feat0,
         _dt(tables.dtype), _dt(grad_dtype), optimizer, float(lr),
         lr_tensor.data_ptr() if lr_tensor is not None else None, float(eps), ws.data_ptr(),

@@ -115,12 +115,18 @@ int b200_sort_dedup_noalloc(const uint32_t* d_keys, const uint32_t* d_vals, int6
  *   d_row_base  int64 [T+1] exclusive prefix sum of table row counts
  *   d_grad      grad of the pooled output, addressed like d_out of b200_emb_fwd
  *   d_state     Adagrad: device array [T] of fp32 state_sum tables; SGD: NULL
+ *   d_trail     bf16 tables only, optional: device array [T] of uint16 [rows_t, D] tables holding the
+ *               LOWER 16 bits of the fp32 master weights (the bf16 table holds the upper 16): the
+ *               update is then exact in fp32 while the forward gathers half the bytes -- the
+ *               split-SGD storage of the reference's to_bfloat16_train() (P/dlrm_s_pytorch.py:920-933).
+ *               NULL: plain bf16 rows, rounded to nearest after the update.
  *   lr / d_lr   learning rate by value, or (if d_lr != NULL) read from device memory at
  *               kernel time so a captured graph follows the LR schedule
  *   ws          b200_emb_bwd_workspace_bytes(nnz, D) bytes
  */
 size_t b200_emb_bwd_workspace_bytes(int64_t nnz, int64_t D);
-int b200_emb_bwd_update(void* const* d_weights, float* const* d_state, const int64_t* d_rows,
+int b200_emb_bwd_update(void* const* d_weights, float* const* d_state, uint16_t* const* d_trail,
+                        const int64_t* d_rows,
                         const int64_t* d_row_base, const int64_t* d_indices,
                         const int64_t* d_offsets, int64_t nnz, const void* d_grad, int64_t T,
                         int64_t B, int64_t D, int64_t grad_stride_table, int64_t grad_stride_bag,
@@ -138,7 +144,8 @@ int b200_emb_bwd_prepare(const int64_t* d_rows, const int64_t* d_row_base, const
                          const int64_t* d_offsets, int64_t nnz, int64_t T, int64_t B, int64_t D,
                          int64_t total_rows, void* ws, size_t ws_bytes, int32_t* d_error,
                          b200_stream_t stream);
-int b200_emb_bwd_apply(void* const* d_weights, float* const* d_state, const int64_t* d_row_base,
+int b200_emb_bwd_apply(void* const* d_weights, float* const* d_state, uint16_t* const* d_trail,
+                       const int64_t* d_row_base,
                        int64_t nnz, const void* d_grad, int64_t T, int64_t B, int64_t D,
                        int64_t grad_stride_table, int64_t grad_stride_bag, int w_dtype, int grad_dtype,
                        int optimizer, float lr, const float* d_lr, float eps, void* ws, size_t ws_bytes,
@@ -162,7 +169,8 @@ int b200_emb_fwd_sharded(const void* const* d_weights, const int64_t* d_rows, co
                          const int64_t* d_offsets, void* const* d_out_ptrs, int64_t nnz, int64_t T,
                          int64_t B, int64_t D, int64_t lN, int64_t F, int64_t feat0, int w_dtype,
                          int out_dtype, int32_t* d_error, b200_stream_t stream);
-int b200_emb_bwd_apply_sharded(void* const* d_weights, float* const* d_state, const int64_t* d_row_base,
+int b200_emb_bwd_apply_sharded(void* const* d_weights, float* const* d_state, uint16_t* const* d_trail,
+                               const int64_t* d_row_base,
                                int64_t nnz, const void* const* d_grad_ptrs, int64_t T, int64_t B,
                                int64_t D, int64_t lN, int64_t F, int64_t feat0, int w_dtype,
                                int grad_dtype, int optimizer, float lr, const float* d_lr, float eps,

@@ -127,7 +127,10 @@ def test_per_table_embedding_bag_seam(opt_name):
         np.testing.assert_array_equal(g._indices().cpu().numpy(), gr.indices().numpy())
         np.testing.assert_allclose(g._values().cpu().numpy(), gr.values().numpy(), rtol=1e-5, atol=1e-5)
         o_ref.step(), o_mine.step()
-        np.testing.assert_allclose(mine.weight.detach().cpu().numpy(), ref.weight.detach().numpy(), rtol=1e-5, atol=1e-6)
+        # the optimisers are torch's own (CPU vs CUDA sparse kernels); Adagrad's CUDA path is allowed a
+        # looser bound than the gradient it was fed (checked to 1e-5 above)
+        tol = dict(rtol=1e-5, atol=1e-6) if opt_name == "sgd" else dict(rtol=1e-4, atol=5e-5)
+        np.testing.assert_allclose(mine.weight.detach().cpu().numpy(), ref.weight.detach().numpy(), **tol)
 
 
 def test_train_entry_point_logs_and_checkpoint(tmp_path, capsys):
@@ -154,3 +157,28 @@ def test_train_entry_point_logs_and_checkpoint(tmp_path, capsys):
     out2 = capsys.readouterr().out
     assert "Loaded model" in out2 and "it 8/8" in out2
     assert not torch.equal(net2.emb_l.weights[0], net.emb_l.weights[0])  # kept training from the checkpoint
+
+
+def test_to_bfloat16_train_keeps_fp32_master():
+    """MergedEmbeddingBagWithSGD.to_bfloat16_train(): bf16 lookups, fp32-exact fused updates (trail)."""
+    from cloudtik_b200.merged_embedding import MergedEmbeddingBagWithSGD
+    rs = np.random.RandomState(4)
+    rows, D, B, lr = [500, 7, 3000], 64, 400, 1e-3
+    Ws = [rs.uniform(-0.5, 0.5, size=(n, D)).astype(np.float32) for n in rows]
+    m = MergedEmbeddingBagWithSGD([torch.tensor(W).cuda() for W in Ws], lr=lr).to_bfloat16_train()
+    assert m.weights[0].dtype == torch.bfloat16 and len(m.sgd_args.bf16_trail) == 3
+    for a, W in zip(m.master_weights(), Ws):
+        np.testing.assert_array_equal(a.cpu().numpy(), W)          # split is lossless
+    idx = [torch.tensor(rs.randint(0, n, size=B)).cuda() for n in rows]
+    off = [torch.arange(B).cuda() for _ in rows]
+    ly = m((idx, off, [False] * 3), torch.BoolTensor([True]))
+    for t in range(3):  # forward reads the truncated-bf16 table
+        trunc = (torch.tensor(Ws[t]).view(torch.int32) & ~0xFFFF).view(torch.float32).numpy()
+        np.testing.assert_array_equal(ly[t].detach().float().cpu().numpy(), trunc[idx[t].cpu().numpy()])
+    g = [torch.tensor(rs.randn(B, D).astype(np.float32)).bfloat16().cuda() for _ in rows]
+    torch.autograd.backward(ly, g)
+    for t in range(3):
+        G = np.zeros((rows[t], D))
+        np.add.at(G, idx[t].cpu().numpy(), g[t].float().cpu().numpy().astype(np.float64))
+        np.testing.assert_allclose(m.master_weights()[t].cpu().numpy(), (Ws[t] - lr * G).astype(np.float32),
+                                   rtol=2e-5, atol=1e-6)

@@ -255,6 +255,54 @@ def test_emb_bwd_hot_window_boundaries():
     np.testing.assert_array_equal(W.cpu().numpy(), want)
 
 
+@pytest.mark.parametrize("opt", ["sgd", "adagrad"])
+def test_bf16_tables_with_trail_update_in_fp32(opt):
+    """bf16 tables + 16-bit trail (the reference's split-SGD storage): the fused update must behave like
+    an fp32 update -- tiny steps that a plain bf16 row would round away accumulate exactly."""
+    ops = _ops()
+    rs = np.random.RandomState(12)
+    rows, B, D, lr = [3, 900, 50], 700, 128, 1e-4
+    Ws = [rs.uniform(-1, 1, size=(n, D)).astype(np.float32) for n in rows]
+    his, los = [], []
+    for W in Ws:
+        bits = torch.tensor(W).view(torch.int32)
+        his.append((bits >> 16).to(torch.int16).view(torch.bfloat16).cuda().contiguous())
+        los.append((bits & 0xFFFF).to(torch.int16).cuda().contiguous())
+    ts = ops.TableSet(his)
+    ts.set_trails(los)
+    states = None
+    if opt == "adagrad":
+        ts.set_states([torch.zeros(n, D, device="cuda") for n in rows])
+        states = [np.zeros((n, D), np.float32) for n in rows]
+    T, F = len(rows), len(rows) + 1
+    Wref = [W.copy() for W in Ws]
+    ws = None
+    for step in range(3):
+        idx_l, off_l = _make_bags(rs, rows, B, 2, True)
+        indices, offsets, _ = ref.linearize_indices_and_offsets(idx_l, off_l, rows)
+        g = torch.tensor(rs.randn(B, F, D).astype(np.float32)).cuda()
+        ws = torch.empty(ops.emb_bwd_workspace_bytes(len(indices), D), dtype=torch.uint8, device="cuda")
+        ops.emb_bwd_update(ts, torch.tensor(indices).cuda(), torch.tensor(offsets).cuda(), B, g[:, 1:], D, F * D,
+                           lr=lr, ws=ws, optimizer=ops.OPT_ADAGRAD if opt == "adagrad" else ops.OPT_SGD)
+        gr = g.cpu().numpy()
+        for t in range(T):
+            if opt == "adagrad":
+                ref.sparse_adagrad_update(Wref[t], states[t], idx_l[t], off_l[t], gr[:, 1 + t], lr, 1e-10)
+            else:
+                G = np.zeros((rows[t], D))
+                np.add.at(G, idx_l[t], gr[:, 1 + t][ref.offset2bag(off_l[t], len(idx_l[t]))].astype(np.float64))
+                Wref[t] = (Wref[t] - lr * G).astype(np.float32)
+    torch.cuda.synchronize()
+    for t in range(T):
+        hi = his[t].view(torch.int16).to(torch.int32) << 16
+        lo = los[t].to(torch.int32) & 0xFFFF
+        got = (hi | lo).view(torch.float32).cpu().numpy()
+        np.testing.assert_allclose(got, Wref[t], rtol=2e-5, atol=1e-6)
+        # a plain bf16 row could not have followed: the accumulated change is below bf16 resolution
+        moved = np.abs(got - Ws[t]) > 0
+        assert moved.any() and np.abs(got - Ws[t])[moved].min() < 1e-3
+
+
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_interaction_golden(golden, dtype):
     ops = _ops()
