@@ -56,7 +56,7 @@ class DLRM_Net(nn.Module):
 
     def __init__(self, m_spa=None, ln_emb=None, ln_bot=None, ln_top=None, sigmoid_bot=-1, sigmoid_top=-1,
                  weighted_pooling=None, loss_threshold=0.0, np_init_emb_weight=False, device="cuda",
-                 lr=0.01, emb_optimizer="sgd", bf16=False):
+                 lr=0.01, emb_optimizer="sgd", bf16=False, n_rowwise=0):
         super().__init__()
         if weighted_pooling is not None:
             raise NotImplementedError("weighted pooling is not on the reference's product path")
@@ -65,9 +65,13 @@ class DLRM_Net(nn.Module):
         self.fused_mlp = True
         self.peer_exchange = None  # set by enable_peer_exchange(): fused a2a over NVLink peer memory
         ln_emb = np.asarray(ln_emb)
+        # the LAST n_rowwise tables are row-wise sharded over the ranks (hot tables, config 5); the others
+        # are partitioned table-wise exactly like the reference (P/dlrm_s_pytorch.py:256-264)
+        self.n_rowwise = int(n_rowwise) if ext_dist.my_size > 1 else 0
+        self.rowwise = None
         if ext_dist.my_size > 1:
-            n_emb = len(ln_emb)
-            self.n_global_emb = n_emb
+            n_emb = len(ln_emb) - self.n_rowwise
+            self.n_global_emb = len(ln_emb)
             self.rank = ext_dist.dist.get_rank()
             self.ln_emb = [i for i in range(n_emb)]
             self.n_local_emb, self.n_emb_per_rank = ext_dist.get_split_lengths(n_emb)
@@ -82,6 +86,12 @@ class DLRM_Net(nn.Module):
         self.interaction_pad = 8  # interaction output rounded up to a multiple of 8 columns
         self.emb_l = self.create_emb(m_spa, ln_emb, self.local_ln_emb, np_init_emb_weight, device, lr,
                                      emb_optimizer)
+        if self.n_rowwise:
+            from .rowwise import RowWiseShardedTables
+            hot = [int(n) for n in ln_emb[len(ln_emb) - self.n_rowwise:]]
+            self.rowwise = RowWiseShardedTables(hot, m_spa, ext_dist.my_size, self.rank, device, lr=lr,
+                                                optimizer=emb_optimizer,
+                                                out_dtype=torch.bfloat16 if bf16 else None)
         if bf16:
             self.emb_l.output_dtype = torch.bfloat16
         if ext_dist.my_size > 1:
@@ -153,15 +163,21 @@ class DLRM_Net(nn.Module):
 def _p2p_forward(self, dense_x, *emb_args):
     """distributed_forward with the all-to-all fused into the embedding kernels (cloudtik_b200.p2p)."""
     from .p2p import sharded_emb_interact
-    if len(emb_args) == 3:
+    rw_i = rw_o = None
+    if len(emb_args) >= 3:
         indices, offsets = emb_args[0], emb_args[1]
+        if len(emb_args) == 5:  # (+ linearised GLOBAL-batch bags of the row-wise sharded hot tables)
+            rw_i, rw_o = emb_args[3], emb_args[4]
     else:
         lS_o, lS_i = emb_args
         indices, offsets, _ = self.emb_l.linearize_indices_and_offsets(list(lS_i), list(lS_o), [False] * len(lS_i))
+    if (self.rowwise is not None) != (rw_i is not None):
+        raise RuntimeError("row-wise sharded tables need (indices, offsets, None, rw_indices, rw_offsets)")
     with torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.bf16):
         x = self.apply_mlp(self._pad_dense(dense_x), self.bot_l)
         z = sharded_emb_interact(x, self.emb_l, self.peer_exchange, indices, offsets,
-                                 1 + self.local_ln_emb_slice.start, pad_to=self.interaction_pad)
+                                 1 + self.local_ln_emb_slice.start, pad_to=self.interaction_pad,
+                                 rowwise=self.rowwise, rw_indices=rw_i, rw_offsets=rw_o)
         p = self.apply_mlp(z, self.top_l)
     return self._clamp(p)
 

@@ -251,7 +251,10 @@ class DenseGradAllreduce(object):
     ``ext_dist.DDP(bot_l) / DDP(top_l)`` (``P/dlrm_s_pytorch.py:955-957``: mean over ranks); used when the
     MLPs run through the fused bf16 path, whose autograd functions bypass ``DDP.forward``."""
 
-    def __init__(self, params):
+    def __init__(self, params, average: bool = True):
+        """``average=False`` sums instead (use it when every rank already divides its loss by the world
+        size -- the way to keep a scale-sensitive table optimiser such as Adagrad exact, see tools/dist_parity.py)."""
+        self.average = average
         self.params = [p for p in params if p.requires_grad]
         n = sum(p.numel() for p in self.params)
         self.flat = torch.zeros(n, dtype=torch.float32, device=self.params[0].device)
@@ -267,6 +270,7 @@ class DenseGradAllreduce(object):
         grads = [p.grad if p.grad is not None else torch.zeros_like(p) for p in self.params]
         torch._foreach_copy_(self.views, grads)
         dist.all_reduce(self.flat)
-        self.flat.mul_(1.0 / my_size)
+        if self.average:
+            self.flat.mul_(1.0 / my_size)
         for p, v in zip(self.params, self.views):
             p.grad = v  # the optimizer reads the averaged gradient straight from the flat buffer

@@ -53,15 +53,21 @@ class _ShardedEmbInteractFn(torch.autograd.Function):
     """x [lN, D] (+ this rank's tables, global-batch indices) -> interaction output R [lN, ldr]."""
 
     @staticmethod
-    def forward(ctx, x, trigger, emb, exch, indices, offsets, feat0, pad_to):
+    def forward(ctx, x, trigger, emb, exch, indices, offsets, feat0, pad_to, rowwise=None, rw_indices=None,
+                rw_offsets=None):
         B_glob = exch.lN * exch.world
-        ops.emb_fwd_sharded(emb.tables, indices, offsets, B_glob, exch.T_ptrs_dev, exch.lN, exch.F, feat0, exch.dtype,
-                            emb.error_flag)
-        emb._launch_prepare(indices, offsets, B_glob)  # sort / dedup on the side stream
+        if emb is not None:
+            ops.emb_fwd_sharded(emb.tables, indices, offsets, B_glob, exch.T_ptrs_dev, exch.lN, exch.F, feat0,
+                                exch.dtype, emb.error_flag)
+            emb._launch_prepare(indices, offsets, B_glob)  # sort / dedup on the side stream
+        ctx.rw_ctx = None
+        if rowwise is not None:  # row-wise sharded hot tables occupy the LAST feature slots
+            rw_out, ctx.rw_ctx = rowwise.pool(rw_indices, rw_offsets, exch.lN)
+            exch.T[:, exch.F - rowwise.k:].copy_(rw_out)
         exch.T[:, 0].copy_(x)
         exch.barrier(0)  # B1
         R = ops.interact_fwd(exch.T, pad_to=pad_to)
-        ctx.emb, ctx.exch, ctx.feat0 = emb, exch, feat0
+        ctx.emb, ctx.exch, ctx.feat0, ctx.rowwise = emb, exch, feat0, rowwise
         ctx.save_for_backward(indices, offsets)
         ctx.x_dtype = x.dtype
         return R
@@ -73,10 +79,16 @@ class _ShardedEmbInteractFn(torch.autograd.Function):
         B_glob = exch.lN * exch.world
         ops.interact_bwd(exch.T, dR.contiguous().to(exch.dtype), out=exch.dT)
         exch.barrier(1)  # B2
-        emb._apply_update_sharded(indices, offsets, B_glob, exch, ctx.feat0)
+        if emb is not None:
+            emb._apply_update_sharded(indices, offsets, B_glob, exch, ctx.feat0)
+        if ctx.rowwise is not None:
+            ctx.rowwise.update(exch.dT[:, exch.F - ctx.rowwise.k:], ctx.rw_ctx)
         dx = exch.dT[:, 0].clone()  # dT is overwritten by the next step; the bottom MLP backward runs now
-        return dx.to(ctx.x_dtype), None, None, None, None, None, None, None
+        return (dx.to(ctx.x_dtype),) + (None,) * 10
 
 
-def sharded_emb_interact(x, emb, exch: PeerExchange, indices, offsets, feat0: int, pad_to: int = 1):
-    return _ShardedEmbInteractFn.apply(x, emb._trigger, emb, exch, indices, offsets, feat0, pad_to)
+def sharded_emb_interact(x, emb, exch: PeerExchange, indices, offsets, feat0: int, pad_to: int = 1, rowwise=None,
+                         rw_indices=None, rw_offsets=None, trigger=None):
+    trig = trigger if trigger is not None else (emb._trigger if emb is not None else rowwise.emb._trigger)
+    return _ShardedEmbInteractFn.apply(x, trig, emb, exch, indices, offsets, feat0, pad_to, rowwise, rw_indices,
+                                       rw_offsets)

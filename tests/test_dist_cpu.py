@@ -77,3 +77,23 @@ def test_alltoall_two_ranks_gloo(n_tables, N):
     port = _free_port()
     mp.spawn(_worker, args=(world, port, n_tables, N, 3, ret), nprocs=world, join=True)
     assert dict(ret) == {0: "ok", 1: "ok"}
+
+
+def test_rowwise_filter_owned_matches_per_bag_filter():
+    """cloudtik_b200.rowwise.filter_owned (pure index arithmetic, runs on CPU): bags over global row ids ->
+    bags over the rows rank r owns (id % W == r, local id = id // W), empty bags preserved."""
+    from cloudtik_b200.rowwise import filter_owned
+    rs = np.random.RandomState(0)
+    for W in (2, 3, 8):
+        lens = rs.randint(0, 6, size=40)
+        off = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+        idx = rs.randint(0, 1000, size=int(lens.sum())).astype(np.int64)
+        for r in range(W):
+            li, lo = filter_owned(torch.tensor(idx), torch.tensor(off), W, r)
+            want_i, want_o = [], [0]
+            for b in range(len(lens)):
+                bag = idx[off[b]:off[b + 1]]
+                keep = bag[bag % W == r] // W
+                want_i += keep.tolist()
+                want_o.append(len(want_i))
+            assert li.tolist() == want_i and lo.tolist() == want_o

@@ -29,6 +29,8 @@ def main():
     ap.add_argument("--batch", type=int, default=512, help="GLOBAL batch")
     ap.add_argument("--ddp", action="store_true", help="wrap the MLPs in DDP instead of the flat all-reduce")
     ap.add_argument("--p2p", action="store_true", help="fused embedding + all-to-all over NVLink peer memory")
+    ap.add_argument("--rowwise", type=int, default=0, help="row-wise shard the last K tables (needs --p2p)")
+    ap.add_argument("--adagrad", action="store_true", help="Adagrad on the tables (oracle: torch sparse Adagrad)")
     a = ap.parse_args()
 
     from cloudtik_b200 import ext_dist
@@ -47,11 +49,16 @@ def main():
     port = DLRMPort(D, rows, ln_bot, ln_top)
     np.random.seed(11)
     net = DLRM_Net(D, np.array(rows), np.array(ln_bot), np.array(ln_top), sigmoid_top=len(ln_top) - 2,
-                   np_init_emb_weight=True, device=dev, lr=lr / world, bf16=a.bf16)
+                   np_init_emb_weight=True, device=dev, lr=lr if a.adagrad else lr / world, bf16=a.bf16,
+                   n_rowwise=a.rowwise,
+                   emb_optimizer="adagrad" if a.adagrad else "sgd")
     local = net.local_ln_emb
+    n_tw = len(rows) - a.rowwise
     with torch.no_grad():
         for k, t in enumerate(local):
             net.emb_l.weights[k].copy_(port.emb_l[t].weight)
+        for k in range(a.rowwise):
+            net.rowwise.emb.weights[k].copy_(port.emb_l[n_tw + k].weight[rank::world])
         for dst, src in ((net.bot_l, port.bot_l), (net.top_l, port.top_l)):
             for pd, ps in zip(dst.parameters(), src.parameters()):
                 pd.copy_(ps)
@@ -60,13 +67,33 @@ def main():
     if a.ddp:
         net.bot_l = ext_dist.DDP(net.bot_l, device_ids=[dev.index])
         net.top_l = ext_dist.DDP(net.top_l, device_ids=[dev.index])
-    copt = torch.optim.SGD(port.parameters(), lr=lr)
+    if a.adagrad:  # oracle: sparse Adagrad on the tables (lr as is: the oracle sees the global-mean loss), SGD on MLPs
+        emb_params = list(port.emb_l.parameters())
+        # a non-zero initial accumulator on both sides: from zero, the first Adagrad step is lr * sign(g) and
+        # any last-bit difference of a near-zero gradient flips a whole step -- that would test noise, not kernels
+        copt_emb = torch.optim.Adagrad(emb_params, lr=lr, eps=1e-10, initial_accumulator_value=0.1)
+        for st in net.emb_l.tables.states + (net.rowwise.emb.tables.states if a.rowwise else []):
+            st.fill_(0.1)
+        copt_mlp = torch.optim.SGD(list(port.bot_l.parameters()) + list(port.top_l.parameters()), lr=lr)
+
+        class _Both:
+            def zero_grad(self, set_to_none=True):
+                copt_emb.zero_grad(set_to_none=set_to_none), copt_mlp.zero_grad(set_to_none=set_to_none)
+
+            def step(self):
+                copt_emb.step(), copt_mlp.step()
+        copt = _Both()
+    else:
+        copt = torch.optim.SGD(port.parameters(), lr=lr)
     dense = [p for p in net.parameters() if p.requires_grad]
     gopt = torch.optim.SGD(dense, lr=lr)
-    sync_dense = (lambda: None) if a.ddp else ext_dist.DenseGradAllreduce(dense)
+    # SGD: sharded-table lr = lr / world (T/dlrm_s_pytorch.py:1020-1031).  Adagrad is not linear in the gradient
+    # scale, so there every rank divides its loss by world instead and the MLP gradients are summed.
+    sync_dense = (lambda: None) if a.ddp else ext_dist.DenseGradAllreduce(dense, average=not a.adagrad)
     rs = np.random.RandomState(5)
     N, lN = a.batch, a.batch // world
     tol = 1e-2 if a.bf16 else 1e-5
+    atol_w = 2e-3 if a.bf16 else 1e-6  # absolute slack for rows near zero
     for step in range(a.steps):
         X, lS_o, lS_i, T = uniform_batch(rs, N, rows, pooling=3, unique_in_bag=(step % 2 == 1))
         want = cpu_step(port, copt, torch.tensor(X), [torch.tensor(o) for o in lS_o],
@@ -75,10 +102,18 @@ def main():
         Tl = torch.tensor(T[rank * lN:(rank + 1) * lN]).to(dev)
         lo = [torch.tensor(lS_o[t]).to(dev) for t in local]
         li = [torch.tensor(lS_i[t]).to(dev) for t in local]
-        Z = net(Xl, lo, li).float()
+        if a.rowwise:
+            ind, off, _ = net.emb_l.linearize_indices_and_offsets(li, lo, [False] * len(li))
+            from oracle import ops_numpy as onp
+            ri, ro, _ = onp.linearize_indices_and_offsets([lS_i[t] for t in range(n_tw, len(rows))],
+                                                          [lS_o[t] for t in range(n_tw, len(rows))],
+                                                          rows[n_tw:])
+            Z = net(Xl, ind, off, None, torch.tensor(ri).to(dev), torch.tensor(ro).to(dev)).float()
+        else:
+            Z = net(Xl, lo, li).float()
         E = net.loss_fn(Z, Tl)
         gopt.zero_grad(set_to_none=True)
-        E.backward()
+        (E / world if a.adagrad else E).backward()
         sync_dense()
         gopt.step()
         Lm = E.detach().clone()
@@ -88,14 +123,18 @@ def main():
     for k, t in enumerate(local):
         w = net.emb_l.weights[k].float().cpu().numpy()
         np.testing.assert_allclose(w, port.emb_l[t].weight.detach().numpy(), rtol=tol,
-                                   atol=2e-3 if a.bf16 else 1e-6, err_msg=f"table {t}")  # abs: rows near zero
+                                   atol=atol_w, err_msg=f"table {t}")
+    for k in range(a.rowwise):
+        w = net.rowwise.full_table(k).cpu().numpy()
+        np.testing.assert_allclose(w, port.emb_l[n_tw + k].weight.detach().numpy(), rtol=tol,
+                                   atol=atol_w, err_msg=f"row-wise table {n_tw + k}")
     top = net.top_l.module if a.ddp else net.top_l
     for (n1, p1), p2 in zip(top.named_parameters(), port.top_l.parameters()):
         np.testing.assert_allclose(p1.detach().cpu().numpy(), p2.detach().numpy(), rtol=10 * tol,
                                    atol=2e-3 if a.bf16 else 1e-6, err_msg=n1)
     ext_dist.barrier()
     if rank == 0:
-        print(f"dist parity ok: world={world} tables={len(rows)} bf16={a.bf16} p2p={a.p2p} steps={a.steps} "
+        print(f"dist parity ok: world={world} tables={len(rows)} rowwise={a.rowwise} adagrad={a.adagrad} bf16={a.bf16} p2p={a.p2p} steps={a.steps} "
               f"(losses and weights match the single-process oracle)")
     torch.distributed.destroy_process_group()
 
