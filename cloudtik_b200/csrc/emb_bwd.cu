@@ -26,13 +26,12 @@ constexpr int UPD_THREADS = 256;
 // pre-reduces the (at most two) hot runs that cross it into fp32 partial rows, and the update
 // kernel adds the partials of a hot row in window order.  Deterministic, no atomics.
 constexpr int OPT_STORE = 2;  // internal "optimizer": write the per-row gradient sums to values[run index]
-constexpr int HOT_SW = 16;  // windows per super-window (second reduction level for very long runs)
+constexpr int MIN_NG = UPD_THREADS / 32;  // fewest windows per block (one warp per window)
 
 struct BwdLayout {
   uint32_t *keys, *vals, *skeys, *svals, *unique, *seg, *win_run, *first_val;
   int32_t* num_unique;
-  float* partial;   // [2 * nwin][D], nwin = ceil(n / HOT_CH)
-  float* partial2;  // [2 * ceil(nwin / HOT_SW)][D]: per super-window sums for very long runs
+  float* partial;   // [2 * nblk][D], nblk = blocks of the window kernel (<= ceil(nwin / MIN_NG))
   void* sort_ws;
   size_t total;
 };
@@ -51,9 +50,8 @@ static BwdLayout bwd_layout(void* ws, int64_t n, int64_t D) {
   L.seg = reinterpret_cast<uint32_t*>(w + o), o += align_up((size_t)(n + 1) * 4, 256);
   L.num_unique = reinterpret_cast<int32_t*>(w + o), o += 256;
   L.win_run = reinterpret_cast<uint32_t*>(w + o), o += align_up((size_t)(ceil_div(n, HOT_CH) + 1) * 4, 256);
-  L.partial = reinterpret_cast<float*>(w + o), o += align_up((size_t)(2 * ceil_div(n, HOT_CH)) * D * 4, 256);
-  L.partial2 = reinterpret_cast<float*>(w + o),
-  o += align_up((size_t)(2 * ceil_div(ceil_div(n, HOT_CH), HOT_SW)) * D * 4, 256);
+  L.partial = reinterpret_cast<float*>(w + o),
+  o += align_up((size_t)(2 * ceil_div(ceil_div(n, HOT_CH), MIN_NG)) * D * 4, 256);
   L.sort_ws = w + o, o += sort_ws_bytes(n);
   L.total = o;
   return L;
@@ -124,7 +122,6 @@ struct UpdParams {
   const uint32_t* skeys;
   const uint32_t* win_run;
   const uint32_t* first_val;
-  float* partial2;
   float* values;  // OPT_STORE: [n, D] fp32 coalesced gradient rows, row u = sum of run u
   // sharded gradients (fused mirror all-to-all over peer memory): the gradient row of bag b of local
   // table t lives on rank r = b / lN at grad_ptrs[r] + ((b - r*lN) * F + feat0 + t) * D
@@ -202,15 +199,19 @@ struct GradVec<__nv_bfloat16, 4> {
 };
 
 // ---- 3a. window kernel: uniform work per group, independent of the duplicate structure ----
-// One group of G lanes owns a window of HOT_CH consecutive SORTED positions.  It stages the
-// window's keys / gradient-row offsets in shared memory (coalesced), then streams the gradient
-// rows in batches (BS rows in flight per lane, plus the weight rows of the runs that end in the
-// batch) and sums run by run, in position (= bag) order:
-//   * a run that lies entirely inside the window is finished here: ONE read-modify-write of its
-//     weight row (and Adagrad state row);
-//   * a run that crosses a window border leaves an fp32 partial row: slot 0 if it began at or
-//     before the window's first position, slot 1 if it began inside;  window_join_kernel adds the
-//     partials of such a run in window order and updates the row.
+// One group of G lanes owns a window of HOT_CH consecutive SORTED positions; a block owns NG
+// consecutive windows.  A group stages its window's keys / gradient-row addresses in shared
+// memory (coalesced), then streams the gradient rows in batches (BS rows in flight per lane,
+// plus the weight rows of the runs that end in the batch) and sums run by run, in position
+// (= bag) order:
+//   * a run that lies entirely inside the window is finished right there: ONE read-modify-write
+//     of its weight row (and Adagrad state row);
+//   * a run that crosses a window border leaves an fp32 piece in SHARED memory: slot 0 if it
+//     began at or before the window's first position, slot 1 if it began inside.  After a block
+//     barrier the group holding the head of such a run adds the pieces of the following windows
+//     in window order and finishes the row -- no trip through global memory, no extra launch;
+//   * only a run that crosses a BLOCK border leaves a partial row in global memory (same slot
+//     rule, per block); window_join_kernel adds those in block order and updates the row.
 // Every weight row is written by exactly one group: deterministic, no atomics.
 template <int OPT, typename WT>
 __device__ __forceinline__ void apply_row(char* wp, float* sp, const float* acc, const float* w_in, float lr,
@@ -271,7 +272,7 @@ constexpr int UPD_TMAX = 256;  // tables whose base pointers / row bases are cac
 // store: no weight row ever travels to the SM, no registers wait for it.  Each row still gets
 // exactly one update per step from exactly one group, so the result stays deterministic.
 template <typename WT, typename GT, int G, int NV, int OPT, bool RED>
-__global__ void __launch_bounds__(UPD_THREADS) window_update_kernel(const UpdParams p) {
+__global__ void __launch_bounds__(UPD_THREADS, (RED && sizeof(GT) == 2) ? 3 : 1) window_update_kernel(const UpdParams p) {
   static_assert(!RED || (OPT == B200_OPT_SGD && sizeof(WT) == 4), "RED path is fp32 SGD only");
   constexpr int VE = Vec16<WT>::VE;
   constexpr int NG = UPD_THREADS / G;
@@ -285,7 +286,11 @@ __global__ void __launch_bounds__(UPD_THREADS) window_update_kernel(const UpdPar
   __shared__ uint32_t s_key[NG][C + 2];  // [0] = key before the window, [C+1] = key after it
   __shared__ int64_t s_goff[NG][C];      // address of the gradient row of each position
   __shared__ uint16_t s_tab[NG][C];
+  extern __shared__ __align__(16) float s_part[];  // [NG][2][D]: pieces of the runs that cross window borders
   const int gid = threadIdx.x / G, lane = threadIdx.x % G;
+  // programmatic dependent launch: once every block of this grid is resident, the join grid may be
+  // scheduled into the SM slots the last wave leaves free (it waits for this grid before reading p.partial)
+  asm volatile("griddepcontrol.launch_dependents;");
   const bool cached = p.T <= UPD_TMAX && OPT != OPT_STORE;
   if (cached) {
     for (int i = threadIdx.x; i < p.T; i += UPD_THREADS) {
@@ -322,7 +327,7 @@ __global__ void __launch_bounds__(UPD_THREADS) window_update_kernel(const UpdPar
   }
   const float lr = p.d_lr ? *p.d_lr : p.lr;
   __syncthreads();
-  if (cnt == 0) return;
+  // (a group whose window lies beyond the end has cnt == 0: it skips the work but keeps the barriers)
 
   float acc[NV][VE];
 #pragma unroll
@@ -330,9 +335,11 @@ __global__ void __launch_bounds__(UPD_THREADS) window_update_kernel(const UpdPar
 #pragma unroll
     for (int x = 0; x < VE; ++x) acc[k][x] = 0.f;
   // is the run being summed a continuation from the previous window, and where is its head?
-  bool cont = s_key[gid][0] == s_key[gid][1];
+  const bool cont0 = cnt > 0 && s_key[gid][0] == s_key[gid][1];
+  bool cont = cont0;
   int cur_head = cont ? -1 : 0;
-  int64_t uidx = (OPT == OPT_STORE) ? (int64_t)p.win_run[w] : 0;  // index of the run being summed
+  const int64_t uidx0 = (OPT == OPT_STORE && cnt > 0) ? (int64_t)p.win_run[w] : 0;
+  int64_t uidx = uidx0;  // index of the run being summed
 
   for (int c0 = 0; c0 < cnt; c0 += BS) {
     GradVec<GT, VE> g[BS][NV];
@@ -428,13 +435,13 @@ __global__ void __launch_bounds__(UPD_THREADS) window_update_kernel(const UpdPar
               }
             }
           }
-        } else {  // continuation from the previous window that ends here: slot 0
-          float* dst = p.partial + (size_t)(2 * w) * p.D + lane * VE;
+        } else {  // continuation from the previous window that ends here: piece in slot 0
+          float* dst = s_part + (size_t)(2 * gid) * p.D + lane * VE;
 #pragma unroll
           for (int k = 0; k < NV; ++k)
             if (lane + k * G < p.V) {
 #pragma unroll
-              for (int h = 0; h < VE / 4; ++h) store_vec<float, 4, false>(dst + k * G * VE + 4 * h, acc[k] + 4 * h);
+              for (int x = 0; x < VE; ++x) dst[k * G * VE + x] = acc[k][x];
             }
         }
 #pragma unroll
@@ -444,26 +451,100 @@ __global__ void __launch_bounds__(UPD_THREADS) window_update_kernel(const UpdPar
       }
     }
   }
-  // a run still open at the right border: slot 0 if it began at or before the first position
-  if (s_key[gid][cnt] == s_key[gid][cnt + 1]) {
-    float* dst = p.partial + (size_t)(2 * w + (cur_head <= 0 ? 0 : 1)) * p.D + lane * VE;
+  // a run still open at the right border: piece in slot 0 if it began at or before the first position
+  const bool open_r = cnt > 0 && s_key[gid][cnt] == s_key[gid][cnt + 1];
+  const int tail_slot = cur_head <= 0 ? 0 : 1;
+  if (open_r) {
+    float* dst = s_part + (size_t)(2 * gid + tail_slot) * p.D + lane * VE;
 #pragma unroll
     for (int k = 0; k < NV; ++k)
       if (lane + k * G < p.V) {
 #pragma unroll
-        for (int h = 0; h < VE / 4; ++h) store_vec<float, 4, false>(dst + k * G * VE + 4 * h, acc[k] + 4 * h);
+        for (int x = 0; x < VE; ++x) dst[k * G * VE + x] = acc[k][x];
       }
   }
+  __syncthreads();
+  if (cnt == 0) return;
+
+  // ---- in-block join.  The group holding the HEAD of a run that crosses its right border adds the
+  // slot-0 pieces of the following windows (window order) and finishes the run; group 0 does the same
+  // for the run that enters the block from the left.  What crosses a block border goes to p.partial.
+  const int64_t blk_first = (int64_t)blockIdx.x * NG * C;
+  const int ngv = (int)min((int64_t)NG, (p.n - blk_first + C - 1) / C);  // windows of this block with data
+  const int cnt_last = (int)min((int64_t)C, p.n - (blk_first + (int64_t)(ngv - 1) * C));
+  const uint32_t key_after_block = s_key[ngv - 1][cnt_last + 1];
+  // run entering from the previous window covers this whole window and goes on: some earlier group owns it
+  const bool pass_through = cont0 && open_r && s_key[gid][1] == s_key[gid][cnt];
+  auto finish = [&](int slot, uint32_t key, bool from_left, bool open, int pos, int64_t u) {
+    const float* src = s_part + (size_t)(2 * gid + slot) * p.D + lane * VE;
+#pragma unroll
+    for (int k = 0; k < NV; ++k)
+#pragma unroll
+      for (int x = 0; x < VE; ++x) acc[k][x] = (lane + k * G < p.V) ? src[k * G * VE + x] : 0.f;
+    int j = gid + 1;
+    if (open) {
+      for (; j < ngv && s_key[j][1] == key; ++j) {
+        const float* q = s_part + (size_t)(2 * j) * p.D + lane * VE;
+#pragma unroll
+        for (int k = 0; k < NV; ++k)
+          if (lane + k * G < p.V) {
+#pragma unroll
+            for (int x = 0; x < VE; ++x) acc[k][x] += q[k * G * VE + x];
+          }
+      }
+    }
+    const bool to_right = open && j == ngv && key_after_block == key;
+    if (from_left || to_right) {  // crosses a block border: per-block partial row, finished by window_join_kernel
+      const int bslot = (from_left || (gid == 0 && slot == 0)) ? 0 : 1;
+      float* dst = p.partial + (size_t)(2 * (int64_t)blockIdx.x + bslot) * p.D + lane * VE;
+#pragma unroll
+      for (int k = 0; k < NV; ++k)
+        if (lane + k * G < p.V) {
+#pragma unroll
+          for (int h = 0; h < VE / 4; ++h) store_vec<float, 4, false>(dst + k * G * VE + 4 * h, acc[k] + 4 * h);
+        }
+      return;
+    }
+    char* wp;
+    float* sp = nullptr;
+    char* tp = nullptr;
+    if (OPT == OPT_STORE) {
+      wp = reinterpret_cast<char*>(p.values) + ((size_t)u * p.D + lane * VE) * sizeof(WT);
+    } else {
+      const int tt = s_tab[gid][pos];
+      const int64_t row = (int64_t)key - (cached ? s_base[tt] : p.row_base[tt]);
+      wp = (cached ? s_wptr[tt] : static_cast<char*>(p.weights[tt])) + ((size_t)row * p.D + lane * VE) * sizeof(WT);
+      if (OPT == B200_OPT_ADAGRAD) sp = (cached ? s_sptr[tt] : p.state[tt]) + (size_t)row * p.D + lane * VE;
+      if (has_trail) tp = wp + (cached ? s_tdelta[tt] : reinterpret_cast<char*>(p.trail[tt]) - static_cast<char*>(p.weights[tt]));
+    }
+#pragma unroll
+    for (int k = 0; k < NV; ++k)
+      if (lane + k * G < p.V) {
+        if constexpr (RED) {
+          red_add_v4_f32(reinterpret_cast<float*>(wp + (size_t)k * G * 16), -lr * acc[k][0], -lr * acc[k][1],
+                         -lr * acc[k][2], -lr * acc[k][3]);
+        } else {
+          float wf[VE] = {};
+          uint4 tv = make_uint4(0, 0, 0, 0);
+          if (OPT != OPT_STORE) {
+            Vec16<WT>::unpack(wf, ld_v4(wp + (size_t)k * G * 16));
+            if (tp) tv = ld_v4(tp + (size_t)k * G * 16);
+          }
+          apply_row<OPT, WT>(wp + (size_t)k * G * 16, sp ? sp + k * G * VE : nullptr, acc[k], wf, lr, p.eps,
+                             tp ? tp + (size_t)k * G * 16 : nullptr, tv);
+        }
+      }
+  };
+  if (gid == 0 && cont0)  // the run that enters the block from the left (its head is in an earlier block)
+    finish(0, s_key[0][1], true, pass_through, 0, uidx0);
+  if (open_r && !pass_through)  // the run whose head is in this window and that crosses its right border
+    finish(tail_slot, s_key[gid][cnt], false, true, cnt - 1, uidx);
 }
 
-// ---- 3b. join: runs that cross window borders.  Two levels so that no group ever adds more than
-// a few dozen partial rows in sequence (the hottest Criteo rows collect > 10^4 gradients per step):
-//   level 1  window_join_kernel<..., 1>: one group per window border; the border a run crosses
-//            FIRST owns it; runs of at most HOT_SW windows are finished here;
-//            super_window_kernel: one group per super-window (HOT_SW windows) pre-adds the window
-//            partials of the longer runs (at most two per super-window: the one covering its first
-//            position -> slot 0, one beginning inside -> slot 1);
-//   level 2  window_join_kernel<..., 2>: the owner adds the super-window sums and updates the row.
+// ---- 3b. join: runs that cross BLOCK borders of the window kernel (a block = NG windows = NG * HOT_CH
+// positions).  One group per block border; the border a run crosses FIRST owns it, adds the run's
+// per-block partial rows in block order (PB rows in flight) and updates the row.  A row with m duplicates
+// costs m / (NG * HOT_CH) sequential row adds here -- 43 for the hottest Criteo row at batch 32768.
 template <int G, int NV, int VE, int PB>
 __device__ __forceinline__ void add_partial_rows(float (*acc)[VE], const float* base, int64_t first, int64_t last,
                                                  int64_t s_pos, int64_t unit, int D, int V, int lane) {
@@ -496,22 +577,23 @@ __device__ __forceinline__ void add_partial_rows(float (*acc)[VE], const float* 
   }
 }
 
-template <typename WT, int G, int NV, int OPT, bool RED, int LEVEL>
+template <typename WT, int G, int NV, int OPT, bool RED>
 __global__ void __launch_bounds__(UPD_THREADS) window_join_kernel(const UpdParams p) {
   constexpr int VE = Vec16<WT>::VE;
   constexpr int NG = UPD_THREADS / G;
-  constexpr int C = HOT_CH;
+  constexpr int64_t BC = (int64_t)NG * HOT_CH;  // positions per block of the window kernel
   constexpr int PB = (NV * VE >= 32) ? 2 : (NV * VE >= 16 ? 4 : (NV * VE >= 8 ? 8 : 16));  // partial rows in flight
   const int gid = threadIdx.x / G, lane = threadIdx.x % G;
-  const int64_t k = (int64_t)blockIdx.x * NG + gid + 1;  // border between positions kC-1 and kC
-  if (k * C >= p.n) return;
-  if (p.skeys[k * C - 1] != p.skeys[k * C]) return;  // nothing crosses this border
-  const int64_t u = p.win_run[k];
+  const int64_t k = (int64_t)blockIdx.x * NG + gid + 1;  // border between positions k*BC-1 and k*BC
+  if (k * BC >= p.n) return;
+  if (p.skeys[k * BC - 1] != p.skeys[k * BC]) return;  // nothing crosses this border
+  const int64_t u = p.win_run[k * NG];
   const int64_t s = p.seg[u], e = p.seg[u + 1];
-  if (s / C + 1 != k) return;  // an earlier border owns this run
-  const int64_t w0 = s / C, w1 = (e - 1) / C;
-  const bool is_long = w1 - w0 + 1 > HOT_SW;
-  if (is_long != (LEVEL == 2)) return;
+  if (s / BC + 1 != k) return;  // an earlier border owns this run
+  const int64_t w0 = s / BC, w1 = (e - 1) / BC;
+  // everything above reads the sort/dedup outputs only; the partial rows (and the weight rows) need the
+  // window kernel to have finished (no-op when launched without the programmatic-serialization attribute)
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   const float lr = p.d_lr ? *p.d_lr : p.lr;
   char* wp;
   float* sp = nullptr;
@@ -546,10 +628,7 @@ __global__ void __launch_bounds__(UPD_THREADS) window_join_kernel(const UpdParam
   for (int kk = 0; kk < NV; ++kk)
 #pragma unroll
     for (int x = 0; x < VE; ++x) acc[kk][x] = 0.f;
-  if (LEVEL == 1)
-    add_partial_rows<G, NV, VE, PB>(acc, p.partial, w0, w1, s, C, p.D, p.V, lane);
-  else
-    add_partial_rows<G, NV, VE, PB>(acc, p.partial2, w0 / HOT_SW, w1 / HOT_SW, s, (int64_t)C * HOT_SW, p.D, p.V, lane);
+  add_partial_rows<G, NV, VE, PB>(acc, p.partial, w0, w1, s, BC, p.D, p.V, lane);
 #pragma unroll
   for (int kk = 0; kk < NV; ++kk)
     if (lane + kk * G < p.V) {
@@ -563,44 +642,6 @@ __global__ void __launch_bounds__(UPD_THREADS) window_join_kernel(const UpdParam
                            tp ? tp + (size_t)kk * G * 16 : nullptr, tv[kk]);
       }
     }
-}
-
-template <typename WT, int G, int NV>
-__global__ void __launch_bounds__(UPD_THREADS) super_window_kernel(const UpdParams p) {
-  constexpr int VE = Vec16<WT>::VE;
-  constexpr int NG = UPD_THREADS / G;
-  constexpr int C = HOT_CH;
-  constexpr int PB = (NV * VE >= 32) ? 2 : (NV * VE >= 16 ? 4 : (NV * VE >= 8 ? 8 : 16));
-  const int gid = threadIdx.x / G, lane = threadIdx.x % G;
-  const int64_t S = (int64_t)blockIdx.x * NG + gid;
-  const int64_t nwin = (p.n + C - 1) / C;
-  const int64_t a = S * HOT_SW;
-  if (a >= nwin) return;
-  const int64_t last = min(a + HOT_SW, nwin) - 1;
-  auto reduce_run = [&](int64_t u, int slot) {
-    const int64_t s = p.seg[u], e = p.seg[u + 1];
-    const int64_t w0 = s / C, w1 = (e - 1) / C;
-    if (w1 - w0 + 1 <= HOT_SW) return;  // short runs are finished by the level-1 join
-    float acc[NV][VE];
-#pragma unroll
-    for (int kk = 0; kk < NV; ++kk)
-#pragma unroll
-      for (int x = 0; x < VE; ++x) acc[kk][x] = 0.f;
-    add_partial_rows<G, NV, VE, PB>(acc, p.partial, max(a, w0), min(last, w1), s, C, p.D, p.V, lane);
-    float* dst = p.partial2 + (size_t)(2 * S + slot) * p.D + lane * VE;
-#pragma unroll
-    for (int kk = 0; kk < NV; ++kk)
-      if (lane + kk * G < p.V) {
-#pragma unroll
-        for (int h = 0; h < VE / 4; ++h) store_vec<float, 4, false>(dst + kk * G * VE + 4 * h, acc[kk] + 4 * h);
-      }
-  };
-  const int64_t uA = p.win_run[a];  // run covering the super-window's first position
-  reduce_run(uA, 0);
-  const int64_t endpos = min((last + 1) * C, p.n);  // one past the super-window's last position
-  const int64_t uB = endpos < p.n ? (int64_t)p.win_run[last + 1] - (p.skeys[endpos] != p.skeys[endpos - 1] ? 1 : 0)
-                                  : (int64_t)(*p.num_unique) - 1;
-  if (uB != uA) reduce_run(uB, 1);
 }
 
 // scalar fallback (rows not a whole number of 16-byte vectors): thread per (unique row, d)
@@ -670,17 +711,35 @@ static int launch_update(const UpdParams& p, int64_t n, bool vec_ok, cudaStream_
     const char* e = getenv("B200_SGD_RED");
     return e == nullptr || e[0] != '0';
   }();
-#define B200_UPD_LAUNCH(G, NV, RED)                                                                                  \
-  window_update_kernel<WT, GT, G, NV, OPT, RED><<<(unsigned)ceil_div(nwin, UPD_THREADS / G), UPD_THREADS, 0, st>>>(p); \
-  if (nwin > 1) {                                                                                                    \
-    window_join_kernel<WT, G, NV, OPT, RED, 1>                                                                       \
-        <<<(unsigned)ceil_div(nwin - 1, UPD_THREADS / G), UPD_THREADS, 0, st>>>(p);                                  \
-    if (nwin > HOT_SW) {                                                                                             \
-      super_window_kernel<WT, G, NV>                                                                                 \
-          <<<(unsigned)ceil_div(ceil_div(nwin, HOT_SW), UPD_THREADS / G), UPD_THREADS, 0, st>>>(p);                  \
-      window_join_kernel<WT, G, NV, OPT, RED, 2>                                                                     \
-          <<<(unsigned)ceil_div(nwin - 1, UPD_THREADS / G), UPD_THREADS, 0, st>>>(p);                                \
-    }                                                                                                                \
+  static const bool use_pdl = []() {
+    const char* e = getenv("B200_PDL");
+    return e == nullptr || e[0] != '0';
+  }();
+#define B200_UPD_LAUNCH(G, NV, RED)                                                                               \
+  {                                                                                                               \
+    constexpr int NG_ = UPD_THREADS / G;                                                                          \
+    const size_t part_bytes = (size_t)NG_ * 2 * p.D * sizeof(float);                                              \
+    auto kern = window_update_kernel<WT, GT, G, NV, OPT, RED>;                                                    \
+    if (part_bytes > 32 * 1024) {                                                                                 \
+      static const cudaError_t attr_rc =                                                                          \
+          cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);                     \
+      B200_REQUIRE(attr_rc == cudaSuccess && part_bytes <= 96 * 1024, B200_EUNSUPPORTED,                          \
+                   "emb_update: row too long for the in-block join");                                             \
+    }                                                                                                             \
+    const int64_t nblk = ceil_div(nwin, NG_);                                                                     \
+    kern<<<(unsigned)nblk, UPD_THREADS, part_bytes, st>>>(p);                                                     \
+    if (nblk > 1) {                                                                                               \
+      cudaLaunchConfig_t cfg = {};                                                                                \
+      cfg.gridDim = dim3((unsigned)ceil_div(nblk - 1, NG_));                                                      \
+      cfg.blockDim = dim3(UPD_THREADS);                                                                           \
+      cfg.stream = st;                                                                                            \
+      cudaLaunchAttribute at[1];                                                                                  \
+      at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                                              \
+      at[0].val.programmaticStreamSerializationAllowed = 1;                                                       \
+      cfg.attrs = at;                                                                                             \
+      cfg.numAttrs = use_pdl ? 1 : 0;                                                                             \
+      cudaLaunchKernelEx(&cfg, window_join_kernel<WT, G, NV, OPT, RED>, p);                                       \
+    }                                                                                                             \
   }
 #define B200_UPD_CASE(G, NV)                 \
   if constexpr (CAN_RED) {                   \
@@ -786,7 +845,6 @@ static int emb_bwd_apply_impl(void* const* d_weights, float* const* d_state, uin
   p.first_val = L.first_val;
   p.T = (int)T;
   p.partial = L.partial;
-  p.partial2 = L.partial2;
   p.n = nnz;
   p.values = nullptr;
   p.grad_ptrs = d_grad_ptrs;
@@ -887,7 +945,6 @@ extern "C" int b200_emb_bwd_coalesce(const int64_t* d_rows, const int64_t* d_row
   p.win_run = L.win_run;
   p.first_val = L.first_val;
   p.partial = L.partial;
-  p.partial2 = L.partial2;
   p.values = d_values;
   p.n = nnz;
   p.T = (int)T;
