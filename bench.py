@@ -332,13 +332,16 @@ def run_b200_arm(a):
         ach = alg[dom] / (kt[dom] * 1e-3) / 1e9
         roof = {"kernel": dom, "bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
                 "frac": round(ach / peak, 4), "frac_of_8TBps_nominal": round(ach / 8000.0, 4),
-                "peak_source": pk, "traffic": ncu_traffic(dom), "algorithmic_bytes": int(alg[dom]),
+                "peak_source": pk, "traffic": ncu_traffic(dom),
+                "traffic_source": "profiles/roofline_traffic.json <- profiles/r1f_ncu_full.summary.md (ncu --set "
+                                  "full of this bench, table rows capped at 4 M; DRAM read+write bytes per launch)",
+                "algorithmic_bytes": int(alg[dom]),
                 "kernel_ms": round(kt[dom], 4), "measured_in": "eager pass of the same steps, CUDA events",
                 "others": {k: {"ms": round(v, 4), "GBps": round(alg[k] / (v * 1e-3) / 1e9, 1)}
                            for k, v in kt.items() if k != dom}}
 
     bits = max(1, int(sum(rows_local) - 1).bit_length())
-    launches = 1 + 1 + 3 * ((bits + 7) // 8) + 3 + 1 + 2  # fwd, keys, radix passes, dedup, update, interaction f/b
+    launches = 1 + 1 + 3 * ((bits + 7) // 8) + 3 + 2 + 2  # fwd, keys, radix passes, dedup, update + join, interaction f/b
     line = {"metric": "dlrm_train_samples_per_sec", "value": round(value, 1), "unit": "samples/s", "n_gpus": world,
             "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": round(ms_step, 4), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": a.dtype, "data": "synthetic",
