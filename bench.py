@@ -182,9 +182,18 @@ def make_batches(a, rows_local, B_loc, B_glob, dev, rank):
             idx[t] = np.floor(rs.rand(B_glob) * n).astype(np.int64)
         off = np.arange(T * B_glob + 1, dtype=np.int64)
         host = [torch.from_numpy(v).pin_memory() for v in (X, Y, idx.reshape(-1), off)]
+        # the same batch as RAW Criteo records (int32 label, 13 counts, T ids: the CriteoBinDataset format);
+        # the counts are chosen so that log(count + 1) reproduces a dense feature of the same range
+        host_rec = None
+        if B_loc == B_glob:  # single GPU only (a rank of a sharded job would need every table's ids)
+            rec = np.empty((B_glob, 14 + T), dtype=np.int32)
+            rec[:, 0] = Y[:, 0]
+            rec[:, 1:14] = np.floor(np.expm1(4.0 * X))
+            rec[:, 14:] = idx.T
+            host_rec = torch.from_numpy(rec).pin_memory()
         devt = [h.to(dev, non_blocking=True) for h in host]
         uniq = [int(np.unique(idx[t]).size) for t in range(T)]
-        sets.append({"host": host, "dev": devt, "uniq": uniq})
+        sets.append({"host": host, "dev": devt, "uniq": uniq, "host_rec": host_rec})
     torch.cuda.synchronize()
     return sets
 
@@ -306,6 +315,21 @@ def run_b200_arm(a):
         pending.clear()  # the timed region stages its own batches (K+1 H2D copies for K steps)
     ms_e2e, _ = timed(e2e_fn, a.steps)
 
+    # the same end-to-end step fed with RAW records (160 B per sample over PCIe, decoded by b200_criteo_transform)
+    ms_rec = None
+    if use_graph and world == 1:
+        pend = {}
+
+        def rec_fn(i):
+            k = pend.pop(i) if i in pend else gs.prefetch_records(sets[i % len(sets)]["host_rec"])
+            pend[i + 1] = gs.prefetch_records(sets[(i + 1) % len(sets)]["host_rec"])
+            return float(gs.step_records(k).cpu())
+
+        for i in range(2):
+            rec_fn(i)
+        pend.clear()
+        ms_rec, _ = timed(rec_fn, a.steps)
+
     if rank != 0:
         return
     ms_step = ms_total / a.steps
@@ -356,6 +380,11 @@ def run_b200_arm(a):
                        "launch": "whole step replayed as one CUDA graph" if use_graph else "eager"},
             "e2e": {"value": round(e2e_value, 1), "unit": "samples/s", "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": 4, "ms_per_step": round(ms_e2e / a.steps, 4)},
+            "e2e_records": None if ms_rec is None else {
+                "value": round(B_glob * a.steps / (ms_rec / 1e3), 1), "unit": "samples/s",
+                "h2d_bytes_per_step": int(sets[0]["host_rec"].numel() * 4), "d2h_bytes_per_step": 4,
+                "ms_per_step": round(ms_rec / a.steps, 4),
+                "input": "raw int32 Criteo records (CriteoBinDataset format) decoded on the device, one extra launch"},
             "gpu_launches": launches * a.steps, "gpu_launches_per_step": launches,
             "roofline": roof, "clocks": clk, "final_loss": loss_val}
     if world == 1 and not a.no_cpu_baseline:

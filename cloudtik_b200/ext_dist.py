@@ -214,6 +214,29 @@ def alltoall(inputs, per_rank_split_lengths):
     return myreq
 
 
+def shuffle_data(inputs):
+    """T/extend_distributed.py:408-413 (call site T/dlrm_s_pytorch.py:494-497): every rank holds the
+    indices of ALL tables for ITS local batch (a list of T tensors [B_loc]); one equal-split all-to-all
+    hands rank r the indices of ITS tables for every rank's batch.  Returns ``[world, lS*B_loc]``: row s =
+    rank s's local batch for my lS = T/world tables, so ``out[:, i*B_loc:(i+1)*B_loc].reshape(-1)`` is table
+    i's index list for the GLOBAL batch (one-hot only, like the reference: offsets are an arange)."""
+    input = torch.cat(inputs)
+    if input.numel() % my_size != 0:
+        raise ValueError("shuffle_data: the number of tables must be a multiple of the number of ranks")
+    output = input.new_empty(input.size())
+    dist.all_to_all_single(output, input)
+    return output.reshape(my_size, -1)
+
+
+def global_batch_indices(shuffled, n_local_tables):
+    """Per-table GLOBAL-batch index lists + the shared arange offsets from ``shuffle_data``'s output
+    (T/dlrm_s_pytorch.py:495-497)."""
+    b_loc = shuffled.shape[1] // n_local_tables
+    g_i = [shuffled[:, i * b_loc:(i + 1) * b_loc].reshape(-1) for i in range(n_local_tables)]
+    offset = torch.arange(b_loc * my_size, device=shuffled.device)
+    return [offset for _ in range(n_local_tables)], g_i
+
+
 class AllGather(Function):
     # P/extend_distributed.py:335-381 (dim 0 only: the eval path gathers [B_local, 1] scores)
     @staticmethod

@@ -85,6 +85,43 @@ class GraphedTrainStep:
         self.graph.replay()
         return self.loss
 
+    # ---- raw-record operation (cloudtik_b200.criteo_input): the host supplies int32 Criteo records ----
+    def prefetch_records(self, host_records):
+        """Start the H2D copy of a pinned-host batch of RAW records (int32 [B, tot_fea], 160 B per sample);
+        ``step_records()`` decodes it on the device straight into the graph's static inputs."""
+        if not hasattr(self, "_rec_stream"):
+            self._rec_stream = torch.cuda.Stream()
+            dev = self.static[0].device
+            self._rec_stage = [torch.empty(host_records.shape, dtype=torch.int32, device=dev) for _ in range(2)]
+            self._rec_ready = [None, None]
+            self._rec_free = [None, None]
+            self._rec_slot = 0
+        k = self._rec_slot
+        with torch.cuda.stream(self._rec_stream):
+            if self._rec_free[k] is not None:
+                self._rec_stream.wait_event(self._rec_free[k])
+            self._rec_stage[k].copy_(host_records, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(self._rec_stream)
+        self._rec_ready[k] = ev
+        self._rec_slot ^= 1
+        return k
+
+    def step_records(self, k, max_ind_range: int = 0, **slices):
+        """One ``b200_criteo_transform`` launch (records of slot ``k`` -> X, Y, indices, offsets in the static
+        buffers: no device-to-device hop), then the graph replay.  ``slices``: tab_begin / tab_count /
+        row_begin / row_count for a rank of a table-wise sharded job."""
+        from . import ops
+        main = torch.cuda.current_stream()
+        main.wait_event(self._rec_ready[k])
+        X, Y, idx, off = self.static
+        ops.criteo_transform(self._rec_stage[k], max_ind_range, n_dense=X.shape[1], out=(X, Y, idx, off), **slices)
+        ev = torch.cuda.Event()
+        ev.record(main)
+        self._rec_free[k] = ev
+        self.graph.replay()
+        return self.loss
+
     def step(self, X, Y, indices, offsets):
         """Copy one batch into the static buffers and replay; returns the (device) loss tensor."""
         for d, s in zip(self.static, (X, Y, indices, offsets)):

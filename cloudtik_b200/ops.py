@@ -260,3 +260,37 @@ def interact_bwd(T: torch.Tensor, dR: torch.Tensor, out: torch.Tensor | None = N
     check(lib.b200_interact_bwd(T.data_ptr(), dR.data_ptr(), out.data_ptr(), B, F, D, dR.stride(0), _dt(T.dtype),
                                 _stream()), "b200_interact_bwd")
     return out
+
+
+def criteo_transform(records: torch.Tensor, max_ind_range: int = 0, n_dense: int = 13, tab_begin: int = 0,
+                     tab_count: int | None = None, row_begin: int = 0, row_count: int | None = None,
+                     dense_stride: int | None = None, out=None):
+    """Raw Criteo int32 records [N, tot_fea] (on the device) -> (dense fp32 [rows, dense_stride],
+    label fp32 [rows, 1], indices int64 [tab_count * N], offsets int64 [tab_count * N + 1]).
+    See b200_criteo_transform; ``out`` = the same 4-tuple preallocated (CUDA-graph replay)."""
+    _cuda(records, "records", torch.int32)
+    if records.dim() != 2 or not records.is_contiguous():
+        raise _lib.B200Error("criteo_transform: records must be a contiguous [N, tot_fea] int32 tensor")
+    N, tot = records.shape
+    n_tab_all = tot - 1 - n_dense
+    tab_count = n_tab_all - tab_begin if tab_count is None else tab_count
+    row_count = N - row_begin if row_count is None else row_count
+    dense_stride = n_dense if dense_stride is None else dense_stride
+    if out is None:
+        dev = records.device
+        out = (torch.empty(row_count, dense_stride, dtype=torch.float32, device=dev),
+               torch.empty(row_count, 1, dtype=torch.float32, device=dev),
+               torch.empty(tab_count * N, dtype=torch.int64, device=dev),
+               torch.empty(tab_count * N + 1, dtype=torch.int64, device=dev))
+    dense, label, indices, offsets = out
+    if (tuple(dense.shape) != (row_count, dense_stride) or label.numel() != row_count
+            or indices.numel() != tab_count * N or offsets.numel() != tab_count * N + 1):
+        raise _lib.B200Error("criteo_transform: preallocated outputs have the wrong shape")
+    for t, dt in ((dense, torch.float32), (label, torch.float32), (indices, torch.int64), (offsets, torch.int64)):
+        _cuda(t, "out", dt)
+        if not t.is_contiguous():
+            raise _lib.B200Error("criteo_transform: outputs must be contiguous")
+    check(lib.b200_criteo_transform(records.data_ptr(), N, tot, n_dense, int(max_ind_range), tab_begin, tab_count,
+                                    row_begin, row_count, dense.data_ptr(), dense_stride, label.data_ptr(),
+                                    indices.data_ptr(), offsets.data_ptr(), _stream()), "b200_criteo_transform")
+    return out

@@ -211,6 +211,30 @@ int b200_interact_fwd(const void* d_T, void* d_R, int64_t B, int64_t F, int64_t 
 int b200_interact_bwd(const void* d_T, const void* d_dR, void* d_dT, int64_t B, int64_t F,
                       int64_t D, int64_t ldr, int dtype, b200_stream_t stream);
 
+/* ---------------------------------------------------------------------------
+ * Input side: Criteo binary records -> the tensors the step consumes.
+ *
+ * Replaces CriteoBinDataset.__getitem__ (T/data_loader_terabyte.py:259-271: np.frombuffer of
+ * int32 records, view(-1, tot_fea), column split) and _transform_features (:83-102:
+ * ids % max_ind_range, log(float(x) + 1), ids transposed to table-major, offsets = arange per
+ * table, label as float column) with one kernel over the RAW records already copied to the device.
+ *
+ *   d_records  int32 [n_samples, tot_fea]: label, n_dense counts, then the categorical ids
+ *   tab_begin / tab_count    categorical features to emit (a rank's table slice), for ALL samples
+ *   row_begin / row_count    samples whose dense features and labels to emit (a rank's local batch)
+ *   d_dense    fp32 [row_count, dense_stride], columns n_dense..dense_stride-1 are written as 0
+ *   d_label    fp32 [row_count]
+ *   d_indices  int64 [tab_count, n_samples]  (= lS_i of the slice, or the merged-embedding index array)
+ *   d_offsets  int64 [tab_count * n_samples + 1] = 0, 1, 2, ... (one id per bag; lS_o rows are
+ *              d_offsets[t * n_samples ...] - t * n_samples, i.e. the same arange the reference builds)
+ * max_ind_range == 0 leaves the ids as they are; otherwise floor-mod (never negative), like torch.
+ * tot_fea <= 64.
+ */
+int b200_criteo_transform(const int32_t* d_records, int64_t n_samples, int tot_fea, int n_dense,
+                          int64_t max_ind_range, int tab_begin, int tab_count, int64_t row_begin,
+                          int64_t row_count, float* d_dense, int64_t dense_stride, float* d_label,
+                          int64_t* d_indices, int64_t* d_offsets, b200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -9,6 +9,7 @@ What is imported from the reference (read-only, unmodified):
   * ``P/dlrm_s_pytorch.py``  -> ``DLRM_Net`` (model, interaction), ``LRPolicyScheduler``
   * ``P/extend_distributed.py`` -> ``get_my_slice`` / ``get_split_lengths``
   * ``T/dlrm_data_pytorch.py`` -> ``generate_uniform_input_batch`` (ragged multi-hot bags)
+  * ``T/data_loader_terabyte.py`` -> ``_transform_features`` (binary Criteo records -> model inputs)
 with ``P/`` = applications/ai/quickstart/models/recommendation/pytorch/dlrm/product and
 ``T/`` = .../dlrm/training/bfloat16.  Absent third-party modules (mlperf_logging) are
 stubbed in ``sys.modules``; nothing in the reference tree is edited.
@@ -243,6 +244,40 @@ def gen_lr_policy(M):
     np.savez_compressed(os.path.join(OUT, "lr_policy.npz"), **out)
 
 
+def load_T_terabyte():
+    """T/data_loader_terabyte (``_transform_features``), loaded in isolation like the generator."""
+    sys.dont_write_bytecode = True
+    sys.path.insert(0, T_DIR)
+    try:
+        mod = importlib.import_module("data_loader_terabyte")
+    finally:
+        sys.path.remove(T_DIR)
+    for n in _SHARED_NAMES:
+        sys.modules.pop(n, None)
+    return mod
+
+
+def gen_criteo_transform(TB):
+    """Binary-record decode + ``_transform_features`` (T/data_loader_terabyte.py:83-102, :259-271) on
+    synthetic int32 records: label, 13 dense counts (incl. 0 and large values), 26 categorical ids
+    (incl. negative ones = hashed ids that wrapped, and ids >= max_ind_range)."""
+    rs = np.random.RandomState(2024)
+    out = {}
+    for name, N, mir in (("a", 37, 40_000_000), ("b", 64, 1000), ("c", 5, 0)):
+        rec = np.empty((N, 40), dtype=np.int32)
+        rec[:, 0] = rs.randint(0, 2, size=N)
+        rec[:, 1:14] = rs.randint(0, 3_000_000, size=(N, 13)) * (rs.rand(N, 13) < 0.8)
+        rec[:, 14:] = rs.randint(-2**31, 2**31 - 1, size=(N, 26), dtype=np.int64).astype(np.int32)
+        if mir == 0:
+            rec[:, 14:] = np.abs(rec[:, 14:] // 2)
+        t = torch.from_numpy(rec.copy())
+        X, lS_o, lS_i, Y = TB._transform_features(x_int_batch=t[:, 1:14], x_cat_batch=t[:, 14:], y_batch=t[:, 0],
+                                                  max_ind_range=mir, flag_input_torch_tensor=True)
+        out.update({f"{name}_records": rec, f"{name}_max_ind_range": np.int64(mir), f"{name}_X": X.numpy(),
+                    f"{name}_lS_o": lS_o.numpy(), f"{name}_lS_i": lS_i.contiguous().numpy(), f"{name}_Y": Y.numpy()})
+    np.savez_compressed(os.path.join(OUT, "criteo_transform.npz"), **out)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     G = load_T_generator()
@@ -252,6 +287,7 @@ def main():
     gen_lr_policy(M)
     gen_small_model(M, G)
     gen_kaggle_c1(M, G)
+    gen_criteo_transform(load_T_terabyte())
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

@@ -193,3 +193,26 @@ def interact_bwd(x: np.ndarray, ly, dR: np.ndarray):
     dT = np.matmul(dZ + dZ.transpose(0, 2, 1), T)
     dx = dR[:, :D] + dT[:, 0]
     return dx, [dT[:, 1 + k] for k in range(F - 1)]
+
+
+# ---------------------------------------------------------------- Criteo binary records
+def criteo_transform(records: np.ndarray, max_ind_range: int, n_dense: int = 13):
+    """``CriteoBinDataset.__getitem__`` + ``_transform_features``
+    (``T/data_loader_terabyte.py:259-271`` and ``:83-102``, ``flag_input_torch_tensor=True``).
+
+    ``records``: int32 ``[N, 1 + n_dense + T]`` = label, dense counts, categorical ids.
+    Returns ``(X fp32 [N, n_dense], lS_o int64 [T, N], lS_i int64 [T, N], Y fp32 [N, 1])``:
+    ``X = log(float32(x) + 1)``; ids ``% max_ind_range`` when it is > 0 with the sign of the
+    divisor (torch ``%`` on an int tensor = floor-mod: never negative here); ``lS_o[t] = arange(N)``."""
+    records = np.asarray(records, dtype=np.int32)
+    y = records[:, 0].astype(np.float32).reshape(-1, 1)
+    x_int = records[:, 1:1 + n_dense]
+    x_cat = records[:, 1 + n_dense:]
+    if max_ind_range > 0:
+        x_cat = np.mod(x_cat, np.int32(max_ind_range))  # np.mod is floor-mod as well
+    with np.errstate(divide="ignore", invalid="ignore"):
+        X = np.log(x_int.astype(np.float32) + np.float32(1.0)).astype(np.float32)
+    N, T = x_cat.shape
+    lS_o = np.tile(np.arange(N, dtype=np.int64).reshape(1, -1), (T, 1))
+    lS_i = np.ascontiguousarray(x_cat.astype(np.int64).T)
+    return X, lS_o, lS_i, y

@@ -36,3 +36,8 @@ def test_host_side_argument_checks_need_no_gpu():
     rc = _lib.lib.b200_sort_dedup(None, None, 5, 0, None, None, None, None, None, None, 0, None)
     assert rc == 2
     assert _lib.lib.b200_emb_bwd_workspace_bytes(1000, 128) > 6 * 4000
+    # record wider than the staging buffer / table range outside the record
+    rc = _lib.lib.b200_criteo_transform(None, 8, 100, 13, 0, 0, 26, 0, 8, None, 13, None, None, None, None)
+    assert rc == 1 and b"record shape" in _lib.lib.b200_last_error()
+    rc = _lib.lib.b200_criteo_transform(None, 8, 40, 13, 0, 20, 10, 0, 8, None, 13, None, None, None, None)
+    assert rc == 1 and b"table range" in _lib.lib.b200_last_error()

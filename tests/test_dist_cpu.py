@@ -59,6 +59,13 @@ def _worker(rank, world, port, n_tables, N, E, ret):
         got.backward(gout[rank * lN:(rank + 1) * lN])
         gw = torch.cat([gout[:, t * E:(t + 1) * E] for t in local], dim=1)
         assert torch.equal(buf.grad, gw)
+        # shuffle_data: local-batch indices of all tables -> global-batch indices of my tables
+        if n_tables % world == 0:
+            loc_idx = [i[rank * lN:(rank + 1) * lN] for i in idx]
+            sh = ext_dist.shuffle_data(loc_idx)
+            g_o, g_i = ext_dist.global_batch_indices(sh, len(local))
+            for k, t in enumerate(local):
+                assert torch.equal(g_i[k], idx[t]) and torch.equal(g_o[k], torch.arange(N))
         # all_gather of per-rank scores (eval path)
         scores = torch.full((lN, 1), float(rank))
         allg = ext_dist.all_gather(scores, None)

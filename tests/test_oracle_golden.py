@@ -167,3 +167,17 @@ def test_lr_scheduler_mirror_matches_reference_traces(golden):
             opt.step()
             sch.step()
         np.testing.assert_allclose(got, g[f"trace{c}"], rtol=1e-12)
+
+
+def test_criteo_transform_matches_reference_fixture(golden):
+    """oracle.criteo_transform vs T/data_loader_terabyte._transform_features on raw int32 records:
+    ids / offsets / labels bit-exact (negative ids, ids beyond max_ind_range, max_ind_range = 0),
+    dense = log(x + 1) within one float ulp of torch's log."""
+    g = golden("criteo_transform")
+    for tag in "abc":
+        X, lS_o, lS_i, Y = ops.criteo_transform(g[f"{tag}_records"], int(g[f"{tag}_max_ind_range"]))
+        np.testing.assert_array_equal(lS_i, g[f"{tag}_lS_i"])
+        np.testing.assert_array_equal(lS_o, g[f"{tag}_lS_o"])
+        np.testing.assert_array_equal(Y, g[f"{tag}_Y"])
+        np.testing.assert_allclose(X, g[f"{tag}_X"], rtol=2e-7, atol=0)
+        assert lS_i.min() >= 0 or int(g[f"{tag}_max_ind_range"]) == 0
