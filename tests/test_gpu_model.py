@@ -108,7 +108,10 @@ def test_per_table_embedding_bag_seam(opt_name):
     W = rs.randn(n, D).astype(np.float32)
     ref = torch.nn.EmbeddingBag(n, D, mode="sum", sparse=True, _weight=torch.tensor(W.copy()))
     mine = EmbeddingBag(n, D, _weight=torch.tensor(W.copy()))
-    mk = (lambda ps: torch.optim.SGD(ps, lr=0.1)) if opt_name == "sgd" else (lambda ps: torch.optim.Adagrad(ps, lr=0.05))
+    mk = (lambda ps: torch.optim.SGD(ps, lr=0.1)) if opt_name == "sgd" else (
+        # a non-zero initial accumulator: from zero the first Adagrad step is lr * sign(g), and a last-bit
+        # difference in a near-zero summed gradient (CPU vs CUDA summation order) would flip a whole step
+        lambda ps: torch.optim.Adagrad(ps, lr=0.05, initial_accumulator_value=0.1))
     o_ref, o_mine = mk(ref.parameters()), mk(mine.parameters())
     for step in range(3):
         lens = rs.randint(0, 7, size=B)

@@ -357,6 +357,32 @@ def test_interaction_tensor_core_path(B, F, D, pad):
     np.testing.assert_allclose(dT.float().cpu().numpy(), wdT, rtol=1e-2, atol=1e-2 * np.sqrt(F))
 
 
+@pytest.mark.parametrize("B,D,pad", [(1, 128, 1), (5, 128, 8), (1000, 128, 8), (4099, 128, 1), (333, 64, 8), (777, 32, 1)])
+def test_interaction_fp32_register_tiled_path(B, D, pad):
+    """fp32, F = 27, D in {32, 64, 128}: the warp-per-sample register-tiled kernels (interact_f32.cu), against a
+    float64 evaluation of the same inputs at the north_star fp32 bound (1e-5 relative)."""
+    ops = _ops()
+    F = 27
+    rs = np.random.RandomState(B + D)
+    Tn = rs.randn(B, F, D).astype(np.float32)
+    T = torch.tensor(Tn).cuda()
+    W = D + F * (F - 1) // 2
+    R = ops.interact_fwd(T, pad_to=pad)
+    ldr = R.shape[1]
+    T64 = Tn.astype(np.float64)
+    want = ref.interact_fwd(T64[:, 0], [T64[:, k] for k in range(1, F)])
+    got = R.cpu().numpy()
+    np.testing.assert_allclose(got[:, :W], want, rtol=1e-5, atol=1e-5 * np.sqrt(D))
+    np.testing.assert_array_equal(got[:, :D], Tn[:, 0])
+    assert (got[:, W:] == 0).all()
+    dRn = np.zeros((B, ldr), dtype=np.float32)
+    dRn[:, :W] = rs.randn(B, W)
+    dT = ops.interact_bwd(T, torch.tensor(dRn).cuda())
+    dx, dly = ref.interact_bwd(T64[:, 0], [T64[:, k] for k in range(1, F)], dRn[:, :W].astype(np.float64))
+    wdT = np.stack([dx] + dly, axis=1)
+    np.testing.assert_allclose(dT.cpu().numpy(), wdT, rtol=1e-5, atol=1e-5 * np.sqrt(F))
+
+
 def test_interaction_kat():
     ops = _ops()
     T = torch.tensor([[[1.0, 2.0], [3.0, 4.0], [5.0, 6.0]]], device="cuda")
