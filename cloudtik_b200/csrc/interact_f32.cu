@@ -102,7 +102,7 @@ __device__ __forceinline__ void fwd_groups(const float (&t)[F][VPL], float* Rpai
 }
 
 template <int F, int VPL>
-__global__ void __launch_bounds__(IF_THREADS, VPL == 4 ? 3 : 1)
+__global__ void __launch_bounds__(IF_THREADS, VPL >= 2 ? 3 : 5)
     interact_fwd_f32_kernel(const float* __restrict__ T, float* __restrict__ R, int64_t B, int64_t ldr, bool r_vec) {
   constexpr int D = 32 * VPL;
   constexpr int NP = F * (F - 1) / 2;
