@@ -8,7 +8,8 @@ bf16 ``[B, N]`` output gradient for the bias gradient (48 us for 32768 x 1024, a
 ``mlp_forward`` walks the SAME modules (same parameters, same state_dict keys) but calls, per
 (Linear, ReLU) pair, one autograd function that
   * fuses bias + ReLU into the GEMM epilogue (``torch._addmm_activation``),
-  * computes the bias gradient as a skinny tensor-core GEMM ``ones[8, B] @ dY`` instead of a reduction,
+  * masks the output gradient with the ReLU and sums its columns for the bias gradient in ONE pass over the
+    matrix (``b200_relu_bwd_bias``; layers without a ReLU use a skinny tensor-core GEMM ``ones[8, B] @ dY``),
   * casts each weight to bf16 once per step.
 Numerically it is the autocast path (bf16 operands, fp32 accumulation, bf16 activations / gradients).
 """
@@ -17,6 +18,7 @@ from __future__ import annotations
 import torch
 import torch.nn as nn
 
+from . import ops
 from .interaction import PaddedLinear
 
 _ONES = {}
@@ -53,9 +55,14 @@ class _LinearReLU(torch.autograd.Function):
     def backward(ctx, dy):
         x16, w16, y = ctx.saved_tensors
         dy = dy.contiguous()
-        if ctx.relu:
-            dy = torch.ops.aten.threshold_backward(dy, y, 0)
         dx = dw = db = None
+        if ctx.relu:
+            if dy.dtype == torch.bfloat16 and dy.shape[1] % 8 == 0 and dy.data_ptr() % 16 == 0:
+                # one pass: ReLU mask + fp32 column sums (b200_relu_bwd_bias) instead of threshold_backward
+                # followed by a bias-gradient reduction of the same matrix
+                dy, db = ops.relu_bwd_bias(dy, y)
+            else:
+                dy = torch.ops.aten.threshold_backward(dy, y, 0)
         if ctx.needs_input_grad[0]:
             dx = dy @ w16
             if dx.dtype != ctx.x_dtype:
@@ -65,7 +72,7 @@ class _LinearReLU(torch.autograd.Function):
             if ctx.extra > 0:
                 dw = dw[:, :dw.shape[1] - ctx.extra]
             dw = dw.float()
-        if ctx.needs_input_grad[2]:
+        if ctx.needs_input_grad[2] and db is None:
             db = (_ones(dy.shape[0], dy.device) @ dy)[0].float()  # column sums on the tensor cores
         return dx, dw, db, None
 

@@ -294,3 +294,19 @@ def criteo_transform(records: torch.Tensor, max_ind_range: int = 0, n_dense: int
                                     row_begin, row_count, dense.data_ptr(), dense_stride, label.data_ptr(),
                                     indices.data_ptr(), offsets.data_ptr(), _stream()), "b200_criteo_transform")
     return out
+
+
+def relu_bwd_bias(dy: torch.Tensor, y: torch.Tensor):
+    """(dz, db): dz = dy * (y > 0) in bf16, db = fp32 column sums of dz.  See b200_relu_bwd_bias."""
+    _cuda(dy, "dy", torch.bfloat16)
+    _cuda(y, "y", torch.bfloat16)
+    if dy.dim() != 2 or dy.shape != y.shape or not dy.is_contiguous() or not y.is_contiguous():
+        raise _lib.B200Error("relu_bwd_bias: dy and y must be contiguous [B, N] tensors of the same shape")
+    B, N = dy.shape
+    dz = torch.empty_like(dy)
+    db = torch.empty(N, dtype=torch.float32, device=dy.device)
+    nbytes = lib.b200_relu_bwd_bias_workspace_bytes(B, N)
+    ws = torch.empty(max(nbytes, 4) // 4, dtype=torch.float32, device=dy.device)
+    check(lib.b200_relu_bwd_bias(dy.data_ptr(), y.data_ptr(), dz.data_ptr(), db.data_ptr(), B, N, BF16,
+                                 ws.data_ptr(), nbytes, _stream()), "b200_relu_bwd_bias")
+    return dz, db

@@ -235,6 +235,19 @@ int b200_criteo_transform(const int32_t* d_records, int64_t n_samples, int tot_f
                           int64_t row_count, float* d_dense, int64_t dense_stride, float* d_label,
                           int64_t* d_indices, int64_t* d_offsets, b200_stream_t stream);
 
+/* ---------------------------------------------------------------------------
+ * Dense-MLP backward glue.  The MLP GEMMs stay on torch / cuBLAS (north_star); what autograd launches
+ * AROUND them per (Linear, ReLU) pair -- threshold_backward over the [B, N] output gradient plus a column
+ * reduction of the same matrix for the bias gradient (reference MLP build P/dlrm_s_pytorch.py:172-211;
+ * its IPEX path fuses Linear+ReLU, :926-953) -- is one pass here:
+ *   d_dz[b, n] = d_y[b, n] > 0 ? d_dy[b, n] : 0        (bf16, [B, N] contiguous, N % 8 == 0)
+ *   d_db[n]    = sum_b d_dz[b, n]                       (fp32, summed in a fixed order: deterministic)
+ * ws: b200_relu_bwd_bias_workspace_bytes(B, N) bytes of scratch.
+ */
+size_t b200_relu_bwd_bias_workspace_bytes(int64_t B, int64_t N);
+int b200_relu_bwd_bias(const void* d_dy, const void* d_y, void* d_dz, float* d_db, int64_t B, int64_t N,
+                       int dtype, void* ws, size_t ws_bytes, b200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

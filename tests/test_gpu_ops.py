@@ -388,3 +388,24 @@ def test_interaction_kat():
     T = torch.tensor([[[1.0, 2.0], [3.0, 4.0], [5.0, 6.0]]], device="cuda")
     R = ops.interact_fwd(T)
     assert R.cpu().tolist() == [[1.0, 2.0, 11.0, 17.0, 39.0]]
+
+
+@pytest.mark.parametrize("B,N", [(1, 8), (127, 128), (128, 256), (1000, 1024), (4099, 512), (32768, 1024)])
+def test_relu_bwd_bias_matches_torch(B, N):
+    """b200_relu_bwd_bias: the masked gradient must equal aten.threshold_backward BIT FOR BIT (it only zeroes
+    entries), the bias gradient must equal the fp64 column sum of that masked matrix to fp32 accuracy."""
+    ops = _ops()
+    g = torch.Generator(device="cuda").manual_seed(B + N)
+    y = torch.relu(torch.randn(B, N, device="cuda", generator=g)).bfloat16()
+    y[0, 0] = float("nan")      # NaN activation keeps the gradient (torch: `self <= 0 ? 0 : grad`)
+    y[-1, -1] = -0.0
+    dy = torch.randn(B, N, device="cuda", generator=g).bfloat16()
+    dz, db = ops.relu_bwd_bias(dy, y)
+    want = torch.ops.aten.threshold_backward(dy, y, 0)
+    assert torch.equal(dz.view(torch.int16), want.view(torch.int16))
+    ref_db = want.double().sum(0)
+    scale = want.double().abs().sum(0).clamp_min(1.0)
+    assert bool(((db.double() - ref_db).abs() <= 1e-6 * scale).all())
+    # deterministic: same bits on a second call
+    dz2, db2 = ops.relu_bwd_bias(dy, y)
+    assert torch.equal(db, db2)
