@@ -41,6 +41,7 @@ SIGNATURES = {
                                      _p, _c.c_size_t, _p, _p]),
     "b200_interact_fwd": (_int, [_p, _p, _i64, _i64, _i64, _i64, _int, _p]),
     "b200_interact_bwd": (_int, [_p, _p, _p, _i64, _i64, _i64, _i64, _int, _p]),
+    "b200_emb_fwd_q8": (_int, [_p, _p, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i64, _int, _p, _p]),
     "b200_relu_bwd_bias_workspace_bytes": (_c.c_size_t, [_i64, _i64]),
     "b200_relu_bwd_bias": (_int, [_p, _p, _p, _p, _i64, _i64, _int, _p, _c.c_size_t, _p]),
     "b200_criteo_transform": (_int, [_p, _i64, _int, _int, _i64, _int, _int, _i64, _i64, _p, _i64, _p, _p, _p, _p]),

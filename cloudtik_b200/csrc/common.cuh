@@ -32,7 +32,7 @@ void set_error(const char* fmt, ...);
 
 static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
-static inline int dtype_size(int dt) { return dt == B200_BF16 ? 2 : 4; }
+static inline int dtype_size(int dt) { return dt == B200_BF16 ? 2 : (dt == B200_I8 ? 1 : 4); }
 
 // ---------------------------------------------------------------- device helpers
 #ifdef __CUDACC__
@@ -169,6 +169,27 @@ struct Vec16<__nv_bfloat16> {
   }
 };
 
+template <>
+struct Vec16<int8_t> {  // quantised rows (forward only): 16 values per vector, the row scale is applied by the caller
+  static constexpr int VE = 16;
+  __device__ static __forceinline__ void unpack(float* out, uint4 v) {
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int h = 0; h < 4; ++h) {
+      out[4 * h + 0] = (float)(int8_t)(w[h] & 0xffu);
+      out[4 * h + 1] = (float)(int8_t)((w[h] >> 8) & 0xffu);
+      out[4 * h + 2] = (float)(int8_t)((w[h] >> 16) & 0xffu);
+      out[4 * h + 3] = (float)(int8_t)(w[h] >> 24);
+    }
+  }
+  __device__ static __forceinline__ void accum(float* acc, uint4 v) {
+    float f[16];
+    unpack(f, v);
+#pragma unroll
+    for (int x = 0; x < 16; ++x) acc[x] += f[x];
+  }
+};
+
 __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
   __nv_bfloat162 h = __floats2bfloat162_rn(a, b);  // .x = a (low half)
   return *reinterpret_cast<uint32_t*>(&h);
@@ -198,6 +219,16 @@ __device__ __forceinline__ void store_vec<__nv_bfloat16, 8, true>(__nv_bfloat16*
                          pack_bf16x2(v[6], v[7])));
 }
 template <>
+__device__ __forceinline__ void store_vec<float, 16, true>(float* p, const float* v) {
+  store_vec<float, 8, true>(p, v);
+  store_vec<float, 8, true>(p + 8, v + 8);
+}
+template <>
+__device__ __forceinline__ void store_vec<__nv_bfloat16, 16, true>(__nv_bfloat16* p, const float* v) {
+  store_vec<__nv_bfloat16, 8, true>(p, v);
+  store_vec<__nv_bfloat16, 8, true>(p + 8, v + 8);
+}
+template <>
 __device__ __forceinline__ void store_vec<float, 4, false>(float* p, const float* v) {
   st_v4(p, make_uint4(__float_as_uint(v[0]), __float_as_uint(v[1]), __float_as_uint(v[2]),
                       __float_as_uint(v[3])));
@@ -214,6 +245,8 @@ template <>
 __device__ __forceinline__ float to_f32<float>(float v) { return v; }
 template <>
 __device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <>
+__device__ __forceinline__ float to_f32<int8_t>(int8_t v) { return (float)v; }
 template <typename T>
 __device__ __forceinline__ T from_f32(float v);
 template <>

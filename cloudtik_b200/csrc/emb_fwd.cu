@@ -40,7 +40,21 @@ struct EmbFwdParams {
   int64_t lN;
   int64_t F;
   int64_t feat0;
+  const float* const* scales;  // int8 tables: per-table pointer to the fp32 row scales (else unused)
 };
+
+// acc += row (fp32 / bf16 tables) or acc += scale * row (int8 tables)
+template <typename WT>
+__device__ __forceinline__ void accum_row(float* acc, uint4 v, float s) {
+  if constexpr (sizeof(WT) == 1) {
+    float f[16];
+    Vec16<WT>::unpack(f, v);
+#pragma unroll
+    for (int x = 0; x < 16; ++x) acc[x] = fmaf(s, f[x], acc[x]);
+  } else {
+    Vec16<WT>::accum(acc, v);
+  }
+}
 
 template <typename WT, typename OT, int G, int NV>
 __global__ void __launch_bounds__(FWD_THREADS) emb_fwd_kernel(const EmbFwdParams p) {
@@ -98,6 +112,8 @@ __global__ void __launch_bounds__(FWD_THREADS) emb_fwd_kernel(const EmbFwdParams
   const int gid = tid / G;
   const int lane = tid % G;
   const int64_t nrows = p.rows[t];
+  constexpr bool Q8 = sizeof(WT) == 1;
+  const float* S = Q8 ? p.scales[t] : nullptr;  // row scales of an int8 table
   const char* W = static_cast<const char*>(p.weights[t]);
   const size_t row_bytes = (size_t)p.D * sizeof(WT);
   OT* out_t;
@@ -137,9 +153,11 @@ __global__ void __launch_bounds__(FWD_THREADS) emb_fwd_kernel(const EmbFwdParams
 #pragma unroll
       for (int u = 0; u < 4; ++u) row[u] = (r + u * NG < nb) ? s_row[r + u * NG] : 0xffffffffu;
       uint4 v[4][NV];
+      float sc[4];
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const char* src = Wl + (size_t)row[u] * row_bytes;
+        sc[u] = (Q8 && row[u] != 0xffffffffu) ? __ldg(S + row[u]) : 1.f;
 #pragma unroll
         for (int k = 0; k < NV; ++k)
           v[u][k] = (row[u] != 0xffffffffu && lane + k * G < p.V) ? ld_nc_v4(src + (size_t)k * G * 16)
@@ -157,6 +175,10 @@ __global__ void __launch_bounds__(FWD_THREADS) emb_fwd_kernel(const EmbFwdParams
               } else {
                 float f[VE];
                 Vec16<WT>::unpack(f, v[u][k]);
+                if constexpr (Q8) {
+#pragma unroll
+                  for (int x = 0; x < VE; ++x) f[x] *= sc[u];
+                }
                 store_vec<OT, VE, true>(dst + k * G * VE, f);
               }
             }
@@ -178,10 +200,12 @@ __global__ void __launch_bounds__(FWD_THREADS) emb_fwd_kernel(const EmbFwdParams
         for (int x = 0; x < VE; ++x) acc[k][x] = 0.f;
       for (int j = sb; j < eb; j += 4) {
         uint4 v[4][NV];
+        float sc[4];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           const uint32_t row = (j + q < eb) ? s_row[j + q] : 0xffffffffu;
           const char* src = Wl + (size_t)row * row_bytes;
+          sc[q] = (Q8 && row != 0xffffffffu) ? __ldg(S + row) : 0.f;
 #pragma unroll
           for (int k = 0; k < NV; ++k)
             v[q][k] = (row != 0xffffffffu && lane + k * G < p.V) ? ld_nc_v4(src + (size_t)k * G * 16)
@@ -190,7 +214,7 @@ __global__ void __launch_bounds__(FWD_THREADS) emb_fwd_kernel(const EmbFwdParams
 #pragma unroll
         for (int q = 0; q < 4; ++q)
 #pragma unroll
-          for (int k = 0; k < NV; ++k) Vec16<WT>::accum(acc[k], v[q][k]);
+          for (int k = 0; k < NV; ++k) accum_row<WT>(acc[k], v[q][k], sc[q]);
       }
       OT* dst = outl + (int64_t)bag * p.out_stride_bag;
 #pragma unroll
@@ -211,6 +235,7 @@ __global__ void __launch_bounds__(FWD_THREADS) emb_fwd_kernel(const EmbFwdParams
       for (int x = 0; x < VE; ++x) acc[k][x] = 0.f;
     for (int64_t j = sb; j < eb; j += 4) {
       uint4 v[4][NV];
+      float sc[4];
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         bool ok = false;
@@ -220,6 +245,7 @@ __global__ void __launch_bounds__(FWD_THREADS) emb_fwd_kernel(const EmbFwdParams
           ok = (uint64_t)idx < (uint64_t)nrows;
           if (!ok && p.error) *p.error = 1;
         }
+        sc[q] = (Q8 && ok) ? __ldg(S + idx) : 0.f;
         const char* src = Wl + (ok ? (size_t)idx : 0) * row_bytes;
 #pragma unroll
         for (int k = 0; k < NV; ++k)
@@ -228,7 +254,7 @@ __global__ void __launch_bounds__(FWD_THREADS) emb_fwd_kernel(const EmbFwdParams
 #pragma unroll
       for (int q = 0; q < 4; ++q)
 #pragma unroll
-        for (int k = 0; k < NV; ++k) Vec16<WT>::accum(acc[k], v[q][k]);
+        for (int k = 0; k < NV; ++k) accum_row<WT>(acc[k], v[q][k], sc[q]);
     }
     OT* dst = outl + (int64_t)bag * p.out_stride_bag;
 #pragma unroll
@@ -252,7 +278,11 @@ __global__ void emb_fwd_scalar_kernel(const EmbFwdParams p, int64_t T) {
     for (int64_t j = p.offsets[g]; j < p.offsets[g + 1]; ++j) {
       const int64_t idx = p.indices[j];
       if ((uint64_t)idx < (uint64_t)nrows) {
-        acc += to_f32<WT>(W[idx * p.D + d]);
+        if constexpr (sizeof(WT) == 1) {
+          acc = fmaf(p.scales[t][idx], to_f32<WT>(W[idx * p.D + d]), acc);
+        } else {
+          acc += to_f32<WT>(W[idx * p.D + d]);
+        }
       } else if (p.error) {
         *p.error = 1;
       }
@@ -296,16 +326,17 @@ static int emb_fwd_impl(const void* const* d_weights, const int64_t* d_rows, con
                         const int64_t* d_offsets, void* d_out, int64_t nnz, int64_t T, int64_t B, int64_t D,
                         int64_t out_stride_table, int64_t out_stride_bag, int w_dtype, int out_dtype,
                         int32_t* d_error, b200_stream_t stream, void* const* d_out_ptrs, int64_t lN, int64_t F,
-                        int64_t feat0) {
+                        int64_t feat0, const float* const* d_scales = nullptr) {
   B200_REQUIRE(T >= 0 && B >= 0 && D > 0 && nnz >= 0, B200_EINVAL, "emb_fwd: negative size");
   if (T == 0 || B == 0) return B200_OK;
   B200_REQUIRE(d_weights && d_rows && d_offsets && (d_out || d_out_ptrs) && (d_indices || nnz == 0), B200_EINVAL,
                "emb_fwd: null pointer");
   B200_REQUIRE(T <= 65535, B200_EUNSUPPORTED, "emb_fwd: more than 65535 tables");
-  B200_REQUIRE((w_dtype == B200_F32 || w_dtype == B200_BF16) &&
+  B200_REQUIRE((w_dtype == B200_F32 || w_dtype == B200_BF16 || (w_dtype == B200_I8 && d_scales)) &&
                    (out_dtype == B200_F32 || out_dtype == B200_BF16),
                B200_EINVAL, "emb_fwd: bad dtype");
   EmbFwdParams p;
+  p.scales = d_scales;
   p.weights = d_weights;
   p.rows = d_rows;
   p.indices = d_indices;
@@ -346,6 +377,11 @@ static int emb_fwd_impl(const void* const* d_weights, const int64_t* d_rows, con
                                 : FN<float, __nv_bfloat16>(p, T, st))              \
        : (out_dtype == B200_F32 ? FN<__nv_bfloat16, float>(p, T, st)               \
                                 : FN<__nv_bfloat16, __nv_bfloat16>(p, T, st)))
+  if (w_dtype == B200_I8) {
+    if (vec_ok) return out_dtype == B200_F32 ? launch_fwd<int8_t, float>(p, T, st) : launch_fwd<int8_t, __nv_bfloat16>(p, T, st);
+    return out_dtype == B200_F32 ? launch_fwd_scalar<int8_t, float>(p, T, st)
+                                 : launch_fwd_scalar<int8_t, __nv_bfloat16>(p, T, st);
+  }
   if (vec_ok) return B200_DISPATCH(launch_fwd);
   return B200_DISPATCH(launch_fwd_scalar);
 #undef B200_DISPATCH
@@ -358,6 +394,15 @@ extern "C" int b200_emb_fwd(const void* const* d_weights, const int64_t* d_rows,
                             b200_stream_t stream) {
   return emb_fwd_impl(d_weights, d_rows, d_indices, d_offsets, d_out, nnz, T, B, D, out_stride_table,
                       out_stride_bag, w_dtype, out_dtype, d_error, stream, nullptr, 0, 0, 0);
+}
+
+extern "C" int b200_emb_fwd_q8(const void* const* d_weights, const float* const* d_scales, const int64_t* d_rows,
+                               const int64_t* d_indices, const int64_t* d_offsets, void* d_out, int64_t nnz,
+                               int64_t T, int64_t B, int64_t D, int64_t out_stride_table, int64_t out_stride_bag,
+                               int out_dtype, int32_t* d_error, b200_stream_t stream) {
+  B200_REQUIRE(d_scales || T == 0 || B == 0, B200_EINVAL, "emb_fwd_q8: null scale table");
+  return emb_fwd_impl(d_weights, d_rows, d_indices, d_offsets, d_out, nnz, T, B, D, out_stride_table,
+                      out_stride_bag, B200_I8, out_dtype, d_error, stream, nullptr, 0, 0, 0, d_scales);
 }
 
 extern "C" int b200_emb_fwd_sharded(const void* const* d_weights, const int64_t* d_rows,

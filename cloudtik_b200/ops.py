@@ -310,3 +310,43 @@ def relu_bwd_bias(dy: torch.Tensor, y: torch.Tensor):
     check(lib.b200_relu_bwd_bias(dy.data_ptr(), y.data_ptr(), dz.data_ptr(), db.data_ptr(), B, N, BF16,
                                  ws.data_ptr(), nbytes, _stream()), "b200_relu_bwd_bias")
     return dz, db
+
+
+class QuantTableSet:
+    """int8 tables [rows_t, D] with one fp32 scale per row (zero point 0): inference only."""
+
+    def __init__(self, qweights, scales):
+        assert len(qweights) > 0 and len(qweights) == len(scales)
+        self.weights, self.scales = list(qweights), list(scales)
+        self.D = int(qweights[0].shape[1])
+        self.device = qweights[0].device
+        for q, s in zip(qweights, scales):
+            _cuda(q, "qweight", torch.int8)
+            _cuda(s, "scale", torch.float32)
+            if q.shape[1] != self.D or not q.is_contiguous() or s.numel() != q.shape[0] or not s.is_contiguous():
+                raise _lib.B200Error("int8 tables: [rows, D] contiguous weights and one scale per row")
+            if q.data_ptr() % 16:
+                raise _lib.B200Error("table base pointers must be 16-byte aligned")
+        self.rows = [int(q.shape[0]) for q in qweights]
+        self.d_ptrs = torch.tensor([q.data_ptr() for q in qweights], dtype=torch.int64, device=self.device)
+        self.d_scale_ptrs = torch.tensor([s.data_ptr() for s in scales], dtype=torch.int64, device=self.device)
+        self.d_rows = torch.tensor(self.rows, dtype=torch.int64, device=self.device)
+
+    def __len__(self):
+        return len(self.weights)
+
+
+def emb_fwd_q8(tables: QuantTableSet, indices, offsets, B: int, out: torch.Tensor, stride_table: int,
+               stride_bag: int, error: torch.Tensor | None = None):
+    """Pooled forward over int8 tables, dequantised on the fly.  See b200_emb_fwd_q8."""
+    _cuda(indices, "indices", torch.int64)
+    _cuda(offsets, "offsets", torch.int64)
+    _cuda(out, "out")
+    T = len(tables)
+    if offsets.numel() != T * B + 1:
+        raise _lib.B200Error(f"offsets must have T*B+1 = {T * B + 1} entries, got {offsets.numel()}")
+    check(lib.b200_emb_fwd_q8(tables.d_ptrs.data_ptr(), tables.d_scale_ptrs.data_ptr(), tables.d_rows.data_ptr(),
+                              indices.data_ptr(), offsets.data_ptr(), out.data_ptr(), indices.numel(), T, B,
+                              tables.D, stride_table, stride_bag, _dt(out.dtype),
+                              error.data_ptr() if error is not None else None, _stream()), "b200_emb_fwd_q8")
+    return out

@@ -28,7 +28,7 @@ extern "C" {
 
 typedef struct CUstream_st* b200_stream_t; /* == cudaStream_t */
 
-enum { B200_F32 = 0, B200_BF16 = 1 };
+enum { B200_F32 = 0, B200_BF16 = 1, B200_I8 = 2 /* tables of b200_emb_fwd_q8 only */ };
 
 enum {
   B200_OK = 0,
@@ -234,6 +234,19 @@ int b200_criteo_transform(const int32_t* d_records, int64_t n_samples, int tot_f
                           int64_t max_ind_range, int tab_begin, int tab_count, int64_t row_begin,
                           int64_t row_count, float* d_dense, int64_t dense_stride, float* d_label,
                           int64_t* d_indices, int64_t* d_offsets, b200_stream_t stream);
+
+/* ---------------------------------------------------------------------------
+ * Inference with int8 tables.  The reference's --int8 path quantises every
+ * EmbeddingBag weight with a symmetric int8 observer (P/dlrm_s_pytorch.py:428-437,868-883: QConfig(weight =
+ * PerChannelMinMaxObserver(qint8, per_channel_symmetric)), calibration file P/int8_configure.json); here a
+ * table is int8 [rows, D] plus one fp32 scale per ROW (zero point 0), and the pooled forward dequantises on
+ * the fly:  out[t, b, :] = sum over the bag of  d_scales[t][r] * float(d_weights[t][r, :]).
+ * Same arguments as b200_emb_fwd otherwise (d_scales: T device pointers to fp32 [rows_t]); forward only.
+ */
+int b200_emb_fwd_q8(const void* const* d_weights, const float* const* d_scales, const int64_t* d_rows,
+                    const int64_t* d_indices, const int64_t* d_offsets, void* d_out, int64_t nnz, int64_t T,
+                    int64_t B, int64_t D, int64_t out_stride_table, int64_t out_stride_bag, int out_dtype,
+                    int32_t* d_error, b200_stream_t stream);
 
 /* ---------------------------------------------------------------------------
  * Dense-MLP backward glue.  The MLP GEMMs stay on torch / cuBLAS (north_star); what autograd launches

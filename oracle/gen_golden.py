@@ -278,6 +278,29 @@ def gen_criteo_transform(TB):
     np.savez_compressed(os.path.join(OUT, "criteo_transform.npz"), **out)
 
 
+def gen_int8_tables():
+    """Weight half of the reference's int8 QConfig (P/dlrm_s_pytorch.py:431-432,870-871):
+    PerChannelMinMaxObserver(dtype=qint8, qscheme=per_channel_symmetric) on an EmbeddingBag weight (channel axis 0
+    = one scale per row) + torch.quantize_per_channel -- run here with torch's own implementation."""
+    from torch.ao.quantization import PerChannelMinMaxObserver
+    rs = np.random.RandomState(77)
+    W = (rs.randn(200, 64) * (rs.rand(200, 1) * 2 + 1e-3)).astype(np.float32)
+    W[3] = 0.0            # all-zero row: scale = eps
+    W[4, :] = 1e-20       # below eps * 127.5
+    W[5, 0] = -7.0        # min dominates
+    obs = PerChannelMinMaxObserver(ch_axis=0, dtype=torch.qint8, qscheme=torch.per_channel_symmetric)
+    obs(torch.tensor(W))
+    scale, zp = obs.calculate_qparams()
+    q = torch.quantize_per_channel(torch.tensor(W), scale, zp, 0, torch.qint8)
+    lens = rs.randint(0, 5, size=50)
+    off = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    idx = rs.randint(0, 200, size=int(lens.sum())).astype(np.int64)
+    deq = q.dequantize()
+    pooled = torch.nn.functional.embedding_bag(torch.tensor(idx), deq, torch.tensor(off[:-1]), mode="sum")
+    np.savez_compressed(os.path.join(OUT, "int8_tables.npz"), W=W, scale=scale.float().numpy(),
+                        zero_point=zp.numpy(), q=q.int_repr().numpy(), idx=idx, off=off, pooled=pooled.numpy())
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     G = load_T_generator()
@@ -288,6 +311,7 @@ def main():
     gen_small_model(M, G)
     gen_kaggle_c1(M, G)
     gen_criteo_transform(load_T_terabyte())
+    gen_int8_tables()
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

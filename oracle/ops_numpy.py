@@ -216,3 +216,27 @@ def criteo_transform(records: np.ndarray, max_ind_range: int, n_dense: int = 13)
     lS_o = np.tile(np.arange(N, dtype=np.int64).reshape(1, -1), (T, 1))
     lS_i = np.ascontiguousarray(x_cat.astype(np.int64).T)
     return X, lS_o, lS_i, y
+
+
+# ---------------------------------------------------------------- int8 tables for inference
+def quantize_rowwise_int8(W: np.ndarray):
+    """Symmetric int8 quantisation with one scale per ROW, zero point 0 -- the arithmetic of
+    ``torch.ao.quantization.PerChannelMinMaxObserver(ch_axis=0, dtype=qint8, qscheme=per_channel_symmetric)``
+    followed by ``torch.quantize_per_channel`` (the weight half of the reference's int8 QConfig,
+    ``P/dlrm_s_pytorch.py:431-432,870-871``):
+    ``scale = max(max(-min, max) / 127.5, eps_fp32)``, ``q = clamp(rint(w / scale), -128, 127)`` with fp32
+    arithmetic and round-half-to-even.  Returns (q int8 [n, D], scale fp32 [n])."""
+    W = np.asarray(W, dtype=np.float32)
+    mn = np.minimum(W.min(axis=1), 0).astype(np.float32)
+    mx = np.maximum(W.max(axis=1), 0).astype(np.float32)
+    amax = np.maximum(-mn, mx).astype(np.float32)
+    scale = np.maximum(amax / np.float32(127.5), np.float32(np.finfo(np.float32).eps)).astype(np.float32)
+    inv = (np.float32(1.0) / scale).astype(np.float32)
+    q = np.clip(np.rint((W * inv[:, None]).astype(np.float32)), -128, 127).astype(np.int8)
+    return q, scale
+
+
+def embedding_bag_sum_int8(q: np.ndarray, scale: np.ndarray, indices: np.ndarray, offsets: np.ndarray) -> np.ndarray:
+    """Sum pooling over dequantised rows ``scale[r] * q[r]`` (fp32, index order); empty bag -> zeros."""
+    deq = (q.astype(np.float32) * scale.astype(np.float32)[:, None]).astype(np.float32)
+    return embedding_bag_sum(deq, indices, offsets)

@@ -181,3 +181,15 @@ def test_criteo_transform_matches_reference_fixture(golden):
         np.testing.assert_array_equal(Y, g[f"{tag}_Y"])
         np.testing.assert_allclose(X, g[f"{tag}_X"], rtol=2e-7, atol=0)
         assert lS_i.min() >= 0 or int(g[f"{tag}_max_ind_range"]) == 0
+
+
+def test_int8_rowwise_quantisation_matches_torch_observer(golden):
+    """oracle.quantize_rowwise_int8 / embedding_bag_sum_int8 vs the fixture written with torch.ao's
+    PerChannelMinMaxObserver + quantize_per_channel (the observers the reference's int8 QConfig names)."""
+    g = golden("int8_tables")
+    q, s = ops.quantize_rowwise_int8(g["W"])
+    np.testing.assert_array_equal(q, g["q"])
+    np.testing.assert_array_equal(s, g["scale"])
+    assert not g["zero_point"].any()
+    got = ops.embedding_bag_sum_int8(q, s, g["idx"], g["off"][:-1])
+    np.testing.assert_allclose(got, g["pooled"], rtol=1e-6, atol=1e-6)
