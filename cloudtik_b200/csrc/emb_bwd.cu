@@ -271,9 +271,10 @@ constexpr int UPD_TMAX = 256;  // tables whose base pointers / row bases are cac
 // reduction per 16 bytes (REDG.ADD.F32x4, executed by the L2 atomic unit) instead of a load +
 // store: no weight row ever travels to the SM, no registers wait for it.  Each row still gets
 // exactly one update per step from exactly one group, so the result stays deterministic.
-template <typename WT, typename GT, int G, int NV, int OPT, bool RED>
-__global__ void __launch_bounds__(UPD_THREADS, (RED && sizeof(GT) == 2) ? 3 : 1) window_update_kernel(const UpdParams p) {
+template <typename WT, typename GT, int G, int NV, int OPT, bool RED, bool TRAIL>
+__global__ void __launch_bounds__(UPD_THREADS, (sizeof(GT) == 2 && !TRAIL && OPT != B200_OPT_ADAGRAD) ? 3 : 2) window_update_kernel(const UpdParams p) {
   static_assert(!RED || (OPT == B200_OPT_SGD && sizeof(WT) == 4), "RED path is fp32 SGD only");
+  static_assert(!TRAIL || sizeof(WT) == 2, "a trail belongs to bf16 tables");
   constexpr int VE = Vec16<WT>::VE;
   constexpr int NG = UPD_THREADS / G;
   constexpr int C = HOT_CH;
@@ -301,7 +302,7 @@ __global__ void __launch_bounds__(UPD_THREADS, (RED && sizeof(GT) == 2) ? 3 : 1)
                         ? reinterpret_cast<char*>(p.trail[i]) - static_cast<char*>(p.weights[i]) : 0;
     }
   }
-  const bool has_trail = sizeof(WT) == 2 && p.trail != nullptr;
+  constexpr bool has_trail = TRAIL;  // compile-time: plain bf16 tables carry no trail registers
   const int64_t w = (int64_t)blockIdx.x * NG + gid;
   const int64_t a = w * C;
   const int cnt = a < p.n ? (int)min((int64_t)C, p.n - a) : 0;
@@ -340,12 +341,33 @@ __global__ void __launch_bounds__(UPD_THREADS, (RED && sizeof(GT) == 2) ? 3 : 1)
   int cur_head = cont ? -1 : 0;
   const int64_t uidx0 = (OPT == OPT_STORE && cnt > 0) ? (int64_t)p.win_run[w] : 0;
   int64_t uidx = uidx0;  // index of the run being summed
+  // Load/store variants: the group that holds the head of a run crossing its right border will finish that row
+  // after the block barrier -- fetch the weight (and trail) row NOW so that the read overlaps the window loop.
+  [[maybe_unused]] uint4 pre_w[NV], pre_t[NV];
+  [[maybe_unused]] bool pre_ok = false;
+  if constexpr (!RED && OPT != OPT_STORE) {
+    const bool own_tail = cnt > 0 && s_key[gid][cnt] == s_key[gid][cnt + 1] &&
+                          !(cont0 && s_key[gid][1] == s_key[gid][cnt]);
+    if (own_tail) {
+      pre_ok = true;
+      const int tt = s_tab[gid][cnt - 1];
+      const int64_t row = (int64_t)s_key[gid][cnt] - (cached ? s_base[tt] : p.row_base[tt]);
+      const char* wq = (cached ? s_wptr[tt] : static_cast<char*>(p.weights[tt])) + ((size_t)row * p.D + lane * VE) * sizeof(WT);
+      const int64_t td = !has_trail ? 0 : (cached ? s_tdelta[tt] : reinterpret_cast<char*>(p.trail[tt]) - static_cast<char*>(p.weights[tt]));
+#pragma unroll
+      for (int k = 0; k < NV; ++k) {
+        const bool in = lane + k * G < p.V;
+        pre_w[k] = in ? ld_v4(wq + (size_t)k * G * 16) : make_uint4(0, 0, 0, 0);
+        pre_t[k] = (in && has_trail) ? ld_v4(wq + td + (size_t)k * G * 16) : make_uint4(0, 0, 0, 0);
+      }
+    }
+  }
 
   for (int c0 = 0; c0 < cnt; c0 += BS) {
     GradVec<GT, VE> g[BS][NV];
     uint4 wv[RED ? 1 : BS][NV];
-    uint4 tv[(RED || sizeof(WT) != 2) ? 1 : BS][NV];  // trail halves of the rows in wv
-    int64_t tdel[(RED || sizeof(WT) != 2) ? 1 : BS];
+    [[maybe_unused]] uint4 tv[TRAIL ? BS : 1][NV];  // trail halves of the rows in wv
+    [[maybe_unused]] int64_t tdel[TRAIL ? BS : 1];
     char* wp[RED ? 1 : BS];
     float* sp[RED ? 1 : BS];
     bool ends[BS], closed[BS];
@@ -386,13 +408,11 @@ __global__ void __launch_bounds__(UPD_THREADS, (RED && sizeof(GT) == 2) ? 3 : 1)
 #pragma unroll
             for (int k = 0; k < NV; ++k)
               if (lane + k * G < p.V) wv[c][k] = ld_v4(wp[c] + (size_t)k * G * 16);
-            if constexpr (sizeof(WT) == 2) {
-              tdel[c] = !has_trail ? 0
-                        : (cached ? s_tdelta[tt] : reinterpret_cast<char*>(p.trail[tt]) - static_cast<char*>(p.weights[tt]));
+            if constexpr (TRAIL) {
+              tdel[c] = cached ? s_tdelta[tt] : reinterpret_cast<char*>(p.trail[tt]) - static_cast<char*>(p.weights[tt]);
 #pragma unroll
               for (int k = 0; k < NV; ++k)
-                tv[c][k] = (has_trail && lane + k * G < p.V) ? ld_v4(wp[c] + tdel[c] + (size_t)k * G * 16)
-                                                             : make_uint4(0, 0, 0, 0);
+                tv[c][k] = (lane + k * G < p.V) ? ld_v4(wp[c] + tdel[c] + (size_t)k * G * 16) : make_uint4(0, 0, 0, 0);
             }
           }
         }
@@ -425,9 +445,9 @@ __global__ void __launch_bounds__(UPD_THREADS, (RED && sizeof(GT) == 2) ? 3 : 1)
               } else {
                 float wf[VE];
                 Vec16<WT>::unpack(wf, wv[c][k]);
-                if constexpr (sizeof(WT) == 2) {
+                if constexpr (TRAIL) {
                   apply_row<OPT, WT>(wp[c] + (size_t)k * G * 16, sp[c] ? sp[c] + k * G * VE : nullptr, acc[k], wf, lr,
-                                     p.eps, has_trail ? wp[c] + tdel[c] + (size_t)k * G * 16 : nullptr, tv[c][k]);
+                                     p.eps, wp[c] + tdel[c] + (size_t)k * G * 16, tv[c][k]);
                 } else {
                   apply_row<OPT, WT>(wp[c] + (size_t)k * G * 16, sp[c] ? sp[c] + k * G * VE : nullptr, acc[k], wf, lr,
                                      p.eps);
@@ -475,7 +495,7 @@ __global__ void __launch_bounds__(UPD_THREADS, (RED && sizeof(GT) == 2) ? 3 : 1)
   const uint32_t key_after_block = s_key[ngv - 1][cnt_last + 1];
   // run entering from the previous window covers this whole window and goes on: some earlier group owns it
   const bool pass_through = cont0 && open_r && s_key[gid][1] == s_key[gid][cnt];
-  auto finish = [&](int slot, uint32_t key, bool from_left, bool open, int pos, int64_t u) {
+  auto finish = [&](int slot, uint32_t key, bool from_left, bool open, int pos, int64_t u, bool use_pre) {
     const float* src = s_part + (size_t)(2 * gid + slot) * p.D + lane * VE;
 #pragma unroll
     for (int k = 0; k < NV; ++k)
@@ -526,9 +546,14 @@ __global__ void __launch_bounds__(UPD_THREADS, (RED && sizeof(GT) == 2) ? 3 : 1)
         } else {
           float wf[VE] = {};
           uint4 tv = make_uint4(0, 0, 0, 0);
-          if (OPT != OPT_STORE) {
-            Vec16<WT>::unpack(wf, ld_v4(wp + (size_t)k * G * 16));
-            if (tp) tv = ld_v4(tp + (size_t)k * G * 16);
+          if constexpr (OPT != OPT_STORE) {
+            if (use_pre) {
+              Vec16<WT>::unpack(wf, pre_w[k]);
+              tv = pre_t[k];
+            } else {
+              Vec16<WT>::unpack(wf, ld_v4(wp + (size_t)k * G * 16));
+              if (tp) tv = ld_v4(tp + (size_t)k * G * 16);
+            }
           }
           apply_row<OPT, WT>(wp + (size_t)k * G * 16, sp ? sp + k * G * VE : nullptr, acc[k], wf, lr, p.eps,
                              tp ? tp + (size_t)k * G * 16 : nullptr, tv);
@@ -536,9 +561,9 @@ __global__ void __launch_bounds__(UPD_THREADS, (RED && sizeof(GT) == 2) ? 3 : 1)
       }
   };
   if (gid == 0 && cont0)  // the run that enters the block from the left (its head is in an earlier block)
-    finish(0, s_key[0][1], true, pass_through, 0, uidx0);
+    finish(0, s_key[0][1], true, pass_through, 0, uidx0, false);
   if (open_r && !pass_through)  // the run whose head is in this window and that crosses its right border
-    finish(tail_slot, s_key[gid][cnt], false, true, cnt - 1, uidx);
+    finish(tail_slot, s_key[gid][cnt], false, true, cnt - 1, uidx, pre_ok);
 }
 
 // ---- 3b. join: runs that cross BLOCK borders of the window kernel (a block = NG windows = NG * HOT_CH
@@ -716,10 +741,20 @@ static int launch_update(const UpdParams& p, int64_t n, bool vec_ok, cudaStream_
     return e == nullptr || e[0] != '0';
   }();
 #define B200_UPD_LAUNCH(G, NV, RED)                                                                               \
+  if constexpr (sizeof(WT) == 2) {                                                                                \
+    if (p.trail != nullptr) {                                                                                     \
+      B200_UPD_LAUNCH_T(G, NV, RED, true)                                                                         \
+    } else {                                                                                                      \
+      B200_UPD_LAUNCH_T(G, NV, RED, false)                                                                        \
+    }                                                                                                             \
+  } else {                                                                                                        \
+    B200_UPD_LAUNCH_T(G, NV, RED, false)                                                                          \
+  }
+#define B200_UPD_LAUNCH_T(G, NV, RED, TRAIL)                                                                               \
   {                                                                                                               \
     constexpr int NG_ = UPD_THREADS / G;                                                                          \
     const size_t part_bytes = (size_t)NG_ * 2 * p.D * sizeof(float);                                              \
-    auto kern = window_update_kernel<WT, GT, G, NV, OPT, RED>;                                                    \
+    auto kern = window_update_kernel<WT, GT, G, NV, OPT, RED, TRAIL>;                                                  \
     if (part_bytes > 32 * 1024) {                                                                                 \
       static const cudaError_t attr_rc =                                                                          \
           cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);                     \
@@ -759,6 +794,7 @@ static int launch_update(const UpdParams& p, int64_t n, bool vec_ok, cudaStream_
   else { B200_UPD_CASE(32, 4); }
 #undef B200_UPD_CASE
 #undef B200_UPD_LAUNCH
+#undef B200_UPD_LAUNCH_T
   B200_CHECK_LAUNCH("emb_update");
   return B200_OK;
 }

@@ -21,17 +21,23 @@ from .merged_embedding import _register_pooled
 _EPS = float(torch.finfo(torch.float32).eps)
 
 
-def quantize_rowwise_int8(w: torch.Tensor):
+def quantize_rowwise_int8(w: torch.Tensor, chunk_rows: int = 2_000_000):
     """(q int8 [n, D], scale fp32 [n]): PerChannelMinMaxObserver(ch_axis=0, qint8, per_channel_symmetric) +
-    quantize_per_channel, in fp32 on the device (bit-exact with ``oracle.ops_numpy.quantize_rowwise_int8``)."""
-    w = w.detach().float()
-    mn = torch.clamp(w.amin(dim=1), max=0.0)
-    mx = torch.clamp(w.amax(dim=1), min=0.0)
-    # tensor / tensor: a scalar divisor would be turned into a multiplication by its reciprocal on CUDA
-    scale = torch.clamp(torch.maximum(-mn, mx) / torch.full_like(mn, 127.5), min=_EPS)
-    inv = torch.ones_like(scale) / scale
-    q = torch.clamp(torch.round(w * inv[:, None]), -128, 127).to(torch.int8)
-    return q.contiguous(), scale.contiguous()
+    quantize_per_channel, in fp32 on the device (bit-exact with ``oracle.ops_numpy.quantize_rowwise_int8``).
+    Done in row chunks so that a 20 GB table needs ~3 GB of temporaries, not three copies of itself."""
+    n = w.shape[0]
+    q = torch.empty(w.shape, dtype=torch.int8, device=w.device)
+    scale = torch.empty(n, dtype=torch.float32, device=w.device)
+    for a in range(0, n, chunk_rows):
+        c = w[a:a + chunk_rows].detach().float()
+        mn = torch.clamp(c.amin(dim=1), max=0.0)
+        mx = torch.clamp(c.amax(dim=1), min=0.0)
+        # tensor / tensor: a scalar divisor would be turned into a multiplication by its reciprocal on CUDA
+        sc = torch.clamp(torch.maximum(-mn, mx) / torch.full_like(mn, 127.5), min=_EPS)
+        inv = torch.ones_like(sc) / sc
+        q[a:a + chunk_rows] = torch.clamp(torch.round(c * inv[:, None]), -128, 127).to(torch.int8)
+        scale[a:a + chunk_rows] = sc
+    return q, scale
 
 
 class QuantizedMergedEmbeddingBag(nn.Module):
