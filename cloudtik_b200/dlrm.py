@@ -142,7 +142,7 @@ class DLRM_Net(nn.Module):
     def distributed_forward(self, dense_x, *emb_args):
         # P/dlrm_s_pytorch.py:342-369: local tables on the GLOBAL batch -> all-to-all -> local batch
         batch_size = dense_x.size()[0]
-        vector_lenght = self.emb_l.weights[0].size()[1]
+        vector_lenght = self.emb_l.dim
         if batch_size < ext_dist.my_size:
             sys.exit("ERROR: batch_size (%d) must be larger than number of ranks (%d)"
                      % (batch_size, ext_dist.my_size))
@@ -162,7 +162,7 @@ class DLRM_Net(nn.Module):
 
 def _p2p_forward(self, dense_x, *emb_args):
     """distributed_forward with the all-to-all fused into the embedding kernels (cloudtik_b200.p2p)."""
-    from .p2p import sharded_emb_interact
+    from .p2p import prelaunch, sharded_emb_interact
     rw_i = rw_o = None
     if len(emb_args) >= 3:
         indices, offsets = emb_args[0], emb_args[1]
@@ -173,6 +173,9 @@ def _p2p_forward(self, dense_x, *emb_args):
         indices, offsets, _ = self.emb_l.linearize_indices_and_offsets(list(lS_i), list(lS_o), [False] * len(lS_i))
     if (self.rowwise is not None) != (rw_i is not None):
         raise RuntimeError("row-wise sharded tables need (indices, offsets, None, rw_indices, rw_offsets)")
+    feat0 = 1 + self.local_ln_emb_slice.start
+    if self.training and torch.is_grad_enabled():
+        prelaunch(self.emb_l, self.peer_exchange, indices, offsets, feat0)  # NVLink exchange || bottom MLP
     with torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.bf16):
         x = self.apply_mlp(self._pad_dense(dense_x), self.bot_l)
         z = sharded_emb_interact(x, self.emb_l, self.peer_exchange, indices, offsets,
@@ -191,7 +194,7 @@ def enable_peer_exchange(dlrm, local_batch: int):
     from .p2p import PeerExchange
     n_feat = 1 + dlrm.n_global_emb
     dt = torch.bfloat16 if dlrm.bf16 else dlrm.emb_l.tables.dtype
-    dlrm.peer_exchange = PeerExchange(local_batch, n_feat, dlrm.emb_l.dim, dt, dlrm.emb_l.weights[0].device)
+    dlrm.peer_exchange = PeerExchange(local_batch, n_feat, dlrm.emb_l.dim, dt, dlrm.emb_l.tables.device)
     return dlrm.peer_exchange
 
 

@@ -34,6 +34,7 @@ class GraphedTrainStep:
             for _ in range(warmup):
                 self._eager()
         torch.cuda.current_stream().wait_stream(s)
+        emb.join()  # no event from outside the capture may be waited on inside it
         torch.cuda.synchronize()
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph):
@@ -49,6 +50,7 @@ class GraphedTrainStep:
         if self.post_backward is not None:
             self.post_backward()
         self.opt.step()
+        self.net.emb_l.join()  # a side-stream update (peer-memory path) joins the step, and the capture, here
         return E.detach()
 
     # ---- host-fed operation: pinned-host batches are staged by a copy stream one step ahead ----

@@ -134,6 +134,11 @@ class MergedEmbeddingBagWithSGD(nn.Module):
         self._ws = None
         self._side_stream = None
         self._prep_event = None
+        # peer-memory (sharded) path: the NVLink-bound kernels run on the side stream next to the bottom MLP
+        # (forward) and next to the bottom-MLP backward / gradient all-reduce / optimizer (update)
+        self.overlap_sharded = True
+        self._pending_sharded = None  # (indices, offsets, event) of a sharded forward launched ahead
+        self._apply_event = None      # last fused update issued on the side stream
         self._rebuild_tables()
         if optimizer == "adagrad":
             self.tables.set_states([torch.zeros_like(w, dtype=torch.float32) for w in self.weights])
@@ -157,14 +162,29 @@ class MergedEmbeddingBagWithSGD(nn.Module):
 
     @property
     def weights(self) -> List[torch.Tensor]:
+        self.join()  # readers on the current stream see the last fused update
+        return self._raw_weights()
+
+    def _raw_weights(self) -> List[torch.Tensor]:
         return [getattr(self, str(k)).weight.data for k in range(self.n_tables)]
+
+    def state_dict(self, *args, **kwargs):
+        self.join()
+        return super().state_dict(*args, **kwargs)
+
+    def join(self):
+        """Order the current stream after the last fused update issued on the side stream (no-op otherwise)."""
+        ev = self._apply_event
+        if ev is not None:
+            torch.cuda.current_stream().wait_event(ev)
+            self._apply_event = None
 
     def linearize_indices_and_offsets(self, indices: List[torch.Tensor], offsets: List[torch.Tensor],
                                       include_last_offsets: List[bool]):
         """Per-table (indices, offsets) -> (indices, offsets, indices_with_row_offsets):
         concatenated indices, one CSR array over all T*B bags with the trailing total, and
         global row ids."""
-        dev = self.weights[0].device
+        dev = self._raw_weights()[0].device
         idx = [i.to(dev, torch.int64) for i in indices]
         offs = []
         for o, inc in zip(offsets, include_last_offsets):
@@ -242,7 +262,7 @@ class MergedEmbeddingBagWithSGD(nn.Module):
         old = getattr(self, "tables", None)
         states = old.states if old is not None else None
         trails = old.trails if old is not None else None
-        self.tables = ops.TableSet(self.weights, states)
+        self.tables = ops.TableSet(self._raw_weights(), states)
         if trails is not None and self.tables.dtype == torch.bfloat16:
             self.tables.set_trails(trails)
 
@@ -255,7 +275,7 @@ class MergedEmbeddingBagWithSGD(nn.Module):
     def _workspace(self, nnz: int) -> torch.Tensor:
         need = ops.emb_bwd_workspace_bytes(nnz, self.dim)
         if self._ws is None or self._ws.numel() < need:
-            self._ws = torch.empty(need, dtype=torch.uint8, device=self.weights[0].device)
+            self._ws = torch.empty(need, dtype=torch.uint8, device=self._raw_weights()[0].device)
         return self._ws
 
     @contextlib.contextmanager
@@ -292,10 +312,46 @@ class MergedEmbeddingBagWithSGD(nn.Module):
             ev.record(self._side_stream)
         self._prep_event = ev
 
+    def _launch_forward_sharded_async(self, indices, offsets, B, exch, feat0):
+        """Peer-memory path: issue the pooled forward (rows written straight into the destination ranks' T) and
+        the index stage of the backward on the side stream NOW -- the caller runs the bottom MLP next on the
+        current stream, the sharded autograd function waits for the recorded event before its barrier."""
+        main = torch.cuda.current_stream()
+        if self._side_stream is None:
+            self._side_stream = torch.cuda.Stream(device=indices.device)
+        side = self._side_stream
+        ws = self._workspace(indices.numel())
+        side.wait_stream(main)  # batch ready, last step's barriers passed; the previous update precedes on `side`
+        with torch.cuda.stream(side):
+            ops.emb_fwd_sharded(self.tables, indices, offsets, B, exch.T_ptrs_dev, exch.lN, exch.F, feat0,
+                                exch.dtype, self.error_flag)
+            ev = torch.cuda.Event()
+            ev.record(side)
+            ops.emb_bwd_prepare(self.tables, indices, offsets, B, ws, self.error_flag)
+            pe = torch.cuda.Event()
+            pe.record(side)
+        self._prep_event = pe
+        self._apply_event = None  # the update before this forward is ordered by the side stream itself
+        self._pending_sharded = (indices, offsets, ev)
+
     def _apply_update_sharded(self, indices, offsets, B, exch, feat0):
         """Backward of the peer-memory path (cloudtik_b200.p2p): gradients are read from every rank's dT."""
         opt = ops.OPT_ADAGRAD if self.optimizer_kind == "adagrad" else ops.OPT_SGD
         ws = self._workspace(indices.numel())
+        if self.overlap_sharded and self._prep_event is not None and self.profile is None:
+            # NVLink-bound gather of the peers' gradient rows: run it on the side stream (already behind the index
+            # stage) while the current stream does the bottom-MLP backward, the all-reduce and the optimizer
+            side = self._side_stream
+            side.wait_stream(torch.cuda.current_stream())  # dT complete on every rank (barrier B2 is before us)
+            self._prep_event = None
+            with torch.cuda.stream(side):
+                ops.emb_bwd_apply_sharded(self.tables, indices.numel(), B, exch.dT_ptrs_dev, exch.lN, exch.F, feat0,
+                                          exch.dtype, self.sgd_args.lr, ws, optimizer=opt, eps=self.eps,
+                                          lr_tensor=self.lr_tensor)
+                ev = torch.cuda.Event()
+                ev.record(side)
+            self._apply_event = ev
+            return
         if self._prep_event is not None:
             torch.cuda.current_stream().wait_event(self._prep_event)
             self._prep_event = None

@@ -57,9 +57,14 @@ class _ShardedEmbInteractFn(torch.autograd.Function):
                 rw_offsets=None):
         B_glob = exch.lN * exch.world
         if emb is not None:
-            ops.emb_fwd_sharded(emb.tables, indices, offsets, B_glob, exch.T_ptrs_dev, exch.lN, exch.F, feat0,
-                                exch.dtype, emb.error_flag)
-            emb._launch_prepare(indices, offsets, B_glob)  # sort / dedup on the side stream
+            pend, emb._pending_sharded = emb._pending_sharded, None
+            if pend is not None and pend[0] is indices and pend[1] is offsets:
+                torch.cuda.current_stream().wait_event(pend[2])  # launched ahead of the bottom MLP (prelaunch())
+            else:
+                emb.join()
+                ops.emb_fwd_sharded(emb.tables, indices, offsets, B_glob, exch.T_ptrs_dev, exch.lN, exch.F, feat0,
+                                    exch.dtype, emb.error_flag)
+                emb._launch_prepare(indices, offsets, B_glob)  # sort / dedup on the side stream
         ctx.rw_ctx = None
         if rowwise is not None:  # row-wise sharded hot tables occupy the LAST feature slots
             rw_out, ctx.rw_ctx = rowwise.pool(rw_indices, rw_offsets, exch.lN)
@@ -85,6 +90,13 @@ class _ShardedEmbInteractFn(torch.autograd.Function):
             ctx.rowwise.update(exch.dT[:, exch.F - ctx.rowwise.k:], ctx.rw_ctx)
         dx = exch.dT[:, 0].clone()  # dT is overwritten by the next step; the bottom MLP backward runs now
         return (dx.to(ctx.x_dtype),) + (None,) * 10
+
+
+def prelaunch(emb, exch: PeerExchange, indices, offsets, feat0: int):
+    """Start this rank's pooled forward + exchange on the embedding's side stream before the caller runs the
+    bottom MLP; ``sharded_emb_interact`` with the same (indices, offsets) tensors picks it up."""
+    if emb is not None and emb.overlap_sharded and emb.overlap_prepare and emb.profile is None:
+        emb._launch_forward_sharded_async(indices, offsets, exch.lN * exch.world, exch, feat0)
 
 
 def sharded_emb_interact(x, emb, exch: PeerExchange, indices, offsets, feat0: int, pad_to: int = 1, rowwise=None,

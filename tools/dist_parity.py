@@ -131,7 +131,7 @@ def main():
     top = net.top_l.module if a.ddp else net.top_l
     for (n1, p1), p2 in zip(top.named_parameters(), port.top_l.parameters()):
         np.testing.assert_allclose(p1.detach().cpu().numpy(), p2.detach().numpy(), rtol=10 * tol,
-                                   atol=2e-3 if a.bf16 else 1e-6, err_msg=n1)
+                                   atol=2e-3 if a.bf16 else 5e-6, err_msg=n1)  # abs: 1e-5 of the ~0.1 weight scale
     ext_dist.barrier()
     if rank == 0:
         print(f"dist parity ok: world={world} tables={len(rows)} rowwise={a.rowwise} adagrad={a.adagrad} bf16={a.bf16} p2p={a.p2p} steps={a.steps} "
