@@ -53,6 +53,8 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="run the step eagerly instead of as one CUDA graph")
     ap.add_argument("--no-p2p", action="store_true", help="multi-GPU: NCCL all-to-all instead of the fused peer-memory exchange")
+    ap.add_argument("--no-microbench", action="store_true",
+                    help="skip the BASELINE configs[1] EmbeddingBag micro-benchmark appended to the N=1 line")
     ap.add_argument("--cpu-rows-cap", type=int, default=200000)
     ap.add_argument("--cpu-steps", type=int, default=3)
     return ap.parse_args()
@@ -196,6 +198,34 @@ def make_batches(a, rows_local, B_loc, B_glob, dev, rank):
         sets.append({"host": host, "dev": devt, "uniq": uniq, "host_rec": host_rec})
     torch.cuda.synchronize()
     return sets
+
+
+def embeddingbag_microbench(net, gs):
+    """BASELINE.json configs[1] (the configuration the metric's "EmbeddingBag HBM GB/s vs ~8 TB/s" half is
+    quoted on): 26 tables x 1 M rows, dim 128, pooling 1 / 32 / 128, fp32 and bf16 tables, forward and the
+    fused backward+update.  CUDA events around single launches, rotating index sets (rows L2-cold),
+    algorithmic bytes of SURVEY.md section 8d.  Runs after the timed regions; the step's model is released first."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import gc
+
+    import microbench as mb
+    del gs
+    net.emb_l = None  # 96 GB of tables are not needed any more
+    gc.collect()
+    torch.cuda.empty_cache()
+    out = []
+    for dtype in ("fp32", "bf16"):
+        for r in mb.run_cases([1_000_000] * 26, D, dtype, "", ((262144, 1), (8192, 32), (2048, 128)), iters=10,
+                              n_sets=3, interact=False):
+            if r["kernel"] in ("emb_fwd", "emb_bwd_apply", "emb_bwd_sgd"):
+                out.append({k: r[k] for k in ("kernel", "dtype", "B", "P", "ms", "GBps", "frac_8TBps")}
+                           | {"frac_measured": r.get("frac_measured")})
+        gc.collect()
+        torch.cuda.empty_cache()
+    return {"config": "26 tables x 1M rows, dim 128, pooling 1/32/128 (BASELINE configs[1])",
+            "kernels": "emb_fwd = pooled forward; emb_bwd_apply = segment-reduce + row update; emb_bwd_sgd = "
+                       "index sort/dedup + emb_bwd_apply back to back on one stream (in the training step the index stage "
+                       "runs on a side stream under the dense forward/backward)", "results": out}
 
 
 def run_b200_arm(a):
@@ -387,6 +417,8 @@ def run_b200_arm(a):
                 "input": "raw int32 Criteo records (CriteoBinDataset format) decoded on the device, one extra launch"},
             "gpu_launches": launches * a.steps, "gpu_launches_per_step": launches,
             "roofline": roof, "clocks": clk, "final_loss": loss_val}
+    if world == 1 and not a.no_microbench:
+        line["embeddingbag_microbench"] = embeddingbag_microbench(net, gs if use_graph else None)
     if world == 1 and not a.no_cpu_baseline:
         r = cpu_reference_run(a.batch, a.cpu_rows_cap, a.cpu_steps, 1, bf16)
         line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}

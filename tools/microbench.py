@@ -42,32 +42,20 @@ def time_ms(fn, iters, warmup=3):
     return ts[len(ts) // 2], ts[0]
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--rows", type=int, default=1_000_000)
-    ap.add_argument("--tables", type=int, default=26)
-    ap.add_argument("--dim", type=int, default=128)
-    ap.add_argument("--dtype", default="fp32")
-    ap.add_argument("--cases", default="262144:1,8192:32,2048:128,32768:1")
-    ap.add_argument("--iters", type=int, default=20)
-    ap.add_argument("--sets", type=int, default=4)
-    ap.add_argument("--c3", action="store_true", help="use the config-3 (Criteo-Terabyte) table sizes; fp32 tables")
-    ap.add_argument("--c3-cap", type=int, default=0, help="cap config-3 table rows (0 = full, 96 GB)")
-    ap.add_argument("--act", default="", help="activation / gradient dtype (default: same as --dtype)")
-    ap.add_argument("--no-interact", action="store_true")
-    a = ap.parse_args()
-    dt = torch.float32 if a.dtype == "fp32" else torch.bfloat16
-    es = 4 if a.dtype == "fp32" else 2
-    T, D, n = a.tables, a.dim, a.rows
-    F = T + 1
-    dev = "cuda"
-    peak, pk = peak_hbm()
-    C3 = [39884406, 39043, 17289, 7420, 20263, 3, 7120, 1543, 63, 38532951, 2953546, 403346, 10, 2208, 11938, 155, 4,
-          976, 14, 39979771, 25641295, 39664984, 585935, 12972, 108, 36]
-    rows = [min(r, a.c3_cap) if a.c3_cap else r for r in C3] if a.c3 else [n] * T
+C3 = [39884406, 39043, 17289, 7420, 20263, 3, 7120, 1543, 63, 38532951, 2953546, 403346, 10, 2208, 11938, 155, 4,
+      976, 14, 39979771, 25641295, 39664984, 585935, 12972, 108, 36]
+
+
+def run_cases(rows, D, dtype="fp32", act="", cases=((262144, 1), (8192, 32), (2048, 128), (32768, 1)), iters=20,
+              n_sets=4, interact=True, dev="cuda"):
+    """Generator of result dicts, one per (kernel, case).  ``rows``: rows per table; ``dtype``: table dtype;
+    ``act``: activation / gradient dtype ("" = same as the tables)."""
+    dt = torch.float32 if dtype == "fp32" else torch.bfloat16
+    es = 4 if dtype == "fp32" else 2
     T = len(rows)
     F = T + 1
-    adt = dt if not a.act else (torch.float32 if a.act == "fp32" else torch.bfloat16)
+    peak, pk = peak_hbm()
+    adt = dt if not act else (torch.float32 if act == "fp32" else torch.bfloat16)
     ea = 4 if adt == torch.float32 else 2
     tw = []
     for r in rows:
@@ -78,11 +66,10 @@ def main():
     rows_t = torch.tensor(rows, device=dev, dtype=torch.float64)
     g = torch.Generator(device=dev)
     g.manual_seed(1234)
-    for case in a.cases.split(","):
-        B, P = (int(v) for v in case.split(":"))
+    for B, P in cases:
         nnz_t = B * P
         sets = []
-        for _ in range(a.sets):
+        for _ in range(n_sets):
             u01 = torch.rand(T, nnz_t, device=dev, generator=g, dtype=torch.float64)
             idx = torch.floor(u01 * rows_t[:, None]).to(torch.int64).reshape(-1)
             U = sum(int(torch.unique(idx[t * nnz_t:(t + 1) * nnz_t]).numel()) for t in range(T))
@@ -110,15 +97,14 @@ def main():
 
         for name, fn, nbytes in (("emb_fwd", f_fwd, fwd_bytes), ("emb_bwd_sgd", f_bwd, bwd_bytes),
                                  ("emb_bwd_prepare", f_prep, common), ("emb_bwd_apply", f_apply, bwd_bytes)):
-            med, best = time_ms(fn, a.iters)
+            med, best = time_ms(fn, iters)
             gbs = nbytes / med / 1e6
-            print(json.dumps({"kernel": name, "B": B, "P": P, "T": T, "D": D, "dtype": a.dtype, "ms": round(med, 4),
-                              "ms_best": round(best, 4), "alg_GB": round(nbytes / 1e9, 4), "GBps": round(gbs, 1),
-                              "frac_" + pk: round(gbs / peak, 3), "frac_8TBps": round(gbs / 8000, 3),
-                              "unique_rows": int(Uavg)}), flush=True)
+            yield {"kernel": name, "B": B, "P": P, "T": T, "D": D, "dtype": dtype, "ms": round(med, 4),
+                   "ms_best": round(best, 4), "alg_GB": round(nbytes / 1e9, 4), "GBps": round(gbs, 1),
+                   "frac_" + pk: round(gbs / peak, 3), "frac_8TBps": round(gbs / 8000, 3), "unique_rows": int(Uavg)}
         del buf, grad, ws, sets
     # interaction at the training shape
-    for B in (() if a.no_interact else (32768,)):
+    for B in ((32768,) if interact else ()):
         Tt = torch.randn(B, F, D, device=dev).to(dt)
         R = torch.empty(B, D + F * (F - 1) // 2, dtype=dt, device=dev)
         dR = torch.randn_like(R)
@@ -127,11 +113,30 @@ def main():
         bb = B * (2 * F * D + D + F * (F - 1) // 2) * es
         for name, fn, nbytes in (("interact_fwd", lambda i: ops.interact_fwd(Tt, R), fb),
                                  ("interact_bwd", lambda i: ops.interact_bwd(Tt, dR, dT), bb)):
-            med, best = time_ms(fn, a.iters)
+            med, best = time_ms(fn, iters)
             gbs = nbytes / med / 1e6
-            print(json.dumps({"kernel": name, "B": B, "F": F, "D": D, "dtype": a.dtype, "ms": round(med, 4),
-                              "alg_GB": round(nbytes / 1e9, 4), "GBps": round(gbs, 1),
-                              "frac_" + pk: round(gbs / peak, 3)}), flush=True)
+            yield {"kernel": name, "B": B, "F": F, "D": D, "dtype": dtype, "ms": round(med, 4),
+                   "alg_GB": round(nbytes / 1e9, 4), "GBps": round(gbs, 1), "frac_" + pk: round(gbs / peak, 3)}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--rows", type=int, default=1_000_000)
+    ap.add_argument("--tables", type=int, default=26)
+    ap.add_argument("--dim", type=int, default=128)
+    ap.add_argument("--dtype", default="fp32")
+    ap.add_argument("--cases", default="262144:1,8192:32,2048:128,32768:1")
+    ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--sets", type=int, default=4)
+    ap.add_argument("--c3", action="store_true", help="use the config-3 (Criteo-Terabyte) table sizes; fp32 tables")
+    ap.add_argument("--c3-cap", type=int, default=0, help="cap config-3 table rows (0 = full, 96 GB)")
+    ap.add_argument("--act", default="", help="activation / gradient dtype (default: same as --dtype)")
+    ap.add_argument("--no-interact", action="store_true")
+    a = ap.parse_args()
+    rows = [min(r, a.c3_cap) if a.c3_cap else r for r in C3] if a.c3 else [a.rows] * a.tables
+    cases = [tuple(int(v) for v in c.split(":")) for c in a.cases.split(",")]
+    for r in run_cases(rows, a.dim, a.dtype, a.act, cases, a.iters, a.sets, not a.no_interact):
+        print(json.dumps(r), flush=True)
 
 
 if __name__ == "__main__":
