@@ -6,9 +6,11 @@
 //   1. build_keys : key[j] = global row id (table-local index + row base), val[j] = global
 //                   bag id t*B+b   (coalesced; bag of j found from the CSR offsets)
 //   2. sort_pairs / dedup_runs (sort_dedup.cu): stable radix sort, unique rows, run starts
-//   3. update     : one sub-warp group per unique row: sum grad rows of the run (fp32, in
-//                   bag order), then ONE read-modify-write of the weight row (and of the
-//                   Adagrad state row).  The [nnz, D] COO gradient is never materialised.
+//   3. update     : the sorted positions are cut into windows of HOT_CH; one sub-warp group per
+//                   window sums the gradient rows run by run (fp32, in bag order) and gives every
+//                   row ONE read-modify-write (weight row, Adagrad state row, bf16 trail); runs that
+//                   cross windows are joined in shared memory, runs that cross CTAs by a small
+//                   second kernel.  The [nnz, D] COO gradient is never materialised.
 #include <stdlib.h>
 
 #include <algorithm>
@@ -21,10 +23,10 @@ namespace b200 {
 constexpr int KEYS_THREADS = 256;
 constexpr int UPD_THREADS = 256;
 
-// Runs longer than HOT_CH positions ("hot" rows: tiny tables, Zipf heads) are not summed by one
-// group serially: the sorted array is cut into windows of HOT_CH positions, every window
-// pre-reduces the (at most two) hot runs that cross it into fp32 partial rows, and the update
-// kernel adds the partials of a hot row in window order.  Deterministic, no atomics.
+// Runs longer than HOT_CH positions ("hot" rows: tiny tables, Zipf heads) are never summed by one
+// group serially: every window pre-reduces the (at most two) runs that cross its borders into fp32
+// pieces and the pieces of a row are added in window order.  Deterministic, no data-path atomics
+// (the fp32 SGD variant issues ONE vector reduction per 16 bytes of a row, from one group).
 constexpr int OPT_STORE = 2;  // internal "optimizer": write the per-row gradient sums to values[run index]
 constexpr int MIN_NG = UPD_THREADS / 32;  // fewest windows per block (one warp per window)
 
