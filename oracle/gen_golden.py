@@ -10,6 +10,7 @@ What is imported from the reference (read-only, unmodified):
   * ``P/extend_distributed.py`` -> ``get_my_slice`` / ``get_split_lengths``
   * ``T/dlrm_data_pytorch.py`` -> ``generate_uniform_input_batch`` (ragged multi-hot bags)
   * ``T/data_loader_terabyte.py`` -> ``_transform_features`` (binary Criteo records -> model inputs)
+  * ``T/tricks/{qr,md}_embedding_bag.py`` -> ``QREmbeddingBag``, ``PrEmbeddingBag``, ``md_solver``
 with ``P/`` = applications/ai/quickstart/models/recommendation/pytorch/dlrm/product and
 ``T/`` = .../dlrm/training/bfloat16.  Absent third-party modules (mlperf_logging) are
 stubbed in ``sys.modules``; nothing in the reference tree is edited.
@@ -301,6 +302,64 @@ def gen_int8_tables():
                         zero_point=zp.numpy(), q=q.int_repr().numpy(), idx=idx, off=off, pooled=pooled.numpy())
 
 
+def gen_tricks():
+    """T/tricks (QREmbeddingBag, PrEmbeddingBag, md_solver) run on the CPU: one forward + backward each, and the
+    dimension solver's answers.  Includes ids above 2**24, where the reference's float32 quotient is inexact."""
+    sys.dont_write_bytecode = True
+    sys.path.insert(0, T_DIR)
+    try:
+        qr = importlib.import_module("tricks.qr_embedding_bag")
+        md = importlib.import_module("tricks.md_embedding_bag")
+    finally:
+        sys.path.remove(T_DIR)
+    rs = np.random.RandomState(31)
+    out = {}
+    B, D, C = 40, 16, 7
+    lens = rs.randint(0, 5, size=B)
+    off = np.concatenate([[0], np.cumsum(lens)[:-1]]).astype(np.int64)
+    for op in ("mult", "add", "concat"):
+        ncat = 40_000_003 if op == "mult" else 1000
+        nq = int(np.ceil(ncat / C))
+        idx = rs.randint(0, ncat, size=int(lens.sum())).astype(np.int64)
+        if op == "mult":
+            idx[:4] = [33554433, 16777217, 40_000_002, 25_165_829]  # > 2**24: float32 quotient territory
+        # only the rows that are touched get random values (a 5.7 M x 16 table of noise would bloat the fixture)
+        wq = np.full((nq, D), 0.25, dtype=np.float32)
+        q_rows = np.unique(np.concatenate([(torch.tensor(idx) / C).long().numpy(), idx // C]))
+        wq[q_rows] = rs.randn(len(q_rows), D)
+        wr = rs.randn(C, D).astype(np.float32)
+        m = qr.QREmbeddingBag(ncat, D, C, operation=op, mode="sum", sparse=True,
+                              _weight=[torch.tensor(wq), torch.tensor(wr)])
+        y = m(torch.tensor(idx), torch.tensor(off))
+        gy = rs.randn(*y.shape).astype(np.float32)
+        y.backward(torch.tensor(gy))
+        gq, gr = m.weight_q.grad.coalesce(), m.weight_r.grad.coalesce()
+        out.update({f"qr_{op}_ncat": np.int64(ncat), f"qr_{op}_idx": idx, f"qr_{op}_off": off,
+                    f"qr_{op}_q_rows": q_rows, f"qr_{op}_wq_rows": wq[q_rows], f"qr_{op}_wr": wr,
+                    f"qr_{op}_y": y.detach().numpy(), f"qr_{op}_gy": gy,
+                    f"qr_{op}_gq_idx": gq.indices().numpy()[0], f"qr_{op}_gq_val": gq.values().numpy(),
+                    f"qr_{op}_gr_idx": gr.indices().numpy()[0], f"qr_{op}_gr_val": gr.values().numpy()})
+    # PrEmbeddingBag
+    torch.manual_seed(5)
+    pm = md.PrEmbeddingBag(500, 8, 32)
+    idx = rs.randint(0, 500, size=int(lens.sum())).astype(np.int64)
+    y = pm(torch.tensor(idx), torch.tensor(off))
+    gy = rs.randn(*y.shape).astype(np.float32)
+    y.backward(torch.tensor(gy))
+    ge = pm.embs.weight.grad.coalesce()
+    out.update({"pr_w": pm.embs.weight.detach().numpy(), "pr_proj": pm.proj.weight.detach().numpy(), "pr_idx": idx,
+                "pr_off": off, "pr_y": y.detach().numpy(), "pr_gy": gy, "pr_ge_idx": ge.indices().numpy()[0],
+                "pr_ge_val": ge.values().numpy(), "pr_gproj": pm.proj.weight.grad.numpy()})
+    # dimension solver
+    n = torch.tensor([39884406, 39043, 17289, 7420, 20263, 3, 7120, 1543, 63, 38532951, 2953546, 403346, 10])
+    for a_, alpha in enumerate((0.0, 0.25, 0.5)):
+        out[f"md_d0_{a_}"] = md.md_solver(n.clone(), alpha, d0=128, round_dim=True).numpy()
+        out[f"md_raw_{a_}"] = md.md_solver(n.clone(), alpha, d0=128, round_dim=False).numpy()
+    out["md_n"] = n.numpy()
+    out["md_budget"] = md.md_solver(n.clone(), 0.3, B=1.0e8, round_dim=False).numpy()
+    np.savez_compressed(os.path.join(OUT, "tricks.npz"), **out)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     G = load_T_generator()
@@ -312,6 +371,7 @@ def main():
     gen_kaggle_c1(M, G)
     gen_criteo_transform(load_T_terabyte())
     gen_int8_tables()
+    gen_tricks()
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

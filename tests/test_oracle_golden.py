@@ -193,3 +193,14 @@ def test_int8_rowwise_quantisation_matches_torch_observer(golden):
     assert not g["zero_point"].any()
     got = ops.embedding_bag_sum_int8(q, s, g["idx"], g["off"][:-1])
     np.testing.assert_allclose(got, g["pooled"], rtol=1e-6, atol=1e-6)
+
+
+def test_md_solver_mirror_matches_reference(golden):
+    """cloudtik_b200.tricks.md_solver (pure index arithmetic, CPU) vs T/tricks/md_embedding_bag.md_solver."""
+    from cloudtik_b200.tricks import md_solver
+    g = golden("tricks")
+    n = torch.tensor(g["md_n"])
+    for k, alpha in enumerate((0.0, 0.25, 0.5)):
+        np.testing.assert_array_equal(md_solver(n.clone(), alpha, d0=128, round_dim=True).numpy(), g[f"md_d0_{k}"])
+        np.testing.assert_array_equal(md_solver(n.clone(), alpha, d0=128, round_dim=False).numpy(), g[f"md_raw_{k}"])
+    np.testing.assert_array_equal(md_solver(n.clone(), 0.3, B=1.0e8, round_dim=False).numpy(), g["md_budget"])
