@@ -409,3 +409,57 @@ def test_relu_bwd_bias_matches_torch(B, N):
     # deterministic: same bits on a second call
     dz2, db2 = ops.relu_bwd_bias(dy, y)
     assert torch.equal(db, db2)
+
+
+@pytest.mark.parametrize("D,variant", [(128, "sgd_fp32"), (128, "sgd_bf16grad"), (128, "adagrad"), (128, "bf16_trail"),
+                                       (16, "sgd_fp32"), (64, "adagrad"), (256, "sgd_fp32"), (128, "coalesce")])
+def test_emb_bwd_block_and_window_borders(D, variant):
+    """Crafted run lengths around the window (32 positions) and CTA (8 .. 64 windows) borders of the update kernel:
+    runs that end exactly on a border, start on one, span several CTAs (in-block join, per-CTA partial rows, the
+    cross-CTA join) for every update flavour.  Integer gradients: all sums are exact, so SGD must be bit-exact."""
+    ops = _ops()
+    lens = [31, 1, 32, 33, 255, 1, 256, 257, 3, 511, 513, 1, 1, 1024, 7, 2047, 2, 2049, 700, 5000, 9, 64, 64, 64, 1, 8191]
+    n_rows = len(lens) + 2
+    idx = np.concatenate([np.full(n, r) for r, n in enumerate(lens)]).astype(np.int64)
+    rs = np.random.RandomState(D + len(variant))
+    rs.shuffle(idx)
+    B = len(idx)
+    off = np.arange(B + 1, dtype=np.int64)
+    gdt = torch.bfloat16 if variant in ("sgd_bf16grad", "bf16_trail") else torch.float32
+    g = torch.tensor(rs.randint(-3, 4, size=(B, D)).astype(np.float32)).to(gdt).cuda()
+    G = np.zeros((n_rows, D), np.float64)
+    np.add.at(G, idx, g.float().cpu().numpy().astype(np.float64))
+    d_idx, d_off = torch.tensor(idx).cuda(), torch.tensor(off).cuda()
+    ws = torch.empty(ops.emb_bwd_workspace_bytes(B, D), dtype=torch.uint8, device="cuda")
+    W0 = rs.randint(-5, 6, size=(n_rows, D)).astype(np.float32)
+    if variant == "coalesce":
+        ts = ops.TableSet([torch.tensor(W0).cuda()])
+        rows_u, vals = ops.emb_bwd_coalesce(ts, d_idx, d_off, B, g, B * D, D, ws)
+        np.testing.assert_array_equal(rows_u.cpu().numpy(), np.arange(len(lens)))
+        np.testing.assert_array_equal(vals.cpu().numpy(), G[:len(lens)].astype(np.float32))
+        return
+    if variant == "bf16_trail":
+        w = torch.tensor(W0).cuda()
+        bits = w.view(torch.int32)
+        trail = (bits & 0xFFFF).to(torch.int16)
+        ts = ops.TableSet([(bits >> 16).to(torch.int16).view(torch.bfloat16).contiguous()])
+        ts.set_trails([trail])
+    else:
+        ts = ops.TableSet([torch.tensor(W0).cuda()])
+    if variant == "adagrad":
+        ts.set_states([torch.full((n_rows, D), 0.5, device="cuda")])
+    ops.emb_bwd_update(ts, d_idx, d_off, B, g, B * D, D, lr=1.0, ws=ws,
+                       optimizer=ops.OPT_ADAGRAD if variant == "adagrad" else ops.OPT_SGD)
+    torch.cuda.synchronize()
+    if variant == "bf16_trail":
+        hi = ts.weights[0].view(torch.int16).to(torch.int32) << 16
+        got = (hi | (ts.trails[0].to(torch.int32) & 0xFFFF)).view(torch.float32).cpu().numpy()
+    else:
+        got = ts.weights[0].cpu().numpy()
+    if variant == "adagrad":
+        st = 0.5 + G * G
+        want = W0 - G / (np.sqrt(st) + 1e-10)
+        np.testing.assert_allclose(got, want, rtol=2e-6, atol=1e-6)
+        np.testing.assert_allclose(ts.states[0].cpu().numpy(), st, rtol=1e-6)
+    else:
+        np.testing.assert_array_equal(got, (W0 - G).astype(np.float32))
