@@ -463,3 +463,41 @@ def test_emb_bwd_block_and_window_borders(D, variant):
         np.testing.assert_allclose(ts.states[0].cpu().numpy(), st, rtol=1e-6)
     else:
         np.testing.assert_array_equal(got, (W0 - G).astype(np.float32))
+
+
+@pytest.mark.parametrize("W,lN,dtype", [(1, 96, torch.float32), (2, 64, torch.float32), (4, 48, torch.bfloat16),
+                                        (8, 32, torch.float32), (3, 40, torch.float32)])
+def test_sharded_entry_points_on_one_gpu(W, lN, dtype):
+    """b200_emb_fwd_sharded / b200_emb_bwd_apply_sharded with the W destination "ranks" emulated by W buffers on
+    one GPU: the rows must land where a pooled forward followed by the reference's all-to-all would put them, and
+    the update fed from the W gradient buffers must equal the plain update fed from one contiguous gradient."""
+    ops = _ops()
+    rs = np.random.RandomState(W * 100 + lN)
+    rows, D, F, feat0 = [700, 5, 3000], 128, 9, 4   # this "rank" owns features 4, 5, 6 of 9
+    T, B = len(rows), W * lN
+    Wr, tw = _tables(rs, rows, D, torch.float32)
+    idx_l, off_l = _make_bags(rs, rows, B, 3, True)
+    indices, offsets, _ = ref.linearize_indices_and_offsets(idx_l, off_l, rows)
+    d_idx, d_off = torch.tensor(indices).cuda(), torch.tensor(offsets).cuda()
+    ts = ops.TableSet(tw)
+    # forward: plain layout [B, T, D] vs the W destination buffers [lN, F, D]
+    plain = torch.empty(B, T, D, dtype=dtype, device="cuda")
+    ops.emb_fwd(ts, d_idx, d_off, B, plain, D, T * D)
+    bufs = [torch.full((lN, F, D), -7.0, dtype=dtype, device="cuda") for _ in range(W)]
+    ptrs = torch.tensor([b.data_ptr() for b in bufs], dtype=torch.int64, device="cuda")
+    ops.emb_fwd_sharded(ts, d_idx, d_off, B, ptrs.data_ptr(), lN, F, feat0, dtype)
+    for r in range(W):
+        assert torch.equal(bufs[r][:, feat0:feat0 + T], plain[r * lN:(r + 1) * lN])
+        assert bool((bufs[r][:, :feat0] == -7).all()) and bool((bufs[r][:, feat0 + T:] == -7).all())
+    # backward: gradients scattered over W buffers vs one contiguous gradient
+    g = torch.tensor(rs.randint(-3, 4, size=(B, F, D)).astype(np.float32)).to(dtype).cuda()
+    gbufs = [g[r * lN:(r + 1) * lN].contiguous() for r in range(W)]
+    gptrs = torch.tensor([b.data_ptr() for b in gbufs], dtype=torch.int64, device="cuda")
+    tw2 = [w.clone() for w in tw]
+    ts2 = ops.TableSet(tw2)
+    ws = torch.empty(ops.emb_bwd_workspace_bytes(len(indices), D), dtype=torch.uint8, device="cuda")
+    ops.emb_bwd_update(ts, d_idx, d_off, B, g[:, feat0:], D, F * D, lr=0.5, ws=ws)
+    ops.emb_bwd_prepare(ts2, d_idx, d_off, B, ws)
+    ops.emb_bwd_apply_sharded(ts2, len(indices), B, gptrs.data_ptr(), lN, F, feat0, dtype, 0.5, ws)
+    for a, b in zip(tw, tw2):
+        assert torch.equal(a, b)
