@@ -298,6 +298,8 @@ def run_b200_arm(a):
         last = None
         for i in range(steps):
             last = fn(i)
+        if hasattr(fn, "flush"):
+            fn.flush()  # losses still in flight are read on the host before the clock stops
         e1.record()
         barrier()
         ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
@@ -325,12 +327,22 @@ def run_b200_arm(a):
 
         pending = {}
 
+        readers = []
+
         def e2e_fn(i):
             # every step: H2D of its pinned-host batch (issued one step ahead on a copy stream so that it
-            # overlaps the previous step's compute), graph replay, D2H read of the loss
+            # overlaps the previous step's compute), graph replay, D2H copy of the loss; the host READS each
+            # loss one step later (inside the timed region), so the GPU never waits for the host
             k = pending.pop(i) if i in pending else gs.prefetch(sets[i % len(sets)]["host"])
             pending[i + 1] = gs.prefetch(sets[(i + 1) % len(sets)]["host"])
-            return float(gs.step_prefetched(k).cpu())
+            gs.step_prefetched(k)
+            readers.append(gs.loss_to_host_async())
+            return readers.pop(0)() if len(readers) > 1 else None
+
+        def e2e_flush():
+            while readers:
+                readers.pop(0)()
+        e2e_fn.flush = e2e_flush
 
         for i in range(3):
             step_fn(i)
@@ -342,6 +354,7 @@ def run_b200_arm(a):
     for i in range(2):
         e2e_fn(i)
     if use_graph:
+        e2e_flush()
         pending.clear()  # the timed region stages its own batches (K+1 H2D copies for K steps)
     ms_e2e, _ = timed(e2e_fn, a.steps)
 
@@ -353,10 +366,14 @@ def run_b200_arm(a):
         def rec_fn(i):
             k = pend.pop(i) if i in pend else gs.prefetch_records(sets[i % len(sets)]["host_rec"])
             pend[i + 1] = gs.prefetch_records(sets[(i + 1) % len(sets)]["host_rec"])
-            return float(gs.step_records(k).cpu())
+            gs.step_records(k)
+            readers.append(gs.loss_to_host_async())
+            return readers.pop(0)() if len(readers) > 1 else None
+        rec_fn.flush = e2e_flush
 
         for i in range(2):
             rec_fn(i)
+        e2e_flush()
         pend.clear()
         ms_rec, _ = timed(rec_fn, a.steps)
 

@@ -124,6 +124,24 @@ class GraphedTrainStep:
         self.graph.replay()
         return self.loss
 
+    def loss_to_host_async(self):
+        """Queue a device-to-host copy of the step's loss into a pinned slot and return a zero-argument reader.
+        Calling the reader one step later costs nothing (the copy is long done) and keeps the GPU busy back to
+        back -- the reference's per-step ``E.detach().cpu()`` (``P/dlrm_s_pytorch.py:1048``) stalls it every step."""
+        if not hasattr(self, "_loss_host"):
+            self._loss_host = [torch.empty((), dtype=self.loss.dtype).pin_memory() for _ in range(4)]
+            self._loss_slot = 0
+        k = self._loss_slot
+        self._loss_slot = (k + 1) % len(self._loss_host)
+        self._loss_host[k].copy_(self.loss, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+
+        def read():
+            ev.synchronize()
+            return float(self._loss_host[k])
+        return read
+
     def step(self, X, Y, indices, offsets):
         """Copy one batch into the static buffers and replay; returns the (device) loss tensor."""
         for d, s in zip(self.static, (X, Y, indices, offsets)):
