@@ -255,6 +255,9 @@ def run_b200_arm(a):
         enable_peer_exchange(net, B_loc)
     dense_params = [p for p in net.parameters() if p.requires_grad]
     opt = torch.optim.SGD(dense_params, lr=LR)
+    if bf16:  # bf16 copies of the MLP parameters refreshed by one multi-tensor copy after opt.step()
+        from cloudtik_b200.mlp import enable_bf16_shadows
+        enable_bf16_shadows([net.bot_l, net.top_l], opt)
     # MLPs are data-parallel: one flat all-reduce of their 2.4 M gradients per step (the fused bf16 MLP
     # path bypasses DDP.forward, so the averaging the reference gets from DDP is done explicitly)
     sync_dense = ext_dist.DenseGradAllreduce(dense_params) if world > 1 else (lambda: None)

@@ -23,6 +23,61 @@ from .interaction import PaddedLinear
 
 _ONES = {}
 
+# ---- bf16 shadows of the fp32 MLP parameters ------------------------------------------------------
+# Autocast-style training casts every weight and bias to bf16 in every forward: 16 tiny kernels per step for
+# the 8 DLRM layers (plus a zero-pad for the two K-padded ones).  enable_bf16_shadows() keeps a bf16 copy of
+# each parameter (already padded), refreshed by ONE multi-tensor copy right after optimizer.step() (the
+# reference's IPEX path keeps bf16 weights next to fp32-precision masters the same way, P/dlrm_s_pytorch.py:
+# 926-953).  A shadow is used only while its recorded version matches the parameter's: any other in-place
+# change of a parameter (load_state_dict, manual edits) silently falls back to the per-step cast.
+_SHADOWS = {}  # id(param) -> [weakref(param), shadow, version, pad]
+
+
+def enable_bf16_shadows(layers_list, optimizer):
+    """``layers_list``: the model's nn.Sequential MLPs; ``optimizer``: the torch optimizer that steps their
+    parameters.  Returns the refresh function (also installed as a step post-hook of ``optimizer``)."""
+    import weakref
+    entries = []
+    for layers in layers_list:
+        mods = list(layers)
+        for i, m in enumerate(mods):
+            if not isinstance(m, (nn.Linear, PaddedLinear)):
+                continue
+            pad = (-m.in_features) % 8 if isinstance(m, PaddedLinear) else 0
+            w = m.weight
+            sh = torch.zeros(w.shape[0], w.shape[1] + pad, dtype=torch.bfloat16, device=w.device)
+            entries.append([weakref.ref(w), sh, -1, pad])
+            _SHADOWS[id(w)] = entries[-1]
+            if m.bias is not None:
+                entries.append([weakref.ref(m.bias), torch.zeros_like(m.bias, dtype=torch.bfloat16), -1, 0])
+                _SHADOWS[id(m.bias)] = entries[-1]
+
+    def refresh(*_a, **_k):
+        dst, src = [], []
+        for e in entries:
+            p = e[0]()
+            if p is None:
+                continue
+            if e[3]:
+                e[1][:, :p.shape[1]].copy_(p.data)  # padded weight: strided destination, its own copy
+            else:
+                dst.append(e[1]), src.append(p.data)
+            e[2] = p._version
+        if dst:
+            torch._foreach_copy_(dst, src)
+    refresh()
+    optimizer.register_step_post_hook(refresh)
+    return refresh
+
+
+def _bf16_of(param, width=None):
+    """bf16 value of a parameter: its shadow when fresh (and of the requested padded width), else a cast."""
+    e = _SHADOWS.get(id(param))
+    if e is not None and e[0]() is param and e[2] == param._version and (width is None or e[1].shape[1] == width):
+        return e[1], True
+    return param.to(torch.bfloat16), False
+
+
 
 def _ones(rows: int, device) -> torch.Tensor:
     key = (rows, device)
@@ -36,11 +91,11 @@ class _LinearReLU(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, bias, relu: bool):
         x16 = x if x.dtype == torch.bfloat16 else x.to(torch.bfloat16)
-        w16 = weight.to(torch.bfloat16)
-        extra = x16.shape[1] - w16.shape[1]
-        if extra > 0:  # PaddedLinear: input carries zero columns beyond in_features
+        extra = x16.shape[1] - weight.shape[1]
+        w16, padded = _bf16_of(weight, x16.shape[1])
+        if extra > 0 and not padded:  # PaddedLinear: input carries zero columns beyond in_features
             w16 = torch.nn.functional.pad(w16, (0, extra))
-        b16 = bias.to(torch.bfloat16)
+        b16, _ = _bf16_of(bias)
         if relu:
             y = torch._addmm_activation(b16, x16, w16.t())  # bias + ReLU in the GEMM epilogue
         else:

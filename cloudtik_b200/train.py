@@ -111,6 +111,9 @@ def run(argv=None):
         enable_peer_exchange(dlrm, lB)
     dense = [p for p in dlrm.parameters() if p.requires_grad]
     optimizer = torch.optim.SGD(dense, lr=args.learning_rate)
+    if args.bf16:
+        from .mlp import enable_bf16_shadows
+        enable_bf16_shadows([dlrm.bot_l, dlrm.top_l], optimizer)
     sync_dense = ext_dist.DenseGradAllreduce(dense) if world > 1 else (lambda: None)
     lr_scheduler = LRPolicyScheduler(optimizer, args.lr_num_warmup_steps, args.lr_decay_start_step,
                                      args.lr_num_decay_steps)

@@ -185,3 +185,40 @@ def test_to_bfloat16_train_keeps_fp32_master():
         np.add.at(G, idx[t].cpu().numpy(), g[t].float().cpu().numpy().astype(np.float64))
         np.testing.assert_allclose(m.master_weights()[t].cpu().numpy(), (Ws[t] - lr * G).astype(np.float32),
                                    rtol=2e-5, atol=1e-6)
+
+
+def test_bf16_shadows_keep_the_step_bit_identical():
+    """enable_bf16_shadows: same losses and same MLP weights, bit for bit, as the per-step casts; a parameter
+    changed behind the optimizer's back (load_state_dict) falls back to the cast until the next step."""
+    from cloudtik_b200.dlrm import DLRM_Net, train_step
+    from cloudtik_b200.mlp import enable_bf16_shadows, _SHADOWS
+    from oracle.dlrm_port import uniform_batch
+    D, rows = 128, [300, 7, 1000]
+    F = len(rows) + 1
+    ln_bot, ln_top = [13, 64, D], [D + F * (F - 1) // 2, 64, 1]
+
+    def make(shadows):
+        np.random.seed(9)
+        net = DLRM_Net(D, np.array(rows), np.array(ln_bot), np.array(ln_top), sigmoid_top=len(ln_top) - 2,
+                       np_init_emb_weight=True, lr=0.1, bf16=True)
+        opt = torch.optim.SGD([p for p in net.parameters() if p.requires_grad], lr=0.1)
+        if shadows:
+            enable_bf16_shadows([net.bot_l, net.top_l], opt)
+        return net, opt
+    (na, oa), (nb, ob) = make(False), make(True)
+    rs = np.random.RandomState(3)
+    for step in range(4):
+        X, lS_o, lS_i, T = uniform_batch(rs, 128, rows, pooling=2)
+        args = (torch.tensor(X).cuda(), ([torch.tensor(o).cuda() for o in lS_o], [torch.tensor(i).cuda() for i in lS_i]),
+                torch.tensor(T).cuda())
+        la = train_step(na, oa, *args)
+        lb = train_step(nb, ob, *args)
+        assert torch.equal(la, lb), step
+        if step == 1:  # overwrite a weight outside the optimizer on both models: the stale shadow must not be used
+            for n_ in (na, nb):
+                with torch.no_grad():
+                    n_.top_l[0].weight.mul_(0.5)
+            e = _SHADOWS[id(nb.top_l[0].weight)]
+            assert e[2] != nb.top_l[0].weight._version
+    for pa, pb in zip(na.parameters(), nb.parameters()):
+        assert torch.equal(pa, pb)
