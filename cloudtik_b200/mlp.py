@@ -123,10 +123,10 @@ class _LinearReLU(torch.autograd.Function):
             if dx.dtype != ctx.x_dtype:
                 dx = dx.to(ctx.x_dtype)
         if ctx.needs_input_grad[1]:
-            dw = dy.t() @ x16
+            # fp32 weight gradient straight out of the GEMM (aten::mm.dtype): no bf16 rounding of dW, no cast kernel
+            dw = torch.mm(dy.t(), x16, out_dtype=torch.float32)
             if ctx.extra > 0:
                 dw = dw[:, :dw.shape[1] - ctx.extra]
-            dw = dw.float()
         if ctx.needs_input_grad[2] and db is None:
             db = (_ones(dy.shape[0], dy.device) @ dy)[0].float()  # column sums on the tensor cores
         return dx, dw, db, None
