@@ -415,7 +415,9 @@ def run_b200_arm(a):
                            for k, v in kt.items() if k != dom}}
 
     bits = max(1, int(sum(rows_local) - 1).bit_length())
-    launches = 1 + 1 + 3 * ((bits + 7) // 8) + 3 + 2 + 2  # fwd, keys, radix passes, dedup, update + join, interaction f/b
+    n_relu = (len(LN_BOT) - 1) + (len(LN_TOP) - 2)  # every MLP layer but the sigmoid one: relu_bwd_bias + chunk sum
+    # fwd, keys, radix passes, dedup, update + join, interaction f/b, MLP backward glue (bf16 path only)
+    launches = 1 + 1 + 3 * ((bits + 7) // 8) + 3 + 2 + 2 + (2 * n_relu if bf16 else 0)
     line = {"metric": "dlrm_train_samples_per_sec", "value": round(value, 1), "unit": "samples/s", "n_gpus": world,
             "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": round(ms_step, 4), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": a.dtype, "data": "synthetic",
