@@ -120,7 +120,7 @@ class ClockSampler:
         self.p = None
         try:
             self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                       "-lms", "100", "-i", str(index)], stdout=subprocess.PIPE,
+                                       "-lms", "20", "-i", str(index)], stdout=subprocess.PIPE,
                                       stderr=subprocess.DEVNULL, text=True)
         except Exception:
             self.p = None
@@ -351,7 +351,6 @@ def run_b200_arm(a):
             step_fn(i)
     clocks = ClockSampler(local_rank) if rank == 0 else None
     ms_total, last_loss = timed(step_fn, a.steps)
-    clk = clocks.stop() if clocks else None
     loss_val = float(last_loss.cpu())
 
     for i in range(2):
@@ -380,6 +379,7 @@ def run_b200_arm(a):
         pend.clear()
         ms_rec, _ = timed(rec_fn, a.steps)
 
+    clk = clocks.stop() if clocks else None  # sampled every 20 ms across the three timed legs (all under load)
     if rank != 0:
         return
     ms_step = ms_total / a.steps
