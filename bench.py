@@ -414,6 +414,13 @@ def run_b200_arm(a):
                 "others": {k: {"ms": round(v, 4), "GBps": round(alg[k] / (v * 1e-3) / 1e9, 1)}
                            for k, v in kt.items() if k != dom}}
 
+    if roof is not None and use_p2p:
+        # NVLink side of the same two kernels: (W-1)/W of the pooled rows are WRITTEN to peers by the forward and
+        # (W-1)/W of the gradient rows are READ from peers by the update (900 GB/s per direction)
+        nv_bytes = T_loc * B_glob * D * ea * (world - 1) / world
+        roof["nvlink"] = {"bytes_per_rank_per_direction": int(nv_bytes), "peak": 900.0, "unit": "GB/s", "kernels": {
+            k: {"ms": round(v, 4), "GBps": round(nv_bytes / (v * 1e-3) / 1e9, 1), "frac": round(nv_bytes / (v * 1e-3) / 1e9 / 900.0, 3)}
+            for k, v in kt.items()}, "note": "rank 0; measured in the eager pass with the side-stream overlap off"}
     bits = max(1, int(sum(rows_local) - 1).bit_length())
     n_relu = (len(LN_BOT) - 1) + (len(LN_TOP) - 2)  # every MLP layer but the sigmoid one: relu_bwd_bias + chunk sum
     # fwd, keys, radix passes, dedup, update + join, interaction f/b, MLP backward glue (bf16 path only)

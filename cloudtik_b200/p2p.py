@@ -62,8 +62,9 @@ class _ShardedEmbInteractFn(torch.autograd.Function):
                 torch.cuda.current_stream().wait_event(pend[2])  # launched ahead of the bottom MLP (prelaunch())
             else:
                 emb.join()
-                ops.emb_fwd_sharded(emb.tables, indices, offsets, B_glob, exch.T_ptrs_dev, exch.lN, exch.F, feat0,
-                                    exch.dtype, emb.error_flag)
+                with emb._timed("emb_fwd"):
+                    ops.emb_fwd_sharded(emb.tables, indices, offsets, B_glob, exch.T_ptrs_dev, exch.lN, exch.F,
+                                        feat0, exch.dtype, emb.error_flag)
                 emb._launch_prepare(indices, offsets, B_glob)  # sort / dedup on the side stream
         ctx.rw_ctx = None
         if rowwise is not None:  # row-wise sharded hot tables occupy the LAST feature slots
