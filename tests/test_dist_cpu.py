@@ -66,6 +66,16 @@ def _worker(rank, world, port, n_tables, N, E, ret):
             g_o, g_i = ext_dist.global_batch_indices(sh, len(local))
             for k, t in enumerate(local):
                 assert torch.equal(g_i[k], idx[t]) and torch.equal(g_o[k], torch.arange(N))
+        # flat all-reduce of the data-parallel MLP gradients (stand-in for DDP): mean and sum flavours
+        ps = [torch.nn.Parameter(torch.zeros(3, 2)), torch.nn.Parameter(torch.zeros(5))]
+        for average in (True, False):
+            for k, p_ in enumerate(ps):
+                p_.grad = torch.full_like(p_, float((rank + 1) * (k + 1)))
+            ext_dist.DenseGradAllreduce(ps, average=average)()
+            tot = sum(r + 1 for r in range(world))
+            for k, p_ in enumerate(ps):
+                want = tot * (k + 1) / (world if average else 1)
+                assert torch.equal(p_.grad, torch.full_like(p_, want))
         # all_gather of per-rank scores (eval path)
         scores = torch.full((lN, 1), float(rank))
         allg = ext_dist.all_gather(scores, None)
