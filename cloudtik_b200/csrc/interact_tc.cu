@@ -274,7 +274,7 @@ __device__ __forceinline__ uint32_t s_off(int f, int g) {
 }
 
 template <int KB>  // D / 64 (2 or 4)
-__global__ void __launch_bounds__(320, 1)
+__global__ void __launch_bounds__(448, 1)
     interact_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
   constexpr int D = KB * 64;
   constexpr int MB = D / 128;                    // 128-row accumulator blocks per sample
@@ -374,11 +374,13 @@ __global__ void __launch_bounds__(320, 1)
       if (++st == stages) { st = 0; ph ^= 1; }
       if (++as == ACC_STAGES) { as = 0; aph ^= 1; }
     }
-  } else if (warp < 6) {
-    // ---------------- epilogue: warp q reads TMEM lanes [32q, 32q+32) = d-values 32q + lane (+128 mb)
+  } else if (warp < 6 || warp >= 10) {
+    // ---------------- epilogue: warp q reads TMEM lanes [32q, 32q+32) = d-values 32q + lane (+128 mb).
+    // TWO sets of four warps (2..5 and 10..13) take alternate tiles: the epilogue (TMEM load, bf16 packing, 32
+    // row stores per sample) was the slowest stage of the pipeline, not HBM
     const int q = warp & 3;
-    int as = 0;
-    uint32_t aph = 0;
+    const int eset = warp >= 10 ? 1 : 0;
+    auto tile_of = [&](int i) { return (int)(blockIdx.x + (int64_t)i * gridDim.x); };
     // dR[:, :D] flows into feature 0; prefetched one tile ahead (TC_NS x MB values per thread)
     float pass_cur[TC_NS][MB], pass_nxt[TC_NS][MB];
     auto load_pass = [&](int tile, float (*dst)[MB]) {
@@ -390,9 +392,12 @@ __global__ void __launch_bounds__(320, 1)
           dst[s][mb] = (tile < p.n_tiles && b < p.B) ? __bfloat162float(p.dR[b * p.ldr + mb * 128 + 32 * q + lane]) : 0.f;
       }
     };
-    load_pass(blockIdx.x, pass_cur);
-    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
-      load_pass(tile + gridDim.x, pass_nxt);
+    load_pass(tile_of(eset), pass_cur);
+    for (int it = eset; tile_of(it) < p.n_tiles; it += 2) {
+      const int tile = tile_of(it);
+      const int as = it % ACC_STAGES;
+      const uint32_t aph = (uint32_t)(it / ACC_STAGES) & 1u;
+      load_pass(tile_of(it + 2), pass_nxt);
       mbar_wait_bounded(&acc_full[as], aph);
       tc_fence_after();
 #pragma unroll
@@ -428,7 +433,6 @@ __global__ void __launch_bounds__(320, 1)
       for (int s = 0; s < TC_NS; ++s)
 #pragma unroll
         for (int mb = 0; mb < MB; ++mb) pass_cur[s][mb] = pass_nxt[s][mb];
-      if (++as == ACC_STAGES) { as = 0; aph ^= 1; }
     }
   } else {
     // ---------------- S builders (warps 6..9): S[i][j] = S[j][i] = dR[b, D + i(i-1)/2 + j]
@@ -587,10 +591,10 @@ int interact_bwd_tc(const void* T, const void* dR, void* dT, int64_t B, int64_t 
   const int grid = std::min(p.n_tiles, sm_count());
   if (KB == 2) {
     cudaFuncSetAttribute(interact_bwd_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    interact_bwd_tc_kernel<2><<<grid, 320, smem, st>>>(map, p);
+    interact_bwd_tc_kernel<2><<<grid, 448, smem, st>>>(map, p);
   } else {
     cudaFuncSetAttribute(interact_bwd_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    interact_bwd_tc_kernel<4><<<grid, 320, smem, st>>>(map, p);
+    interact_bwd_tc_kernel<4><<<grid, 448, smem, st>>>(map, p);
   }
   B200_CHECK_LAUNCH("interact_bwd_tc");
   return B200_OK;
