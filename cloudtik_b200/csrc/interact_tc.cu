@@ -10,6 +10,9 @@
 //   warp 1      MMA issuer (one elected lane): tcgen05.mma kind::f16, accumulators in TMEM.
 //   warps 2..5  epilogue: tcgen05.ld the accumulator quarter their warp may touch, write out.
 //   warps 6..9  (backward only) build the symmetric dZ tiles from dR in shared memory.
+//   warps 10..13 (backward only) a second epilogue set: the two sets take alternate tiles, because the
+//               backward epilogue (32 TMEM columns -> packed bf16 -> 32 row stores per sample) is the
+//               slowest stage of that pipeline.
 // Forward:  Z = A A^t with A = the 128-row tile (4 samples x 32 padded features), K = D; the four
 //           32x32 diagonal blocks are the per-sample Gram matrices (the off-diagonal MMA work is
 //           free: the kernel is HBM-bound).
