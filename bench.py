@@ -53,6 +53,10 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="run the step eagerly instead of as one CUDA graph")
     ap.add_argument("--no-p2p", action="store_true", help="multi-GPU: NCCL all-to-all instead of the fused peer-memory exchange")
+    ap.add_argument("--workload", default="c3", choices=["c3", "c5"],
+                    help="c3 = Criteo-Terabyte one-hot step (the headline line); c5 = BASELINE configs[4]: multi-hot "
+                         "bags, row-wise sharded hot tables, fused Adagrad, bf16 activations (eager, N >= 1)")
+    ap.add_argument("--pooling", type=int, default=20, help="c5: indices per bag")
     ap.add_argument("--no-microbench", action="store_true",
                     help="skip the BASELINE configs[1] EmbeddingBag micro-benchmark appended to the N=1 line")
     ap.add_argument("--cpu-rows-cap", type=int, default=200000)
@@ -456,10 +460,134 @@ def run_b200_arm(a):
     print(json.dumps(line), flush=True)
 
 
+def run_c5_arm(a):
+    """BASELINE configs[4]: multi-hot DLRM (pooling ~20), the three largest tables ROW-WISE sharded over the ranks
+    (reduce-scatter forward / all-gather backward), the other 23 table-wise (fused peer-memory exchange), fused
+    Adagrad on every table, bf16 MLPs / interaction / pooled rows.  Eager (the row filter of the row-wise path has
+    data-dependent shapes), CUDA-event timed, max over ranks.  On one GPU every table is local."""
+    from cloudtik_b200 import ext_dist
+    from cloudtik_b200.dlrm import DLRM_Net, enable_peer_exchange
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        ext_dist.init_distributed(rank=rank, size=world, backend="nccl")
+    cap = a.rows_cap or (12_000_000 if world == 1 else 0)  # fp32 tables + fp32 Adagrad state: 1 KB per row
+    big = sorted(range(len(C3_ROWS)), key=lambda i: -C3_ROWS[i])[:3]
+    order = [i for i in range(len(C3_ROWS)) if i not in big] + sorted(big)  # hot (largest) tables last
+    rows = [min(C3_ROWS[i], cap) if cap else C3_ROWS[i] for i in order]
+    n_rw = 3 if world > 1 else 0
+    P, B_loc = a.pooling, a.batch
+    B_glob = B_loc * world
+    lr, lr_emb = 0.01, 1e-3  # Adagrad's first steps are +-lr per touched element: keep them small next to U(+-sqrt(1/n))
+    np.random.seed(727)
+    torch.manual_seed(727 + rank)
+    net = DLRM_Net(D, np.array(rows), np.array(LN_BOT), np.array(LN_TOP), sigmoid_top=len(LN_TOP) - 2,
+                   np_init_emb_weight=False, device=dev, lr=lr_emb, emb_optimizer="adagrad", bf16=True, n_rowwise=n_rw)
+    n_tw = len(rows) - n_rw
+    local_ids = list(range(n_tw)) if world == 1 else net.local_ln_emb
+    if world > 1:
+        enable_peer_exchange(net, B_loc)
+    dense = [p for p in net.parameters() if p.requires_grad]
+    opt = torch.optim.SGD(dense, lr=lr)
+    from cloudtik_b200.mlp import enable_bf16_shadows
+    enable_bf16_shadows([net.bot_l, net.top_l], opt)
+    # Adagrad is not linear in the gradient scale: every rank divides its loss by world, MLP gradients are summed
+    sync_dense = ext_dist.DenseGradAllreduce(dense, average=False) if world > 1 else (lambda: None)
+
+    def bags(rs, n_rows_list):
+        idx = np.stack([np.floor(rs.rand(B_glob * P) * n).astype(np.int64) for n in n_rows_list])
+        off = np.arange(len(n_rows_list) * B_glob + 1, dtype=np.int64) * P
+        return idx.reshape(-1), off
+    sets = []
+    for k in range(2):
+        rs_loc = np.random.RandomState(1000 * rank + k)
+        rs_glob = np.random.RandomState(99 + k)  # row-wise bags: every rank must see the SAME global batch
+        X = rs_loc.rand(B_loc, 13).astype(np.float32)
+        Y = np.round(rs_loc.rand(B_loc, 1)).astype(np.float32)
+        idx, off = bags(rs_loc, [rows[i] for i in local_ids])
+        host = [X, Y, idx, off]
+        if n_rw:
+            host += list(bags(rs_glob, rows[n_tw:]))
+        host = [torch.from_numpy(v).pin_memory() for v in host]
+        sets.append({"host": host, "dev": [h.to(dev, non_blocking=True) for h in host]})
+    torch.cuda.synchronize()
+
+    def step(t):
+        X, Y, idx, off = t[:4]
+        Z = (net(X, idx, off, None, t[4], t[5]) if n_rw else net(X, idx, off, None)).float()
+        E = net.loss_fn(Z, Y)
+        opt.zero_grad(set_to_none=True)
+        (E / world).backward()
+        sync_dense()
+        opt.step()
+        return E.detach()
+
+    stage = [torch.empty_like(t) for t in sets[0]["dev"]]
+
+    def step_e2e(i):
+        for d, h in zip(stage, sets[i % 2]["host"]):
+            d.copy_(h, non_blocking=True)
+        return float(step(stage).cpu())
+
+    def timed(fn, steps):
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        last = None
+        for i in range(steps):
+            last = fn(i)
+        e1.record()
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            torch.distributed.all_reduce(ms, op=torch.distributed.ReduceOp.MAX)
+        return float(ms.item()), last
+
+    for i in range(max(a.warmup, 3)):
+        step(sets[i % 2]["dev"])
+    clocks = ClockSampler(local_rank) if rank == 0 else None
+    ms_total, last = timed(lambda i: step(sets[i % 2]["dev"]), a.steps)
+    loss_val = float(last.cpu())
+    step_e2e(0)
+    ms_e2e, _ = timed(step_e2e, a.steps)
+    clk = clocks.stop() if clocks else None
+    if rank != 0:
+        return
+    h2d = sum(t.numel() * t.element_size() for t in sets[0]["host"])
+    line = {"metric": "dlrm_train_samples_per_sec", "value": round(B_glob * a.steps / (ms_total / 1e3), 1),
+            "unit": "samples/s", "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
+            "ms_per_step": round(ms_total / a.steps, 4), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": "dlrm_multihot_rowwise_adagrad_c5", "batch_per_gpu": B_loc, "global_batch": B_glob,
+                       "dim": D, "tables": len(rows), "pooling": P, "rows_cap": cap or None,
+                       "row_wise_tables": n_rw, "row_wise_rows": [int(r) for r in rows[n_tw:]] if n_rw else [],
+                       "optimizer": "fused sparse Adagrad (tables) + torch SGD (MLPs)", "table_dtype": "fp32",
+                       "parallelism": "single" if world == 1 else
+                       f"table-wise x{world} (fused peer-memory exchange) + row-wise x{world} (NCCL reduce-scatter / "
+                       "all-gather) + data-parallel MLPs",
+                       "l2": "inputs larger than L2", "launch": "eager"},
+            "e2e": {"value": round(B_glob * a.steps / (ms_e2e / 1e3), 1), "unit": "samples/s",
+                    "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4, "ms_per_step": round(ms_e2e / a.steps, 4)},
+            "clocks": clk, "final_loss": loss_val, "roofline": None, "cpu_baseline": None}
+    print(json.dumps(line), flush=True)
+
+
 def main():
     a = parse()
     if a.impl == "reference":
         run_reference_arm(a)
+    elif a.workload == "c5":
+        run_c5_arm(a)
+        if torch.distributed.is_available() and torch.distributed.is_initialized():
+            torch.distributed.destroy_process_group()
     else:
         run_b200_arm(a)
         if torch.distributed.is_available() and torch.distributed.is_initialized():
