@@ -29,8 +29,9 @@ def main():
     for name, (n, t) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
         print(f"| `{name}` | {n} | {t:.1f} | {t / n:.1f} | {100 * t / total:.1f}% |")
     ours = sum(t for k, (n, t) in agg.items() if "b200::" in k)
-    print(f"\nb200:: kernels: {ours / 1000:.3f} ms = {100 * ours / total:.1f}% of the captured time"
-          f" ({steps} step(s) captured => {total / 1000 / steps:.3f} ms/step serialised)")
+    tail = (f" ({steps} step(s) captured => {total / 1000 / steps:.3f} ms/step serialised)" if "--steps" in sys.argv
+            else " (the capture window is a launch count, not a whole number of steps)")
+    print(f"\nb200:: kernels: {ours / 1000:.3f} ms = {100 * ours / total:.1f}% of the captured time" + tail)
 
 
 if __name__ == "__main__":
