@@ -487,6 +487,11 @@ def run_c5_arm(a):
     torch.manual_seed(727 + rank)
     net = DLRM_Net(D, np.array(rows), np.array(LN_BOT), np.array(LN_TOP), sigmoid_top=len(LN_TOP) - 2,
                    np_init_emb_weight=False, device=dev, lr=lr_emb, emb_optimizer="adagrad", bf16=True, n_rowwise=n_rw)
+    # non-zero initial accumulator (torch.optim.Adagrad's initial_accumulator_value): from zero, the first steps move
+    # every touched element by +-lr whatever the gradient, and with 5 M lookups per table per step the synthetic
+    # model saturates within a few steps
+    for st in net.emb_l.tables.states + (net.rowwise.emb.tables.states if net.rowwise is not None else []):
+        st.fill_(0.1)
     n_tw = len(rows) - n_rw
     local_ids = list(range(n_tw)) if world == 1 else net.local_ln_emb
     if world > 1:
