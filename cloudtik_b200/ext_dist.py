@@ -276,7 +276,7 @@ class DenseGradAllreduce(object):
 
     def __init__(self, params, average: bool = True):
         """``average=False`` sums instead (use it when every rank already divides its loss by the world
-        size -- the way to keep a scale-sensitive table optimiser such as Adagrad exact, see tools/dist_parity.py)."""
+        size -- the way to keep a scale-sensitive table optimiser such as Adagrad exact, see tests/dist_parity.py)."""
         self.average = average
         self.params = [p for p in params if p.requires_grad]
         n = sum(p.numel() for p in self.params)

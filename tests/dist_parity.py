@@ -2,7 +2,7 @@
 global-batch CPU oracle (that run IS the multi-GPU oracle).
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 \
-        --master-port 29533 tools/dist_parity.py [--bf16] [--tables 5]
+        --master-port 29533 tests/dist_parity.py [--bf16] [--tables 5]
 
 Every rank builds the same oracle port on the CPU, copies its slice of the tables (and the MLPs) into the
 B200 model, trains `--steps` steps on its slice of the global batch and checks: mean-of-rank losses vs the
