@@ -77,36 +77,37 @@ class QREmbeddingBag(nn.Module):
 
 
 def md_solver(n, alpha, d0=None, B=None, round_dim=True, k=None):
-    """``md_embedding_bag.py:20-41``: mixed-dimension assignment with the alpha power rule."""
-    n, indices = torch.sort(n)
-    k = k[indices] if k is not None else torch.ones(len(n))
-    d = alpha_power_rule(n.type(torch.float) / k, alpha, d0=d0, B=B)
+    """``md_embedding_bag.py:20-41``: embedding dimension per table from its row count (popularity-weighted when
+    ``k`` gives the queries per inference), by the alpha power rule; dims come back in the caller's table order."""
+    n_sorted, perm = torch.sort(n)
+    weight = torch.ones(n_sorted.numel()) if k is None else k[perm]
+    dims = alpha_power_rule(n_sorted.to(torch.float) / weight, alpha, d0=d0, B=B)
     if round_dim:
-        d = pow_2_round(d)
-    undo_sort = [0] * len(indices)
-    for i, v in enumerate(indices):
-        undo_sort[v] = i
-    return d[undo_sort]
+        dims = pow_2_round(dims)
+    back = torch.empty_like(perm)
+    back[perm] = torch.arange(perm.numel())
+    return dims[back]
 
 
 def alpha_power_rule(n, alpha, d0=None, B=None):
+    """``md_embedding_bag.py:43-56``: d_i = lambda * n_i^-alpha, at least 1, rounded; lambda from the base
+    dimension ``d0`` of the smallest table (which then keeps exactly ``d0``) or from a parameter budget ``B``."""
+    nf = n.to(torch.float)
     if d0 is not None:
-        lamb = d0 * (n[0].type(torch.float) ** alpha)
+        lam = d0 * nf[0] ** alpha
     elif B is not None:
-        lamb = B / torch.sum(n.type(torch.float) ** (1 - alpha))
+        lam = B / (nf ** (1 - alpha)).sum()
     else:
         raise ValueError("Must specify either d0 or B")
-    d = torch.ones(len(n)) * lamb * (n.type(torch.float) ** (-alpha))
-    for i in range(len(d)):
-        if i == 0 and d0 is not None:
-            d[i] = d0
-        else:
-            d[i] = 1 if d[i] < 1 else d[i]
-    return torch.round(d).type(torch.long)
+    dims = torch.clamp(torch.ones(nf.numel()) * lam * nf ** (-alpha), min=1.0)
+    if d0 is not None:
+        dims[0] = d0
+    return torch.round(dims).to(torch.long)
 
 
 def pow_2_round(dims):
-    return 2 ** torch.round(torch.log2(dims.type(torch.float)))
+    """``md_embedding_bag.py:59-60``: nearest power of two (in log space)."""
+    return torch.pow(2.0, torch.round(torch.log2(dims.to(torch.float))))
 
 
 class PrEmbeddingBag(nn.Module):
