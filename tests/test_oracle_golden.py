@@ -204,3 +204,13 @@ def test_md_solver_mirror_matches_reference(golden):
         np.testing.assert_array_equal(md_solver(n.clone(), alpha, d0=128, round_dim=True).numpy(), g[f"md_d0_{k}"])
         np.testing.assert_array_equal(md_solver(n.clone(), alpha, d0=128, round_dim=False).numpy(), g[f"md_raw_{k}"])
     np.testing.assert_array_equal(md_solver(n.clone(), 0.3, B=1.0e8, round_dim=False).numpy(), g["md_budget"])
+
+
+def test_product_side_quantiser_matches_fixture_on_cpu(golden):
+    """cloudtik_b200.quantized.quantize_rowwise_int8 is plain torch arithmetic: on CPU tensors it must give the
+    fixture's codes and scales bit for bit (the GPU run of the same function is checked in tests/test_gpu_inference.py)."""
+    from cloudtik_b200.quantized import quantize_rowwise_int8
+    g = golden("int8_tables")
+    q, s = quantize_rowwise_int8(torch.tensor(g["W"]), chunk_rows=64)   # several chunks
+    np.testing.assert_array_equal(q.numpy(), g["q"])
+    np.testing.assert_array_equal(s.numpy(), g["scale"])
