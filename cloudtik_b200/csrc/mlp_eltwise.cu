@@ -6,27 +6,31 @@
 // matrix for the bias gradient -- two trips through HBM plus (in the bf16 fast path) a skinny GEMM with
 // a split-K reduction.  This kernel makes ONE trip: it reads dY and the saved activation Y, writes
 // dZ = dY * (Y > 0) and accumulates the fp32 column sums of dZ on the way.
-//   grid = (column tiles of 256, row chunks of RB_ROWS); thread = 8 consecutive columns (one 16-byte
-//   vector) x every 8th row of the chunk, 4 row vectors of each operand in flight;
+//   grid = (column tiles of 256, row chunks of 32..128 rows, sized so that even a narrow layer fills the
+//   GPU); thread = 8 consecutive columns (one 16-byte vector) x every 8th row of the chunk, 4 row vectors
+//   of each operand in flight;
 //   per-chunk sums go to a [chunks, N] fp32 scratch and a second tiny kernel adds the chunks in order
 //   (deterministic: no atomics).
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace b200 {
 
 constexpr int RB_THREADS = 256;
-constexpr int RB_ROWS = 128;   // rows per CTA
+constexpr int RB_ROWS = 128;   // most rows per CTA
+constexpr int RB_ROWS_MIN = 32;  // fewest (= one pass of the 8 row lanes x 4 vectors in flight)
 constexpr int RB_CV = 32;      // column vectors (8 bf16 each) per CTA = 256 columns
 constexpr int RB_RL = RB_THREADS / RB_CV;  // row lanes per CTA
 
 __global__ void __launch_bounds__(RB_THREADS)
     relu_bwd_bias_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y, uint4* __restrict__ dz,
-                         float* __restrict__ partial, int64_t B, int64_t NV /* N / 8 */) {
+                         float* __restrict__ partial, int64_t B, int64_t NV /* N / 8 */, int rows_per_cta) {
   __shared__ float s_sum[RB_RL][RB_CV * 8 + 8];
   const int tx = threadIdx.x % RB_CV, ty = threadIdx.x / RB_CV;
   const int64_t cv = (int64_t)blockIdx.x * RB_CV + tx;
-  const int64_t r0 = (int64_t)blockIdx.y * RB_ROWS;
-  const int64_t r1 = min(r0 + RB_ROWS, B);
+  const int64_t r0 = (int64_t)blockIdx.y * rows_per_cta;
+  const int64_t r1 = min(r0 + rows_per_cta, B);
   float acc[8];
 #pragma unroll
   for (int x = 0; x < 8; ++x) acc[x] = 0.f;
@@ -111,7 +115,7 @@ using namespace b200;
 
 extern "C" size_t b200_relu_bwd_bias_workspace_bytes(int64_t B, int64_t N) {
   if (B <= 0 || N <= 0) return 0;
-  return (size_t)ceil_div(B, RB_ROWS) * (size_t)N * sizeof(float);
+  return (size_t)ceil_div(B, RB_ROWS_MIN) * (size_t)N * sizeof(float);  // the most chunks a launch may use
 }
 
 extern "C" int b200_relu_bwd_bias(const void* d_dy, const void* d_y, void* d_dz, float* d_db, int64_t B, int64_t N,
@@ -132,11 +136,16 @@ extern "C" int b200_relu_bwd_bias(const void* d_dy, const void* d_y, void* d_dz,
                B200_EINVAL, "relu_bwd_bias: operands must be 16-byte aligned");
   B200_REQUIRE(ws_bytes >= b200_relu_bwd_bias_workspace_bytes(B, N), B200_EWORKSPACE,
                "relu_bwd_bias: workspace too small");
-  const int64_t NV = N / 8, chunks = ceil_div(B, RB_ROWS);
-  B200_REQUIRE(chunks <= 65535, B200_EUNSUPPORTED, "relu_bwd_bias: more than 65535 row chunks");
+  // rows per CTA: as many as keep >= 8 CTAs per SM in the grid (a 256-column layer has ONE column tile),
+  // a multiple of 32, within [32, 128]; more only if the grid's y dimension would overflow
+  const int64_t NV = N / 8, col_tiles = ceil_div(NV, RB_CV);
+  int64_t rows = B / ceil_div((int64_t)148 * 8, col_tiles) / RB_ROWS_MIN * RB_ROWS_MIN;
+  rows = std::max<int64_t>(RB_ROWS_MIN, std::min<int64_t>(RB_ROWS, rows));
+  if (ceil_div(B, rows) > 65535) rows = ceil_div(ceil_div(B, (int64_t)65535), RB_ROWS_MIN) * RB_ROWS_MIN;
+  const int64_t chunks = ceil_div(B, rows);
   dim3 grid((unsigned)ceil_div(NV, RB_CV), (unsigned)chunks);
   relu_bwd_bias_kernel<<<grid, RB_THREADS, 0, st>>>(static_cast<const uint4*>(d_dy), static_cast<const uint4*>(d_y),
-                                                    static_cast<uint4*>(d_dz), static_cast<float*>(ws), B, NV);
+                                                    static_cast<uint4*>(d_dz), static_cast<float*>(ws), B, NV, (int)rows);
   bias_chunks_sum_kernel<<<(unsigned)ceil_div(N, 32), 256, 0, st>>>(static_cast<const float*>(ws), d_db, chunks, N);
   B200_CHECK_LAUNCH("relu_bwd_bias");
   return B200_OK;
