@@ -757,10 +757,10 @@ static int launch_update(const UpdParams& p, int64_t n, bool vec_ok, cudaStream_
     constexpr int NG_ = UPD_THREADS / G;                                                                          \
     const size_t part_bytes = (size_t)NG_ * 2 * p.D * sizeof(float);                                              \
     auto kern = window_update_kernel<WT, GT, G, NV, OPT, RED, TRAIL>;                                                  \
-    if (part_bytes > 32 * 1024) {                                                                                 \
-      static const cudaError_t attr_rc =                                                                          \
-          cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);                     \
-      B200_REQUIRE(attr_rc == cudaSuccess && part_bytes <= 96 * 1024, B200_EUNSUPPORTED,                          \
+    if (part_bytes > 48 * 1024) { /* per device, so set on every such launch (cheap) rather than once per process */ \
+      const cudaError_t attr_rc =                                                                                 \
+          cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)part_bytes);               \
+      B200_REQUIRE(attr_rc == cudaSuccess && part_bytes <= 128 * 1024, B200_EUNSUPPORTED,                         \
                    "emb_update: row too long for the in-block join");                                             \
     }                                                                                                             \
     const int64_t nblk = ceil_div(nwin, NG_);                                                                     \

@@ -150,6 +150,8 @@ BWD_CASES = [
     ([1000, 37, 5000], 257, 128, 4, True, torch.float32, torch.float32, "adagrad"),
     ([40, 30], 64, 8, 3, True, torch.float32, torch.float32, "adagrad"),
     ([50, 20, 10], 7, 2, 2, True, torch.float32, torch.float32, "adagrad"),
+    ([40, 300], 70, 1024, 3, True, torch.bfloat16, torch.bfloat16, "sgd"),        # 2 KB rows: 64 KB of in-block pieces
+    ([40, 300], 70, 512, 3, True, torch.float32, torch.float32, "sgd"),           # widest fp32 row (V = 128)
 ]
 
 
