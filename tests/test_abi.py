@@ -41,3 +41,22 @@ def test_host_side_argument_checks_need_no_gpu():
     assert rc == 1 and b"record shape" in _lib.lib.b200_last_error()
     rc = _lib.lib.b200_criteo_transform(None, 8, 40, 13, 0, 20, 10, 0, 8, None, 13, None, None, None, None)
     assert rc == 1 and b"table range" in _lib.lib.b200_last_error()
+
+
+def test_header_is_c99_and_library_links_from_plain_c(tmp_path):
+    """include/b200dlrm.h compiles as C99 (-pedantic, warnings are errors) and tests/abi_client.c, linked against the
+    library with no torch / Python in sight, gets the documented answers from the host-side checks."""
+    import shutil
+    import subprocess
+    from cloudtik_b200 import _lib
+    if shutil.which("gcc") is None:
+        import pytest
+        pytest.skip("no gcc")
+    exe = tmp_path / "abi_client"
+    libdir = os.path.dirname(_lib.LIB_PATH)
+    r = subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I", os.path.join(ROOT, "include"),
+                        os.path.join(ROOT, "tests", "abi_client.c"), "-o", str(exe), "-L", libdir, "-lb200dlrm",
+                        "-Wl,-rpath," + libdir], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    r = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert r.returncode == 0 and "0 failure(s)" in r.stdout, r.stdout + r.stderr
