@@ -60,7 +60,7 @@ def parse():
     ap.add_argument("--no-microbench", action="store_true",
                     help="skip the BASELINE configs[1] EmbeddingBag micro-benchmark appended to the N=1 line")
     ap.add_argument("--cpu-rows-cap", type=int, default=200000)
-    ap.add_argument("--cpu-steps", type=int, default=3)
+    ap.add_argument("--cpu-steps", type=int, default=24, help="timed steps of the cpu_baseline leg (~10 s of CPU work)")
     return ap.parse_args()
 
 
@@ -101,7 +101,7 @@ def run_reference_arm(a):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    steps, warm = max(1, min(a.steps, 5)), max(1, min(a.warmup, 2))
+    steps, warm = max(1, min(a.steps, 30)), max(1, min(a.warmup, 3))  # ~0.4 s per step on 16 host threads
     r = cpu_reference_run(a.batch, a.cpu_rows_cap, steps, warm, a.dtype == "bf16")
     line = {"impl": "reference", "metric": "dlrm_train_samples_per_sec", "value": r["value"], "unit": "samples/s",
             "n_gpus": a.gpus, "steps": steps, "warmup": warm, "ms_per_step": r["ms_per_step"],
