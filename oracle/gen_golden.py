@@ -11,6 +11,8 @@ What is imported from the reference (read-only, unmodified):
   * ``T/dlrm_data_pytorch.py`` -> ``generate_uniform_input_batch`` (ragged multi-hot bags)
   * ``T/data_loader_terabyte.py`` -> ``_transform_features`` (binary Criteo records -> model inputs)
   * ``T/tricks/{qr,md}_embedding_bag.py`` -> ``QREmbeddingBag``, ``PrEmbeddingBag``, ``md_solver``
+  * ``T/dlrm_s_pytorch.py`` + ``T/dlrm_data_pytorch.py`` -> the two configurations of the reference's own test
+    script ``T/test/dlrm_s_test.sh`` (model, random data loader, MSE / SGD loop)
 with ``P/`` = applications/ai/quickstart/models/recommendation/pytorch/dlrm/product and
 ``T/`` = .../dlrm/training/bfloat16.  Absent third-party modules (mlperf_logging) are
 stubbed in ``sys.modules``; nothing in the reference tree is edited.
@@ -360,6 +362,79 @@ def gen_tricks():
     np.savez_compressed(os.path.join(OUT, "tricks.npz"), **out)
 
 
+def load_T_model():
+    """T/dlrm_s_pytorch (the training/bfloat16 variant of the model) + its data module, imported as modules: the
+    absent third-party imports at T/dlrm_s_pytorch.py:90,102-103 and T/mlperf_logger.py:26-27 are stubbed."""
+    sys.dont_write_bytecode = True
+    _stub("onnx")
+    core = _stub("intel_pytorch_extension.core")
+    _stub("intel_pytorch_extension", core=core, is_available=lambda: False)
+    consts = _stub("mlperf_logging.mllog.constants")
+    mllog = _stub("mlperf_logging.mllog", constants=consts, get_mllogger=lambda: types.SimpleNamespace())
+    _stub("mlperf_logging", mllog=mllog)
+    for n in _SHARED_NAMES + ["dlrm_s_pytorch"]:
+        sys.modules.pop(n, None)
+    sys.path.insert(0, T_DIR)
+    try:
+        TM = importlib.import_module("dlrm_s_pytorch")
+        dp = importlib.import_module("dlrm_data_pytorch")
+    finally:
+        sys.path.remove(T_DIR)
+    for n in _SHARED_NAMES + ["dlrm_s_pytorch"]:
+        sys.modules.pop(n, None)
+    return TM, dp
+
+
+def gen_T_smoke():
+    """The reference's OWN test configurations (T/test/dlrm_s_test.sh:24 and :26 -- the only tests it has for this
+    path; they diff PyTorch against Caffe2 at run time and store no values).  Same sequence as the script's
+    __main__ for ``--mini-batch-size=2 --data-size=4|5 --nepochs=1|3 --arch-interaction-op=dot --learning-rate=0.1``
+    with every other flag at its default (tables 4-3-2, D = 2, bottom 4-3-2, top 4-2-1 -> 8-4-2-1, MSE loss,
+    seed 123, up to 10 indices per lookup): seeds (T/dlrm_s_pytorch.py:743-746), random data loader (:811), model
+    (:945), MSELoss (:1001), SGD (:1018), loop (:1184-1256).  Expected loss traces (SURVEY.md section 8c /
+    BASELINE.md): 0.028790, 0.156787 and the nine values of the 3-epoch run -- asserted here."""
+    TM, dp = load_T_model()
+    out = {}
+    want = {"c2": [0.028790, 0.156787],
+            "c4": [0.028790, 0.156787, 0.183348, 0.022413, 0.134285, 0.165428, 0.016494, 0.111174, 0.137763]}
+    for tag, data_size, nepochs in (("c2", 4, 1), ("c4", 5, 3)):
+        args = types.SimpleNamespace(data_size=data_size, num_batches=0, mini_batch_size=2, num_indices_per_lookup=10,
+                                     num_indices_per_lookup_fixed=False, round_targets=False, data_generation="random",
+                                     data_trace_file="./input/dist_emb_j.log", data_trace_enable_padding=False,
+                                     numpy_rand_seed=123, num_workers=0)
+        np.random.seed(123)
+        torch.manual_seed(123)
+        ln_emb, ln_bot, m_spa = np.array([4, 3, 2]), np.array([4, 3, 2]), 2
+        _, train_ld = dp.make_random_data_and_loader(args, ln_emb, 4)
+        ln_top = np.array([4 * 3 // 2 + 2, 4, 2, 1])
+        net = TM.DLRM_Net(m_spa, ln_emb, ln_bot, ln_top, arch_interaction_op="dot", arch_interaction_itself=False,
+                          sigmoid_bot=-1, sigmoid_top=ln_top.size - 2, sync_dense_params=True, loss_threshold=0.0,
+                          ndevices=-1)
+        params0 = [p.detach().numpy().copy() for p in net.parameters()]
+        names = [n for n, _ in net.named_parameters()]
+        loss_fn = torch.nn.MSELoss(reduction="mean")
+        opt = torch.optim.SGD(net.parameters(), lr=0.1)
+        losses, step = [], 0
+        for _ep in range(nepochs):
+            for (X, lS_o, lS_i, T) in train_ld:
+                E = loss_fn(net(X, lS_o, lS_i), T)
+                opt.zero_grad()
+                E.backward()
+                opt.step()
+                losses.append(float(E.detach()))
+                out[f"{tag}_X{step}"], out[f"{tag}_T{step}"] = X.numpy(), T.numpy()
+                for t in range(3):
+                    out[f"{tag}_o{step}_{t}"], out[f"{tag}_i{step}_{t}"] = lS_o[t].numpy(), lS_i[t].numpy()
+                step += 1
+        assert [round(v, 6) for v in losses] == want[tag], (tag, losses)
+        out[f"{tag}_losses"], out[f"{tag}_steps"] = np.array(losses, dtype=np.float64), np.int64(step)
+        out[f"{tag}_param_names"] = np.array(names)
+        for k, (a, b) in enumerate(zip(params0, net.parameters())):
+            out[f"{tag}_init{k}"], out[f"{tag}_final{k}"] = a, b.detach().numpy().copy()
+    out["ln_emb"], out["ln_bot"], out["ln_top"] = np.array([4, 3, 2]), np.array([4, 3, 2]), np.array([8, 4, 2, 1])
+    np.savez_compressed(os.path.join(OUT, "t_smoke.npz"), **out)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     G = load_T_generator()
@@ -372,6 +447,7 @@ def main():
     gen_criteo_transform(load_T_terabyte())
     gen_int8_tables()
     gen_tricks()
+    gen_T_smoke()
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

@@ -214,3 +214,37 @@ def test_product_side_quantiser_matches_fixture_on_cpu(golden):
     q, s = quantize_rowwise_int8(torch.tensor(g["W"]), chunk_rows=64)   # several chunks
     np.testing.assert_array_equal(q.numpy(), g["q"])
     np.testing.assert_array_equal(s.numpy(), g["scale"])
+
+
+def _t_smoke_state(g, tag, which):
+    return {str(n): torch.tensor(g[f"{tag}_{which}{k}"]) for k, n in enumerate(g[f"{tag}_param_names"])}
+
+
+def _t_smoke_batches(g, tag):
+    for s in range(int(g[f"{tag}_steps"])):
+        yield (torch.tensor(g[f"{tag}_X{s}"]), [torch.tensor(g[f"{tag}_o{s}_{t}"]) for t in range(3)],
+               [torch.tensor(g[f"{tag}_i{s}_{t}"]) for t in range(3)], torch.tensor(g[f"{tag}_T{s}"]))
+
+
+def test_port_reproduces_the_reference_test_script_configs(golden):
+    """The two configurations of the reference's own test script (T/test/dlrm_s_test.sh:24,26; MSE loss, ragged
+    bags of up to 10 indices, D = 2): the fixture holds the losses the T/ model printed (0.028790, 0.156787, ...);
+    the oracle port, started from the same weights, must print the same six decimals (losses within 1e-6)."""
+    g = golden("t_smoke")
+    assert [round(float(v), 6) for v in g["c2_losses"]] == [0.028790, 0.156787]
+    assert [round(float(v), 6) for v in g["c4_losses"]] == [0.028790, 0.156787, 0.183348, 0.022413, 0.134285,
+                                                           0.165428, 0.016494, 0.111174, 0.137763]
+    for tag in ("c2", "c4"):
+        np.random.seed(0)
+        net = DLRMPort(2, g["ln_emb"], g["ln_bot"], g["ln_top"])
+        net.load_state_dict(_t_smoke_state(g, tag, "init"))
+        net.loss_fn = torch.nn.MSELoss(reduction="mean")
+        opt = torch.optim.SGD(net.parameters(), lr=0.1)
+        losses = [train_step(net, opt, *b) for b in _t_smoke_batches(g, tag)]
+        # (the dense-vs-sparse summation order explained below reaches the losses from the second epoch on: 1e-8)
+        np.testing.assert_allclose(np.array(losses), g[f"{tag}_losses"], rtol=1e-6, atol=0)
+        assert [round(v, 6) for v in losses] == [round(float(v), 6) for v in g[f"{tag}_losses"]]
+        # final weights: the T/ variant builds tables of < 2048 rows with sparse=False (T/dlrm_s_pytorch.py:266-269),
+        # i.e. a dense gradient whose duplicate rows are summed in another order than the sparse path's: last-ulp
+        for k, v in _t_smoke_state(g, tag, "final").items():
+            np.testing.assert_allclose(net.state_dict()[k].numpy(), v.numpy(), rtol=1e-6, atol=1e-7)
