@@ -248,3 +248,38 @@ def test_port_reproduces_the_reference_test_script_configs(golden):
         # i.e. a dense gradient whose duplicate rows are summed in another order than the sparse path's: last-ulp
         for k, v in _t_smoke_state(g, tag, "final").items():
             np.testing.assert_allclose(net.state_dict()[k].numpy(), v.numpy(), rtol=1e-6, atol=1e-7)
+
+
+def test_batch_producers_reproduce_the_reference_stream(golden):
+    """cloudtik_b200.data (host-side mirror of T/dlrm_data_pytorch's random path): for the reference's seed and
+    flags it must hand out the very batches the reference's RandomDataset + DataLoader produced (fixture t_smoke:
+    ragged bags of up to 10 unique sorted ids, same batches again in every epoch), and the module-level generator
+    must reproduce the small_model fixture drawn with the reference's generate_uniform_input_batch."""
+    import types
+    from cloudtik_b200 import data as D
+    g = golden("t_smoke")
+    for tag, data_size, nepochs in (("c2", 4, 1), ("c4", 5, 3)):
+        args = types.SimpleNamespace(data_size=data_size, num_batches=0, mini_batch_size=2, num_indices_per_lookup=10,
+                                     num_indices_per_lookup_fixed=False, round_targets=False, data_generation="random",
+                                     numpy_rand_seed=123)
+        _, ld = D.make_random_data_and_loader(args, g["ln_emb"], 4)
+        s = 0
+        for _ep in range(nepochs):
+            for X, lS_o, lS_i, T in ld:
+                np.testing.assert_array_equal(X.numpy(), g[f"{tag}_X{s}"])
+                np.testing.assert_array_equal(T.numpy(), g[f"{tag}_T{s}"])
+                for t in range(3):
+                    np.testing.assert_array_equal(lS_o[t].numpy(), g[f"{tag}_o{s}_{t}"])
+                    np.testing.assert_array_equal(lS_i[t].numpy(), g[f"{tag}_i{s}_{t}"])
+                s += 1
+        assert s == int(g[f"{tag}_steps"])
+    sm = golden("small_model")
+    ra = np.random.RandomState(int(sm["seed"]) + 1)
+    for s in range(int(sm["steps"])):
+        X, lS_o, lS_i = D.generate_uniform_input_batch(13, sm["ln_emb"], int(sm["B"]), 5, False, ra=ra)
+        T = D.generate_random_output_batch(int(sm["B"]), 1, round_targets=True, ra=ra)
+        np.testing.assert_array_equal(X.numpy(), sm[f"X{s}"])
+        np.testing.assert_array_equal(T.numpy(), sm[f"T{s}"])
+        for t in range(len(sm["ln_emb"])):
+            np.testing.assert_array_equal(lS_o[t].numpy(), sm[f"o{s}_{t}"])
+            np.testing.assert_array_equal(lS_i[t].numpy(), sm[f"i{s}_{t}"])
