@@ -14,7 +14,6 @@ cloudtik-run env), tables are sharded table-wise exactly like the reference's ``
 from __future__ import annotations
 
 import argparse
-import os
 import sys
 import time
 

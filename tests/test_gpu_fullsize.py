@@ -7,7 +7,6 @@ checked through size-independent properties instead of the element-by-element CP
 * interaction at B = 32768: against a bmm evaluation of the same bf16 inputs within the bf16 bound, and
   the pass-through / padding columns exactly.
 """
-import numpy as np
 import pytest
 import torch
 
