@@ -612,15 +612,24 @@ __global__ void __launch_bounds__(UPD_THREADS) window_join_kernel(const UpdParam
   constexpr int PB = (NV * VE >= 32) ? 2 : (NV * VE >= 16 ? 4 : (NV * VE >= 8 ? 8 : 16));  // partial rows in flight
   const int gid = threadIdx.x / G, lane = threadIdx.x % G;
   const int64_t k = (int64_t)blockIdx.x * NG + gid + 1;  // border between positions k*BC-1 and k*BC
-  if (k * BC >= p.n) return;
-  if (p.skeys[k * BC - 1] != p.skeys[k * BC]) return;  // nothing crosses this border
-  const int64_t u = p.win_run[k * NG];
-  const int64_t s = p.seg[u], e = p.seg[u + 1];
-  if (s / BC + 1 != k) return;  // an earlier border owns this run
-  const int64_t w0 = s / BC, w1 = (e - 1) / BC;
-  // everything above reads the sort/dedup outputs only; the partial rows (and the weight rows) need the
-  // window kernel to have finished (no-op when launched without the programmatic-serialization attribute)
+  // Does a run cross this border, and is this the FIRST border it crosses (the one that owns it)?
+  // These checks read the sort/dedup outputs only, so they run before the window kernel has finished.
+  bool mine = k * BC < p.n && p.skeys[k * BC - 1] == p.skeys[k * BC];
+  int64_t u = 0, s = 0, e = 0;
+  if (mine) {
+    u = p.win_run[k * NG];
+    s = p.seg[u];
+    e = p.seg[u + 1];
+    mine = s / BC + 1 == k;  // otherwise an earlier border owns this run
+  }
+  // EVERY thread waits for the window kernel, including those with nothing to join: a dependent grid
+  // launched with programmatic serialization is ordered behind its primary only through this instruction,
+  // and the next kernel on the stream is ordered behind THIS grid -- if a group left without waiting, a
+  // step with no border-crossing run would let that next kernel start while weight rows are still being
+  // written.  (No-op when launched without the attribute.)
   asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (!mine) return;
+  const int64_t w0 = s / BC, w1 = (e - 1) / BC;
   const float lr = p.d_lr ? *p.d_lr : p.lr;
   char* wp;
   float* sp = nullptr;

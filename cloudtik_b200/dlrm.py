@@ -174,13 +174,14 @@ def _p2p_forward(self, dense_x, *emb_args):
     if (self.rowwise is not None) != (rw_i is not None):
         raise RuntimeError("row-wise sharded tables need (indices, offsets, None, rw_indices, rw_offsets)")
     feat0 = 1 + self.local_ln_emb_slice.start
-    if self.training and torch.is_grad_enabled():
+    train = self.training and torch.is_grad_enabled()
+    if train:
         prelaunch(self.emb_l, self.peer_exchange, indices, offsets, feat0)  # NVLink exchange || bottom MLP
     with torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.bf16):
         x = self.apply_mlp(self._pad_dense(dense_x), self.bot_l)
-        z = sharded_emb_interact(x, self.emb_l, self.peer_exchange, indices, offsets,
-                                 1 + self.local_ln_emb_slice.start, pad_to=self.interaction_pad,
-                                 rowwise=self.rowwise, rw_indices=rw_i, rw_offsets=rw_o)
+        z = sharded_emb_interact(x, self.emb_l, self.peer_exchange, indices, offsets, feat0,
+                                 pad_to=self.interaction_pad, rowwise=self.rowwise, rw_indices=rw_i,
+                                 rw_offsets=rw_o, train=train)
         p = self.apply_mlp(z, self.top_l)
     return self._clamp(p)
 

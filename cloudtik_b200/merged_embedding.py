@@ -172,6 +172,26 @@ class MergedEmbeddingBagWithSGD(nn.Module):
         self.join()
         return super().state_dict(*args, **kwargs)
 
+    def optimizer_state_dict(self):
+        """What the fused update keeps OUTSIDE the weights: Adagrad ``state_sum`` tables and the low-half trails of
+        bf16 tables.  A checkpoint that drops them silently resets the accumulators / truncates the master weights."""
+        self.join()
+        return {"schema": 1, "optimizer": self.optimizer_kind, "lr": self.sgd_args.lr, "eps": self.eps,
+                "states": None if self.tables.states is None else [s.clone() for s in self.tables.states],
+                "trails": None if self.tables.trails is None else [t.clone() for t in self.tables.trails]}
+
+    def load_optimizer_state_dict(self, sd):
+        if sd.get("schema") != 1 or sd.get("optimizer") != self.optimizer_kind:
+            raise RuntimeError("embedding optimizer state: wrong schema / optimizer kind")
+        self.join()
+        for name, cur in (("states", self.tables.states), ("trails", self.tables.trails)):
+            saved = sd.get(name)
+            if (saved is None) != (cur is None):
+                raise RuntimeError(f"embedding optimizer state: {name} present on one side only")
+            if saved is not None:
+                for d, s_ in zip(cur, saved):
+                    d.copy_(s_.to(d.device))
+
     def join(self):
         """Order the current stream after the last fused update issued on the side stream (no-op otherwise)."""
         ev = self._apply_event
@@ -275,7 +295,14 @@ class MergedEmbeddingBagWithSGD(nn.Module):
     def _workspace(self, nnz: int) -> torch.Tensor:
         need = ops.emb_bwd_workspace_bytes(nnz, self.dim)
         if self._ws is None or self._ws.numel() < need:
-            self._ws = torch.empty(need, dtype=torch.uint8, device=self._raw_weights()[0].device)
+            old = self._ws
+            if old is not None and self._side_stream is not None:
+                # a fused update of the previous step may still be reading the old block on the side stream: tell
+                # the caching allocator, so that the block is not handed out again before that work has finished
+                old.record_stream(self._side_stream)
+            # grow geometrically (ragged bags: nnz changes from step to step)
+            self._ws = torch.empty(max(need, 0 if old is None else old.numel() * 3 // 2), dtype=torch.uint8,
+                                   device=self._raw_weights()[0].device)
         return self._ws
 
     @contextlib.contextmanager

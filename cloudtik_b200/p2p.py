@@ -54,7 +54,7 @@ class _ShardedEmbInteractFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, trigger, emb, exch, indices, offsets, feat0, pad_to, rowwise=None, rw_indices=None,
-                rw_offsets=None):
+                rw_offsets=None, train=True):
         B_glob = exch.lN * exch.world
         if emb is not None:
             pend, emb._pending_sharded = emb._pending_sharded, None
@@ -65,7 +65,8 @@ class _ShardedEmbInteractFn(torch.autograd.Function):
                 with emb._timed("emb_fwd"):
                     ops.emb_fwd_sharded(emb.tables, indices, offsets, B_glob, exch.T_ptrs_dev, exch.lN, exch.F,
                                         feat0, exch.dtype, emb.error_flag)
-                emb._launch_prepare(indices, offsets, B_glob)  # sort / dedup on the side stream
+                if train:  # sort / dedup on the side stream: only a backward consumes it
+                    emb._launch_prepare(indices, offsets, B_glob)
         ctx.rw_ctx = None
         if rowwise is not None:  # row-wise sharded hot tables occupy the LAST feature slots
             rw_out, ctx.rw_ctx = rowwise.pool(rw_indices, rw_offsets, exch.lN)
@@ -73,6 +74,11 @@ class _ShardedEmbInteractFn(torch.autograd.Function):
         exch.T[:, 0].copy_(x)
         exch.barrier(0)  # B1
         R = ops.interact_fwd(exch.T, pad_to=pad_to)
+        if not train:
+            # forward-only (eval / no_grad): there is no backward and hence no B2 -- without a second barrier a
+            # faster rank could start the NEXT forward and store into this rank's T while interact_fwd above is
+            # still reading it
+            exch.barrier(1)
         ctx.emb, ctx.exch, ctx.feat0, ctx.rowwise = emb, exch, feat0, rowwise
         ctx.save_for_backward(indices, offsets)
         ctx.x_dtype = x.dtype
@@ -90,7 +96,7 @@ class _ShardedEmbInteractFn(torch.autograd.Function):
         if ctx.rowwise is not None:
             ctx.rowwise.update(exch.dT[:, exch.F - ctx.rowwise.k:], ctx.rw_ctx)
         dx = exch.dT[:, 0].clone()  # dT is overwritten by the next step; the bottom MLP backward runs now
-        return (dx.to(ctx.x_dtype),) + (None,) * 10
+        return (dx.to(ctx.x_dtype),) + (None,) * 11
 
 
 def prelaunch(emb, exch: PeerExchange, indices, offsets, feat0: int):
@@ -101,7 +107,11 @@ def prelaunch(emb, exch: PeerExchange, indices, offsets, feat0: int):
 
 
 def sharded_emb_interact(x, emb, exch: PeerExchange, indices, offsets, feat0: int, pad_to: int = 1, rowwise=None,
-                         rw_indices=None, rw_offsets=None, trigger=None):
+                         rw_indices=None, rw_offsets=None, trigger=None, train=None):
+    """``train`` (default: grad mode is on): False = forward only -- no index stage is launched for a backward that
+    will not come, and a second barrier replaces the one the backward would have issued."""
     trig = trigger if trigger is not None else (emb._trigger if emb is not None else rowwise.emb._trigger)
+    if train is None:
+        train = torch.is_grad_enabled()
     return _ShardedEmbInteractFn.apply(x, trig, emb, exch, indices, offsets, feat0, pad_to, rowwise, rw_indices,
-                                       rw_offsets)
+                                       rw_offsets, bool(train))

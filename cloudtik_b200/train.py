@@ -80,6 +80,11 @@ def random_batch(rs, B, ln_emb_local, m_den, P, fixed, round_targets, dev):
     return X, T, idx_l, off_l
 
 
+def _ckpt_path(path, rank, world):
+    """Rank 0 (and a single-process run) uses the given name, the other ranks append ``.rank<r>``."""
+    return path if world == 1 or rank == 0 else "{}.rank{}".format(path, rank)
+
+
 def run(argv=None):
     args = parse(argv)
     if args.data_generation != "random":
@@ -118,9 +123,14 @@ def run(argv=None):
                                      args.lr_num_decay_steps)
     start_iter = 0
     if args.load_model:
-        ld = torch.load(args.load_model, map_location=dev)
+        # every rank reads its own shard (tables are table-wise sharded; the MLPs are replicated in each shard)
+        ld = torch.load(_ckpt_path(args.load_model, rank, world), map_location=dev)
         dlrm.load_state_dict(ld["state_dict"])
         optimizer.load_state_dict(ld["opt_state_dict"])
+        if ld.get("emb_opt_state") is not None:
+            dlrm.emb_l.load_optimizer_state_dict(ld["emb_opt_state"])
+        if ld.get("lr_sched_state") is not None:
+            lr_scheduler.load_state_dict(ld["lr_sched_state"])
         start_iter = ld.get("iter", 0)
         if rank == 0:
             print("Loaded model {} (iter {})".format(args.load_model, start_iter))
@@ -170,11 +180,17 @@ def run(argv=None):
         start_iter = 0
     if rank == 0 and perf_iters > 0:
         print("Throughput: {:.3f} fps".format(perf_iters * B / perf_time))
-    if args.save_model and rank == 0:
+    if args.save_model:
         # checkpoint schema of T/dlrm_s_pytorch.py:1408-1423 (state_dict keys emb_l.{k}.weight, bot_l..., top_l...)
+        # plus what the fused update keeps outside the weights (Adagrad sums, bf16 trails) and the LR policy state.
+        # One file per rank when the tables are sharded: "local_tables" names the global ids behind emb_l.0..k.
         torch.save({"epoch": args.nepochs, "iter": nbatches, "nepochs": args.nepochs, "nbatches": nbatches,
-                    "state_dict": dlrm.state_dict(), "opt_state_dict": optimizer.state_dict()}, args.save_model)
-        print("Saving model to {}".format(args.save_model))
+                    "state_dict": dlrm.state_dict(), "opt_state_dict": optimizer.state_dict(),
+                    "emb_opt_state": dlrm.emb_l.optimizer_state_dict(),
+                    "lr_sched_state": lr_scheduler.state_dict(), "world": world, "rank": rank,
+                    "local_tables": [int(t) for t in local]}, _ckpt_path(args.save_model, rank, world))
+        if rank == 0:
+            print("Saving model to {}".format(args.save_model))
     if world > 1:
         ext_dist.barrier()
         torch.distributed.destroy_process_group()

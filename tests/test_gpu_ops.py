@@ -257,6 +257,29 @@ def test_emb_bwd_hot_window_boundaries():
     np.testing.assert_array_equal(W.cpu().numpy(), want)
 
 
+def test_emb_bwd_reader_right_behind_update_with_all_distinct_rows():
+    """No run crosses any block border here (every key is distinct), so no group of the join grid has rows to
+    add -- the join grid must still order itself behind the window kernel (programmatic dependent launch), or the
+    next kernel on the stream (here: a copy of the table) could read rows that are still being written."""
+    ops = _ops()
+    D, n = 128, 1 << 20
+    rs = np.random.RandomState(5)
+    idx = rs.permutation(n).astype(np.int64)
+    off = np.arange(n + 1, dtype=np.int64)
+    ti, to = torch.tensor(idx).cuda(), torch.tensor(off).cuda()
+    g = torch.ones(n, D, device="cuda")
+    ws = torch.empty(ops.emb_bwd_workspace_bytes(n, D), dtype=torch.uint8, device="cuda")
+    for rep in range(3):
+        W = torch.zeros(n, D, device="cuda")
+        ts = ops.TableSet([W])
+        ops.emb_bwd_prepare(ts, ti, to, n, ws)
+        torch.cuda.synchronize()
+        ops.emb_bwd_apply(ts, n, n, g, n * D, D, 1.0, ws)
+        snap = W.clone()  # launched right behind the update on the same stream
+        torch.cuda.synchronize()
+        assert bool((snap == -1.0).all()), f"rep {rep}: {int((snap != -1.0).sum())} stale elements"
+
+
 @pytest.mark.parametrize("opt", ["sgd", "adagrad"])
 def test_bf16_tables_with_trail_update_in_fp32(opt):
     """bf16 tables + 16-bit trail (the reference's split-SGD storage): the fused update must behave like
