@@ -47,7 +47,14 @@ def parse():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
-    ap.add_argument("--batch", type=int, default=32768, help="samples per GPU")
+    ap.add_argument("--batch", type=int, default=32768, help="samples per GPU (weak scaling: fixed as N grows)")
+    ap.add_argument("--global-batch", type=int, default=0,
+                    help="strong scaling: fixed GLOBAL batch split over the GPUs (BASELINE configs[3]: 65536); "
+                         "overrides --batch and reports \"scaling\": \"strong\"")
+    ap.add_argument("--chunks", type=int, default=0,
+                    help="multi-GPU peer-memory path: micro-batches per step (0 = 1 on one GPU, 2 on several); one "
+                         "chunk's NVLink exchange runs under another chunk's compute")
+    ap.add_argument("--no-parity", action="store_true", help="multi-GPU: skip the pre-flight parity check")
     ap.add_argument("--rows-cap", type=int, default=0, help="debug: cap table rows (0 = full config 3)")
     ap.add_argument("--sets", type=int, default=4, help="distinct synthetic batches rotated")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -59,6 +66,8 @@ def parse():
     ap.add_argument("--pooling", type=int, default=20, help="c5: indices per bag")
     ap.add_argument("--no-microbench", action="store_true",
                     help="skip the BASELINE configs[1] EmbeddingBag micro-benchmark appended to the N=1 line")
+    ap.add_argument("--timeline", default="", help="after the timed legs: profile 3 more steps with torch.profiler and "
+                    "write every rank's kernel list (name, stream, start, duration) to <path>.rank<r>.json")
     ap.add_argument("--cpu-rows-cap", type=int, default=200000)
     ap.add_argument("--cpu-steps", type=int, default=24, help="timed steps of the cpu_baseline leg (~10 s of CPU work)")
     return ap.parse_args()
@@ -97,17 +106,48 @@ def cpu_reference_run(batch, rows_cap, steps, warmup, bf16, threads=None):
             "ms_per_step": dt * 1e3}
 
 
+def host_threads():
+    """Every host core this process may use.  torch.distributed.run exports OMP_NUM_THREADS=1 to its workers: the CPU
+    arm must not inherit that (the reference's own launcher gives a rank all cores of its socket,
+    QS/scripts/recommendation/pytorch/dlrm/training/cpu/distribute_training.sh:73-105)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
+def batch_sizes(a, world):
+    """(samples per GPU, global batch, scaling) for this run."""
+    if a.global_batch:
+        if a.global_batch % world:
+            sys.exit("--global-batch must be a multiple of the number of GPUs")
+        return a.global_batch // world, a.global_batch, "strong"
+    return a.batch, a.batch * world, "weak"
+
+
 def run_reference_arm(a):
+    """The reference's CPU implementation of the step (pinned port, oracle/dlrm_port.py) on ALL host threads, on
+    the SAME global batch the B200 arm processes per step at this N (one process: the CPU arm has no ranks).  The
+    96 GB of tables do not fit the host, so the rows are capped (same architecture, same batch, `same_config`
+    false for that reason only; a smaller table is cache-friendlier, i.e. the cap favours the CPU)."""
     rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
         return
-    steps, warm = max(1, min(a.steps, 30)), max(1, min(a.warmup, 3))  # ~0.4 s per step on 16 host threads
-    r = cpu_reference_run(a.batch, a.cpu_rows_cap, steps, warm, a.dtype == "bf16")
+    _, B_glob, scaling = batch_sizes(a, max(world, a.gpus, 1))
+    # ~11 us per sample on 16 threads: bound the whole run to about a minute
+    est = B_glob * 11e-6
+    steps = max(1, min(a.steps, 30, int(60.0 / est)))
+    warm = max(1, min(max(a.warmup, 3), 3, int(15.0 / est)))
+    r = cpu_reference_run(B_glob, a.cpu_rows_cap, steps, warm, a.dtype == "bf16", threads=host_threads())
     line = {"impl": "reference", "metric": "dlrm_train_samples_per_sec", "value": r["value"], "unit": "samples/s",
             "n_gpus": a.gpus, "steps": steps, "warmup": warm, "ms_per_step": r["ms_per_step"],
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": a.dtype, "data": "synthetic",
-            "config": {"workload": "dlrm_criteo_terabyte_c3", "batch_per_gpu": a.batch, "dim": D,
-                       "tables": len(C3_ROWS), "cpu_table_rows_cap": a.cpu_rows_cap},
+            "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": a.dtype, "data": "synthetic",
+            "config": {"workload": "dlrm_criteo_terabyte_c3", "global_batch": B_glob, "dim": D,
+                       "tables": len(C3_ROWS), "cpu_table_rows_cap": a.cpu_rows_cap, "same_config": False,
+                       "same_config_note": f"same architecture and global batch; table rows capped at "
+                                           f"{a.cpu_rows_cap} (96 GB of tables do not fit host memory)",
+                       "host_threads": r["cores"], "processes": 1},
             "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": r["value"], "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -173,21 +213,27 @@ def ncu_traffic(kernel):
         return None
 
 
-def make_batches(a, rows_local, B_loc, B_glob, dev, rank):
+def make_batches(a, rows_local, B_loc, B_glob, dev, rank, n_chunks=1):
     """Synthetic Criteo-shaped inputs: dense U[0,1), targets round(U), one index per
     (sample, table) uniform over the table's rows.  Generated on the host with numpy, kept both in
-    pinned host memory (e2e leg) and on the device (HBM-resident leg)."""
+    pinned host memory (e2e leg) and on the device (HBM-resident leg).
+    A batch is the flat tuple (X, Y, indices_0, offsets_0[, indices_1, offsets_1, ...]): one pair of linearised
+    bags per micro-batch, micro-batch c = the c-th slice of every rank's samples (dlrm.train_step_chunked)."""
     rs = np.random.RandomState(727 + 1000 * rank)
     T = len(rows_local)
     sets = []
+    Bc = B_glob // n_chunks
     for _ in range(a.sets):
         X = rs.rand(B_loc, 13).astype(np.float32)
         Y = np.round(rs.rand(B_loc, 1)).astype(np.float32)
         idx = np.empty((T, B_glob), dtype=np.int64)
         for t, n in enumerate(rows_local):
             idx[t] = np.floor(rs.rand(B_glob) * n).astype(np.int64)
-        off = np.arange(T * B_glob + 1, dtype=np.int64)
-        host = [torch.from_numpy(v).pin_memory() for v in (X, Y, idx.reshape(-1), off)]
+        flat = [X, Y]
+        for c in range(n_chunks):
+            flat.append(np.ascontiguousarray(idx[:, c * Bc:(c + 1) * Bc]).reshape(-1))
+            flat.append(np.arange(T * Bc + 1, dtype=np.int64))
+        host = [torch.from_numpy(v).pin_memory() for v in flat]
         # the same batch as RAW Criteo records (int32 label, 13 counts, T ids: the CriteoBinDataset format);
         # the counts are chosen so that log(count + 1) reproduces a dense feature of the same range
         host_rec = None
@@ -232,6 +278,125 @@ def embeddingbag_microbench(net, gs):
                        "runs on a side stream under the dense forward/backward)", "results": out}
 
 
+def parity_preflight(world, rank, dev, use_p2p, n_chunks, use_graph, steps=3):
+    """Multi-GPU parity, checked in the same process right before the timed run: a small-table model of the bench's
+    architecture takes `steps` training steps through EXACTLY the sharded path the bench times (table-wise shards,
+    peer-memory exchange or NCCL all-to-all, micro-batches, CUDA graph, flat MLP all-reduce, lr / world on the
+    tables), and every rank also runs the single-process model (DLRM_Net(distributed=False), the path the one-GPU
+    tests pin to the oracle) on the GLOBAL batch with the same initial weights.  The single-process global-batch run
+    is the multi-GPU oracle of the reference (T/dlrm_s_pytorch.py:483-522, lr/world at
+    :1020-1031).  Compared: the mean-of-ranks loss of every step and, after the last step, the rows of the tables
+    this rank owns and the MLP weights (largest deviation relative to the largest reference magnitude)."""
+    from cloudtik_b200 import ext_dist
+    from cloudtik_b200.dlrm import DLRM_Net, enable_peer_exchange, train_step_chunked
+    from cloudtik_b200.graph import GraphedTrainStep
+    rows = [min(r, 3000) for r in C3_ROWS]
+    T = len(rows)
+    lB = 1024
+    Bg = lB * world
+    lr = 0.5
+    out = {"steps": steps, "tables": T, "rows_cap": 3000, "global_batch": Bg, "micro_batches": n_chunks,
+           "exchange": "peer-memory" if use_p2p else "nccl all-to-all", "graph": bool(use_graph),
+           "oracle": "single-process cloudtik_b200 run on the global batch (every rank)"}
+    ok_all = True
+    for tag, bf16, tol in (("fp32", False, 1e-5), ("bf16", True, 1e-2)):
+        g = torch.Generator(device="cpu").manual_seed(4242)
+        W0 = [(torch.rand(n, D, generator=g) * 2 - 1) * (1.0 / n) ** 0.5 for n in rows]
+        np.random.seed(99)
+        ref = DLRM_Net(D, np.array(rows), np.array(LN_BOT), np.array(LN_TOP), sigmoid_top=len(LN_TOP) - 2,
+                       device=dev, lr=lr, bf16=bf16, distributed=False)
+        np.random.seed(99)
+        net = DLRM_Net(D, np.array(rows), np.array(LN_BOT), np.array(LN_TOP), sigmoid_top=len(LN_TOP) - 2,
+                       device=dev, lr=lr / world, bf16=bf16)
+        with torch.no_grad():  # same MLPs by the same numpy stream; tables from the common draw
+            for k, w in enumerate(ref.emb_l.weights):
+                w.copy_(W0[k])
+            for k, t in enumerate(net.local_ln_emb):
+                net.emb_l.weights[k].copy_(W0[t])
+        if use_p2p:
+            enable_peer_exchange(net, lB, n_chunks)
+        nc = n_chunks if use_p2p else 1
+        dense_r = [p for p in ref.parameters() if p.requires_grad]
+        dense_n = [p for p in net.parameters() if p.requires_grad]
+        opt_r, opt_n = torch.optim.SGD(dense_r, lr=lr), torch.optim.SGD(dense_n, lr=lr)
+        sync = ext_dist.DenseGradAllreduce(dense_n)
+        rs = np.random.RandomState(5)
+        batches = []
+        for _ in range(steps):
+            X = rs.rand(Bg, 13).astype(np.float32)
+            Y = np.round(rs.rand(Bg, 1)).astype(np.float32)
+            idx = np.stack([np.floor(rs.rand(Bg) * n).astype(np.int64) for n in rows])  # [T, Bg]
+            batches.append((X, Y, idx))
+
+        def shard(X, Y, idx):
+            """This rank's view: its samples, and its tables' ids for every rank's samples, micro-batch by micro-batch."""
+            mine = [torch.from_numpy(X[rank * lB:(rank + 1) * lB]).to(dev), torch.from_numpy(Y[rank * lB:(rank + 1) * lB]).to(dev)]
+            loc = idx[net.local_ln_emb]                       # [T_loc, Bg], sample b belongs to rank b // lB
+            per = lB // nc
+            v = loc.reshape(len(loc), world, nc, per)
+            for c in range(nc):
+                mine.append(torch.from_numpy(np.ascontiguousarray(v[:, :, c]).reshape(-1)).to(dev))
+                mine.append(torch.arange(len(loc) * world * per + 1, dtype=torch.int64, device=dev))
+            return mine
+
+        gs = GraphedTrainStep(net, opt_n, shard(*batches[0]), post_backward=sync) if use_graph else None
+        if gs is not None:  # the capture's warm-up steps trained on batch 0: start again from the common weights
+            with torch.no_grad():
+                for k, t in enumerate(net.local_ln_emb):
+                    net.emb_l.weights[k].copy_(W0[t])
+                for pn, pr in zip(dense_n, dense_r):
+                    pn.copy_(pr)
+        worst_loss = 0.0
+        for X, Y, idx in batches:
+            b = shard(X, Y, idx)
+            E = gs.step(*b) if gs is not None else train_step_chunked(net, opt_n, b, sync)
+            E = E.clone()
+            torch.distributed.all_reduce(E)
+            got = float(E.item()) / world
+            gb = [torch.from_numpy(X).to(dev), torch.from_numpy(Y).to(dev),
+                  torch.from_numpy(idx.reshape(-1)).to(dev), torch.arange(T * Bg + 1, dtype=torch.int64, device=dev)]
+            want = float(train_step_chunked(ref, opt_r, gb).item())
+            worst_loss = max(worst_loss, abs(got - want) / abs(want))
+        worst_rows = 0.0
+        for k, t in enumerate(net.local_ln_emb):
+            a_, b_ = net.emb_l.weights[k].float(), ref.emb_l.weights[t].float()
+            worst_rows = max(worst_rows, float((a_ - b_).abs().max() / b_.abs().max()))
+        worst_mlp = max(float((pn - pr).abs().max() / pr.abs().max()) for pn, pr in zip(dense_n, dense_r))
+        w = torch.tensor([worst_loss, worst_rows, worst_mlp], device=dev, dtype=torch.float64)
+        torch.distributed.all_reduce(w, op=torch.distributed.ReduceOp.MAX)
+        worst_loss, worst_rows, worst_mlp = (float(x) for x in w)
+        ok = worst_loss <= tol and worst_rows <= tol and worst_mlp <= tol
+        ok_all = ok_all and ok
+        out[tag] = {"max_rel_loss": worst_loss, "max_rel_rows": worst_rows, "max_rel_mlp": worst_mlp, "tol": tol,
+                    "ok": ok}
+        del net, ref, gs
+        torch.cuda.synchronize()
+        torch.distributed.barrier()
+    out["ok"] = ok_all
+    return out
+
+
+def write_timeline(path, rank, step_fn, barrier, steps=3):
+    """Kernel timeline of `steps` more steps of the timed loop on THIS rank (torch.profiler / CUPTI sees the kernels
+    of a replayed graph too).  One JSON per rank; tools/timeline_summary.py turns them into the per-rank table."""
+    from torch.profiler import ProfilerActivity, profile
+    barrier()
+    with profile(activities=[ProfilerActivity.CUDA]) as prof:
+        for i in range(steps):
+            step_fn(i)
+        torch.cuda.synchronize()
+    ev = []
+    for e in prof.events():
+        if e.device_type == torch.autograd.DeviceType.CUDA:
+            ev.append({"name": e.name, "ts_us": e.time_range.start, "dur_us": e.time_range.elapsed_us(),
+                       "stream": getattr(e, "device_resource_id", None)})
+    ev.sort(key=lambda x: x["ts_us"])
+    os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
+    with open(f"{path}.rank{rank}.json", "w") as f:
+        json.dump({"rank": rank, "steps": steps, "events": ev}, f)
+    barrier()
+
+
 def run_b200_arm(a):
     from cloudtik_b200 import ext_dist
     from cloudtik_b200.dlrm import DLRM_Net, enable_peer_exchange
@@ -245,7 +410,14 @@ def run_b200_arm(a):
         ext_dist.init_distributed(rank=rank, size=world, backend="nccl")
     bf16 = a.dtype == "bf16"
     rows = table_rows(a.rows_cap)
-    B_loc, B_glob = a.batch, a.batch * world
+    B_loc, B_glob, scaling = batch_sizes(a, world)
+    use_p2p = world > 1 and not a.no_p2p
+    n_chunks = a.chunks if a.chunks > 0 else (2 if use_p2p else 1)
+    if not use_p2p:
+        n_chunks = 1
+    parity = None
+    if world > 1 and not a.no_parity:
+        parity = parity_preflight(world, rank, dev, use_p2p, n_chunks, not a.no_graph)
 
     np.random.seed(727)
     torch.manual_seed(727 + rank)
@@ -254,9 +426,8 @@ def run_b200_arm(a):
                    np_init_emb_weight=False, device=dev, lr=LR / world, bf16=bf16)
     local_ids = list(range(len(rows))) if world == 1 else net.local_ln_emb
     rows_local = [rows[i] for i in local_ids]
-    use_p2p = world > 1 and not a.no_p2p
     if use_p2p:
-        enable_peer_exchange(net, B_loc)
+        enable_peer_exchange(net, B_loc, n_chunks)
     dense_params = [p for p in net.parameters() if p.requires_grad]
     opt = torch.optim.SGD(dense_params, lr=LR)
     if bf16:  # bf16 copies of the MLP parameters refreshed by one multi-tensor copy after opt.step()
@@ -265,18 +436,13 @@ def run_b200_arm(a):
     # MLPs are data-parallel: one flat all-reduce of their 2.4 M gradients per step (the fused bf16 MLP
     # path bypasses DDP.forward, so the averaging the reference gets from DDP is done explicitly)
     sync_dense = ext_dist.DenseGradAllreduce(dense_params) if world > 1 else (lambda: None)
-    sets = make_batches(a, rows_local, B_loc, B_glob, dev, rank)
+    sets = make_batches(a, rows_local, B_loc, B_glob, dev, rank, n_chunks)
     emb = net.emb_l
+    from cloudtik_b200.dlrm import train_step_chunked
+    post = sync_dense if world > 1 else None
 
     def step_dev(i):
-        X, Y, idx, off = sets[i % len(sets)]["dev"]
-        Z = net(X, idx, off, None).float()
-        E = net.loss_fn(Z, Y)
-        opt.zero_grad(set_to_none=True)
-        E.backward()
-        sync_dense()
-        opt.step()
-        return E.detach()
+        return train_step_chunked(net, opt, sets[i % len(sets)]["dev"], post)
 
     stage = [torch.empty_like(t) for t in sets[0]["dev"]]
 
@@ -284,14 +450,8 @@ def run_b200_arm(a):
         host = sets[i % len(sets)]["host"]
         for d, h in zip(stage, host):
             d.copy_(h, non_blocking=True)
-        X, Y, idx, off = stage
-        Z = net(X, idx, off, None).float()
-        E = net.loss_fn(Z, Y)
-        opt.zero_grad(set_to_none=True)
-        E.backward()
-        sync_dense()
-        opt.step()
-        return float(E.detach().cpu())  # D2H read of the step's loss (reference: P/dlrm_s_pytorch.py:1048)
+        E = train_step_chunked(net, opt, stage, post)
+        return float(E.cpu())  # D2H read of the step's loss (reference: P/dlrm_s_pytorch.py:1048)
 
     def barrier():
         if world > 1:
@@ -327,7 +487,7 @@ def run_b200_arm(a):
     step_fn, e2e_fn = step_dev, step_e2e
     if use_graph:
         from cloudtik_b200.graph import GraphedTrainStep
-        gs = GraphedTrainStep(net, opt, sets[0]["dev"], post_backward=sync_dense if world > 1 else None)
+        gs = GraphedTrainStep(net, opt, sets[0]["dev"], post_backward=post)
 
         def step_fn(i):
             return gs.step(*sets[i % len(sets)]["dev"])
@@ -384,6 +544,8 @@ def run_b200_arm(a):
         ms_rec, _ = timed(rec_fn, a.steps)
 
     clk = clocks.stop() if clocks else None  # sampled every 20 ms across the three timed legs (all under load)
+    if a.timeline:
+        write_timeline(a.timeline, rank, step_fn, barrier)
     if rank != 0:
         return
     ms_step = ms_total / a.steps
@@ -396,13 +558,13 @@ def run_b200_arm(a):
     T_loc = len(rows_local)
     nnz = T_loc * B_glob
     U = statistics.mean(sum(s["uniq"]) for s in sets)
-    common = nnz * 8 + (T_loc * B_glob + 1) * 8
+    common = nnz * 8 + (T_loc * B_glob + n_chunks) * 8
     alg = {"emb_fwd": U * D * ew + common + T_loc * B_glob * D * ea,
            "emb_bwd_apply": T_loc * B_glob * D * ea + common + 2 * U * D * ew}
     kt = {}
     for k, evs in prof.items():
-        if k in alg and evs:
-            kt[k] = statistics.mean(x.elapsed_time(y) for x, y in evs)
+        if k in alg and evs:  # n_chunks launches per step: their sum is the per-step kernel time
+            kt[k] = statistics.mean(x.elapsed_time(y) for x, y in evs) * n_chunks
     peak, pk = peak_hbm()
     roof = None
     if kt:
@@ -431,8 +593,9 @@ def run_b200_arm(a):
     launches = 1 + 1 + 3 * ((bits + 7) // 8) + 3 + 2 + 2 + (2 * n_relu if bf16 else 0)
     line = {"metric": "dlrm_train_samples_per_sec", "value": round(value, 1), "unit": "samples/s", "n_gpus": world,
             "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": round(ms_step, 4), "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": a.dtype, "data": "synthetic",
+            "scaling": scaling, "vs_baseline": None, "dtype": a.dtype, "data": "synthetic",
             "config": {"workload": "dlrm_criteo_terabyte_c3", "batch_per_gpu": B_loc, "global_batch": B_glob,
+                       "micro_batches_per_step": n_chunks,
                        "dim": D, "tables": len(rows), "total_rows": int(sum(rows)), "pooling": 1,
                        "table_dtype": "fp32", "mlp": "bot 13-512-256-128 / top 479-1024-1024-512-256-1",
                        "optimizer": "SGD lr 1.0 (fused sparse update + torch SGD on MLPs)",
@@ -450,10 +613,12 @@ def run_b200_arm(a):
                 "input": "raw int32 Criteo records (CriteoBinDataset format) decoded on the device, one extra launch"},
             "gpu_launches": launches * a.steps, "gpu_launches_per_step": launches,
             "roofline": roof, "clocks": clk, "final_loss": loss_val}
+    if parity is not None:
+        line["parity"] = parity
     if world == 1 and not a.no_microbench:
         line["embeddingbag_microbench"] = embeddingbag_microbench(net, gs if use_graph else None)
     if world == 1 and not a.no_cpu_baseline:
-        r = cpu_reference_run(a.batch, a.cpu_rows_cap, a.cpu_steps, 1, bf16)
+        r = cpu_reference_run(a.batch, a.cpu_rows_cap, a.cpu_steps, 3, bf16, threads=host_threads())
         line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
     else:
         line["cpu_baseline"] = None

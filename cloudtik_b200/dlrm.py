@@ -56,20 +56,24 @@ class DLRM_Net(nn.Module):
 
     def __init__(self, m_spa=None, ln_emb=None, ln_bot=None, ln_top=None, sigmoid_bot=-1, sigmoid_top=-1,
                  weighted_pooling=None, loss_threshold=0.0, np_init_emb_weight=False, device="cuda",
-                 lr=0.01, emb_optimizer="sgd", bf16=False, n_rowwise=0):
+                 lr=0.01, emb_optimizer="sgd", bf16=False, n_rowwise=0, distributed=None):
+        """``distributed=False`` builds the single-process model (all tables local) even inside an initialised
+        process group -- the oracle of the multi-GPU parity checks runs that way next to the sharded model."""
         super().__init__()
+        self.world = ext_dist.my_size if (distributed is None or distributed) and ext_dist.my_size > 1 else 1
         if weighted_pooling is not None:
             raise NotImplementedError("weighted pooling is not on the reference's product path")
         self.loss_threshold = loss_threshold
         self.bf16 = bf16
         self.fused_mlp = True
         self.peer_exchange = None  # set by enable_peer_exchange(): fused a2a over NVLink peer memory
+        self.peer_exchanges = None  # one per micro-batch of a step (peer_exchange is the first)
         ln_emb = np.asarray(ln_emb)
         # the LAST n_rowwise tables are row-wise sharded over the ranks (hot tables, config 5); the others
         # are partitioned table-wise exactly like the reference (P/dlrm_s_pytorch.py:256-264)
-        self.n_rowwise = int(n_rowwise) if ext_dist.my_size > 1 else 0
+        self.n_rowwise = int(n_rowwise) if self.world > 1 else 0
         self.rowwise = None
-        if ext_dist.my_size > 1:
+        if self.world > 1:
             n_emb = len(ln_emb) - self.n_rowwise
             self.n_global_emb = len(ln_emb)
             self.rank = ext_dist.dist.get_rank()
@@ -94,7 +98,7 @@ class DLRM_Net(nn.Module):
                                                 out_dtype=torch.bfloat16 if bf16 else None)
         if bf16:
             self.emb_l.output_dtype = torch.bfloat16
-        if ext_dist.my_size > 1:
+        if self.world > 1:
             self.emb_l.reserve_dense_slot = False  # pooled rows go straight into the a2a send layout
         self.need_linearize_indices_and_offsets = torch.BoolTensor([False])
         self.loss_fn = torch.nn.BCELoss(reduction="mean")
@@ -120,10 +124,25 @@ class DLRM_Net(nn.Module):
     def interact_features(self, x, ly):
         return interaction(x, *ly, pad_to=self.interaction_pad)
 
-    def forward(self, dense_x, *emb_args):
-        if ext_dist.my_size > 1:
-            return self.distributed_forward(dense_x, *emb_args)
+    def forward(self, dense_x, *emb_args, chunk=0):
+        """``chunk``: which micro-batch of a step cut by ``enable_peer_exchange(..., n_chunks)`` this call is
+        (0 when the step is not cut)."""
+        if self.world > 1:
+            return self.distributed_forward(dense_x, *emb_args, chunk=chunk)
         return self.sequential_forward(dense_x, *emb_args)
+
+    def begin_step(self, chunk_args):
+        """Micro-batched peer-memory step: queue EVERY chunk's pooled forward + exchange (and index stage) on the
+        embedding's side stream before the first chunk's bottom MLP runs.  ``chunk_args``: one (indices, offsets)
+        pair of linearised GLOBAL-micro-batch bags per chunk.  No-op for other configurations."""
+        if self.peer_exchanges is None or not (self.training and torch.is_grad_enabled()):
+            return
+        if len(chunk_args) != len(self.peer_exchanges):
+            raise RuntimeError("begin_step: %d chunks given, the peer exchange was built for %d"
+                               % (len(chunk_args), len(self.peer_exchanges)))
+        from .p2p import prelaunch
+        prelaunch(self.emb_l, self.peer_exchanges, [a[0] for a in chunk_args], [a[1] for a in chunk_args],
+                  1 + self.local_ln_emb_slice.start)
 
     def _clamp(self, p):
         if 0.0 < self.loss_threshold < 1.0:
@@ -132,6 +151,8 @@ class DLRM_Net(nn.Module):
 
     def sequential_forward(self, dense_x, *emb_args):
         # P/dlrm_s_pytorch.py:372-397
+        if len(emb_args) == 3:  # linearised bags: the pooled lookup starts now, next to the bottom MLP
+            self.emb_l.prelaunch_forward(emb_args[0], emb_args[1])
         with torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.bf16):
             x = self.apply_mlp(self._pad_dense(dense_x), self.bot_l)
             ly = self.apply_emb(self.emb_l, *emb_args)
@@ -139,15 +160,14 @@ class DLRM_Net(nn.Module):
             p = self.apply_mlp(z, self.top_l)
         return self._clamp(p)
 
-    def distributed_forward(self, dense_x, *emb_args):
+    def distributed_forward(self, dense_x, *emb_args, chunk=0):
         # P/dlrm_s_pytorch.py:342-369: local tables on the GLOBAL batch -> all-to-all -> local batch
         batch_size = dense_x.size()[0]
-        vector_lenght = self.emb_l.dim
         if batch_size < ext_dist.my_size:
             sys.exit("ERROR: batch_size (%d) must be larger than number of ranks (%d)"
                      % (batch_size, ext_dist.my_size))
         if self.peer_exchange is not None:
-            return self._p2p_forward(dense_x, *emb_args)
+            return self._p2p_forward(dense_x, *emb_args, chunk=chunk)
         with torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.bf16):
             ly = self.apply_emb(self.emb_l, *emb_args)
             a2a_req = ext_dist.alltoall(ly, self.n_emb_per_rank)
@@ -160,9 +180,10 @@ class DLRM_Net(nn.Module):
         return self._clamp(p)
 
 
-def _p2p_forward(self, dense_x, *emb_args):
+def _p2p_forward(self, dense_x, *emb_args, chunk=0):
     """distributed_forward with the all-to-all fused into the embedding kernels (cloudtik_b200.p2p)."""
     from .p2p import prelaunch, sharded_emb_interact
+    exch = self.peer_exchanges[chunk]
     rw_i = rw_o = None
     if len(emb_args) >= 3:
         indices, offsets = emb_args[0], emb_args[1]
@@ -175,11 +196,11 @@ def _p2p_forward(self, dense_x, *emb_args):
         raise RuntimeError("row-wise sharded tables need (indices, offsets, None, rw_indices, rw_offsets)")
     feat0 = 1 + self.local_ln_emb_slice.start
     train = self.training and torch.is_grad_enabled()
-    if train:
-        prelaunch(self.emb_l, self.peer_exchange, indices, offsets, feat0)  # NVLink exchange || bottom MLP
+    if train and len(self.peer_exchanges) == 1:
+        prelaunch(self.emb_l, exch, indices, offsets, feat0)  # NVLink exchange || bottom MLP
     with torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.bf16):
         x = self.apply_mlp(self._pad_dense(dense_x), self.bot_l)
-        z = sharded_emb_interact(x, self.emb_l, self.peer_exchange, indices, offsets, feat0,
+        z = sharded_emb_interact(x, self.emb_l, exch, indices, offsets, feat0,
                                  pad_to=self.interaction_pad, rowwise=self.rowwise, rw_indices=rw_i,
                                  rw_offsets=rw_o, train=train)
         p = self.apply_mlp(z, self.top_l)
@@ -189,13 +210,21 @@ def _p2p_forward(self, dense_x, *emb_args):
 DLRM_Net._p2p_forward = _p2p_forward
 
 
-def enable_peer_exchange(dlrm, local_batch: int):
+def enable_peer_exchange(dlrm, local_batch: int, n_chunks: int = 1):
     """Switch a table-wise sharded DLRM_Net (one process per GPU on one NVLink box) to the fused
-    peer-memory exchange; ``local_batch`` = samples per rank (fixed: the buffers are symmetric)."""
+    peer-memory exchange; ``local_batch`` = samples per rank (fixed: the buffers are symmetric).
+    ``n_chunks`` > 1 cuts every step into that many micro-batches (``local_batch`` must divide), each with its own
+    exchange buffers, so that one chunk's NVLink traffic runs under another chunk's compute (cloudtik_b200.p2p)."""
     from .p2p import PeerExchange
+    if n_chunks < 1 or local_batch % n_chunks:
+        raise ValueError("enable_peer_exchange: the local batch must be a multiple of n_chunks")
+    if n_chunks > 1 and dlrm.rowwise is not None:
+        raise NotImplementedError("micro-batched steps with row-wise sharded tables")
     n_feat = 1 + dlrm.n_global_emb
     dt = torch.bfloat16 if dlrm.bf16 else dlrm.emb_l.tables.dtype
-    dlrm.peer_exchange = PeerExchange(local_batch, n_feat, dlrm.emb_l.dim, dt, dlrm.emb_l.tables.device)
+    dlrm.peer_exchanges = [PeerExchange(local_batch // n_chunks, n_feat, dlrm.emb_l.dim, dt,
+                                        dlrm.emb_l.tables.device, chunk=c) for c in range(n_chunks)]
+    dlrm.peer_exchange = dlrm.peer_exchanges[0]
     return dlrm.peer_exchange
 
 
@@ -210,3 +239,34 @@ def train_step(dlrm, optimizer, X, emb_args, T, lr=None):
     E.backward()
     optimizer.step()
     return E.detach()
+
+
+def train_step_chunked(dlrm, optimizer, batch, post_backward=None):
+    """One iteration on a batch given as the flat tuple ``(X, Y, indices_0, offsets_0[, indices_1, offsets_1, ...])``:
+    one (indices, offsets) pair of linearised bags per micro-batch (a single pair = the plain step above).  Chunk c
+    covers ``X[c*n:(c+1)*n]`` of this rank's samples and, in ``indices_c``, the same slice of EVERY rank's samples
+    (rank-major), i.e. the global micro-batch this rank's tables are looked up for.  MLP gradients accumulate over
+    the chunks; each chunk's loss is scaled by 1/n_chunks so that their sum is the batch mean the reference
+    back-propagates.  ``post_backward`` (the MLP-gradient all-reduce) runs once, before the optimizer step.
+    Returns the batch-mean loss tensor."""
+    X, Y = batch[0], batch[1]
+    pairs = [(batch[2 + 2 * c], batch[3 + 2 * c]) for c in range((len(batch) - 2) // 2)]
+    n = len(pairs)
+    optimizer.zero_grad(set_to_none=True)
+    if n > 1:
+        if dlrm.peer_exchanges is None or len(dlrm.peer_exchanges) != n:
+            raise RuntimeError("a micro-batched step needs enable_peer_exchange(dlrm, local_batch, n_chunks=%d)" % n)
+        dlrm.begin_step(pairs)
+    per = X.shape[0] // n
+    total = None
+    for c, (idx, off) in enumerate(pairs):
+        Xc, Yc = (X, Y) if n == 1 else (X[c * per:(c + 1) * per], Y[c * per:(c + 1) * per])
+        Z = dlrm(Xc, idx, off, None, chunk=c).float()
+        E = dlrm.loss_fn(Z, Yc)
+        (E if n == 1 else E / n).backward()
+        total = E.detach() if total is None else total + E.detach()
+    if post_backward is not None:
+        post_backward()
+    optimizer.step()
+    dlrm.emb_l.join()  # a side-stream update joins the step (and a graph capture) here
+    return total if n == 1 else total / n

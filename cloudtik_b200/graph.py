@@ -15,7 +15,8 @@ import torch
 
 class GraphedTrainStep:
     def __init__(self, net, optimizer, example, warmup: int = 3, post_backward=None):
-        """``example`` = (X, Y, indices, offsets) device tensors with the shapes of every later batch.
+        """``example`` = (X, Y, indices, offsets) device tensors with the shapes of every later batch -- or, for a
+        micro-batched step, (X, Y, indices_0, offsets_0, indices_1, offsets_1, ...), see ``dlrm.train_step_chunked``.
         ``post_backward``: optional callable run between backward and the optimizer step (the flat
         all-reduce of the MLP gradients in the multi-GPU case; NCCL collectives are captured too)."""
         self.net, self.opt = net, optimizer
@@ -28,7 +29,12 @@ class GraphedTrainStep:
             raise RuntimeError("disable MergedEmbeddingBagWithSGD.profile before capturing a graph")
         # warm up on a side stream (allocator pools, cuBLAS handles / workspaces, the embedding
         # workspace, the tensor-map entry point) -- nothing may allocate lazily during capture
-        s = torch.cuda.Stream()
+        # The step's main chain (MLPs, interaction) is captured on a HIGH-priority stream; the embedding's side
+        # stream (index stage, HBM- / NVLink-bound exchange and update kernels) has the default, lowest priority.
+        # Kernel nodes keep the priority of the stream they were captured on, so when both have thread blocks
+        # waiting the block scheduler places the main chain's first: the side work fills the SM slots the main
+        # chain leaves free instead of queueing thousands of blocks ahead of a small GEMM.
+        s = torch.cuda.Stream(priority=-1)
         s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):
             for _ in range(warmup):
@@ -37,21 +43,13 @@ class GraphedTrainStep:
         emb.join()  # no event from outside the capture may be waited on inside it
         torch.cuda.synchronize()
         self.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.graph):
+        with torch.cuda.graph(self.graph, stream=s):
             self.loss = self._eager()
         torch.cuda.synchronize()
 
     def _eager(self):
-        X, Y, idx, off = self.static
-        Z = self.net(X, idx, off, None).float()
-        E = self.net.loss_fn(Z, Y)
-        self.opt.zero_grad(set_to_none=True)
-        E.backward()
-        if self.post_backward is not None:
-            self.post_backward()
-        self.opt.step()
-        self.net.emb_l.join()  # a side-stream update (peer-memory path) joins the step, and the capture, here
-        return E.detach()
+        from .dlrm import train_step_chunked
+        return train_step_chunked(self.net, self.opt, self.static, self.post_backward)
 
     # ---- host-fed operation: pinned-host batches are staged by a copy stream one step ahead ----
     def prefetch(self, host_batch):
@@ -116,7 +114,7 @@ class GraphedTrainStep:
         from . import ops
         main = torch.cuda.current_stream()
         main.wait_event(self._rec_ready[k])
-        X, Y, idx, off = self.static
+        X, Y, idx, off = self.static[:4]
         ops.criteo_transform(self._rec_stage[k], max_ind_range, n_dense=X.shape[1], out=(X, Y, idx, off), **slices)
         ev = torch.cuda.Event()
         ev.record(main)
@@ -142,9 +140,10 @@ class GraphedTrainStep:
             return float(self._loss_host[k])
         return read
 
-    def step(self, X, Y, indices, offsets):
-        """Copy one batch into the static buffers and replay; returns the (device) loss tensor."""
-        for d, s in zip(self.static, (X, Y, indices, offsets)):
+    def step(self, *batch):
+        """Copy one batch (same tuple layout as ``example``) into the static buffers and replay; returns the
+        (device) loss tensor."""
+        for d, s in zip(self.static, batch):
             if d.data_ptr() != s.data_ptr():
                 d.copy_(s, non_blocking=True)
         self.graph.replay()

@@ -71,14 +71,20 @@ class _MergedEmbFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, trigger, module, indices, offsets, B):
         T, D = module.n_tables, module.dim
-        out_dtype = module.output_dtype or module.tables.dtype
         s0 = 1 if module.reserve_dense_slot else 0
-        buf = torch.empty(B, T + s0, D, dtype=out_dtype, device=indices.device)
-        if s0:
-            _register_pooled(buf)
-        with module._timed("emb_fwd"):
-            ops.emb_fwd(module.tables, indices, offsets, B, buf[:, s0:], D, (T + s0) * D, module.error_flag)
-        module._launch_prepare(indices, offsets, B)
+        pend, module._pending_fwd = module._pending_fwd, None
+        if pend is not None and pend[0] is indices and pend[1] is offsets:
+            buf = pend[2]  # pooled rows launched ahead on the side stream (prelaunch_forward)
+            torch.cuda.current_stream().wait_event(pend[3])
+            # that event is behind the previous step's update on the side stream: nothing left to join
+            module._apply_event = None
+            module._held_grad = None
+        else:
+            module.join()  # the previous step's update may still be running on the side stream
+            buf = module._alloc_pooled(B, indices.device)
+            with module._timed("emb_fwd"):
+                ops.emb_fwd(module.tables, indices, offsets, B, buf[:, s0:], D, (T + s0) * D, module.error_flag)
+            module._launch_prepare(indices, offsets, B)
         ctx.module, ctx.B = module, B
         ctx.save_for_backward(indices, offsets)
         ctx.set_materialize_grads(False)
@@ -137,8 +143,15 @@ class MergedEmbeddingBagWithSGD(nn.Module):
         # peer-memory (sharded) path: the NVLink-bound kernels run on the side stream next to the bottom MLP
         # (forward) and next to the bottom-MLP backward / gradient all-reduce / optimizer (update)
         self.overlap_sharded = True
-        self._pending_sharded = None  # (indices, offsets, event) of a sharded forward launched ahead
+        self._pending_sharded = {}    # chunk -> (indices, offsets, event) of a sharded forward launched ahead
         self._apply_event = None      # last fused update issued on the side stream
+        self._chunk_ws = {}           # chunk -> backward workspace (micro-batched peer-memory path)
+        # single-process path: the fused update runs on the side stream next to the bottom-MLP backward and the
+        # dense optimizer step (both only need the interaction backward, like the update); join() orders readers
+        self.overlap_update = True
+        self._pending_fwd = None      # (indices, offsets, pooled buffer, event) of a forward launched ahead
+        self._held_grad = None        # keeps the gradient buffer alive while the side stream reads it
+        self._chunk_prep = {}         # chunk -> event of that chunk's index stage on the side stream
         self._rebuild_tables()
         if optimizer == "adagrad":
             self.tables.set_states([torch.zeros_like(w, dtype=torch.float32) for w in self.weights])
@@ -198,6 +211,7 @@ class MergedEmbeddingBagWithSGD(nn.Module):
         if ev is not None:
             torch.cuda.current_stream().wait_event(ev)
             self._apply_event = None
+        self._held_grad = None
 
     def linearize_indices_and_offsets(self, indices: List[torch.Tensor], offsets: List[torch.Tensor],
                                       include_last_offsets: List[bool]):
@@ -271,11 +285,45 @@ class MergedEmbeddingBagWithSGD(nn.Module):
             return list(_MergedEmbFn.apply(self._trigger, self, indices, offsets, B))
         T, D = self.n_tables, self.dim
         s0 = 1 if self.reserve_dense_slot else 0
-        buf = torch.empty(B, T + s0, D, dtype=self.output_dtype or self.tables.dtype, device=indices.device)
-        if s0:
-            _register_pooled(buf)
+        self.join()
+        buf = self._alloc_pooled(B, indices.device)
         ops.emb_fwd(self.tables, indices, offsets, B, buf[:, s0:], D, (T + s0) * D, self.error_flag)
         return [buf[:, s0 + k] for k in range(T)]
+
+    def _alloc_pooled(self, B, device):
+        s0 = 1 if self.reserve_dense_slot else 0
+        buf = torch.empty(B, self.n_tables + s0, self.dim, dtype=self.output_dtype or self.tables.dtype, device=device)
+        if s0:
+            _register_pooled(buf)
+        return buf
+
+    def prelaunch_forward(self, indices, offsets):
+        """Queue the pooled forward (and the index stage of the backward) of already linearised bags on the side
+        stream NOW, so that they run next to whatever the caller does next on the current stream (the bottom MLP);
+        the following ``forward`` with the same (indices, offsets) tensors picks the result up.  Training mode only;
+        does nothing while per-kernel profiling is on."""
+        if not (self.overlap_prepare and self.overlap_update and self.profile is None
+                and torch.is_grad_enabled() and self.training):
+            return
+        B = (offsets.numel() - 1) // self.n_tables
+        T, D = self.n_tables, self.dim
+        s0 = 1 if self.reserve_dense_slot else 0
+        main = torch.cuda.current_stream()
+        if self._side_stream is None:
+            self._side_stream = torch.cuda.Stream(device=indices.device)
+        side = self._side_stream
+        buf = self._alloc_pooled(B, indices.device)
+        ws = self._workspace(indices.numel())
+        side.wait_stream(main)  # inputs ready; the previous step's update is already ahead of us on `side`
+        with torch.cuda.stream(side):
+            ops.emb_fwd(self.tables, indices, offsets, B, buf[:, s0:], D, (T + s0) * D, self.error_flag)
+            ev = torch.cuda.Event()
+            ev.record(side)
+            ops.emb_bwd_prepare(self.tables, indices, offsets, B, ws, self.error_flag)
+            pe = torch.cuda.Event()
+            pe.record(side)
+        self._prep_event = pe
+        self._pending_fwd = (indices, offsets, buf, ev)
 
     # ---- internals -----------------------------------------------------------------
     def _rebuild_tables(self):
@@ -292,7 +340,15 @@ class MergedEmbeddingBagWithSGD(nn.Module):
             self._rebuild_tables()
         return r
 
-    def _workspace(self, nnz: int) -> torch.Tensor:
+    def _workspace(self, nnz: int, chunk: int = 0) -> torch.Tensor:
+        if chunk != 0:  # every micro-batch in flight needs its own sort / dedup results
+            ws = self._chunk_ws.get(chunk)
+            need = ops.emb_bwd_workspace_bytes(nnz, self.dim)
+            if ws is None or ws.numel() < need:
+                if ws is not None and self._side_stream is not None:
+                    ws.record_stream(self._side_stream)
+                ws = self._chunk_ws[chunk] = torch.empty(need, dtype=torch.uint8, device=self._raw_weights()[0].device)
+            return ws
         need = ops.emb_bwd_workspace_bytes(nnz, self.dim)
         if self._ws is None or self._ws.numel() < need:
             old = self._ws
@@ -321,13 +377,28 @@ class MergedEmbeddingBagWithSGD(nn.Module):
         b.record()
         self.profile.setdefault(name, []).append((a, b))
 
-    def _launch_prepare(self, indices, offsets, B):
+    def _set_prep(self, chunk, ev):
+        if chunk == 0:
+            self._prep_event = ev
+        else:
+            self._chunk_prep[chunk] = ev
+
+    def _take_prep(self, chunk):
+        if chunk == 0:
+            ev, self._prep_event = self._prep_event, None
+            return ev
+        return self._chunk_prep.pop(chunk, None)
+
+    def _take_pending_sharded(self, chunk):
+        return self._pending_sharded.pop(chunk, None)
+
+    def _launch_prepare(self, indices, offsets, B, chunk: int = 0):
         """Index stage of the backward (keys -> stable sort -> dedup).  It depends only on this
         step's indices, so it is issued on a side stream right after the forward gather and
         overlaps the interaction / MLP forward+backward; ``_apply_update`` joins it."""
-        ws = self._workspace(indices.numel())
+        ws = self._workspace(indices.numel(), chunk)
         if not self.overlap_prepare:
-            self._prep_event = None
+            self._set_prep(chunk, None)
             return
         main = torch.cuda.current_stream()
         if self._side_stream is None:
@@ -337,40 +408,46 @@ class MergedEmbeddingBagWithSGD(nn.Module):
             ops.emb_bwd_prepare(self.tables, indices, offsets, B, ws, self.error_flag)
             ev = torch.cuda.Event()
             ev.record(self._side_stream)
-        self._prep_event = ev
+        self._set_prep(chunk, ev)
 
-    def _launch_forward_sharded_async(self, indices, offsets, B, exch, feat0):
-        """Peer-memory path: issue the pooled forward (rows written straight into the destination ranks' T) and
-        the index stage of the backward on the side stream NOW -- the caller runs the bottom MLP next on the
-        current stream, the sharded autograd function waits for the recorded event before its barrier."""
+    def _launch_forward_sharded_async(self, chunks, feat0):
+        """Peer-memory path: issue the pooled forward of every micro-batch (rows written straight into the
+        destination ranks' T) and then their index stages on the side stream NOW -- the caller runs the bottom MLP
+        next on the current stream, the sharded autograd function waits for the recorded event before its barrier.
+        ``chunks``: list of (indices, offsets, PeerExchange)."""
         main = torch.cuda.current_stream()
+        dev = chunks[0][0].device
         if self._side_stream is None:
-            self._side_stream = torch.cuda.Stream(device=indices.device)
+            self._side_stream = torch.cuda.Stream(device=dev)
         side = self._side_stream
-        ws = self._workspace(indices.numel())
+        wss = [self._workspace(idx.numel(), exch.chunk) for idx, _, exch in chunks]
         side.wait_stream(main)  # batch ready, last step's barriers passed; the previous update precedes on `side`
         with torch.cuda.stream(side):
-            ops.emb_fwd_sharded(self.tables, indices, offsets, B, exch.T_ptrs_dev, exch.lN, exch.F, feat0,
-                                exch.dtype, self.error_flag)
-            ev = torch.cuda.Event()
-            ev.record(side)
-            ops.emb_bwd_prepare(self.tables, indices, offsets, B, ws, self.error_flag)
-            pe = torch.cuda.Event()
-            pe.record(side)
-        self._prep_event = pe
+            for idx, off, exch in chunks:  # every chunk reads the tables BEFORE any chunk's update (queued later)
+                ops.emb_fwd_sharded(self.tables, idx, off, exch.lN * exch.world, exch.T_ptrs_dev, exch.lN, exch.F,
+                                    feat0, exch.dtype, self.error_flag)
+                ev = torch.cuda.Event()
+                ev.record(side)
+                self._pending_sharded[exch.chunk] = (idx, off, ev)
+            for (idx, off, exch), ws in zip(chunks, wss):
+                ops.emb_bwd_prepare(self.tables, idx, off, exch.lN * exch.world, ws, self.error_flag)
+                pe = torch.cuda.Event()
+                pe.record(side)
+                self._set_prep(exch.chunk, pe)
         self._apply_event = None  # the update before this forward is ordered by the side stream itself
-        self._pending_sharded = (indices, offsets, ev)
 
     def _apply_update_sharded(self, indices, offsets, B, exch, feat0):
         """Backward of the peer-memory path (cloudtik_b200.p2p): gradients are read from every rank's dT."""
         opt = ops.OPT_ADAGRAD if self.optimizer_kind == "adagrad" else ops.OPT_SGD
-        ws = self._workspace(indices.numel())
-        if self.overlap_sharded and self._prep_event is not None and self.profile is None:
+        chunk = exch.chunk
+        ws = self._workspace(indices.numel(), chunk)
+        prep = self._take_prep(chunk)
+        if self.overlap_sharded and prep is not None and self.profile is None:
             # NVLink-bound gather of the peers' gradient rows: run it on the side stream (already behind the index
-            # stage) while the current stream does the bottom-MLP backward, the all-reduce and the optimizer
+            # stage) while the current stream does the bottom-MLP backward, the all-reduce and the optimizer -- or,
+            # in a micro-batched step, the next chunk's forward / backward
             side = self._side_stream
             side.wait_stream(torch.cuda.current_stream())  # dT complete on every rank (barrier B2 is before us)
-            self._prep_event = None
             with torch.cuda.stream(side):
                 ops.emb_bwd_apply_sharded(self.tables, indices.numel(), B, exch.dT_ptrs_dev, exch.lN, exch.F, feat0,
                                           exch.dtype, self.sgd_args.lr, ws, optimizer=opt, eps=self.eps,
@@ -379,9 +456,8 @@ class MergedEmbeddingBagWithSGD(nn.Module):
                 ev.record(side)
             self._apply_event = ev
             return
-        if self._prep_event is not None:
-            torch.cuda.current_stream().wait_event(self._prep_event)
-            self._prep_event = None
+        if prep is not None:
+            torch.cuda.current_stream().wait_event(prep)
         else:
             ops.emb_bwd_prepare(self.tables, indices, offsets, B, ws, self.error_flag)
         with self._timed("emb_bwd_apply"):
@@ -392,6 +468,20 @@ class MergedEmbeddingBagWithSGD(nn.Module):
     def _apply_update(self, indices, offsets, B, grad_base, stride_table, stride_bag):
         opt = ops.OPT_ADAGRAD if self.optimizer_kind == "adagrad" else ops.OPT_SGD
         ws = self._workspace(indices.numel())
+        if self.overlap_update and self._prep_event is not None and self.profile is None:
+            # HBM-bound update on the side stream (already behind the index stage there); the current stream goes
+            # on with the bottom-MLP backward and the dense optimizer step, which need nothing from it
+            side = self._side_stream
+            side.wait_stream(torch.cuda.current_stream())  # the gradient rows are complete
+            self._prep_event = None
+            with torch.cuda.stream(side):
+                ops.emb_bwd_apply(self.tables, indices.numel(), B, grad_base, stride_table, stride_bag,
+                                  self.sgd_args.lr, ws, optimizer=opt, eps=self.eps, lr_tensor=self.lr_tensor)
+                ev = torch.cuda.Event()
+                ev.record(side)
+            self._apply_event = ev
+            self._held_grad = grad_base  # freed on the current stream only after join()
+            return
         if self._prep_event is not None:
             torch.cuda.current_stream().wait_event(self._prep_event)
             self._prep_event = None

@@ -17,6 +17,16 @@ Two barriers per step order everything (kernels are stream-ordered on each rank)
   B1 after emb_fwd_sharded  : all rows of T have landed           (also: peers finished reading my dT)
   B2 after interact_bwd     : all dT are complete                 (also: nobody still needs last T)
 Single box only (NVLink / NVSwitch peers); uses ``torch.distributed._symmetric_memory`` for the mapping.
+
+Micro-batch pipeline.  Both exchange kernels are bound by NVLink (at 8 ranks 7/8 of every pooled row and of every
+gradient row crosses it), and inside ONE batch the dependency chain exchange -> interaction -> top MLP -> interaction
+backward -> gradient exchange leaves only the small bottom MLP to hide them behind.  A step may therefore be cut
+into ``n_chunks`` micro-batches (chunk c = every rank's c-th slice of its local batch), each with its own ``T`` / ``dT``
+buffers, barriers and backward workspace.  All chunks' forward exchanges are issued on the embedding's side stream at
+the start of the step (they all read the tables BEFORE any update, exactly like one big batch); chunk c+1's exchange
+then runs under chunk c's interaction / top MLP, and chunk c's gradient-gathering update runs under chunk c+1's
+compute.  The updates are applied chunk after chunk (SGD: W -= lr*g_0, then W -= lr*g_1 -- the sum of the reference's
+single update up to fp32 rounding).  See ``cloudtik_b200.graph.train_step_chunked`` for the driver of one step.
 """
 from __future__ import annotations
 
@@ -29,8 +39,11 @@ from . import ops
 class PeerExchange:
     """Symmetric T / dT buffers of one model replica plus their per-rank pointer tables."""
 
-    def __init__(self, lN: int, F: int, D: int, dtype: torch.dtype, device):
+    def __init__(self, lN: int, F: int, D: int, dtype: torch.dtype, device, chunk: int = 0):
+        """``lN``: samples per rank in one (micro-)batch; ``chunk``: which micro-batch of the step these buffers
+        serve (a step cut into n chunks owns n PeerExchange objects, see the module docstring)."""
         import torch.distributed._symmetric_memory as symm
+        self.chunk = int(chunk)
         self.lN, self.F, self.D, self.dtype = lN, F, D, dtype
         self.world, self.rank = dist.get_world_size(), dist.get_rank()
         group = dist.group.WORLD.group_name
@@ -57,7 +70,7 @@ class _ShardedEmbInteractFn(torch.autograd.Function):
                 rw_offsets=None, train=True):
         B_glob = exch.lN * exch.world
         if emb is not None:
-            pend, emb._pending_sharded = emb._pending_sharded, None
+            pend = emb._take_pending_sharded(exch.chunk)
             if pend is not None and pend[0] is indices and pend[1] is offsets:
                 torch.cuda.current_stream().wait_event(pend[2])  # launched ahead of the bottom MLP (prelaunch())
             else:
@@ -66,7 +79,7 @@ class _ShardedEmbInteractFn(torch.autograd.Function):
                     ops.emb_fwd_sharded(emb.tables, indices, offsets, B_glob, exch.T_ptrs_dev, exch.lN, exch.F,
                                         feat0, exch.dtype, emb.error_flag)
                 if train:  # sort / dedup on the side stream: only a backward consumes it
-                    emb._launch_prepare(indices, offsets, B_glob)
+                    emb._launch_prepare(indices, offsets, B_glob, chunk=exch.chunk)
         ctx.rw_ctx = None
         if rowwise is not None:  # row-wise sharded hot tables occupy the LAST feature slots
             rw_out, ctx.rw_ctx = rowwise.pool(rw_indices, rw_offsets, exch.lN)
@@ -99,11 +112,16 @@ class _ShardedEmbInteractFn(torch.autograd.Function):
         return (dx.to(ctx.x_dtype),) + (None,) * 11
 
 
-def prelaunch(emb, exch: PeerExchange, indices, offsets, feat0: int):
+def prelaunch(emb, exch, indices, offsets, feat0: int):
     """Start this rank's pooled forward + exchange on the embedding's side stream before the caller runs the
-    bottom MLP; ``sharded_emb_interact`` with the same (indices, offsets) tensors picks it up."""
-    if emb is not None and emb.overlap_sharded and emb.overlap_prepare and emb.profile is None:
-        emb._launch_forward_sharded_async(indices, offsets, exch.lN * exch.world, exch, feat0)
+    bottom MLP; ``sharded_emb_interact`` with the same (indices, offsets) tensors picks it up.
+    Micro-batched step: pass lists (one PeerExchange / indices / offsets per chunk) -- every chunk's exchange is
+    queued now, in chunk order, followed by every chunk's index stage."""
+    if emb is None or not (emb.overlap_sharded and emb.overlap_prepare and emb.profile is None):
+        return
+    if isinstance(exch, PeerExchange):
+        exch, indices, offsets = [exch], [indices], [offsets]
+    emb._launch_forward_sharded_async(list(zip(indices, offsets, exch)), feat0)
 
 
 def sharded_emb_interact(x, emb, exch: PeerExchange, indices, offsets, feat0: int, pad_to: int = 1, rowwise=None,
@@ -115,3 +133,27 @@ def sharded_emb_interact(x, emb, exch: PeerExchange, indices, offsets, feat0: in
         train = torch.is_grad_enabled()
     return _ShardedEmbInteractFn.apply(x, trig, emb, exch, indices, offsets, feat0, pad_to, rowwise, rw_indices,
                                        rw_offsets, bool(train))
+
+
+def split_global_batch(idx_l, off_l, world: int, n_chunks: int):
+    """Cut per-table bags of a GLOBAL batch (bag b belongs to rank ``b // lN``) into ``n_chunks`` micro-batches:
+    micro-batch c holds, rank after rank, the c-th slice of every rank's samples -- the bag order
+    ``b200_emb_fwd_sharded`` expects for a chunk.  ``idx_l[t]`` int64[nnz_t], ``off_l[t]`` int64[B_glob] start
+    offsets.  Returns a list over chunks of (idx_l_c, off_l_c).  Host-side helper (tests, the training CLI): it
+    synchronises; a production input pipeline emits its batches in this order in the first place."""
+    out = [([], []) for _ in range(n_chunks)]
+    for idx, off in zip(idx_l, off_l):
+        B = off.numel()
+        lN = B // world
+        per = lN // n_chunks
+        ends = torch.cat([off[1:], torch.tensor([idx.numel()], dtype=off.dtype, device=off.device)])
+        lens = ends - off
+        bag = torch.arange(B, device=off.device)
+        chunk_of_bag = (bag % lN) // per
+        elem_chunk = torch.repeat_interleave(chunk_of_bag, lens)
+        for c in range(n_chunks):
+            lc = lens[chunk_of_bag == c]
+            oc = torch.cumsum(lc, 0) - lc
+            out[c][0].append(idx[elem_chunk == c])
+            out[c][1].append(oc)
+    return out

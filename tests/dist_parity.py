@@ -33,6 +33,9 @@ def main():
     ap.add_argument("--adagrad", action="store_true", help="Adagrad on the tables (oracle: torch sparse Adagrad)")
     ap.add_argument("--no-overlap", action="store_true", help="peer-memory path: keep every kernel on the main stream")
     ap.add_argument("--report", action="store_true", help="print the largest deviations instead of asserting on weights")
+    ap.add_argument("--chunks", type=int, default=1, help="peer-memory path: micro-batches per step (SGD only)")
+    ap.add_argument("--eval-steps", type=int, default=0,
+                    help="after training: forward-only passes (eval mode, no_grad) compared with the oracle's predictions")
     a = ap.parse_args()
 
     from cloudtik_b200 import ext_dist
@@ -65,7 +68,7 @@ def main():
             for pd, ps in zip(dst.parameters(), src.parameters()):
                 pd.copy_(ps)
     if a.p2p:
-        enable_peer_exchange(net, a.batch // world)
+        enable_peer_exchange(net, a.batch // world, a.chunks)
     if a.no_overlap:
         net.emb_l.overlap_sharded = False
     if a.ddp:
@@ -113,6 +116,19 @@ def main():
                                                           [lS_o[t] for t in range(n_tw, len(rows))],
                                                           rows[n_tw:])
             Z = net(Xl, ind, off, None, torch.tensor(ri).to(dev), torch.tensor(ro).to(dev)).float()
+        elif a.chunks > 1:
+            from cloudtik_b200.dlrm import train_step_chunked
+            from cloudtik_b200.p2p import split_global_batch
+            flat = [Xl, Tl]
+            for ic, oc in split_global_batch(li, lo, world, a.chunks):
+                ind, off, _ = net.emb_l.linearize_indices_and_offsets(ic, oc, [False] * len(ic))
+                flat += [ind, off]
+            E = train_step_chunked(net, gopt, flat, sync_dense)
+            Lm = E.detach().clone()
+            torch.distributed.all_reduce(Lm)
+            got = float(Lm.cpu()) / world
+            assert abs(got - want) <= tol * abs(want), f"step {step}: loss {got} vs oracle {want}"
+            continue
         else:
             Z = net(Xl, lo, li).float()
         E = net.loss_fn(Z, Tl)
@@ -124,6 +140,22 @@ def main():
         torch.distributed.all_reduce(Lm)
         got = float(Lm.cpu()) / world
         assert abs(got - want) <= tol * abs(want), f"step {step}: loss {got} vs oracle {want}"
+    if a.eval_steps and a.chunks == 1 and not a.rowwise:
+        # forward only: no backward, hence no second barrier from it -- back-to-back calls must still not overwrite a
+        # peer's T while that peer reads it (the path adds its own barrier), and no index stage may be left pending
+        net.eval()
+        port.eval()
+        for step in range(a.eval_steps):
+            X, lS_o, lS_i, T = uniform_batch(rs, N, rows, pooling=2)
+            with torch.no_grad():
+                with torch.autocast("cpu", dtype=torch.bfloat16, enabled=a.bf16):
+                    want = port(torch.tensor(X), [torch.tensor(o) for o in lS_o], [torch.tensor(i) for i in lS_i]).float()
+                Z = net(torch.tensor(X[rank * lN:(rank + 1) * lN]).to(dev), [torch.tensor(lS_o[t]).to(dev) for t in local],
+                        [torch.tensor(lS_i[t]).to(dev) for t in local]).float()
+            np.testing.assert_allclose(Z.cpu().numpy(), want[rank * lN:(rank + 1) * lN].numpy(), rtol=10 * tol,
+                                       atol=10 * tol, err_msg=f"forward-only pass {step}")
+        net.train()
+        port.train()
     if a.report:
         top = net.top_l.module if a.ddp else net.top_l
         dm = max(float(np.abs(p1.detach().cpu().numpy() - p2.detach().numpy()).max())
