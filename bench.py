@@ -55,6 +55,9 @@ def parse():
                     help="multi-GPU peer-memory path: micro-batches per step (0 = 1 on one GPU, 2 on several); one "
                          "chunk's NVLink exchange runs under another chunk's compute")
     ap.add_argument("--no-parity", action="store_true", help="multi-GPU: skip the pre-flight parity check")
+    ap.add_argument("--sparse-dense-boundary", type=int, default=2048,
+                    help="multi-GPU: tables with fewer rows are replicated on every rank instead of sharded (the "
+                         "reference training variant's flag and default, T/dlrm_s_pytorch.py:266-269); 0 = shard all")
     ap.add_argument("--rows-cap", type=int, default=0, help="debug: cap table rows (0 = full config 3)")
     ap.add_argument("--sets", type=int, default=4, help="distinct synthetic batches rotated")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -213,7 +216,7 @@ def ncu_traffic(kernel):
         return None
 
 
-def make_batches(a, rows_local, B_loc, B_glob, dev, rank, n_chunks=1):
+def make_batches(a, rows_local, B_loc, B_glob, dev, rank, n_chunks=1, rows_repl=()):
     """Synthetic Criteo-shaped inputs: dense U[0,1), targets round(U), one index per
     (sample, table) uniform over the table's rows.  Generated on the host with numpy, kept both in
     pinned host memory (e2e leg) and on the device (HBM-resident leg).
@@ -233,6 +236,10 @@ def make_batches(a, rows_local, B_loc, B_glob, dev, rank, n_chunks=1):
         for c in range(n_chunks):
             flat.append(np.ascontiguousarray(idx[:, c * Bc:(c + 1) * Bc]).reshape(-1))
             flat.append(np.arange(T * Bc + 1, dtype=np.int64))
+        if len(rows_repl):  # replicated small tables: this rank's LOCAL bags, as the last pair of the tuple
+            ridx = np.stack([np.floor(rs.rand(B_loc) * n).astype(np.int64) for n in rows_repl])
+            flat.append(ridx.reshape(-1))
+            flat.append(np.arange(len(rows_repl) * B_loc + 1, dtype=np.int64))
         host = [torch.from_numpy(v).pin_memory() for v in flat]
         # the same batch as RAW Criteo records (int32 label, 13 counts, T ids: the CriteoBinDataset format);
         # the counts are chosen so that log(count + 1) reproduces a dense feature of the same range
@@ -278,7 +285,12 @@ def embeddingbag_microbench(net, gs):
                        "runs on a side stream under the dense forward/backward)", "results": out}
 
 
-def parity_preflight(world, rank, dev, use_p2p, n_chunks, use_graph, steps=3):
+def _dev(a_, b_, rtol, atol):
+    """allclose-style deviation, scaled so that `<= rtol` means |a - b| <= atol + rtol * |b| everywhere."""
+    return float(((a_ - b_).abs() / (atol + rtol * b_.abs())).max()) * rtol
+
+
+def parity_preflight(world, rank, dev, use_p2p, n_chunks, use_graph, boundary=0, steps=3):
     """Multi-GPU parity, checked in the same process right before the timed run: a small-table model of the bench's
     architecture takes `steps` training steps through EXACTLY the sharded path the bench times (table-wise shards,
     peer-memory exchange or NCCL all-to-all, micro-batches, CUDA graph, flat MLP all-reduce, lr / world on the
@@ -286,7 +298,9 @@ def parity_preflight(world, rank, dev, use_p2p, n_chunks, use_graph, steps=3):
     tests pin to the oracle) on the GLOBAL batch with the same initial weights.  The single-process global-batch run
     is the multi-GPU oracle of the reference (T/dlrm_s_pytorch.py:483-522, lr/world at
     :1020-1031).  Compared: the mean-of-ranks loss of every step and, after the last step, the rows of the tables
-    this rank owns and the MLP weights (largest deviation relative to the largest reference magnitude)."""
+    this rank owns (sharded and replicated) and the MLP weights, with the tolerances of tests/dist_parity.py:
+    |a - b| <= atol + tol * |b|, atol 1e-6 (fp32) / 2e-3 (bf16) for table rows, 10 x tol and 5e-6 / 2e-3 for the
+    MLPs; the reported figures are scaled so that `<= tol` is a pass."""
     from cloudtik_b200 import ext_dist
     from cloudtik_b200.dlrm import DLRM_Net, enable_peer_exchange, train_step_chunked
     from cloudtik_b200.graph import GraphedTrainStep
@@ -297,6 +311,7 @@ def parity_preflight(world, rank, dev, use_p2p, n_chunks, use_graph, steps=3):
     lr = 0.5
     out = {"steps": steps, "tables": T, "rows_cap": 3000, "global_batch": Bg, "micro_batches": n_chunks,
            "exchange": "peer-memory" if use_p2p else "nccl all-to-all", "graph": bool(use_graph),
+           "sparse_dense_boundary": boundary,
            "oracle": "single-process cloudtik_b200 run on the global batch (every rank)"}
     ok_all = True
     for tag, bf16, tol in (("fp32", False, 1e-5), ("bf16", True, 1e-2)):
@@ -304,22 +319,30 @@ def parity_preflight(world, rank, dev, use_p2p, n_chunks, use_graph, steps=3):
         W0 = [(torch.rand(n, D, generator=g) * 2 - 1) * (1.0 / n) ** 0.5 for n in rows]
         np.random.seed(99)
         ref = DLRM_Net(D, np.array(rows), np.array(LN_BOT), np.array(LN_TOP), sigmoid_top=len(LN_TOP) - 2,
-                       device=dev, lr=lr, bf16=bf16, distributed=False)
+                       device=dev, lr=lr, bf16=bf16, distributed=False, sparse_dense_boundary=boundary,
+                       dense_tables_first=True)
         np.random.seed(99)
         net = DLRM_Net(D, np.array(rows), np.array(LN_BOT), np.array(LN_TOP), sigmoid_top=len(LN_TOP) - 2,
-                       device=dev, lr=lr / world, bf16=bf16)
-        with torch.no_grad():  # same MLPs by the same numpy stream; tables from the common draw
-            for k, w in enumerate(ref.emb_l.weights):
-                w.copy_(W0[k])
-            for k, t in enumerate(net.local_ln_emb):
-                net.emb_l.weights[k].copy_(W0[t])
+                       device=dev, lr=lr / world, bf16=bf16, sparse_dense_boundary=boundary)
+        order = ref.table_order  # table behind each feature slot (small replicated tables first when boundary > 0)
+
+        def reset_tables():  # same MLPs by the same numpy stream; tables from the common draw
+            with torch.no_grad():
+                for k, w in enumerate(ref.emb_l.weights):
+                    w.copy_(W0[order[k]])
+                for k, t in enumerate(net.local_ln_emb):
+                    net.emb_l.weights[k].copy_(W0[t])
+                if net.emb_dense is not None:
+                    for p_, t in zip(net.emb_dense.params(), net.ln_emb_dense):
+                        p_.copy_(W0[t])
+        reset_tables()
         if use_p2p:
             enable_peer_exchange(net, lB, n_chunks)
         nc = n_chunks if use_p2p else 1
         dense_r = [p for p in ref.parameters() if p.requires_grad]
         dense_n = [p for p in net.parameters() if p.requires_grad]
         opt_r, opt_n = torch.optim.SGD(dense_r, lr=lr), torch.optim.SGD(dense_n, lr=lr)
-        sync = ext_dist.DenseGradAllreduce(dense_n)
+        sync = ext_dist.DenseGradAllreduce(dense_n, early=list(net.top_l.parameters()))
         rs = np.random.RandomState(5)
         batches = []
         for _ in range(steps):
@@ -337,14 +360,18 @@ def parity_preflight(world, rank, dev, use_p2p, n_chunks, use_graph, steps=3):
             for c in range(nc):
                 mine.append(torch.from_numpy(np.ascontiguousarray(v[:, :, c]).reshape(-1)).to(dev))
                 mine.append(torch.arange(len(loc) * world * per + 1, dtype=torch.int64, device=dev))
+            if net.emb_dense is not None:
+                rep = idx[net.ln_emb_dense][:, rank * lB:(rank + 1) * lB]
+                mine.append(torch.from_numpy(np.ascontiguousarray(rep).reshape(-1)).to(dev))
+                mine.append(torch.arange(rep.size + 1, dtype=torch.int64, device=dev))
             return mine
 
         gs = GraphedTrainStep(net, opt_n, shard(*batches[0]), post_backward=sync) if use_graph else None
+        mlp_n = [p for n_, p in net.named_parameters() if p.requires_grad and not n_.startswith("emb_dense")]
         if gs is not None:  # the capture's warm-up steps trained on batch 0: start again from the common weights
+            reset_tables()
             with torch.no_grad():
-                for k, t in enumerate(net.local_ln_emb):
-                    net.emb_l.weights[k].copy_(W0[t])
-                for pn, pr in zip(dense_n, dense_r):
+                for pn, pr in zip(mlp_n, dense_r):
                     pn.copy_(pr)
         worst_loss = 0.0
         for X, Y, idx in batches:
@@ -354,14 +381,19 @@ def parity_preflight(world, rank, dev, use_p2p, n_chunks, use_graph, steps=3):
             torch.distributed.all_reduce(E)
             got = float(E.item()) / world
             gb = [torch.from_numpy(X).to(dev), torch.from_numpy(Y).to(dev),
-                  torch.from_numpy(idx.reshape(-1)).to(dev), torch.arange(T * Bg + 1, dtype=torch.int64, device=dev)]
+                  torch.from_numpy(np.ascontiguousarray(idx[order]).reshape(-1)).to(dev),
+                  torch.arange(T * Bg + 1, dtype=torch.int64, device=dev)]
             want = float(train_step_chunked(ref, opt_r, gb).item())
             worst_loss = max(worst_loss, abs(got - want) / abs(want))
         worst_rows = 0.0
-        for k, t in enumerate(net.local_ln_emb):
-            a_, b_ = net.emb_l.weights[k].float(), ref.emb_l.weights[t].float()
-            worst_rows = max(worst_rows, float((a_ - b_).abs().max() / b_.abs().max()))
-        worst_mlp = max(float((pn - pr).abs().max() / pr.abs().max()) for pn, pr in zip(dense_n, dense_r))
+        slot = {t: k for k, t in enumerate(order)}  # table id -> position in the single-process model
+        atol_w, atol_m = (2e-3, 2e-3) if bf16 else (1e-6, 5e-6)
+        mine = [(net.emb_l.weights[k], t) for k, t in enumerate(net.local_ln_emb)]
+        if net.emb_dense is not None:
+            mine += [(p_.data, t) for p_, t in zip(net.emb_dense.params(), net.ln_emb_dense)]
+        for w_, t in mine:
+            worst_rows = max(worst_rows, _dev(w_.float(), ref.emb_l.weights[slot[t]].float(), tol, atol_w))
+        worst_mlp = max(_dev(pn.data, pr.data, 10 * tol, atol_m) / 10 for pn, pr in zip(mlp_n, dense_r))
         w = torch.tensor([worst_loss, worst_rows, worst_mlp], device=dev, dtype=torch.float64)
         torch.distributed.all_reduce(w, op=torch.distributed.ReduceOp.MAX)
         worst_loss, worst_rows, worst_mlp = (float(x) for x in w)
@@ -415,17 +447,19 @@ def run_b200_arm(a):
     n_chunks = a.chunks if a.chunks > 0 else (2 if use_p2p else 1)
     if not use_p2p:
         n_chunks = 1
+    boundary = a.sparse_dense_boundary if use_p2p and n_chunks == 1 else 0
     parity = None
     if world > 1 and not a.no_parity:
-        parity = parity_preflight(world, rank, dev, use_p2p, n_chunks, not a.no_graph)
+        parity = parity_preflight(world, rank, dev, use_p2p, n_chunks, not a.no_graph, boundary)
 
     np.random.seed(727)
     torch.manual_seed(727 + rank)
     # sharded tables see the sum of every rank's local-mean gradient: lr/world (T/dlrm_s_pytorch.py:1020-1031)
     net = DLRM_Net(D, np.array(rows), np.array(LN_BOT), np.array(LN_TOP), sigmoid_top=len(LN_TOP) - 2,
-                   np_init_emb_weight=False, device=dev, lr=LR / world, bf16=bf16)
+                   np_init_emb_weight=False, device=dev, lr=LR / world, bf16=bf16, sparse_dense_boundary=boundary)
     local_ids = list(range(len(rows))) if world == 1 else net.local_ln_emb
     rows_local = [rows[i] for i in local_ids]
+    rows_repl = [rows[i] for i in net.ln_emb_dense] if world > 1 else []
     if use_p2p:
         enable_peer_exchange(net, B_loc, n_chunks)
     dense_params = [p for p in net.parameters() if p.requires_grad]
@@ -435,8 +469,10 @@ def run_b200_arm(a):
         enable_bf16_shadows([net.bot_l, net.top_l], opt)
     # MLPs are data-parallel: one flat all-reduce of their 2.4 M gradients per step (the fused bf16 MLP
     # path bypasses DDP.forward, so the averaging the reference gets from DDP is done explicitly)
-    sync_dense = ext_dist.DenseGradAllreduce(dense_params) if world > 1 else (lambda: None)
-    sets = make_batches(a, rows_local, B_loc, B_glob, dev, rank, n_chunks)
+    # (the top MLP's share is reduced from inside backward, under the interaction backward and the table update)
+    sync_dense = (ext_dist.DenseGradAllreduce(dense_params, early=list(net.top_l.parameters()))
+                  if world > 1 else (lambda: None))
+    sets = make_batches(a, rows_local, B_loc, B_glob, dev, rank, n_chunks, rows_repl)
     emb = net.emb_l
     from cloudtik_b200.dlrm import train_step_chunked
     post = sync_dense if world > 1 else None
@@ -596,6 +632,8 @@ def run_b200_arm(a):
             "scaling": scaling, "vs_baseline": None, "dtype": a.dtype, "data": "synthetic",
             "config": {"workload": "dlrm_criteo_terabyte_c3", "batch_per_gpu": B_loc, "global_batch": B_glob,
                        "micro_batches_per_step": n_chunks,
+                       "sparse_dense_boundary": boundary if world > 1 else None,
+                       "tables_sharded": len(rows) - len(rows_repl), "tables_replicated": len(rows_repl),
                        "dim": D, "tables": len(rows), "total_rows": int(sum(rows)), "pooling": 1,
                        "table_dtype": "fp32", "mlp": "bot 13-512-256-128 / top 479-1024-1024-512-256-1",
                        "optimizer": "SGD lr 1.0 (fused sparse update + torch SGD on MLPs)",

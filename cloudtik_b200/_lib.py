@@ -39,6 +39,7 @@ SIGNATURES = {
                                           _c.c_float, _p, _c.c_float, _p, _c.c_size_t, _p]),
     "b200_emb_bwd_coalesce": (_int, [_p, _p, _p, _p, _i64, _p, _i64, _i64, _i64, _i64, _i64, _int, _i64, _p, _p, _p,
                                      _p, _c.c_size_t, _p, _p]),
+    "b200_emb_bwd_dense_grad": (_int, [_p, _i64, _p, _i64, _i64, _i64, _i64, _i64, _int, _p, _p, _c.c_size_t, _p]),
     "b200_interact_fwd": (_int, [_p, _p, _i64, _i64, _i64, _i64, _int, _p]),
     "b200_interact_bwd": (_int, [_p, _p, _p, _i64, _i64, _i64, _i64, _int, _p]),
     "b200_emb_fwd_q8": (_int, [_p, _p, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i64, _int, _p, _p]),

@@ -125,6 +125,9 @@ struct UpdParams {
   const uint32_t* win_run;
   const uint32_t* first_val;
   float* values;  // OPT_STORE: [n, D] fp32 coalesced gradient rows, row u = sum of run u
+  // OPT_STORE with by_key: values is a DENSE [total_rows, D] gradient, the sum of run u goes to row unique[u]
+  // (rows no bag touched are left as the caller initialised them)
+  int by_key;
   // sharded gradients (fused mirror all-to-all over peer memory): the gradient row of bag b of local
   // table t lives on rank r = b / lN at grad_ptrs[r] + ((b - r*lN) * F + feat0 + t) * D
   const void* const* grad_ptrs;
@@ -401,7 +404,7 @@ __global__ void __launch_bounds__(UPD_THREADS, (sizeof(GT) == 2 && !TRAIL && OPT
         for (int k = 0; k < NV; ++k) wv[c][k] = make_uint4(0, 0, 0, 0);
         if (closed[c]) {
           if (OPT == OPT_STORE) {
-            wp[c] = reinterpret_cast<char*>(p.values) + ((size_t)uidx * p.D + lane * VE) * sizeof(WT);
+            wp[c] = reinterpret_cast<char*>(p.values) + ((size_t)(p.by_key ? (int64_t)key : uidx) * p.D + lane * VE) * sizeof(WT);
           } else {
             const int tt = s_tab[gid][pos];
             const int64_t row = (int64_t)key - (cached ? s_base[tt] : p.row_base[tt]);
@@ -531,7 +534,7 @@ __global__ void __launch_bounds__(UPD_THREADS, (sizeof(GT) == 2 && !TRAIL && OPT
     float* sp = nullptr;
     char* tp = nullptr;
     if (OPT == OPT_STORE) {
-      wp = reinterpret_cast<char*>(p.values) + ((size_t)u * p.D + lane * VE) * sizeof(WT);
+      wp = reinterpret_cast<char*>(p.values) + ((size_t)(p.by_key ? (int64_t)key : u) * p.D + lane * VE) * sizeof(WT);
     } else {
       const int tt = s_tab[gid][pos];
       const int64_t row = (int64_t)key - (cached ? s_base[tt] : p.row_base[tt]);
@@ -634,7 +637,7 @@ __global__ void __launch_bounds__(UPD_THREADS) window_join_kernel(const UpdParam
   char* wp;
   float* sp = nullptr;
   if (OPT == OPT_STORE) {
-    wp = reinterpret_cast<char*>(p.values) + ((size_t)u * p.D + lane * VE) * sizeof(WT);
+    wp = reinterpret_cast<char*>(p.values) + ((size_t)(p.by_key ? (int64_t)p.unique[u] : u) * p.D + lane * VE) * sizeof(WT);
   } else {
     const uint32_t tt = p.first_val[u] / p.B;
     const int64_t row = (int64_t)p.unique[u] - p.row_base[tt];
@@ -701,7 +704,7 @@ __global__ void emb_update_scalar_kernel(const UpdParams p, int64_t n_max) {
                                                       (int64_t)b * p.grad_stride_bag + d]);
     }
     if (OPT == OPT_STORE) {
-      p.values[u * p.D + d] = acc;
+      p.values[(p.by_key ? (int64_t)p.unique[u] : u) * p.D + d] = acc;
       continue;
     }
     WT* w = static_cast<WT*>(p.weights[t]) + row * p.D + d;
@@ -894,6 +897,7 @@ static int emb_bwd_apply_impl(void* const* d_weights, float* const* d_state, uin
   p.partial = L.partial;
   p.n = nnz;
   p.values = nullptr;
+  p.by_key = 0;
   p.grad_ptrs = d_grad_ptrs;
   p.lN = lN;
   p.F = F;
@@ -958,23 +962,11 @@ extern "C" int b200_emb_bwd_update(void* const* d_weights, float* const* d_state
                             stream);
 }
 
-extern "C" int b200_emb_bwd_coalesce(const int64_t* d_rows, const int64_t* d_row_base, const int64_t* d_indices,
-                                     const int64_t* d_offsets, int64_t nnz, const void* d_grad, int64_t T,
-                                     int64_t B, int64_t D, int64_t grad_stride_table, int64_t grad_stride_bag,
-                                     int grad_dtype, int64_t total_rows, int64_t* d_unique_rows, float* d_values,
-                                     int32_t* d_num_unique, void* ws, size_t ws_bytes, int32_t* d_error,
-                                     b200_stream_t stream) {
-  B200_REQUIRE(d_num_unique, B200_EINVAL, "emb_bwd_coalesce: null output");
-  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  if (T == 0 || B == 0 || nnz == 0) {
-    cudaMemsetAsync(d_num_unique, 0, sizeof(int32_t), st);
-    return B200_OK;
-  }
-  B200_REQUIRE(d_unique_rows && d_values && d_grad, B200_EINVAL, "emb_bwd_coalesce: null pointer");
-  B200_REQUIRE(grad_dtype == B200_F32 || grad_dtype == B200_BF16, B200_EINVAL, "emb_bwd_coalesce: bad dtype");
-  int rc = b200_emb_bwd_prepare(d_rows, d_row_base, d_indices, d_offsets, nnz, T, B, D, total_rows, ws, ws_bytes,
-                                d_error, stream);
-  if (rc) return rc;
+// segment sums of the gradient rows into `d_values`: row u of a compact [U, D] array, or (by_key) row unique[u]
+// of a dense [total_rows, D] array.  The workspace must hold the result of b200_emb_bwd_prepare.
+static int store_run_sums(const int64_t* d_row_base, int64_t nnz, const void* d_grad, int64_t T, int64_t B, int64_t D,
+                          int64_t grad_stride_table, int64_t grad_stride_bag, int grad_dtype, float* d_values,
+                          int by_key, void* ws, cudaStream_t st) {
   BwdLayout L = bwd_layout(ws, nnz, D);
   UpdParams p{};
   p.row_base = d_row_base;
@@ -993,15 +985,52 @@ extern "C" int b200_emb_bwd_coalesce(const int64_t* d_rows, const int64_t* d_row
   p.first_val = L.first_val;
   p.partial = L.partial;
   p.values = d_values;
+  p.by_key = by_key;
   p.n = nnz;
   p.T = (int)T;
   const int gsz = dtype_size(grad_dtype);
   const bool vec_ok = (D * 4) % 16 == 0 && p.V <= 128 && (reinterpret_cast<uintptr_t>(d_grad) % 16) == 0 &&
                       (reinterpret_cast<uintptr_t>(d_values) % 16) == 0 && (grad_stride_table * gsz) % 16 == 0 &&
                       (grad_stride_bag * gsz) % 16 == 0;
-  rc = grad_dtype == B200_F32 ? launch_update<float, float, OPT_STORE>(p, nnz, vec_ok, st)
-                              : launch_update<float, __nv_bfloat16, OPT_STORE>(p, nnz, vec_ok, st);
+  return grad_dtype == B200_F32 ? launch_update<float, float, OPT_STORE>(p, nnz, vec_ok, st)
+                                : launch_update<float, __nv_bfloat16, OPT_STORE>(p, nnz, vec_ok, st);
+}
+
+extern "C" int b200_emb_bwd_dense_grad(const int64_t* d_row_base, int64_t nnz, const void* d_grad, int64_t T,
+                                       int64_t B, int64_t D, int64_t grad_stride_table, int64_t grad_stride_bag,
+                                       int grad_dtype, float* d_dense_grad, void* ws, size_t ws_bytes,
+                                       b200_stream_t stream) {
+  B200_REQUIRE(T >= 0 && B >= 0 && D > 0 && nnz >= 0, B200_EINVAL, "emb_bwd_dense_grad: negative size");
+  if (T == 0 || B == 0 || nnz == 0) return B200_OK;
+  B200_REQUIRE(d_row_base && d_grad && d_dense_grad && ws, B200_EINVAL, "emb_bwd_dense_grad: null pointer");
+  B200_REQUIRE(grad_dtype == B200_F32 || grad_dtype == B200_BF16, B200_EINVAL, "emb_bwd_dense_grad: bad dtype");
+  B200_REQUIRE(ws_bytes >= b200_emb_bwd_workspace_bytes(nnz, D), B200_EWORKSPACE,
+               "emb_bwd_dense_grad: workspace too small");
+  return store_run_sums(d_row_base, nnz, d_grad, T, B, D, grad_stride_table, grad_stride_bag, grad_dtype,
+                        d_dense_grad, 1, ws, reinterpret_cast<cudaStream_t>(stream));
+}
+
+extern "C" int b200_emb_bwd_coalesce(const int64_t* d_rows, const int64_t* d_row_base, const int64_t* d_indices,
+                                     const int64_t* d_offsets, int64_t nnz, const void* d_grad, int64_t T,
+                                     int64_t B, int64_t D, int64_t grad_stride_table, int64_t grad_stride_bag,
+                                     int grad_dtype, int64_t total_rows, int64_t* d_unique_rows, float* d_values,
+                                     int32_t* d_num_unique, void* ws, size_t ws_bytes, int32_t* d_error,
+                                     b200_stream_t stream) {
+  B200_REQUIRE(d_num_unique, B200_EINVAL, "emb_bwd_coalesce: null output");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (T == 0 || B == 0 || nnz == 0) {
+    cudaMemsetAsync(d_num_unique, 0, sizeof(int32_t), st);
+    return B200_OK;
+  }
+  B200_REQUIRE(d_unique_rows && d_values && d_grad, B200_EINVAL, "emb_bwd_coalesce: null pointer");
+  B200_REQUIRE(grad_dtype == B200_F32 || grad_dtype == B200_BF16, B200_EINVAL, "emb_bwd_coalesce: bad dtype");
+  int rc = b200_emb_bwd_prepare(d_rows, d_row_base, d_indices, d_offsets, nnz, T, B, D, total_rows, ws, ws_bytes,
+                                d_error, stream);
   if (rc) return rc;
+  rc = store_run_sums(d_row_base, nnz, d_grad, T, B, D, grad_stride_table, grad_stride_bag, grad_dtype, d_values, 0,
+                      ws, st);
+  if (rc) return rc;
+  BwdLayout L = bwd_layout(ws, nnz, D);
   unique_to_i64_kernel<<<(unsigned)ceil_div(nnz, 256), 256, 0, st>>>(L.unique, L.num_unique, d_unique_rows, nnz);
   cudaMemcpyAsync(d_num_unique, L.num_unique, sizeof(int32_t), cudaMemcpyDeviceToDevice, st);
   B200_CHECK_LAUNCH("emb_bwd_coalesce");

@@ -56,9 +56,18 @@ class DLRM_Net(nn.Module):
 
     def __init__(self, m_spa=None, ln_emb=None, ln_bot=None, ln_top=None, sigmoid_bot=-1, sigmoid_top=-1,
                  weighted_pooling=None, loss_threshold=0.0, np_init_emb_weight=False, device="cuda",
-                 lr=0.01, emb_optimizer="sgd", bf16=False, n_rowwise=0, distributed=None):
+                 lr=0.01, emb_optimizer="sgd", bf16=False, n_rowwise=0, distributed=None,
+                 sparse_dense_boundary=0, dense_tables_first=False):
         """``distributed=False`` builds the single-process model (all tables local) even inside an initialised
-        process group -- the oracle of the multi-GPU parity checks runs that way next to the sharded model."""
+        process group -- the oracle of the multi-GPU parity checks runs that way next to the sharded model.
+
+        ``sparse_dense_boundary`` (T/dlrm_s_pytorch.py:266-269,353-358; 0 = off, the product variant's behaviour):
+        when distributed, tables with fewer rows are REPLICATED on every rank (``emb_dense``: dense parameters,
+        local-batch lookups, gradients all-reduced with the MLPs') and only the others are sharded table-wise; the
+        interaction then sees ``[x] + dense tables + sharded tables`` -- the reference's permuted feature order
+        (``ly = ly_dense + list(ly_sparse)``, T/dlrm_s_pytorch.py:509).  ``dense_tables_first=True`` gives the
+        single-process model the same table order (``table_order``), which makes it the parity oracle of such a
+        run (the reference's own sequential_forward keeps the natural order, SURVEY.md section 8c caveat)."""
         super().__init__()
         self.world = ext_dist.my_size if (distributed is None or distributed) and ext_dist.my_size > 1 else 1
         if weighted_pooling is not None:
@@ -73,16 +82,24 @@ class DLRM_Net(nn.Module):
         # are partitioned table-wise exactly like the reference (P/dlrm_s_pytorch.py:256-264)
         self.n_rowwise = int(n_rowwise) if self.world > 1 else 0
         self.rowwise = None
+        self.emb_dense = None
+        self.sparse_dense_boundary = int(sparse_dense_boundary)
+        n_tw = len(ln_emb) - self.n_rowwise
+        split = self.sparse_dense_boundary > 0 and (self.world > 1 or dense_tables_first)
+        self.ln_emb_dense = [i for i in range(n_tw) if split and ln_emb[i] < self.sparse_dense_boundary]
+        self.ln_emb_sparse = [i for i in range(n_tw) if i not in self.ln_emb_dense]
+        # order of the tables as interaction features (identity unless small tables are moved to the front)
+        self.table_order = self.ln_emb_dense + self.ln_emb_sparse + list(range(n_tw, len(ln_emb)))
         if self.world > 1:
-            n_emb = len(ln_emb) - self.n_rowwise
+            n_emb = len(self.ln_emb_sparse)
             self.n_global_emb = len(ln_emb)
             self.rank = ext_dist.dist.get_rank()
-            self.ln_emb = [i for i in range(n_emb)]
+            self.ln_emb = list(self.ln_emb_sparse)
             self.n_local_emb, self.n_emb_per_rank = ext_dist.get_split_lengths(n_emb)
             self.local_ln_emb_slice = ext_dist.get_my_slice(n_emb)
             self.local_ln_emb = self.ln_emb[self.local_ln_emb_slice]
         else:
-            self.local_ln_emb = None
+            self.local_ln_emb = None if not self.ln_emb_dense else list(self.table_order)
         self.l_emb_seeds = np.random.randint(low=0, high=100000, size=len(ln_emb))
         self.bot_l = self.create_mlp(np.asarray(ln_bot), sigmoid_bot, pad_first=True).to(device)
         self.dense_pad = (-int(ln_bot[0])) % 8  # 13 dense features -> 16 zero-padded columns (aligned GEMM K)
@@ -90,6 +107,10 @@ class DLRM_Net(nn.Module):
         self.interaction_pad = 8  # interaction output rounded up to a multiple of 8 columns
         self.emb_l = self.create_emb(m_spa, ln_emb, self.local_ln_emb, np_init_emb_weight, device, lr,
                                      emb_optimizer)
+        if self.world > 1 and self.ln_emb_dense:
+            from .replicated import ReplicatedEmbeddingBags
+            small = self.create_emb(m_spa, ln_emb, self.ln_emb_dense, np_init_emb_weight, device, lr, "sgd")
+            self.emb_dense = ReplicatedEmbeddingBags(small._raw_weights())
         if self.n_rowwise:
             from .rowwise import RowWiseShardedTables
             hot = [int(n) for n in ln_emb[len(ln_emb) - self.n_rowwise:]]
@@ -119,16 +140,19 @@ class DLRM_Net(nn.Module):
             return emb_l(emb_args, self.need_linearize_indices_and_offsets)
         # list style (P/dlrm_s_pytorch.py:290-305): (lS_o, lS_i) -> linearise on the fly
         lS_o, lS_i = emb_args
+        if self.world == 1 and self.ln_emb_dense:  # natural table order in, dense-first order inside
+            lS_o, lS_i = [lS_o[t] for t in self.table_order], [lS_i[t] for t in self.table_order]
         return emb_l((list(lS_i), list(lS_o), [False] * len(lS_i)), torch.BoolTensor([True]))
 
     def interact_features(self, x, ly):
         return interaction(x, *ly, pad_to=self.interaction_pad)
 
-    def forward(self, dense_x, *emb_args, chunk=0):
+    def forward(self, dense_x, *emb_args, chunk=0, dense_bags=None):
         """``chunk``: which micro-batch of a step cut by ``enable_peer_exchange(..., n_chunks)`` this call is
-        (0 when the step is not cut)."""
+        (0 when the step is not cut).  ``dense_bags``: (indices, offsets) of this rank's LOCAL bags of the replicated
+        small tables, linearised in ``ln_emb_dense`` order (models built with ``sparse_dense_boundary`` only)."""
         if self.world > 1:
-            return self.distributed_forward(dense_x, *emb_args, chunk=chunk)
+            return self.distributed_forward(dense_x, *emb_args, chunk=chunk, dense_bags=dense_bags)
         return self.sequential_forward(dense_x, *emb_args)
 
     def begin_step(self, chunk_args):
@@ -142,7 +166,7 @@ class DLRM_Net(nn.Module):
                                % (len(chunk_args), len(self.peer_exchanges)))
         from .p2p import prelaunch
         prelaunch(self.emb_l, self.peer_exchanges, [a[0] for a in chunk_args], [a[1] for a in chunk_args],
-                  1 + self.local_ln_emb_slice.start)
+                  1 + len(self.ln_emb_dense) + self.local_ln_emb_slice.start)
 
     def _clamp(self, p):
         if 0.0 < self.loss_threshold < 1.0:
@@ -160,14 +184,17 @@ class DLRM_Net(nn.Module):
             p = self.apply_mlp(z, self.top_l)
         return self._clamp(p)
 
-    def distributed_forward(self, dense_x, *emb_args, chunk=0):
+    def distributed_forward(self, dense_x, *emb_args, chunk=0, dense_bags=None):
         # P/dlrm_s_pytorch.py:342-369: local tables on the GLOBAL batch -> all-to-all -> local batch
         batch_size = dense_x.size()[0]
         if batch_size < ext_dist.my_size:
             sys.exit("ERROR: batch_size (%d) must be larger than number of ranks (%d)"
                      % (batch_size, ext_dist.my_size))
         if self.peer_exchange is not None:
-            return self._p2p_forward(dense_x, *emb_args, chunk=chunk)
+            return self._p2p_forward(dense_x, *emb_args, chunk=chunk, dense_bags=dense_bags)
+        if self.emb_dense is not None:
+            raise NotImplementedError("replicated small tables (sparse_dense_boundary) need the peer-memory "
+                                      "exchange: call enable_peer_exchange(), or build the model with boundary 0")
         with torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.bf16):
             ly = self.apply_emb(self.emb_l, *emb_args)
             a2a_req = ext_dist.alltoall(ly, self.n_emb_per_rank)
@@ -180,7 +207,7 @@ class DLRM_Net(nn.Module):
         return self._clamp(p)
 
 
-def _p2p_forward(self, dense_x, *emb_args, chunk=0):
+def _p2p_forward(self, dense_x, *emb_args, chunk=0, dense_bags=None):
     """distributed_forward with the all-to-all fused into the embedding kernels (cloudtik_b200.p2p)."""
     from .p2p import prelaunch, sharded_emb_interact
     exch = self.peer_exchanges[chunk]
@@ -191,10 +218,20 @@ def _p2p_forward(self, dense_x, *emb_args, chunk=0):
             rw_i, rw_o = emb_args[3], emb_args[4]
     else:
         lS_o, lS_i = emb_args
+        if len(lS_i) == self.n_global_emb - self.n_rowwise and len(lS_i) != len(self.local_ln_emb):
+            # the training variant's input (T/dlrm_s_pytorch.py:489-497): EVERY table's bags for this rank's LOCAL
+            # batch.  Small tables stay here; the sharded tables' bags travel to their owners (index all-to-all)
+            if self.emb_dense is not None:
+                dense_bags = self.emb_dense_linearize([lS_i[t] for t in self.ln_emb_dense],
+                                                      [lS_o[t] for t in self.ln_emb_dense])
+            lS_o, lS_i = ext_dist.shuffle_bags([lS_o[t] for t in self.ln_emb_sparse],
+                                               [lS_i[t] for t in self.ln_emb_sparse], self.n_emb_per_rank)
         indices, offsets, _ = self.emb_l.linearize_indices_and_offsets(list(lS_i), list(lS_o), [False] * len(lS_i))
+    if (self.emb_dense is not None) != (dense_bags is not None):
+        raise RuntimeError("replicated small tables need dense_bags=(indices, offsets) of the local batch")
     if (self.rowwise is not None) != (rw_i is not None):
         raise RuntimeError("row-wise sharded tables need (indices, offsets, None, rw_indices, rw_offsets)")
-    feat0 = 1 + self.local_ln_emb_slice.start
+    feat0 = 1 + len(self.ln_emb_dense) + self.local_ln_emb_slice.start
     train = self.training and torch.is_grad_enabled()
     if train and len(self.peer_exchanges) == 1:
         prelaunch(self.emb_l, exch, indices, offsets, feat0)  # NVLink exchange || bottom MLP
@@ -202,12 +239,26 @@ def _p2p_forward(self, dense_x, *emb_args, chunk=0):
         x = self.apply_mlp(self._pad_dense(dense_x), self.bot_l)
         z = sharded_emb_interact(x, self.emb_l, exch, indices, offsets, feat0,
                                  pad_to=self.interaction_pad, rowwise=self.rowwise, rw_indices=rw_i,
-                                 rw_offsets=rw_o, train=train)
+                                 rw_offsets=rw_o, train=train, repl=self.emb_dense,
+                                 repl_indices=None if dense_bags is None else dense_bags[0],
+                                 repl_offsets=None if dense_bags is None else dense_bags[1])
         p = self.apply_mlp(z, self.top_l)
     return self._clamp(p)
 
 
+def _emb_dense_linearize(self, idx_l, off_l):
+    """Per-table LOCAL bags of the replicated tables -> (indices, offsets) in the merged layout."""
+    dev = idx_l[0].device
+    nnz, parts = 0, []
+    for i, o in zip(idx_l, off_l):
+        parts.append(o.to(torch.int64) + nnz)
+        nnz += i.numel()
+    parts.append(torch.tensor([nnz], dtype=torch.int64, device=dev))
+    return torch.cat([i.to(torch.int64) for i in idx_l]), torch.cat(parts)
+
+
 DLRM_Net._p2p_forward = _p2p_forward
+DLRM_Net.emb_dense_linearize = _emb_dense_linearize
 
 
 def enable_peer_exchange(dlrm, local_batch: int, n_chunks: int = 1):
@@ -218,8 +269,8 @@ def enable_peer_exchange(dlrm, local_batch: int, n_chunks: int = 1):
     from .p2p import PeerExchange
     if n_chunks < 1 or local_batch % n_chunks:
         raise ValueError("enable_peer_exchange: the local batch must be a multiple of n_chunks")
-    if n_chunks > 1 and dlrm.rowwise is not None:
-        raise NotImplementedError("micro-batched steps with row-wise sharded tables")
+    if n_chunks > 1 and (dlrm.rowwise is not None or dlrm.emb_dense is not None):
+        raise NotImplementedError("micro-batched steps with row-wise sharded or replicated tables")
     n_feat = 1 + dlrm.n_global_emb
     dt = torch.bfloat16 if dlrm.bf16 else dlrm.emb_l.tables.dtype
     dlrm.peer_exchanges = [PeerExchange(local_batch // n_chunks, n_feat, dlrm.emb_l.dim, dt,
@@ -243,7 +294,9 @@ def train_step(dlrm, optimizer, X, emb_args, T, lr=None):
 
 def train_step_chunked(dlrm, optimizer, batch, post_backward=None):
     """One iteration on a batch given as the flat tuple ``(X, Y, indices_0, offsets_0[, indices_1, offsets_1, ...])``:
-    one (indices, offsets) pair of linearised bags per micro-batch (a single pair = the plain step above).  Chunk c
+    one (indices, offsets) pair of linearised bags per micro-batch (a single pair = the plain step above), followed --
+    only for a model with replicated small tables (``emb_dense``) -- by one more pair: this rank's LOCAL bags of
+    those tables.  Chunk c
     covers ``X[c*n:(c+1)*n]`` of this rank's samples and, in ``indices_c``, the same slice of EVERY rank's samples
     (rank-major), i.e. the global micro-batch this rank's tables are looked up for.  MLP gradients accumulate over
     the chunks; each chunk's loss is scaled by 1/n_chunks so that their sum is the batch mean the reference
@@ -251,8 +304,11 @@ def train_step_chunked(dlrm, optimizer, batch, post_backward=None):
     Returns the batch-mean loss tensor."""
     X, Y = batch[0], batch[1]
     pairs = [(batch[2 + 2 * c], batch[3 + 2 * c]) for c in range((len(batch) - 2) // 2)]
+    dense_bags = pairs.pop() if getattr(dlrm, "emb_dense", None) is not None else None  # LAST pair: replicated tables
     n = len(pairs)
     optimizer.zero_grad(set_to_none=True)
+    if hasattr(post_backward, "begin"):
+        post_backward.begin(n)
     if n > 1:
         if dlrm.peer_exchanges is None or len(dlrm.peer_exchanges) != n:
             raise RuntimeError("a micro-batched step needs enable_peer_exchange(dlrm, local_batch, n_chunks=%d)" % n)
@@ -261,7 +317,8 @@ def train_step_chunked(dlrm, optimizer, batch, post_backward=None):
     total = None
     for c, (idx, off) in enumerate(pairs):
         Xc, Yc = (X, Y) if n == 1 else (X[c * per:(c + 1) * per], Y[c * per:(c + 1) * per])
-        Z = dlrm(Xc, idx, off, None, chunk=c).float()
+        Z = (dlrm(Xc, idx, off, None, chunk=c) if dense_bags is None
+             else dlrm(Xc, idx, off, None, chunk=c, dense_bags=dense_bags)).float()
         E = dlrm.loss_fn(Z, Yc)
         (E if n == 1 else E / n).backward()
         total = E.detach() if total is None else total + E.detach()

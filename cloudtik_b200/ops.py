@@ -230,6 +230,20 @@ def emb_bwd_coalesce(tables: TableSet, indices, offsets, B: int, grad: torch.Ten
     return rows[:U], vals[:U]
 
 
+def emb_bwd_dense_grad(tables: TableSet, nnz: int, B: int, grad: torch.Tensor, stride_table: int, stride_bag: int,
+                       out: torch.Tensor, ws: torch.Tensor):
+    """Dense fp32 gradient ``out[total_rows, D]`` of the pooled lookup from a prepared ``ws`` (rows no bag touched
+    keep what ``out`` held: zero it first).  See b200_emb_bwd_dense_grad."""
+    _cuda(grad, "grad")
+    _cuda(out, "out", torch.float32)
+    if tuple(out.shape) != (tables.total_rows, tables.D) or not out.is_contiguous():
+        raise _lib.B200Error("emb_bwd_dense_grad: out must be a contiguous [total_rows, D] fp32 tensor")
+    check(lib.b200_emb_bwd_dense_grad(tables.d_row_base.data_ptr(), nnz, grad.data_ptr(), len(tables), B, tables.D,
+                                      stride_table, stride_bag, _dt(grad.dtype), out.data_ptr(), ws.data_ptr(),
+                                      ws.numel() * ws.element_size(), _stream()), "b200_emb_bwd_dense_grad")
+    return out
+
+
 def interact_fwd(T: torch.Tensor, out: torch.Tensor | None = None, pad_to: int = 1) -> torch.Tensor:
     """T [B, F, D] contiguous -> R [B, ldr] with ldr = D + F(F-1)/2 rounded up to ``pad_to``
     (padding columns are written as zeros).  See b200_interact_fwd."""

@@ -67,7 +67,7 @@ class _ShardedEmbInteractFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, trigger, emb, exch, indices, offsets, feat0, pad_to, rowwise=None, rw_indices=None,
-                rw_offsets=None, train=True):
+                rw_offsets=None, train=True, repl=None, repl_indices=None, repl_offsets=None, *repl_weights):
         B_glob = exch.lN * exch.world
         if emb is not None:
             pend = emb._take_pending_sharded(exch.chunk)
@@ -85,6 +85,10 @@ class _ShardedEmbInteractFn(torch.autograd.Function):
             rw_out, ctx.rw_ctx = rowwise.pool(rw_indices, rw_offsets, exch.lN)
             exch.T[:, exch.F - rowwise.k:].copy_(rw_out)
         exch.T[:, 0].copy_(x)
+        if repl is not None:  # replicated small tables: LOCAL batch, feature slots 1 .. n right behind x
+            repl.pool_into(repl_indices, repl_offsets, exch.lN, exch.T[:, 1:1 + repl.n_tables], exch.D, exch.F * exch.D)
+            if train:
+                repl.launch_prepare(repl_indices, repl_offsets, exch.lN, emb._side_stream if emb is not None else None)
         exch.barrier(0)  # B1
         R = ops.interact_fwd(exch.T, pad_to=pad_to)
         if not train:
@@ -93,6 +97,7 @@ class _ShardedEmbInteractFn(torch.autograd.Function):
             # still reading it
             exch.barrier(1)
         ctx.emb, ctx.exch, ctx.feat0, ctx.rowwise = emb, exch, feat0, rowwise
+        ctx.repl, ctx.repl_bags = repl, (repl_indices, repl_offsets)
         ctx.save_for_backward(indices, offsets)
         ctx.x_dtype = x.dtype
         return R
@@ -109,7 +114,11 @@ class _ShardedEmbInteractFn(torch.autograd.Function):
         if ctx.rowwise is not None:
             ctx.rowwise.update(exch.dT[:, exch.F - ctx.rowwise.k:], ctx.rw_ctx)
         dx = exch.dT[:, 0].clone()  # dT is overwritten by the next step; the bottom MLP backward runs now
-        return (dx.to(ctx.x_dtype),) + (None,) * 11
+        rg = ()
+        if ctx.repl is not None:  # dense gradients of the replicated tables (all-reduced with the MLPs' by the caller)
+            rg = tuple(ctx.repl.dense_grads(ctx.repl_bags[0], ctx.repl_bags[1], exch.lN,
+                                            exch.dT[:, 1:1 + ctx.repl.n_tables], exch.D, exch.F * exch.D))
+        return (dx.to(ctx.x_dtype),) + (None,) * 14 + rg
 
 
 def prelaunch(emb, exch, indices, offsets, feat0: int):
@@ -125,14 +134,18 @@ def prelaunch(emb, exch, indices, offsets, feat0: int):
 
 
 def sharded_emb_interact(x, emb, exch: PeerExchange, indices, offsets, feat0: int, pad_to: int = 1, rowwise=None,
-                         rw_indices=None, rw_offsets=None, trigger=None, train=None):
+                         rw_indices=None, rw_offsets=None, trigger=None, train=None, repl=None, repl_indices=None,
+                         repl_offsets=None):
     """``train`` (default: grad mode is on): False = forward only -- no index stage is launched for a backward that
-    will not come, and a second barrier replaces the one the backward would have issued."""
+    will not come, and a second barrier replaces the one the backward would have issued.
+    ``repl``: a ``ReplicatedEmbeddingBags`` whose tables fill the feature slots right behind x (``feat0`` of the
+    sharded tables then starts behind them), looked up for the LOCAL bags ``repl_indices`` / ``repl_offsets``."""
     trig = trigger if trigger is not None else (emb._trigger if emb is not None else rowwise.emb._trigger)
     if train is None:
         train = torch.is_grad_enabled()
+    rw = tuple(repl.params()) if repl is not None else ()
     return _ShardedEmbInteractFn.apply(x, trig, emb, exch, indices, offsets, feat0, pad_to, rowwise, rw_indices,
-                                       rw_offsets, bool(train))
+                                       rw_offsets, bool(train), repl, repl_indices, repl_offsets, *rw)
 
 
 def split_global_batch(idx_l, off_l, world: int, n_chunks: int):

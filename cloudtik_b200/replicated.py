@@ -1,0 +1,107 @@
+"""Small embedding tables replicated on every rank (data-parallel), next to the table-wise sharded large ones.
+
+The reference's training variant splits the tables at ``--sparse-dense-boundary`` (default 2048 rows,
+``T/dlrm_s_pytorch.py:266-269``): a table with fewer rows is built with ``sparse=False``, kept on EVERY rank
+(``emb_dense``), looked up for the rank's LOCAL batch only (``T/dlrm_s_pytorch.py:489-509``) and wrapped in DDP so
+that its dense gradient is all-reduced like the MLPs' (``T/dlrm_s_pytorch.py:988-997``); only the tables at or above
+the boundary are sharded and exchanged.  On the Criteo-Terabyte shape that takes 10 of the 26 tables (3 ... 1543
+rows) out of the pooled-embedding all-to-all: the exchange moves 16 tables instead of 26 and, at 8 ranks, every
+rank owns exactly 2 of them.
+
+Here the replicated tables are dense ``nn.Parameter``s ``{k}.weight`` (the optimizer that steps the MLPs steps them
+too, the flat gradient all-reduce covers them), pooled by the same ``b200_emb_fwd`` kernel straight into the
+interaction input, and their dense gradient comes from ``b200_emb_bwd_prepare`` + ``b200_emb_bwd_dense_grad``
+(windowed segment sums: a 3-row table receives a third of the batch per row).
+"""
+from __future__ import annotations
+
+from typing import List
+
+import torch
+import torch.nn as nn
+
+from . import ops
+
+
+class _Table(nn.Module):
+    def __init__(self, weight: torch.Tensor):
+        super().__init__()
+        self.weight = nn.Parameter(weight, requires_grad=True)
+
+
+class ReplicatedEmbeddingBags(nn.Module):
+    def __init__(self, weights: List[torch.Tensor]):
+        super().__init__()
+        if not weights:
+            raise ValueError("ReplicatedEmbeddingBags needs at least one table")
+        for k, w in enumerate(weights):
+            if not w.is_cuda or w.dtype != torch.float32:
+                raise RuntimeError("replicated tables are fp32 CUDA tensors (no CPU path)")
+            self.add_module(str(k), _Table(w.contiguous()))
+        self.n_tables = len(weights)
+        self.dim = int(weights[0].shape[1])
+        self.error_flag = None
+        self._ws = None
+        self._prep_event = None
+        self._rebuild()
+
+    def params(self) -> List[nn.Parameter]:
+        return [getattr(self, str(k)).weight for k in range(self.n_tables)]
+
+    def _rebuild(self):
+        self.tables = ops.TableSet([p.data for p in self.params()])
+
+    def _apply(self, fn, *a, **k):
+        r = super()._apply(fn, *a, **k)
+        if getattr(self, "tables", None) is not None:
+            self._rebuild()
+        return r
+
+    def _tables_checked(self):
+        # the optimizer updates the parameters in place, so the pointer table stays valid; a re-assigned
+        # .data (load_state_dict assigns in place too, but be safe) is picked up here
+        if any(p.data_ptr() != w.data_ptr() for p, w in zip(self.params(), self.tables.weights)):
+            self._rebuild()
+        return self.tables
+
+    def _workspace(self, nnz: int):
+        need = ops.emb_bwd_workspace_bytes(nnz, self.dim)
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = torch.empty(need, dtype=torch.uint8, device=self.tables.device)
+        return self._ws
+
+    def pool_into(self, indices, offsets, B: int, out: torch.Tensor, stride_table: int, stride_bag: int):
+        """Pooled rows of the B local bags of every replicated table into ``out`` (a view of the interaction
+        input: table t of bag b at ``out.data_ptr + (t * stride_table + b * stride_bag)`` elements)."""
+        ops.emb_fwd(self._tables_checked(), indices, offsets, B, out, stride_table, stride_bag, self.error_flag)
+
+    def launch_prepare(self, indices, offsets, B: int, side: torch.cuda.Stream | None):
+        """Index stage of the backward (keys, stable sort, dedup) on ``side`` if given (it only needs the indices)."""
+        ws = self._workspace(indices.numel())
+        tables = self._tables_checked()
+        if side is None:
+            ops.emb_bwd_prepare(tables, indices, offsets, B, ws, self.error_flag)
+            self._prep_event = None
+            return
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            ops.emb_bwd_prepare(tables, indices, offsets, B, ws, self.error_flag)
+            ev = torch.cuda.Event()
+            ev.record(side)
+        self._prep_event = ev
+
+    def dense_grads(self, indices, offsets, B: int, grad_base: torch.Tensor, stride_table: int, stride_bag: int):
+        """Per-table dense fp32 gradients (row-slices of one [total_rows, D] buffer) from the gradient of the
+        pooled rows, addressed like ``pool_into``'s output.  ``launch_prepare`` must have run for these bags."""
+        if self._prep_event is not None:
+            torch.cuda.current_stream().wait_event(self._prep_event)
+            self._prep_event = None
+        tables = self.tables
+        G = torch.zeros(tables.total_rows, self.dim, dtype=torch.float32, device=tables.device)
+        ops.emb_bwd_dense_grad(tables, indices.numel(), B, grad_base, stride_table, stride_bag, G,
+                               self._workspace(indices.numel()))
+        out, base = [], 0
+        for n in tables.rows:
+            out.append(G[base:base + n])
+            base += n
+        return out

@@ -193,6 +193,20 @@ int b200_emb_bwd_coalesce(const int64_t* d_rows, const int64_t* d_row_base, cons
                           b200_stream_t stream);
 
 /*
+ * EmbeddingBag backward as a DENSE gradient, for the small tables the reference replicates on every rank instead
+ * of sharding them: `nn.EmbeddingBag(n, m, mode="sum", sparse=False)` when n < --sparse-dense-boundary
+ * (T/dlrm_s_pytorch.py:266-269), wrapped in DDP so that their dense gradients are all-reduced with the MLPs'
+ * (T/dlrm_s_pytorch.py:988-997).  Second half of a two-call sequence: after b200_emb_bwd_prepare on the same
+ * workspace, every distinct row gets the sum of the gradient rows of the bags that looked it up:
+ *   d_dense_grad[row_base[t] + r, :] = sum_{bags b of table t containing r (with multiplicity)} grad[t, b, :]
+ * fp32, rows no bag touched are NOT written (the caller zeroes the buffer).  Hot rows (a 3-row table receives
+ * B / 3 gradients per row) go through the same windowed reduction as the fused update: deterministic, no atomics.
+ */
+int b200_emb_bwd_dense_grad(const int64_t* d_row_base, int64_t nnz, const void* d_grad, int64_t T, int64_t B,
+                            int64_t D, int64_t grad_stride_table, int64_t grad_stride_bag, int grad_dtype,
+                            float* d_dense_grad, void* ws, size_t ws_bytes, b200_stream_t stream);
+
+/*
  * Pairwise dot-product feature interaction, forward and backward.
  * Replaces DLRM_Net.interact_features (P/dlrm_s_pytorch.py:309-334, T/dlrm_s_pytorch.py:407-444;
  * cat + bmm + tril gather + cat) and ipex.nn.functional.interaction(*T) (P/dlrm_s_pytorch.py:312).

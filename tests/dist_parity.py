@@ -34,6 +34,10 @@ def main():
     ap.add_argument("--no-overlap", action="store_true", help="peer-memory path: keep every kernel on the main stream")
     ap.add_argument("--report", action="store_true", help="print the largest deviations instead of asserting on weights")
     ap.add_argument("--chunks", type=int, default=1, help="peer-memory path: micro-batches per step (SGD only)")
+    ap.add_argument("--boundary", type=int, default=0,
+                    help="sparse_dense_boundary: smaller tables are replicated on every rank (needs --p2p); the ranks "
+                         "are then fed like the reference's training variant -- every table's bags for the LOCAL "
+                         "batch -- and the sharded tables' bags travel through the index all-to-all")
     ap.add_argument("--eval-steps", type=int, default=0,
                     help="after training: forward-only passes (eval mode, no_grad) compared with the oracle's predictions")
     a = ap.parse_args()
@@ -47,6 +51,8 @@ def main():
     dev = torch.device("cuda", torch.cuda.current_device())
     D = 128
     rows = [5000, 37, 20000, 3, 1200, 800, 64, 100000][:a.tables]
+    if a.boundary:  # small tables first: the model's feature order (dense tables, then sharded ones) is then the
+        rows = [r for r in rows if r < a.boundary] + [r for r in rows if r >= a.boundary]  # oracle's natural order
     F = len(rows) + 1
     ln_bot, ln_top = [13, 256, D], [D + F * (F - 1) // 2, 512, 256, 1]
     lr = 0.05
@@ -55,7 +61,7 @@ def main():
     np.random.seed(11)
     net = DLRM_Net(D, np.array(rows), np.array(ln_bot), np.array(ln_top), sigmoid_top=len(ln_top) - 2,
                    np_init_emb_weight=True, device=dev, lr=lr if a.adagrad else lr / world, bf16=a.bf16,
-                   n_rowwise=a.rowwise,
+                   n_rowwise=a.rowwise, sparse_dense_boundary=a.boundary,
                    emb_optimizer="adagrad" if a.adagrad else "sgd")
     local = net.local_ln_emb
     n_tw = len(rows) - a.rowwise
@@ -64,6 +70,9 @@ def main():
             net.emb_l.weights[k].copy_(port.emb_l[t].weight)
         for k in range(a.rowwise):
             net.rowwise.emb.weights[k].copy_(port.emb_l[n_tw + k].weight[rank::world])
+        if net.emb_dense is not None:
+            for p_, t in zip(net.emb_dense.params(), net.ln_emb_dense):
+                p_.copy_(port.emb_l[t].weight)
         for dst, src in ((net.bot_l, port.bot_l), (net.top_l, port.top_l)):
             for pd, ps in zip(dst.parameters(), src.parameters()):
                 pd.copy_(ps)
@@ -116,6 +125,14 @@ def main():
                                                           [lS_o[t] for t in range(n_tw, len(rows))],
                                                           rows[n_tw:])
             Z = net(Xl, ind, off, None, torch.tensor(ri).to(dev), torch.tensor(ro).to(dev)).float()
+        elif a.boundary:
+            def local_bags(t):  # bags [rank*lN, (rank+1)*lN) of table t
+                o = torch.tensor(lS_o[t])
+                s0 = int(o[rank * lN])
+                s1 = int(o[(rank + 1) * lN]) if (rank + 1) * lN < N else len(lS_i[t])
+                return (o[rank * lN:(rank + 1) * lN] - s0).to(dev), torch.tensor(lS_i[t][s0:s1]).to(dev)
+            bags = [local_bags(t) for t in range(len(rows))]
+            Z = net(Xl, [b[0] for b in bags], [b[1] for b in bags]).float()
         elif a.chunks > 1:
             from cloudtik_b200.dlrm import train_step_chunked
             from cloudtik_b200.p2p import split_global_batch
@@ -170,6 +187,10 @@ def main():
         w = net.emb_l.weights[k].float().cpu().numpy()
         np.testing.assert_allclose(w, port.emb_l[t].weight.detach().numpy(), rtol=tol,
                                    atol=atol_w, err_msg=f"table {t}")
+    if net.emb_dense is not None:
+        for p_, t in zip(net.emb_dense.params(), net.ln_emb_dense):
+            np.testing.assert_allclose(p_.detach().cpu().numpy(), port.emb_l[t].weight.detach().numpy(), rtol=tol,
+                                       atol=atol_w, err_msg=f"replicated table {t}")
     for k in range(a.rowwise):
         w = net.rowwise.full_table(k).cpu().numpy()
         np.testing.assert_allclose(w, port.emb_l[n_tw + k].weight.detach().numpy(), rtol=tol,

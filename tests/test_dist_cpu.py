@@ -66,6 +66,57 @@ def _worker(rank, world, port, n_tables, N, E, ret):
             g_o, g_i = ext_dist.global_batch_indices(sh, len(local))
             for k, t in enumerate(local):
                 assert torch.equal(g_i[k], idx[t]) and torch.equal(g_o[k], torch.arange(N))
+        # shuffle_bags: the generalised index all-to-all (uneven table split, ragged multi-hot bags, lengths travel)
+        g = torch.Generator().manual_seed(77)
+        bags = []
+        for t in range(n_tables):
+            lens = torch.randint(0, 4, (N,), generator=g)
+            bags.append((torch.randint(0, 11 + 3 * t, (int(lens.sum()),), generator=g), torch.cumsum(lens, 0) - lens, lens))
+        lo, li = [], []
+        for ind, off, lens in bags:  # this rank's local slice of every table's bags
+            a = int(off[rank * lN]) if lN else 0
+            b = int(off[(rank + 1) * lN]) if (rank + 1) * lN < N else ind.numel()
+            lo.append(off[rank * lN:(rank + 1) * lN] - a)
+            li.append(ind[a:b])
+        g_o, g_i = ext_dist.shuffle_bags(lo, li, splits)
+        assert len(g_i) == len(local)
+        for k, t in enumerate(local):
+            assert torch.equal(g_i[k], bags[t][0]) and torch.equal(g_o[k], bags[t][1]), f"table {t}"
+        # ... and its no-sync flavour for a fixed pooling factor
+        P = 2
+        fixed = [torch.randint(0, 11 + 3 * t, (N * P,), generator=g) for t in range(n_tables)]
+        g_o, g_i = ext_dist.shuffle_bags([torch.arange(lN) * P] * n_tables,
+                                         [f[rank * lN * P:(rank + 1) * lN * P] for f in fixed], splits, fixed_pooling=P)
+        for k, t in enumerate(local):
+            assert torch.equal(g_i[k], fixed[t]) and torch.equal(g_o[k], torch.arange(N) * P)
+        # flat all-reduce with an early bucket reduced from inside backward (post-accumulate hooks)
+        lin1, lin2 = torch.nn.Linear(3, 2), torch.nn.Linear(2, 1)
+        with torch.no_grad():
+            for p_ in list(lin1.parameters()) + list(lin2.parameters()):
+                p_.fill_(0.5)
+        allp = list(lin1.parameters()) + list(lin2.parameters())
+        red = ext_dist.DenseGradAllreduce(allp, average=True, early=list(lin2.parameters()))
+        for passes in (1, 2):
+            for p_ in allp:
+                p_.grad = None
+            red.begin(passes)
+            xs = [torch.full((4, 3), float(rank + 1 + q)) for q in range(passes)]
+            for xq in xs:
+                (lin2(lin1(xq)).sum() / passes).backward()
+            red()
+            # reference: mean over ranks of the same computation
+            want = []
+            for r in range(world):
+                l1, l2 = torch.nn.Linear(3, 2), torch.nn.Linear(2, 1)
+                with torch.no_grad():
+                    for p_ in list(l1.parameters()) + list(l2.parameters()):
+                        p_.fill_(0.5)
+                for q in range(passes):
+                    (l2(l1(torch.full((4, 3), float(r + 1 + q)))).sum() / passes).backward()
+                want.append([p_.grad.clone() for p_ in list(l2.parameters()) + list(l1.parameters())])
+            for k, p_ in enumerate(red.params):
+                w = sum(wr[k] for wr in want) / world
+                assert torch.allclose(p_.grad, w, rtol=1e-6, atol=1e-6), (passes, k)
         # flat all-reduce of the data-parallel MLP gradients (stand-in for DDP): mean and sum flavours
         ps = [torch.nn.Parameter(torch.zeros(3, 2)), torch.nn.Parameter(torch.zeros(5))]
         for average in (True, False):

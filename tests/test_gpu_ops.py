@@ -280,6 +280,35 @@ def test_emb_bwd_reader_right_behind_update_with_all_distinct_rows():
         assert bool((snap == -1.0).all()), f"rep {rep}: {int((snap != -1.0).sum())} stale elements"
 
 
+@pytest.mark.parametrize("rows,B,D,pooling,ragged,gdt", [([3, 1543, 63, 10], 3000, 128, 1, False, torch.float32),
+                                                         ([3, 40, 7], 700, 128, 3, True, torch.bfloat16),
+                                                         ([5, 9], 64, 16, 2, True, torch.float32),
+                                                         ([50, 20, 10], 7, 2, 2, True, torch.float32)])
+def test_emb_bwd_dense_grad(rows, B, D, pooling, ragged, gdt):
+    """Dense gradient of small (replicated) tables: prepare + b200_emb_bwd_dense_grad vs the oracle's scatter-add
+    (what autograd gives nn.EmbeddingBag(sparse=False), T/dlrm_s_pytorch.py:266-269); untouched rows stay zero."""
+    ops = _ops()
+    rs = np.random.RandomState(B + D)
+    _, tw = _tables(rs, rows, D, torch.float32)
+    idx_l, off_l = _make_bags(rs, rows, B, pooling, ragged)
+    indices, offsets, _ = ref.linearize_indices_and_offsets(idx_l, off_l, rows)
+    T, F = len(rows), len(rows) + 1
+    g = torch.tensor(rs.randn(B, F, D).astype(np.float32)).to(gdt).cuda()
+    gr = g.float().cpu().numpy().astype(np.float64)
+    ts = ops.TableSet(tw)
+    ws = torch.empty(ops.emb_bwd_workspace_bytes(len(indices), D), dtype=torch.uint8, device="cuda")
+    ops.emb_bwd_prepare(ts, torch.tensor(indices).cuda(), torch.tensor(offsets).cuda(), B, ws)
+    G = torch.zeros(sum(rows), D, device="cuda")
+    ops.emb_bwd_dense_grad(ts, len(indices), B, g[:, 1:], D, F * D, G, ws)
+    got = G.cpu().numpy()
+    base = 0
+    for t in range(T):
+        want = np.zeros((rows[t], D))
+        np.add.at(want, idx_l[t], gr[:, 1 + t][ref.offset2bag(off_l[t], len(idx_l[t]))])
+        np.testing.assert_allclose(got[base:base + rows[t]], want, rtol=1e-5, atol=1e-5 * max(1.0, np.abs(want).max()))
+        base += rows[t]
+
+
 @pytest.mark.parametrize("opt", ["sgd", "adagrad"])
 def test_bf16_tables_with_trail_update_in_fp32(opt):
     """bf16 tables + 16-bit trail (the reference's split-SGD storage): the fused update must behave like
