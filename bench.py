@@ -52,8 +52,9 @@ def parse():
                     help="strong scaling: fixed GLOBAL batch split over the GPUs (BASELINE configs[3]: 65536); "
                          "overrides --batch and reports \"scaling\": \"strong\"")
     ap.add_argument("--chunks", type=int, default=0,
-                    help="multi-GPU peer-memory path: micro-batches per step (0 = 1 on one GPU, 2 on several); one "
-                         "chunk's NVLink exchange runs under another chunk's compute")
+                    help="multi-GPU peer-memory path: micro-batches per step (default 1); with several, one chunk's "
+                         "NVLink exchange runs under another chunk's compute (measured slower at 2 GPUs: the step's "
+                         "many small kernels do not shrink with the chunk)")
     ap.add_argument("--no-parity", action="store_true", help="multi-GPU: skip the pre-flight parity check")
     ap.add_argument("--sparse-dense-boundary", type=int, default=2048,
                     help="multi-GPU: tables with fewer rows are replicated on every rank instead of sharded (the "
@@ -444,9 +445,7 @@ def run_b200_arm(a):
     rows = table_rows(a.rows_cap)
     B_loc, B_glob, scaling = batch_sizes(a, world)
     use_p2p = world > 1 and not a.no_p2p
-    n_chunks = a.chunks if a.chunks > 0 else (2 if use_p2p else 1)
-    if not use_p2p:
-        n_chunks = 1
+    n_chunks = a.chunks if (a.chunks > 0 and use_p2p) else 1
     boundary = a.sparse_dense_boundary if use_p2p and n_chunks == 1 else 0
     parity = None
     if world > 1 and not a.no_parity:

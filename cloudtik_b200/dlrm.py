@@ -77,6 +77,7 @@ class DLRM_Net(nn.Module):
         self.fused_mlp = True
         self.peer_exchange = None  # set by enable_peer_exchange(): fused a2a over NVLink peer memory
         self.peer_exchanges = None  # one per micro-batch of a step (peer_exchange is the first)
+        self.exchange_first = None  # peer-memory path: start the exchange before the bottom MLP (None = by world size)
         ln_emb = np.asarray(ln_emb)
         # the LAST n_rowwise tables are row-wise sharded over the ranks (hot tables, config 5); the others
         # are partitioned table-wise exactly like the reference (P/dlrm_s_pytorch.py:256-264)
@@ -233,10 +234,18 @@ def _p2p_forward(self, dense_x, *emb_args, chunk=0, dense_bags=None):
         raise RuntimeError("row-wise sharded tables need (indices, offsets, None, rw_indices, rw_offsets)")
     feat0 = 1 + len(self.ln_emb_dense) + self.local_ln_emb_slice.start
     train = self.training and torch.is_grad_enabled()
-    if train and len(self.peer_exchanges) == 1:
-        prelaunch(self.emb_l, exch, indices, offsets, feat0)  # NVLink exchange || bottom MLP
+    # When does the NVLink-bound exchange start on the side stream?  Launched ahead of the (short) bottom MLP, its
+    # thousands of long-lived thread blocks hold every SM slot and stretch the MLP's small kernels to about 150 us;
+    # that only pays when the exchange itself is the longer of the two, i.e. from 4 ranks on (230 us at 8 ranks,
+    # 105 us at 2).  Either way the replicated tables' local lookup runs next to it.
+    first = train and len(self.peer_exchanges) == 1 and (self.exchange_first if self.exchange_first is not None
+                                                          else exch.world > 2)
+    if first:
+        prelaunch(self.emb_l, exch, indices, offsets, feat0)
     with torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.bf16):
         x = self.apply_mlp(self._pad_dense(dense_x), self.bot_l)
+        if train and len(self.peer_exchanges) == 1 and not first:
+            prelaunch(self.emb_l, exch, indices, offsets, feat0)
         z = sharded_emb_interact(x, self.emb_l, exch, indices, offsets, feat0,
                                  pad_to=self.interaction_pad, rowwise=self.rowwise, rw_indices=rw_i,
                                  rw_offsets=rw_o, train=train, repl=self.emb_dense,
@@ -315,6 +324,9 @@ def train_step_chunked(dlrm, optimizer, batch, post_backward=None):
         dlrm.begin_step(pairs)
     per = X.shape[0] // n
     total = None
+    rep = getattr(dlrm, "emb_dense", None)
+    if rep is not None:
+        rep.defer = True  # dense gradients of the replicated tables off the main chain; joined before the all-reduce
     for c, (idx, off) in enumerate(pairs):
         Xc, Yc = (X, Y) if n == 1 else (X[c * per:(c + 1) * per], Y[c * per:(c + 1) * per])
         Z = (dlrm(Xc, idx, off, None, chunk=c) if dense_bags is None
@@ -322,6 +334,9 @@ def train_step_chunked(dlrm, optimizer, batch, post_backward=None):
         E = dlrm.loss_fn(Z, Yc)
         (E if n == 1 else E / n).backward()
         total = E.detach() if total is None else total + E.detach()
+    if rep is not None:
+        rep.defer = False
+        rep.join()
     if post_backward is not None:
         post_backward()
     optimizer.step()

@@ -69,6 +69,12 @@ class _ShardedEmbInteractFn(torch.autograd.Function):
     def forward(ctx, x, trigger, emb, exch, indices, offsets, feat0, pad_to, rowwise=None, rw_indices=None,
                 rw_offsets=None, train=True, repl=None, repl_indices=None, repl_offsets=None, *repl_weights):
         B_glob = exch.lN * exch.world
+        if repl is not None:
+            # replicated small tables: LOCAL batch, feature slots 1 .. n right behind x.  Local reads and writes only,
+            # so it goes first and runs under the tail of the exchange the next lines wait for
+            repl.pool_into(repl_indices, repl_offsets, exch.lN, exch.T[:, 1:1 + repl.n_tables], exch.D, exch.F * exch.D)
+            if train:
+                repl.launch_prepare(repl_indices, repl_offsets, exch.lN)
         if emb is not None:
             pend = emb._take_pending_sharded(exch.chunk)
             if pend is not None and pend[0] is indices and pend[1] is offsets:
@@ -85,10 +91,6 @@ class _ShardedEmbInteractFn(torch.autograd.Function):
             rw_out, ctx.rw_ctx = rowwise.pool(rw_indices, rw_offsets, exch.lN)
             exch.T[:, exch.F - rowwise.k:].copy_(rw_out)
         exch.T[:, 0].copy_(x)
-        if repl is not None:  # replicated small tables: LOCAL batch, feature slots 1 .. n right behind x
-            repl.pool_into(repl_indices, repl_offsets, exch.lN, exch.T[:, 1:1 + repl.n_tables], exch.D, exch.F * exch.D)
-            if train:
-                repl.launch_prepare(repl_indices, repl_offsets, exch.lN, emb._side_stream if emb is not None else None)
         exch.barrier(0)  # B1
         R = ops.interact_fwd(exch.T, pad_to=pad_to)
         if not train:

@@ -43,6 +43,13 @@ class ReplicatedEmbeddingBags(nn.Module):
         self.error_flag = None
         self._ws = None
         self._prep_event = None
+        # The index stage and (when `defer` is set by the step driver) the dense-gradient kernels run on this
+        # module's own low-priority stream: nothing on the step's main chain needs them before the gradient
+        # all-reduce, which `join()` precedes.
+        self._stream = None
+        self._grad_event = None
+        self._pending_grads = None
+        self.defer = False
         self._rebuild()
 
     def params(self) -> List[nn.Parameter]:
@@ -75,14 +82,17 @@ class ReplicatedEmbeddingBags(nn.Module):
         input: table t of bag b at ``out.data_ptr + (t * stride_table + b * stride_bag)`` elements)."""
         ops.emb_fwd(self._tables_checked(), indices, offsets, B, out, stride_table, stride_bag, self.error_flag)
 
-    def launch_prepare(self, indices, offsets, B: int, side: torch.cuda.Stream | None):
-        """Index stage of the backward (keys, stable sort, dedup) on ``side`` if given (it only needs the indices)."""
+    def _own_stream(self):
+        if self._stream is None:
+            self._stream = torch.cuda.Stream(device=self.tables.device)
+        return self._stream
+
+    def launch_prepare(self, indices, offsets, B: int):
+        """Index stage of the backward (keys, stable sort, dedup) on this module's own stream: it only needs the
+        indices, so it runs next to the forward pass."""
         ws = self._workspace(indices.numel())
         tables = self._tables_checked()
-        if side is None:
-            ops.emb_bwd_prepare(tables, indices, offsets, B, ws, self.error_flag)
-            self._prep_event = None
-            return
+        side = self._own_stream()
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
             ops.emb_bwd_prepare(tables, indices, offsets, B, ws, self.error_flag)
@@ -92,16 +102,48 @@ class ReplicatedEmbeddingBags(nn.Module):
 
     def dense_grads(self, indices, offsets, B: int, grad_base: torch.Tensor, stride_table: int, stride_bag: int):
         """Per-table dense fp32 gradients (row-slices of one [total_rows, D] buffer) from the gradient of the
-        pooled rows, addressed like ``pool_into``'s output.  ``launch_prepare`` must have run for these bags."""
-        if self._prep_event is not None:
-            torch.cuda.current_stream().wait_event(self._prep_event)
-            self._prep_event = None
+        pooled rows, addressed like ``pool_into``'s output.  ``launch_prepare`` must have run for these bags.
+        With ``defer`` set the kernels are queued on this module's stream and ``join()`` must be called on the
+        consuming stream before the gradients are read (cloudtik_b200.dlrm.train_step_chunked does)."""
         tables = self.tables
-        G = torch.zeros(tables.total_rows, self.dim, dtype=torch.float32, device=tables.device)
-        ops.emb_bwd_dense_grad(tables, indices.numel(), B, grad_base, stride_table, stride_bag, G,
-                               self._workspace(indices.numel()))
+        ws = self._workspace(indices.numel())
+
+        def run():
+            G = torch.zeros(tables.total_rows, self.dim, dtype=torch.float32, device=tables.device)
+            ops.emb_bwd_dense_grad(tables, indices.numel(), B, grad_base, stride_table, stride_bag, G, ws)
+            return G
+        if self.defer:
+            side = self._own_stream()  # already behind the index stage
+            side.wait_stream(torch.cuda.current_stream())  # the gradient of the pooled rows is complete
+            self._prep_event = None
+            with torch.cuda.stream(side):
+                G = run()
+                ev = torch.cuda.Event()
+                ev.record(side)
+            self._grad_event = ev
+            # autograd must not touch these tensors before join(): hand them to the parameters there, not now
+            views, base = [], 0
+            for n in tables.rows:
+                views.append(G[base:base + n])
+                base += n
+            self._pending_grads = views
+            return [None] * len(views)
+        else:
+            if self._prep_event is not None:
+                torch.cuda.current_stream().wait_event(self._prep_event)
+                self._prep_event = None
+            G = run()
         out, base = [], 0
         for n in tables.rows:
             out.append(G[base:base + n])
             base += n
         return out
+
+    def join(self):
+        """Order the current stream behind deferred dense-gradient kernels (no-op otherwise)."""
+        ev, self._grad_event = self._grad_event, None
+        if ev is not None:
+            torch.cuda.current_stream().wait_event(ev)
+            for p, g in zip(self.params(), self._pending_grads):
+                p.grad = g if p.grad is None else p.grad + g
+            self._pending_grads = None
