@@ -10,6 +10,8 @@
 // (G*16 bytes coalesced per row).  The staged tile is first compacted to 32-bit offsets / row
 // ids (bounds check done once there).  One-hot tiles take a copy-through path with four bags in
 // flight per group; pooled bags accumulate in fp32 in index order, four rows in flight.
+#include <stdlib.h>
+
 #include <algorithm>
 
 #include "common.cuh"
@@ -263,6 +265,309 @@ __global__ void __launch_bounds__(FWD_THREADS) emb_fwd_kernel(const EmbFwdParams
   }
 }
 
+// ------------------------------------------------------------------ persistent, software-pipelined variant
+// grid = a few CTAs per SM; every CTA walks over (table, bag tile) work items w = blockIdx.x, + gridDim.x, ...
+// While the sub-warp groups gather tile i, the TMA engine is already fetching what the next tiles need:
+//   offsets of tile i+3  -> one of three offset slots   (issued by thread 0 at the top of iteration i)
+//   indices of tile i+2  -> one of two index slots      (their window is known once offsets(i+2) have landed)
+// and the 64 -> 32 bit compaction (bounds check, offsets relative to the window) of tile i+1 is done by all
+// threads in the shadow of tile i's FIRST batch of row loads: issue the loads, compact, only then consume them.
+// One __syncthreads per tile.  The one-shot kernel above spends about a third of a CTA's life in the chain
+// offsets -> wait -> indices -> wait -> compaction before its first row load; here that chain is off the path.
+constexpr int FWD_OSLOTS = 3;
+constexpr int FWD_OFF_PAD = FWD_MAX_TILE + 4;
+
+struct FwdTileInfo {
+  int64_t i0;   // first index position of the tile's window
+  int staged;   // window staged in s_idx (fits, in range)
+  int shift;    // i0 - (16-byte aligned start of the bulk copy)
+};
+
+template <typename WT, typename OT, int G, int NV>
+__global__ void __launch_bounds__(FWD_THREADS, 4)
+    emb_fwd_persist_kernel(const EmbFwdParams p, int n_items, int tiles_per_table, int cap) {
+  constexpr int VE = Vec16<WT>::VE;
+  constexpr int NG = FWD_THREADS / G;
+  constexpr bool Q8 = sizeof(WT) == 1;
+  constexpr int UF = NV == 1 ? 8 : 4;  // rows in flight per group on the one-hot path
+  extern __shared__ __align__(16) unsigned char fwd_smem[];
+  // carve-up (all 16-byte aligned): s_off[3][OFF_PAD] i64 | s_idx[2][cap+2] i64 | s_off64[2][MAX_TILE+2] i64 |
+  //                                 s_row[2][cap+2] u32 | s_rel[2][MAX_TILE+4] i32
+  int64_t* s_off = reinterpret_cast<int64_t*>(fwd_smem);
+  int64_t* s_idx = s_off + FWD_OSLOTS * FWD_OFF_PAD;
+  int64_t* s_off64 = s_idx + 2 * (cap + 2);
+  uint32_t* s_row = reinterpret_cast<uint32_t*>(s_off64 + 2 * (FWD_MAX_TILE + 2));
+  int* s_rel = reinterpret_cast<int*>(s_row + 2 * (cap + 2));
+  __shared__ __align__(8) uint64_t bar_off[FWD_OSLOTS];
+  __shared__ __align__(8) uint64_t bar_idx[2];
+  __shared__ FwdTileInfo d_info[FWD_OSLOTS];
+  __shared__ int d_osh[FWD_OSLOTS];     // first offset of the tile sits at s_off[slot][d_osh]
+  __shared__ int d_notone[FWD_OSLOTS];  // some bag of the tile does not hold exactly one index
+
+  const int tid = threadIdx.x, gid = tid / G, lane = tid % G;
+  const int n_mine = (n_items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // blockIdx.x < n_items
+  const int64_t n_off_total = (int64_t)(n_items / tiles_per_table) * p.B + 1;  // entries of the CSR array
+
+  auto item = [&](int li, int& t, int64_t& b0, int& nb) {
+    const int w = (int)blockIdx.x + li * (int)gridDim.x;
+    t = w / tiles_per_table;
+    b0 = (int64_t)(w - t * tiles_per_table) * p.tile;
+    nb = (int)min((int64_t)p.tile, p.B - b0);
+  };
+  // ---- thread 0 only: start the bulk copy of tile li's offsets
+  auto issue_off = [&](int li) {
+    int t, nb;
+    int64_t b0;
+    item(li, t, b0, nb);
+    const int slot = li % FWD_OSLOTS;
+    int64_t* dst = s_off + slot * FWD_OFF_PAD;
+    const int64_t first = (int64_t)t * p.B + b0;
+    const int64_t a = first & ~(int64_t)1;
+    const int sh = (int)(first - a);
+    int n = nb + 1 + sh;
+    if ((n & 1) && a + n + 1 <= n_off_total) ++n;  // round the copy up to 16 bytes when the array allows it
+    const int nbulk = n & ~1;
+    if (n & 1) dst[n - 1] = p.offsets[a + n - 1];  // very last tile of the array only
+    d_osh[slot] = sh;
+    if (nbulk > 0) {
+      mbar_expect_tx(&bar_off[slot], nbulk * 8);
+      bulk_g2s(dst, p.offsets + a, nbulk * 8, &bar_off[slot]);
+    } else {
+      mbar_arrive(&bar_off[slot]);
+    }
+  };
+  // ---- thread 0 only: offsets of tile li have landed -> start the bulk copy of its index window
+  auto issue_idx = [&](int li) {
+    int t, nb;
+    int64_t b0;
+    item(li, t, b0, nb);
+    const int slot = li % FWD_OSLOTS, islot = li & 1;
+    mbar_wait(&bar_off[slot], (uint32_t)(li / FWD_OSLOTS) & 1u);
+    const int64_t* o = s_off + slot * FWD_OFF_PAD + d_osh[slot];
+    const int64_t i0 = o[0], i1 = o[nb];
+    const int64_t a0 = i0 & ~(int64_t)1;
+    FwdTileInfo inf;
+    inf.i0 = i0;
+    inf.shift = (int)(i0 - a0);
+    int64_t n = i1 - a0;
+    inf.staged = (i1 > i0 && n <= cap && i0 >= 0 && i1 <= p.nnz) ? 1 : 0;
+    d_info[slot] = inf;
+    if (inf.staged) {
+      if ((n & 1) && a0 + n + 1 <= p.nnz) ++n;
+      const int nbulk = (int)n & ~1;
+      int64_t* dst = s_idx + islot * (cap + 2);
+      if (n & 1) dst[n - 1] = p.indices[a0 + n - 1];
+      if (nbulk > 0) {
+        mbar_expect_tx(&bar_idx[islot], nbulk * 8);
+        bulk_g2s(dst, p.indices + a0, nbulk * 8, &bar_idx[islot]);
+        return;
+      }
+    }
+    mbar_arrive(&bar_idx[islot]);
+  };
+  // ---- all threads: 64 -> 32 bit compaction of tile li (its index copy was issued an iteration ago)
+  auto compact = [&](int li) {
+    int t, nb;
+    int64_t b0;
+    item(li, t, b0, nb);
+    const int slot = li % FWD_OSLOTS, islot = li & 1, buf = li & 1;
+    mbar_wait(&bar_idx[islot], (uint32_t)(li / 2) & 1u);
+    const FwdTileInfo inf = d_info[slot];
+    const int64_t* o = s_off + slot * FWD_OFF_PAD + d_osh[slot];
+    const int64_t nrows = p.rows[t];
+    if (inf.staged && nrows < 0xffffffffll) {
+      int* rel = s_rel + buf * (FWD_MAX_TILE + 4);
+      bool one = true;
+      for (int i = tid; i <= nb; i += FWD_THREADS) {
+        rel[i] = (int)(o[i] - inf.i0);
+        if (i < nb) one = one && (o[i + 1] - o[i] == 1);
+      }
+      if (!one) d_notone[slot] = 1;
+      const int cnt = (int)(o[nb] - inf.i0);
+      const int64_t* src = s_idx + islot * (cap + 2) + inf.shift;
+      uint32_t* row = s_row + buf * (cap + 2);
+      for (int k = tid; k < cnt; k += FWD_THREADS) {
+        const int64_t idx = src[k];
+        const bool ok = (uint64_t)idx < (uint64_t)nrows;
+        if (!ok && p.error) *p.error = 1;
+        row[k] = ok ? (uint32_t)idx : 0xffffffffu;
+      }
+    } else {  // window too long for the staging buffer: the gather reads the indices from global memory
+      int64_t* o64 = s_off64 + buf * (FWD_MAX_TILE + 2);
+      for (int i = tid; i <= nb; i += FWD_THREADS) o64[i] = o[i];
+      if (tid == 0) d_notone[slot] = 2;  // marks "unstaged"
+    }
+  };
+
+  if (tid == 0) {
+    for (int s_ = 0; s_ < FWD_OSLOTS; ++s_) {
+      mbar_init(&bar_off[s_], 1);
+      d_notone[s_] = 0;
+    }
+    mbar_init(&bar_idx[0], 1);
+    mbar_init(&bar_idx[1], 1);
+    fence_mbar_init();
+    for (int li = 0; li < FWD_OSLOTS && li < n_mine; ++li) issue_off(li);
+    for (int li = 0; li < 2 && li < n_mine; ++li) issue_idx(li);
+  }
+  __syncthreads();
+  compact(0);
+  __syncthreads();
+
+  const size_t row_bytes = (size_t)p.D * sizeof(WT);
+  for (int li = 0; li < n_mine; ++li) {
+    if (tid == 0) {
+      // slot li % 3 held tile li's offsets (compacted one iteration ago): reuse it for tile li + 3
+      if (li + FWD_OSLOTS < n_mine) issue_off(li + FWD_OSLOTS);
+      d_notone[(li + 2) % FWD_OSLOTS] = 0;
+      if (li >= 0 && li + 2 < n_mine) issue_idx(li + 2);
+    }
+    int t, nb;
+    int64_t b0;
+    item(li, t, b0, nb);
+    const int slot = li % FWD_OSLOTS, buf = li & 1;
+    const int mode = d_notone[slot];  // 0: every bag holds one index, 1: ragged / pooled, 2: unstaged
+    const int64_t nrows = p.rows[t];
+    const float* S = Q8 ? p.scales[t] : nullptr;
+    const char* Wl = static_cast<const char*>(p.weights[t]) + (size_t)lane * 16;
+    OT* out_t;
+    if (p.out_ptrs != nullptr) {  // this tile's bags all belong to one destination rank
+      const int64_t r = b0 / p.lN;
+      out_t = static_cast<OT*>(p.out_ptrs[r]) + ((b0 - r * p.lN) * p.F + p.feat0 + t) * p.D;
+    } else {
+      out_t = static_cast<OT*>(p.out) + (int64_t)t * p.out_stride_table + b0 * p.out_stride_bag;
+    }
+    OT* outl = out_t + lane * VE;
+    const uint32_t* row_s = s_row + buf * (cap + 2);
+    const int* rel = s_rel + buf * (FWD_MAX_TILE + 4);
+    bool next_done = li + 1 >= n_mine;
+    // compaction of the NEXT tile, run once by every thread in the shadow of this tile's first batch of loads
+    auto mid = [&]() {
+      if (!next_done) {
+        compact(li + 1);
+        next_done = true;
+      }
+    };
+
+    if (mode == 0) {
+      // every bag of the tile holds exactly one index (Criteo one-hot): bag k reads row s_row[k]
+      for (int r = gid; r < nb; r += UF * NG) {
+        uint32_t row[UF];
+#pragma unroll
+        for (int u = 0; u < UF; ++u) row[u] = (r + u * NG < nb) ? row_s[r + u * NG] : 0xffffffffu;
+        uint4 v[UF][NV];
+        float sc[UF];
+#pragma unroll
+        for (int u = 0; u < UF; ++u) {
+          const char* src = Wl + (size_t)row[u] * row_bytes;
+          sc[u] = (Q8 && row[u] != 0xffffffffu) ? __ldg(S + row[u]) : 1.f;
+#pragma unroll
+          for (int k = 0; k < NV; ++k)
+            v[u][k] = (row[u] != 0xffffffffu && lane + k * G < p.V) ? ld_nc_v4(src + (size_t)k * G * 16)
+                                                                   : make_uint4(0, 0, 0, 0);
+        }
+        mid();
+#pragma unroll
+        for (int u = 0; u < UF; ++u) {
+          if (r + u * NG < nb) {
+            OT* dst = outl + (int64_t)(r + u * NG) * p.out_stride_bag;
+#pragma unroll
+            for (int k = 0; k < NV; ++k) {
+              if (lane + k * G < p.V) {
+                if constexpr (sizeof(WT) == sizeof(OT)) {
+                  st_cs_v4(dst + k * G * VE, v[u][k]);
+                } else {
+                  float f[VE];
+                  Vec16<WT>::unpack(f, v[u][k]);
+                  if constexpr (Q8) {
+#pragma unroll
+                    for (int x = 0; x < VE; ++x) f[x] *= sc[u];
+                  }
+                  store_vec<OT, VE, true>(dst + k * G * VE, f);
+                }
+              }
+            }
+          }
+        }
+      }
+    } else if (mode == 1) {
+      // pooled / ragged bags, indices staged: fp32 accumulation in index order, 4 rows in flight
+      for (int bag = gid; bag < nb; bag += NG) {
+        const int sb = rel[bag], eb = rel[bag + 1];
+        float acc[NV][VE];
+#pragma unroll
+        for (int k = 0; k < NV; ++k)
+#pragma unroll
+          for (int x = 0; x < VE; ++x) acc[k][x] = 0.f;
+        for (int j = sb; j < eb; j += 4) {
+          uint4 v[4][NV];
+          float sc[4];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const uint32_t row = (j + q < eb) ? row_s[j + q] : 0xffffffffu;
+            const char* src = Wl + (size_t)row * row_bytes;
+            sc[q] = (Q8 && row != 0xffffffffu) ? __ldg(S + row) : 0.f;
+#pragma unroll
+            for (int k = 0; k < NV; ++k)
+              v[q][k] = (row != 0xffffffffu && lane + k * G < p.V) ? ld_nc_v4(src + (size_t)k * G * 16)
+                                                                 : make_uint4(0, 0, 0, 0);
+          }
+          mid();
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int k = 0; k < NV; ++k) accum_row<WT>(acc[k], v[q][k], sc[q]);
+        }
+        OT* dst = outl + (int64_t)bag * p.out_stride_bag;
+#pragma unroll
+        for (int k = 0; k < NV; ++k)
+          if (lane + k * G < p.V) store_vec<OT, VE, true>(dst + k * G * VE, acc[k]);
+      }
+    } else {
+      // index window does not fit the staging buffer (very long bags): indices straight from global memory
+      const int64_t* o64 = s_off64 + buf * (FWD_MAX_TILE + 2);
+      for (int bag = gid; bag < nb; bag += NG) {
+        const int64_t sb = o64[bag], eb = o64[bag + 1];
+        float acc[NV][VE];
+#pragma unroll
+        for (int k = 0; k < NV; ++k)
+#pragma unroll
+          for (int x = 0; x < VE; ++x) acc[k][x] = 0.f;
+        for (int64_t j = sb; j < eb; j += 4) {
+          uint4 v[4][NV];
+          float sc[4];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            bool ok = false;
+            int64_t idx = 0;
+            if (j + q < eb && j + q >= 0 && j + q < p.nnz) {
+              idx = __ldg(p.indices + j + q);
+              ok = (uint64_t)idx < (uint64_t)nrows;
+              if (!ok && p.error) *p.error = 1;
+            }
+            sc[q] = (Q8 && ok) ? __ldg(S + idx) : 0.f;
+            const char* src = Wl + (ok ? (size_t)idx : 0) * row_bytes;
+#pragma unroll
+            for (int k = 0; k < NV; ++k)
+              v[q][k] = (ok && lane + k * G < p.V) ? ld_nc_v4(src + (size_t)k * G * 16) : make_uint4(0, 0, 0, 0);
+          }
+          mid();
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int k = 0; k < NV; ++k) accum_row<WT>(acc[k], v[q][k], sc[q]);
+        }
+        OT* dst = outl + (int64_t)bag * p.out_stride_bag;
+#pragma unroll
+        for (int k = 0; k < NV; ++k)
+          if (lane + k * G < p.V) store_vec<OT, VE, true>(dst + k * G * VE, acc[k]);
+      }
+    }
+    mid();  // groups without a bag in this tile (and empty bags) still owe their share of the compaction
+    __syncthreads();
+  }
+}
+
 // Fallback for rows that are not a whole number of 16-byte vectors (tiny D in tests).
 template <typename WT, typename OT>
 __global__ void emb_fwd_scalar_kernel(const EmbFwdParams p, int64_t T) {
@@ -291,9 +596,75 @@ __global__ void emb_fwd_scalar_kernel(const EmbFwdParams p, int64_t T) {
   }
 }
 
+static int fwd_sm_count() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+template <typename WT, typename OT, int G, int NV>
+static int launch_fwd_persist(const EmbFwdParams& p, int64_t T, int cap, int ctas_per_sm, cudaStream_t st) {
+  const int64_t tiles = ceil_div(p.B, p.tile);
+  const int64_t n_items = tiles * T;
+  const size_t smem = (size_t)FWD_OSLOTS * FWD_OFF_PAD * 8 + 2 * (size_t)(cap + 2) * 8 + 2 * (FWD_MAX_TILE + 2) * 8 +
+                      2 * (size_t)(cap + 2) * 4 + 2 * (FWD_MAX_TILE + 4) * 4;
+  auto kern = emb_fwd_persist_kernel<WT, OT, G, NV>;
+  if (smem > 48 * 1024) {
+    const cudaError_t rc = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    B200_REQUIRE(rc == cudaSuccess, B200_ELAUNCH, "emb_fwd: cannot reserve %zu bytes of shared memory", smem);
+  }
+  const int64_t grid = std::min<int64_t>(n_items, (int64_t)fwd_sm_count() * ctas_per_sm);
+  kern<<<(unsigned)grid, FWD_THREADS, smem, st>>>(p, (int)n_items, (int)tiles, cap);
+  B200_CHECK_LAUNCH("emb_fwd_persist");
+  return B200_OK;
+}
+
 template <typename WT, typename OT>
 static int launch_fwd(const EmbFwdParams& p, int64_t T, cudaStream_t st) {
   const int V = p.V;
+  // Which launch shape?  Measured on B200 (tools/fwd_ab.sh): one-shot CTAs at 6 per SM gather 4.67 TB/s on the
+  // config-3 tables and 5.85 TB/s on uniform ones, the persistent pipelined kernel at 4 per SM 4.51 / 5.41 (it
+  // hides the staging chain but holds fewer rows in flight and balances its static work split worse across the two
+  // dies).  So the local forward stays one-shot; the peer-memory forward, which NVLink bounds at a fraction of
+  // that rate, runs persistent with few CTAs per SM and leaves the other slots to the kernels it runs next to.
+  // B200_FWD_PERSIST=0 / 1 forces one shape for A/B runs.
+  static const int persist = []() {
+    const char* e = getenv("B200_FWD_PERSIST");
+    return e == nullptr ? -1 : atoi(e);
+  }();
+  static const int env_ctas = []() {
+    const char* e = getenv("B200_FWD_CTAS");
+    return e == nullptr ? 0 : atoi(e);
+  }();
+  const int64_t n_items = ceil_div(p.B, p.tile) * T;
+  const bool aligned = (reinterpret_cast<uintptr_t>(p.offsets) & 15) == 0 &&
+                       (p.nnz == 0 || (reinterpret_cast<uintptr_t>(p.indices) & 15) == 0);
+  const bool want_persist = persist < 0 ? p.out_ptrs != nullptr : persist != 0;
+  if (want_persist && aligned && n_items < ((int64_t)1 << 30) && p.nnz > 0) {
+    // staging capacity: the average window of a tile with 2x head-room for ragged bags (a longer window falls
+    // back to unstaged reads for that tile), at least 256 entries
+    const int64_t avg_pool = std::max<int64_t>(1, (p.nnz + T * p.B - 1) / (T * p.B));
+    int cap = (int)std::min<int64_t>(FWD_IDX_CAP, std::max<int64_t>(256, 2 * avg_pool * p.tile));
+    cap = (cap + 1) & ~1;
+    // resident CTAs per SM: enough row loads in flight for HBM when the output is local; the peer-memory variant is
+    // bound by NVLink and keeps half of the slots free for the kernels it runs next to
+    int ctas = env_ctas > 0 ? env_ctas : (p.out_ptrs != nullptr ? 3 : 4);
+#define B200_FWDP_CASE(G, NV) return launch_fwd_persist<WT, OT, G, NV>(p, T, cap, ctas, st)
+    if (V <= 1) B200_FWDP_CASE(1, 1);
+    else if (V <= 2) B200_FWDP_CASE(2, 1);
+    else if (V <= 4) B200_FWDP_CASE(4, 1);
+    else if (V <= 8) B200_FWDP_CASE(8, 1);
+    else if (V <= 16) B200_FWDP_CASE(16, 1);
+    else if (V <= 32) B200_FWDP_CASE(32, 1);
+    else if (V <= 64) B200_FWDP_CASE(32, 2);
+    else B200_FWDP_CASE(32, 4);
+#undef B200_FWDP_CASE
+  }
   dim3 grid((unsigned)ceil_div(p.B, p.tile), (unsigned)T);
 #define B200_FWD_CASE(G, NV) emb_fwd_kernel<WT, OT, G, NV><<<grid, FWD_THREADS, 0, st>>>(p)
   if (V <= 1) B200_FWD_CASE(1, 1);
