@@ -1,7 +1,7 @@
 """ctypes binding of libb200dlrm.so (the C-ABI declared in include/b200dlrm.h).
 
 There is NO fallback: if the CUDA library is missing or a symbol cannot be bound, importing
-fails loudly.  Build it with ``python -m cloudtik_b200.build`` (or ``__graft_entry__.build()``).
+fails loudly.  Build it with ``python build_lib.py`` (or ``__graft_entry__.build()``).
 """
 from __future__ import annotations
 
@@ -40,6 +40,14 @@ SIGNATURES = {
     "b200_emb_bwd_coalesce": (_int, [_p, _p, _p, _p, _i64, _p, _i64, _i64, _i64, _i64, _i64, _int, _i64, _p, _p, _p,
                                      _p, _c.c_size_t, _p, _p]),
     "b200_emb_bwd_dense_grad": (_int, [_p, _i64, _p, _i64, _i64, _i64, _i64, _i64, _int, _p, _p, _c.c_size_t, _p]),
+    "b200_interact_fwd_ex": (_int, [_p, _p, _i64, _i64, _i64, _i64, _int, _int, _p]),
+    "b200_interact_bwd_ex": (_int, [_p, _p, _p, _i64, _i64, _i64, _i64, _int, _int, _p]),
+    "b200_workspace_bytes": (_c.c_size_t, [_i64, _i64]),
+    "b200_emb_bwd_sgd": (_int, [_p, _p, _p, _p, _p, _p, _i64, _p, _i64, _i64, _i64, _i64, _i64, _int, _int,
+                                _c.c_float, _p, _i64, _p, _c.c_size_t, _p, _p]),
+    "b200_emb_bwd_adagrad": (_int, [_p, _p, _p, _p, _p, _p, _p, _i64, _p, _i64, _i64, _i64, _i64, _i64, _int, _int,
+                                    _c.c_float, _p, _c.c_float, _i64, _p, _c.c_size_t, _p, _p]),
+    "b200_linearize": (_int, [_p, _p, _p, _p, _i64, _i64, _i64, _p, _p, _p, _p]),
     "b200_interact_fwd": (_int, [_p, _p, _i64, _i64, _i64, _i64, _int, _p]),
     "b200_interact_bwd": (_int, [_p, _p, _p, _i64, _i64, _i64, _i64, _int, _p]),
     "b200_emb_fwd_q8": (_int, [_p, _p, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i64, _int, _p, _p]),
@@ -56,7 +64,7 @@ class B200Error(RuntimeError):
 def _load():
     if not os.path.exists(LIB_PATH):
         raise ImportError(
-            f"{LIB_PATH} not found: the CUDA library is not built. Run `python -m cloudtik_b200.build` "
+            f"{LIB_PATH} not found: the CUDA library is not built. Run `python build_lib.py` at the repository root "
             "(needs nvcc); cloudtik_b200 has no CPU fallback.")
     lib = ctypes.CDLL(LIB_PATH)
     for name, (res, args) in SIGNATURES.items():

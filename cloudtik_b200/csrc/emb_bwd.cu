@@ -1036,3 +1036,28 @@ extern "C" int b200_emb_bwd_coalesce(const int64_t* d_rows, const int64_t* d_row
   B200_CHECK_LAUNCH("emb_bwd_coalesce");
   return B200_OK;
 }
+
+// ---- the three names SURVEY.md section 8b lists for this boundary, as thin forms of the entry points above
+extern "C" size_t b200_workspace_bytes(int64_t nnz, int64_t D) { return b200_emb_bwd_workspace_bytes(nnz, D); }
+
+extern "C" int b200_emb_bwd_sgd(void* const* d_weights, uint16_t* const* d_trail, const int64_t* d_rows,
+                                const int64_t* d_row_base, const int64_t* d_indices, const int64_t* d_offsets,
+                                int64_t nnz, const void* d_grad, int64_t T, int64_t B, int64_t D,
+                                int64_t grad_stride_table, int64_t grad_stride_bag, int w_dtype, int grad_dtype,
+                                float lr, const float* d_lr, int64_t total_rows, void* ws, size_t ws_bytes,
+                                int32_t* d_error, b200_stream_t stream) {
+  return b200_emb_bwd_update(d_weights, nullptr, d_trail, d_rows, d_row_base, d_indices, d_offsets, nnz, d_grad, T, B,
+                             D, grad_stride_table, grad_stride_bag, w_dtype, grad_dtype, B200_OPT_SGD, lr, d_lr, 0.f,
+                             total_rows, ws, ws_bytes, d_error, stream);
+}
+
+extern "C" int b200_emb_bwd_adagrad(void* const* d_weights, float* const* d_state, uint16_t* const* d_trail,
+                                    const int64_t* d_rows, const int64_t* d_row_base, const int64_t* d_indices,
+                                    const int64_t* d_offsets, int64_t nnz, const void* d_grad, int64_t T, int64_t B,
+                                    int64_t D, int64_t grad_stride_table, int64_t grad_stride_bag, int w_dtype,
+                                    int grad_dtype, float lr, const float* d_lr, float eps, int64_t total_rows,
+                                    void* ws, size_t ws_bytes, int32_t* d_error, b200_stream_t stream) {
+  return b200_emb_bwd_update(d_weights, d_state, d_trail, d_rows, d_row_base, d_indices, d_offsets, nnz, d_grad, T, B,
+                             D, grad_stride_table, grad_stride_bag, w_dtype, grad_dtype, B200_OPT_ADAGRAD, lr, d_lr,
+                             eps, total_rows, ws, ws_bytes, d_error, stream);
+}

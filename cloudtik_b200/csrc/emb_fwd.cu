@@ -785,3 +785,44 @@ extern "C" int b200_emb_fwd_sharded(const void* const* d_weights, const int64_t*
   return emb_fwd_impl(d_weights, d_rows, d_indices, d_offsets, nullptr, nnz, T, B, D, 0, 0, w_dtype, out_dtype,
                       d_error, stream, d_out_ptrs, lN, F, feat0);
 }
+
+// ------------------------------------------------------------------ linearisation of per-table bags
+// grid = (chunks, T): table t copies its indices to their place in the merged array (and, shifted by the table's
+// row base, into the global-row-id array) and its B start offsets, shifted by the indices before it.
+namespace b200 {
+__global__ void __launch_bounds__(256)
+    linearize_kernel(const int64_t* const* __restrict__ idx_ptrs, const int64_t* const* __restrict__ off_ptrs,
+                     const int64_t* __restrict__ nnz_prefix, const int64_t* __restrict__ row_base, int64_t B, int T,
+                     int64_t* __restrict__ indices, int64_t* __restrict__ offsets, int64_t* __restrict__ iwro) {
+  const int t = blockIdx.y;
+  const int64_t p0 = nnz_prefix[t], n = nnz_prefix[t + 1] - p0;
+  const int64_t* src = idx_ptrs[t];
+  const int64_t base = row_base ? row_base[t] : 0;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const int64_t v = src[i];
+    indices[p0 + i] = v;
+    if (iwro) iwro[p0 + i] = v + base;
+  }
+  const int64_t* so = off_ptrs[t];
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < B; i += stride) offsets[(int64_t)t * B + i] = so[i] + p0;
+  if (t == T - 1 && blockIdx.x == 0 && threadIdx.x == 0) offsets[(int64_t)T * B] = nnz_prefix[T];
+}
+}  // namespace b200
+
+extern "C" int b200_linearize(const int64_t* const* d_idx_ptrs, const int64_t* const* d_off_ptrs,
+                              const int64_t* d_nnz_prefix, const int64_t* d_row_base, int64_t T, int64_t B,
+                              int64_t max_nnz, int64_t* d_indices, int64_t* d_offsets, int64_t* d_iwro,
+                              b200_stream_t stream) {
+  B200_REQUIRE(T >= 0 && B >= 0 && max_nnz >= 0, B200_EINVAL, "linearize: negative size");
+  if (T == 0) return B200_OK;
+  B200_REQUIRE(T <= 65535, B200_EUNSUPPORTED, "linearize: more than 65535 tables");
+  B200_REQUIRE(d_idx_ptrs && d_off_ptrs && d_nnz_prefix && d_indices && d_offsets, B200_EINVAL,
+               "linearize: null pointer");
+  const int64_t work = std::max<int64_t>(std::max(max_nnz, B), 1);
+  const unsigned gx = (unsigned)std::min<int64_t>(ceil_div(work, 256 * 4), 1024);
+  b200::linearize_kernel<<<dim3(gx, (unsigned)T), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      d_idx_ptrs, d_off_ptrs, d_nnz_prefix, d_row_base, B, (int)T, d_indices, d_offsets, d_iwro);
+  B200_CHECK_LAUNCH("linearize");
+  return B200_OK;
+}

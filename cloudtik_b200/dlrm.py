@@ -46,7 +46,8 @@ class DLRM_Net(nn.Module):
         for i in ids:
             n = int(ln[i])
             if np_init_emb_weight:
-                W = np.random.uniform(low=-np.sqrt(1 / n), high=np.sqrt(1 / n), size=(n, m)).astype(np.float32)
+                ra = np.random.RandomState(self.l_emb_seeds[i]) if self.np_emb_seeds else np.random
+                W = ra.uniform(low=-np.sqrt(1 / n), high=np.sqrt(1 / n), size=(n, m)).astype(np.float32)
                 weights.append(torch.from_numpy(W).to(device))
             else:
                 w = torch.empty(n, m, dtype=torch.float32, device=device)
@@ -57,7 +58,8 @@ class DLRM_Net(nn.Module):
     def __init__(self, m_spa=None, ln_emb=None, ln_bot=None, ln_top=None, sigmoid_bot=-1, sigmoid_top=-1,
                  weighted_pooling=None, loss_threshold=0.0, np_init_emb_weight=False, device="cuda",
                  lr=0.01, emb_optimizer="sgd", bf16=False, n_rowwise=0, distributed=None,
-                 sparse_dense_boundary=0, dense_tables_first=False):
+                 sparse_dense_boundary=0, dense_tables_first=False, arch_interaction_op="dot",
+                 arch_interaction_itself=False, np_emb_seeds=False):
         """``distributed=False`` builds the single-process model (all tables local) even inside an initialised
         process group -- the oracle of the multi-GPU parity checks runs that way next to the sharded model.
 
@@ -69,7 +71,17 @@ class DLRM_Net(nn.Module):
         single-process model the same table order (``table_order``), which makes it the parity oracle of such a
         run (the reference's own sequential_forward keeps the natural order, SURVEY.md section 8c caveat)."""
         super().__init__()
+        # model options of the training variant (T/dlrm_s_pytorch.py:289-305,407-444)
+        if arch_interaction_op not in ("dot", "cat"):
+            sys.exit("ERROR: --arch-interaction-op=" + str(arch_interaction_op) + " is not supported")
+        self.arch_interaction_op = arch_interaction_op
+        self.arch_interaction_itself = bool(arch_interaction_itself)
+        # np_emb_seeds: every table is drawn from its own RandomState(l_emb_seeds[i]) like the training variant
+        # (T/dlrm_s_pytorch.py:240-243) instead of the global stream after the MLPs (product variant)
+        self.np_emb_seeds = bool(np_emb_seeds)
         self.world = ext_dist.my_size if (distributed is None or distributed) and ext_dist.my_size > 1 else 1
+        if self.world > 1 and (self.arch_interaction_itself or self.arch_interaction_op != "dot"):
+            raise NotImplementedError("the sharded paths implement the plain dot interaction only")
         if weighted_pooling is not None:
             raise NotImplementedError("weighted pooling is not on the reference's product path")
         self.loss_threshold = loss_threshold
@@ -146,7 +158,10 @@ class DLRM_Net(nn.Module):
         return emb_l((list(lS_i), list(lS_o), [False] * len(lS_i)), torch.BoolTensor([True]))
 
     def interact_features(self, x, ly):
-        return interaction(x, *ly, pad_to=self.interaction_pad)
+        if self.arch_interaction_op == "cat":
+            from .interaction import interaction_cat
+            return interaction_cat(x, *ly)
+        return interaction(x, *ly, pad_to=self.interaction_pad, itself=self.arch_interaction_itself)
 
     def forward(self, dense_x, *emb_args, chunk=0, dense_bags=None):
         """``chunk``: which micro-batch of a step cut by ``enable_peer_exchange(..., n_chunks)`` this call is

@@ -37,6 +37,9 @@ def _pooled_base(x: torch.Tensor, ly):
 class _InteractionFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, pad_to, x, *ly):
+        itself = pad_to < 0  # sign bit carries the arch_interaction_itself option
+        pad_to = abs(pad_to)
+        ctx.itself = itself
         base = _pooled_base(x, ly)
         if base is not None:
             T = base
@@ -47,12 +50,12 @@ class _InteractionFn(torch.autograd.Function):
         ctx.save_for_backward(T)
         ctx.x_dtype = x.dtype
         ctx.ly_dtypes = [t.dtype for t in ly]
-        return ops.interact_fwd(T, pad_to=pad_to)
+        return ops.interact_fwd(T, pad_to=pad_to, itself=itself)
 
     @staticmethod
     def backward(ctx, dR):
         (T,) = ctx.saved_tensors
-        dT = ops.interact_bwd(T, dR.contiguous().to(T.dtype))
+        dT = ops.interact_bwd(T, dR.contiguous().to(T.dtype), itself=ctx.itself)
         dx = dT[:, 0]
         if dx.dtype != ctx.x_dtype:
             dx = dx.to(ctx.x_dtype)
@@ -106,14 +109,28 @@ def interaction_sharded(x: torch.Tensor, chunks, pad_to: int = 1) -> torch.Tenso
     return _InteractionShardedFn.apply(int(pad_to), x, *chunks)
 
 
-def interaction(x: torch.Tensor, *ly: torch.Tensor, pad_to: int = 1) -> torch.Tensor:
+def interaction_cat(x: torch.Tensor, *ly: torch.Tensor) -> torch.Tensor:
+    """``--arch-interaction-op=cat`` (``T/dlrm_s_pytorch.py:434-436``): ``R = cat([x] + ly, dim=1)``.  When ``ly`` are
+    the merged embedding's views, x is copied into the free slot of the pooled ``[B, F, D]`` buffer and the result
+    is that buffer seen as ``[B, F*D]`` -- no concatenation pass; otherwise a plain ``torch.cat``."""
+    base = _pooled_base(x, ly)
+    if base is None or torch.is_grad_enabled() and (x.requires_grad or any(t.requires_grad for t in ly)):
+        return torch.cat([x.to(ly[0].dtype)] + list(ly), dim=1)  # autograd routes the gradient slices
+    base[:, 0].copy_(x)
+    return base.view(base.shape[0], -1)
+
+
+def interaction(x: torch.Tensor, *ly: torch.Tensor, pad_to: int = 1, itself: bool = False) -> torch.Tensor:
     """``interaction(x, *ly)`` -- see module docstring.  CUDA tensors only.
+
+    ``itself`` (``--arch-interaction-itself``, ``T/dlrm_s_pytorch.py:428``): pairs (i, j <= i), the output is
+    ``[B, D + F(F+1)/2]``.
 
     ``pad_to`` > 1 rounds the output width up to a multiple of ``pad_to`` with zero columns (e.g.
     479 -> 480) so that the GEMM consuming it gets an aligned K; ``PaddedLinear`` accepts that."""
     if not x.is_cuda:
         raise RuntimeError("cloudtik_b200.interaction needs CUDA tensors (no CPU fallback)")
-    return _InteractionFn.apply(int(pad_to), x, *ly)
+    return _InteractionFn.apply(-int(pad_to) if itself else int(pad_to), x, *ly)
 
 
 class PaddedLinear(torch.nn.Linear):

@@ -220,20 +220,9 @@ class MergedEmbeddingBagWithSGD(nn.Module):
         global row ids."""
         dev = self._raw_weights()[0].device
         idx = [i.to(dev, torch.int64) for i in indices]
-        offs = []
-        for o, inc in zip(offsets, include_last_offsets):
-            o = o.to(dev, torch.int64)
-            offs.append(o[:-1] if inc else o)
-        B = offs[0].numel()
-        if any(o.numel() != B for o in offs):
-            raise ValueError("all tables must be indexed with the same number of bags")
-        nnz = torch.tensor([0] + [i.numel() for i in idx], dtype=torch.int64).cumsum(0)
-        lin_idx = torch.cat(idx)
-        lin_off = torch.cat([o + int(nnz[t]) for t, o in enumerate(offs)]
-                            + [torch.tensor([int(nnz[-1])], dtype=torch.int64, device=dev)])
-        base = self.tables.d_row_base
-        iwro = torch.cat([i + base[t] for t, i in enumerate(idx)])
-        return lin_idx, lin_off, iwro
+        offs = [o.to(dev, torch.int64) for o in offsets]
+        # one launch for all tables (b200_linearize) instead of an add per table and three concatenations
+        return ops.linearize(idx, offs, list(include_last_offsets), self.tables.d_row_base)
 
     def to_bfloat16_train(self, keep_trail: bool = True):
         """Store the tables in bf16: the forward gathers half the bytes.  With ``keep_trail`` (default,

@@ -244,36 +244,66 @@ def emb_bwd_dense_grad(tables: TableSet, nnz: int, B: int, grad: torch.Tensor, s
     return out
 
 
-def interact_fwd(T: torch.Tensor, out: torch.Tensor | None = None, pad_to: int = 1) -> torch.Tensor:
-    """T [B, F, D] contiguous -> R [B, ldr] with ldr = D + F(F-1)/2 rounded up to ``pad_to``
-    (padding columns are written as zeros).  See b200_interact_fwd."""
+def interact_fwd(T: torch.Tensor, out: torch.Tensor | None = None, pad_to: int = 1, itself: bool = False) -> torch.Tensor:
+    """T [B, F, D] contiguous -> R [B, ldr] with ldr = D + F(F-1)/2 (``itself``: D + F(F+1)/2, the diagonal
+    included) rounded up to ``pad_to`` (padding columns are written as zeros).  See b200_interact_fwd[_ex]."""
     _cuda(T, "T")
     if T.dim() != 3 or not T.is_contiguous():
         raise _lib.B200Error("interact_fwd: T must be a contiguous [B, F, D] tensor")
     B, F, D = T.shape
-    W = D + F * (F - 1) // 2
+    W = D + F * (F - 1) // 2 + (F if itself else 0)
     if out is None:
         out = torch.empty(B, (W + pad_to - 1) // pad_to * pad_to, dtype=T.dtype, device=T.device)
     if out.dim() != 2 or out.shape[0] != B or out.shape[1] < W or out.stride(1) != 1 or out.dtype != T.dtype:
         raise _lib.B200Error("interact_fwd: bad output tensor")
-    check(lib.b200_interact_fwd(T.data_ptr(), out.data_ptr(), B, F, D, out.stride(0), _dt(T.dtype), _stream()),
-          "b200_interact_fwd")
+    check(lib.b200_interact_fwd_ex(T.data_ptr(), out.data_ptr(), B, F, D, out.stride(0), _dt(T.dtype),
+                                   1 if itself else 0, _stream()), "b200_interact_fwd")
     return out
 
 
-def interact_bwd(T: torch.Tensor, dR: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
-    """dT [B, F, D] from T and dR [B, >= D + F(F-1)/2] (row stride = dR.stride(0)).  See b200_interact_bwd."""
+def interact_bwd(T: torch.Tensor, dR: torch.Tensor, out: torch.Tensor | None = None, itself: bool = False) -> torch.Tensor:
+    """dT [B, F, D] from T and dR [B, >= D + number of pairs] (row stride = dR.stride(0)).  See b200_interact_bwd[_ex]."""
     _cuda(T, "T")
     _cuda(dR, "dR", T.dtype)
     B, F, D = T.shape
-    if (not T.is_contiguous() or dR.dim() != 2 or dR.shape[0] != B or dR.shape[1] < D + F * (F - 1) // 2
-            or dR.stride(1) != 1):
+    if (not T.is_contiguous() or dR.dim() != 2 or dR.shape[0] != B
+            or dR.shape[1] < D + F * (F - 1) // 2 + (F if itself else 0) or dR.stride(1) != 1):
         raise _lib.B200Error("interact_bwd: bad shapes / non-contiguous input")
     if out is None:
         out = torch.empty_like(T)
-    check(lib.b200_interact_bwd(T.data_ptr(), dR.data_ptr(), out.data_ptr(), B, F, D, dR.stride(0), _dt(T.dtype),
-                                _stream()), "b200_interact_bwd")
+    check(lib.b200_interact_bwd_ex(T.data_ptr(), dR.data_ptr(), out.data_ptr(), B, F, D, dR.stride(0), _dt(T.dtype),
+                                   1 if itself else 0, _stream()), "b200_interact_bwd")
     return out
+
+
+def linearize(idx_list, off_list, include_last, row_base: torch.Tensor | None, want_iwro: bool = True):
+    """Per-table bags (device int64 tensors) -> (indices, offsets[, global row ids]) in the merged layout with ONE
+    launch.  ``include_last[t]``: table t's offsets carry a trailing end offset (dropped).  See b200_linearize."""
+    T = len(idx_list)
+    dev = idx_list[0].device
+    idx = [_cuda(i, "indices", torch.int64).contiguous() for i in idx_list]
+    offs = []
+    for o, inc in zip(off_list, include_last):
+        o = _cuda(o, "offsets", torch.int64)
+        offs.append((o[:-1] if inc else o).contiguous())
+    B = offs[0].numel()
+    if any(o.numel() != B for o in offs):
+        raise _lib.B200Error("all tables must be indexed with the same number of bags")
+    prefix = [0]
+    for i in idx:
+        prefix.append(prefix[-1] + i.numel())
+    meta = torch.tensor([i.data_ptr() for i in idx] + [o.data_ptr() for o in offs] + prefix, dtype=torch.int64).to(
+        dev, non_blocking=True)
+    indices = torch.empty(prefix[-1], dtype=torch.int64, device=dev)
+    offsets = torch.empty(T * B + 1, dtype=torch.int64, device=dev)
+    iwro = torch.empty(prefix[-1], dtype=torch.int64, device=dev) if (want_iwro and row_base is not None) else None
+    p0 = meta.data_ptr()
+    check(lib.b200_linearize(p0, p0 + 8 * T, p0 + 16 * T, row_base.data_ptr() if iwro is not None else None, T, B,
+                             max(i.numel() for i in idx), indices.data_ptr(), offsets.data_ptr(),
+                             iwro.data_ptr() if iwro is not None else None, _stream()), "b200_linearize")
+    # the per-table inputs and the pointer table must outlive the launch on this stream: torch's allocator is
+    # stream-ordered, so tensors freed after the launch are not reused before it ran
+    return indices, offsets, iwro
 
 
 def criteo_transform(records: torch.Tensor, max_ind_range: int = 0, n_dense: int = 13, tab_begin: int = 0,

@@ -225,6 +225,51 @@ int b200_interact_fwd(const void* d_T, void* d_R, int64_t B, int64_t F, int64_t 
 int b200_interact_bwd(const void* d_T, const void* d_dR, void* d_dT, int64_t B, int64_t F,
                       int64_t D, int64_t ldr, int dtype, b200_stream_t stream);
 
+/*
+ * The interaction with options.  flags = 0 is b200_interact_fwd / _bwd.  B200_INTERACT_ITSELF adds the diagonal
+ * (a feature's dot product with itself): pairs (i, j <= i) in row-major order, W = D + F(F+1)/2 -- the training
+ * variant's --arch-interaction-itself (T/dlrm_s_pytorch.py:428: `offset = 1 if self.arch_interaction_itself`);
+ * in backward a diagonal entry contributes 2 * dZ[i,i] * T[i].  This option runs the general CUDA-core kernel.
+ * (--arch-interaction-op=cat, T/dlrm_s_pytorch.py:434-436, needs no kernel: it is a view of the pooled buffer.)
+ */
+enum { B200_INTERACT_ITSELF = 1 };
+int b200_interact_fwd_ex(const void* d_T, void* d_R, int64_t B, int64_t F, int64_t D, int64_t ldr, int dtype,
+                         int flags, b200_stream_t stream);
+int b200_interact_bwd_ex(const void* d_T, const void* d_dR, void* d_dT, int64_t B, int64_t F, int64_t D,
+                         int64_t ldr, int dtype, int flags, b200_stream_t stream);
+
+/*
+ * The names SURVEY.md section 8b lists for the fused backward, as thin forms of b200_emb_bwd_update with the
+ * optimiser fixed (SGD: torch.optim.SGD on the sparse gradients, P/dlrm_s_pytorch.py:805,1059; Adagrad: torch's
+ * sparse Adagrad branch, no call site in the reference), and of b200_emb_bwd_workspace_bytes.
+ */
+size_t b200_workspace_bytes(int64_t nnz, int64_t D);
+int b200_emb_bwd_sgd(void* const* d_weights, uint16_t* const* d_trail, const int64_t* d_rows,
+                     const int64_t* d_row_base, const int64_t* d_indices, const int64_t* d_offsets, int64_t nnz,
+                     const void* d_grad, int64_t T, int64_t B, int64_t D, int64_t grad_stride_table,
+                     int64_t grad_stride_bag, int w_dtype, int grad_dtype, float lr, const float* d_lr,
+                     int64_t total_rows, void* ws, size_t ws_bytes, int32_t* d_error, b200_stream_t stream);
+int b200_emb_bwd_adagrad(void* const* d_weights, float* const* d_state, uint16_t* const* d_trail,
+                         const int64_t* d_rows, const int64_t* d_row_base, const int64_t* d_indices,
+                         const int64_t* d_offsets, int64_t nnz, const void* d_grad, int64_t T, int64_t B, int64_t D,
+                         int64_t grad_stride_table, int64_t grad_stride_bag, int w_dtype, int grad_dtype, float lr,
+                         const float* d_lr, float eps, int64_t total_rows, void* ws, size_t ws_bytes,
+                         int32_t* d_error, b200_stream_t stream);
+
+/*
+ * Per-table bags -> the merged layout of the calls above, in one launch.  Replaces
+ * MergedEmbeddingBagWithSGD.linearize_indices_and_offsets (call sites P/dlrm_s_pytorch.py:908-915,1008-1014):
+ *   d_idx_ptrs / d_off_ptrs  device arrays [T] of pointers to table t's int64 indices [nnz_t] / start offsets [B]
+ *   d_nnz_prefix             int64 [T+1] exclusive prefix sum of nnz_t (host-known: the sizes of the index arrays)
+ *   d_row_base               int64 [T+1] or NULL (then d_iwro must be NULL too)
+ *   outputs                  d_indices [sum nnz] = concatenation; d_offsets [T*B+1] = start offsets shifted by the
+ *                            indices of the tables before, then the total; d_iwro [sum nnz] or NULL = global row ids
+ *   max_nnz                  largest nnz_t (sizes the grid)
+ */
+int b200_linearize(const int64_t* const* d_idx_ptrs, const int64_t* const* d_off_ptrs, const int64_t* d_nnz_prefix,
+                   const int64_t* d_row_base, int64_t T, int64_t B, int64_t max_nnz, int64_t* d_indices,
+                   int64_t* d_offsets, int64_t* d_iwro, b200_stream_t stream);
+
 /* ---------------------------------------------------------------------------
  * Input side: Criteo binary records -> the tensors the step consumes.
  *

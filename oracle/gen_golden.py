@@ -435,6 +435,39 @@ def gen_T_smoke():
     np.savez_compressed(os.path.join(OUT, "t_smoke.npz"), **out)
 
 
+def gen_T_options():
+    """Model options of the training variant that the product variant lacks, from T/dlrm_s_pytorch.py itself:
+    --arch-interaction-itself (T/...:428, pairs j <= i) forward + autograd backward, --arch-interaction-op=cat
+    (:434-436) and the wbce loss (:1004-1006,1066-1075)."""
+    TM, _ = load_T_model()
+    net = TM.DLRM_Net.__new__(TM.DLRM_Net)
+    torch.nn.Module.__init__(net)
+    net.bf16 = False
+    out = {}
+    rs = np.random.RandomState(21)
+    for tag, (B, F, D) in {"a": (5, 4, 8), "b": (3, 27, 16), "c": (2, 27, 128)}.items():
+        net.arch_interaction_op, net.arch_interaction_itself = "dot", True
+        x = torch.tensor(rs.randn(B, D).astype(np.float32), requires_grad=True)
+        ly = [torch.tensor(rs.randn(B, D).astype(np.float32), requires_grad=True) for _ in range(F - 1)]
+        R = net.interact_features(x, ly)
+        dR = torch.tensor(rs.randn(*R.shape).astype(np.float32))
+        R.backward(dR)
+        out[f"{tag}_x"], out[f"{tag}_ly"] = x.detach().numpy(), np.stack([t.detach().numpy() for t in ly])
+        out[f"{tag}_R"], out[f"{tag}_dR"] = R.detach().numpy(), dR.numpy()
+        out[f"{tag}_dx"], out[f"{tag}_dly"] = x.grad.numpy(), np.stack([t.grad.numpy() for t in ly])
+        net.arch_interaction_op = "cat"
+        out[f"{tag}_cat"] = net.interact_features(x.detach(), [t.detach() for t in ly]).numpy()
+    # wbce: per-sample BCE weighted by loss_ws[target], then the mean (T/dlrm_s_pytorch.py:1066-1075)
+    Z = torch.tensor(rs.rand(16, 1).astype(np.float32) * 0.98 + 0.01)
+    Tt = torch.tensor(np.round(rs.rand(16, 1)).astype(np.float32))
+    loss_ws = torch.tensor(np.fromstring("1.0-3.0", dtype=float, sep="-"))
+    loss_fn = torch.nn.BCELoss(reduction="none")
+    ws_ = loss_ws[Tt.data.view(-1).long()].view_as(Tt)
+    out["wbce_Z"], out["wbce_T"], out["wbce_ws"] = Z.numpy(), Tt.numpy(), loss_ws.numpy()
+    out["wbce_loss"] = np.float64((ws_ * loss_fn(Z, Tt)).mean().item())
+    np.savez_compressed(os.path.join(OUT, "t_options.npz"), **out)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     G = load_T_generator()
@@ -448,6 +481,7 @@ def main():
     gen_int8_tables()
     gen_tricks()
     gen_T_smoke()
+    gen_T_options()
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

@@ -165,29 +165,31 @@ def sparse_adagrad_update(W, state_sum, indices, offsets, grad_out, lr, eps=1e-1
 # --------------------------------------------------------------------------
 
 
-def tril_pairs(F: int):
+def tril_pairs(F: int, itself: bool = False):
     """Index lists of ``P/dlrm_s_pytorch.py:328-330`` (offset=0): strict lower
-    triangle in row-major order (1,0),(2,0),(2,1),..."""
-    li = np.array([i for i in range(F) for j in range(i)], dtype=np.int64)
-    lj = np.array([j for i in range(F) for j in range(i)], dtype=np.int64)
+    triangle in row-major order (1,0),(2,0),(2,1),...; ``itself`` (``T/dlrm_s_pytorch.py:428-430``,
+    offset=1) includes the diagonal: (0,0),(1,0),(1,1),(2,0),..."""
+    o = 1 if itself else 0
+    li = np.array([i for i in range(F) for j in range(i + o)], dtype=np.int64)
+    lj = np.array([j for i in range(F) for j in range(i + o)], dtype=np.int64)
     return li, lj
 
 
-def interact_fwd(x: np.ndarray, ly) -> np.ndarray:
-    """``DLRM_Net.interact_features`` ``P/dlrm_s_pytorch.py:309-334`` (dot, no self
-    interaction): ``R = [x, (T T^t)[li, lj]]`` with ``T = stack([x] + ly)``."""
+def interact_fwd(x: np.ndarray, ly, itself: bool = False) -> np.ndarray:
+    """``DLRM_Net.interact_features`` ``P/dlrm_s_pytorch.py:309-334`` (dot; self interaction only with
+    ``itself``, ``T/dlrm_s_pytorch.py:407-433``): ``R = [x, (T T^t)[li, lj]]`` with ``T = stack([x] + ly)``."""
     T = np.stack([x] + list(ly), axis=1)  # [B, F, D]
     Z = np.matmul(T, T.transpose(0, 2, 1))
-    li, lj = tril_pairs(T.shape[1])
+    li, lj = tril_pairs(T.shape[1], itself)
     return np.concatenate([x, Z[:, li, lj]], axis=1)
 
 
-def interact_bwd(x: np.ndarray, ly, dR: np.ndarray):
+def interact_bwd(x: np.ndarray, ly, dR: np.ndarray, itself: bool = False):
     """Autograd of ``interact_fwd``: ``dT = (dZ + dZ^t) T`` with dZ scattered from
     ``dR[:, D:]``, plus the pass-through ``dR[:, :D]`` into x.  Returns (dx, [dly])."""
     T = np.stack([x] + list(ly), axis=1)
     B, F, D = T.shape
-    li, lj = tril_pairs(F)
+    li, lj = tril_pairs(F, itself)
     dZ = np.zeros((B, F, F), dtype=dR.dtype)
     dZ[:, li, lj] = dR[:, D:]
     dT = np.matmul(dZ + dZ.transpose(0, 2, 1), T)

@@ -21,7 +21,7 @@ def pytest_sessionstart(session):
     the library arrives prebuilt with the snapshot and this is a no-op."""
     lib = os.path.join(ROOT, "cloudtik_b200", "lib", "libb200dlrm.so")
     if not os.path.exists(lib):
-        from cloudtik_b200.build import build
+        from build_lib import build
         build(force=False)
 
 

@@ -555,3 +555,81 @@ def test_sharded_entry_points_on_one_gpu(W, lN, dtype):
     ops.emb_bwd_apply_sharded(ts2, len(indices), B, gptrs.data_ptr(), lN, F, feat0, dtype, 0.5, ws)
     for a, b in zip(tw, tw2):
         assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("tag", ["a", "b", "c"])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_interaction_itself_and_cat_golden(golden, tag, dtype):
+    """--arch-interaction-itself (pairs j <= i) forward / backward and --arch-interaction-op=cat against vectors
+    written by the reference's training variant (T/dlrm_s_pytorch.py:407-444, tests/golden/t_options.npz)."""
+    ops = _ops()
+    from cloudtik_b200.interaction import interaction, interaction_cat
+    g = golden("t_options")
+    x, ly, R, dR = g[f"{tag}_x"], g[f"{tag}_ly"], g[f"{tag}_R"], g[f"{tag}_dR"]
+    rtol, atol = (RTOL32, 1e-5) if dtype == torch.float32 else (2e-2, 0.25)
+    xt = torch.tensor(x).to(dtype).cuda().requires_grad_(True)
+    lyt = [torch.tensor(t).to(dtype).cuda().requires_grad_(True) for t in ly]
+    out = interaction(xt, *lyt, itself=True)
+    assert tuple(out.shape) == R.shape
+    np.testing.assert_allclose(out.float().detach().cpu().numpy(), R, rtol=rtol, atol=atol)
+    # the oracle restatement agrees with the reference too
+    np.testing.assert_allclose(ref.interact_fwd(x, list(ly), itself=True), R, rtol=1e-5, atol=1e-5)
+    out.backward(torch.tensor(dR).to(dtype).cuda())
+    np.testing.assert_allclose(xt.grad.float().cpu().numpy(), g[f"{tag}_dx"], rtol=rtol, atol=atol * 4)
+    for k, t in enumerate(lyt):
+        np.testing.assert_allclose(t.grad.float().cpu().numpy(), g[f"{tag}_dly"][k], rtol=rtol, atol=atol * 4)
+    with torch.no_grad():
+        cat = interaction_cat(xt, *lyt)
+    np.testing.assert_allclose(cat.float().cpu().numpy(), g[f"{tag}_cat"], rtol=rtol, atol=1e-2 if dtype != torch.float32 else 0)
+
+
+@pytest.mark.parametrize("B,ragged,inc", [(257, False, False), (300, True, False), (64, True, True)])
+def test_linearize_kernel_bit_exact(B, ragged, inc):
+    """b200_linearize (one launch) against the oracle's per-table concatenation (P/dlrm_s_pytorch.py:908-915)."""
+    ops = _ops()
+    rs = np.random.RandomState(B)
+    rows = [1000, 37, 5000, 3]
+    idx_l, off_l = _make_bags(rs, rows, B, 3, ragged)
+    want_i, want_o, want_g = ref.linearize_indices_and_offsets(idx_l, off_l, rows)
+    base = torch.tensor(np.concatenate([[0], np.cumsum(rows)]), dtype=torch.int64).cuda()
+    offs = [torch.tensor(np.concatenate([o, [len(i)]]) if inc else o).cuda() for o, i in zip(off_l, idx_l)]
+    gi, go, gg = ops.linearize([torch.tensor(i).cuda() for i in idx_l], offs, [inc] * len(rows), base)
+    np.testing.assert_array_equal(gi.cpu().numpy(), want_i)
+    np.testing.assert_array_equal(go.cpu().numpy(), want_o)
+    np.testing.assert_array_equal(gg.cpu().numpy(), want_g)
+
+
+def test_survey_named_entry_points_match_update():
+    """b200_emb_bwd_sgd / b200_emb_bwd_adagrad / b200_workspace_bytes (the names of SURVEY.md section 8b) give what
+    b200_emb_bwd_update gives."""
+    ops = _ops()
+    from cloudtik_b200._lib import check, lib
+    rs = np.random.RandomState(9)
+    rows, B, D = [500, 7, 3000], 200, 128
+    idx_l, off_l = _make_bags(rs, rows, B, 3, True)
+    indices, offsets, _ = ref.linearize_indices_and_offsets(idx_l, off_l, rows)
+    ti, to = torch.tensor(indices).cuda(), torch.tensor(offsets).cuda()
+    g = torch.tensor(rs.randn(B, len(rows), D).astype(np.float32)).cuda()
+    assert lib.b200_workspace_bytes(len(indices), D) == ops.emb_bwd_workspace_bytes(len(indices), D)
+    ws = torch.empty(ops.emb_bwd_workspace_bytes(len(indices), D), dtype=torch.uint8, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    for opt in ("sgd", "adagrad"):
+        W0 = [torch.tensor(rs.uniform(-1, 1, size=(n, D)).astype(np.float32)).cuda() for n in rows]
+        S0 = [torch.full((n, D), 0.1, device="cuda") for n in rows]
+        a, b = ops.TableSet([w.clone() for w in W0]), ops.TableSet([w.clone() for w in W0])
+        if opt == "adagrad":
+            a.set_states([s.clone() for s in S0]), b.set_states([s.clone() for s in S0])
+        ops.emb_bwd_update(a, ti, to, B, g, D, len(rows) * D, 0.3, ws,
+                           optimizer=ops.OPT_ADAGRAD if opt == "adagrad" else ops.OPT_SGD)
+        common = (b.d_rows.data_ptr(), b.d_row_base.data_ptr(), ti.data_ptr(), to.data_ptr(), len(indices),
+                  g.data_ptr(), len(rows), B, D, D, len(rows) * D, 0, 0)
+        if opt == "sgd":
+            check(lib.b200_emb_bwd_sgd(b.d_ptrs.data_ptr(), None, *common, 0.3, None, b.total_rows, ws.data_ptr(),
+                                       ws.numel(), None, st), "b200_emb_bwd_sgd")
+        else:
+            check(lib.b200_emb_bwd_adagrad(b.d_ptrs.data_ptr(), b.d_state_ptrs.data_ptr(), None, *common, 0.3, None,
+                                           1e-10, b.total_rows, ws.data_ptr(), ws.numel(), None, st),
+                  "b200_emb_bwd_adagrad")
+        torch.cuda.synchronize()
+        for wa, wb in zip(a.weights, b.weights):
+            assert torch.equal(wa, wb)
