@@ -68,6 +68,8 @@ def parse():
                     help="c3 = Criteo-Terabyte one-hot step (the headline line); c5 = BASELINE configs[4]: multi-hot "
                          "bags, row-wise sharded hot tables, fused Adagrad, bf16 activations (eager, N >= 1)")
     ap.add_argument("--pooling", type=int, default=20, help="c5: indices per bag")
+    ap.add_argument("--no-c5", action="store_true",
+                    help="skip the BASELINE configs[4] (multi-hot, row-wise sharded, fused Adagrad) block appended to the line")
     ap.add_argument("--no-microbench", action="store_true",
                     help="skip the BASELINE configs[1] EmbeddingBag micro-benchmark appended to the N=1 line")
     ap.add_argument("--timeline", default="", help="after the timed legs: profile 3 more steps with torch.profiler and "
@@ -581,6 +583,16 @@ def run_b200_arm(a):
     clk = clocks.stop() if clocks else None  # sampled every 20 ms across the three timed legs (all under load)
     if a.timeline:
         write_timeline(a.timeline, rank, step_fn, barrier)
+    c5 = None
+    if world > 1 and not a.no_c5:
+        # BASELINE configs[4] on the same ranks, after the headline legs (their model is released first)
+        import gc
+        net.emb_l = None
+        gs = None
+        step_fn = e2e_fn = None
+        gc.collect()
+        torch.cuda.empty_cache()
+        c5 = c5_measure(a, world, rank, dev, min(a.steps, 10), 3)
     if rank != 0:
         return
     ms_step = ms_total / a.steps
@@ -654,6 +666,16 @@ def run_b200_arm(a):
         line["parity"] = parity
     if world == 1 and not a.no_microbench:
         line["embeddingbag_microbench"] = embeddingbag_microbench(net, gs if use_graph else None)
+    if world == 1 and not a.no_c5:
+        import gc
+        net.emb_l = None
+        gs = None
+        step_fn = e2e_fn = None
+        gc.collect()
+        torch.cuda.empty_cache()
+        c5 = c5_measure(a, world, rank, dev, min(a.steps, 10), 3)
+    if c5 is not None:
+        line["config5"] = c5
     if world == 1 and not a.no_cpu_baseline:
         r = cpu_reference_run(a.batch, a.cpu_rows_cap, a.cpu_steps, 3, bf16, threads=host_threads())
         line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
@@ -662,21 +684,15 @@ def run_b200_arm(a):
     print(json.dumps(line), flush=True)
 
 
-def run_c5_arm(a):
-    """BASELINE configs[4]: multi-hot DLRM (pooling ~20), the three largest tables ROW-WISE sharded over the ranks
-    (reduce-scatter forward / all-gather backward), the other 23 table-wise (fused peer-memory exchange), fused
-    Adagrad on every table, bf16 MLPs / interaction / pooled rows.  Eager (the row filter of the row-wise path has
-    data-dependent shapes), CUDA-event timed, max over ranks.  On one GPU every table is local."""
+def c5_measure(a, world, rank, dev, steps, warmup):
+    """BASELINE configs[4]: multi-hot DLRM (pooling ~20), the three largest tables ROW-WISE sharded over the ranks,
+    the other 23 table-wise (both exchanges fused into the embedding kernels over peer memory), fused Adagrad on
+    every table, bf16 MLPs / interaction / pooled rows.  The whole step is one CUDA graph (the row filter of the
+    row-wise path has a fixed capacity).  CUDA-event timed, max over ranks.  On one GPU every table is local.
+    Returns the result dict (rank 0) or None."""
     from cloudtik_b200 import ext_dist
-    from cloudtik_b200.dlrm import DLRM_Net, enable_peer_exchange
-
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    if world > 1:
-        ext_dist.init_distributed(rank=rank, size=world, backend="nccl")
+    from cloudtik_b200.dlrm import DLRM_Net, enable_peer_exchange, train_step_chunked
+    from cloudtik_b200.graph import GraphedTrainStep
     cap = a.rows_cap or (12_000_000 if world == 1 else 0)  # fp32 tables + fp32 Adagrad state: 1 KB per row
     big = sorted(range(len(C3_ROWS)), key=lambda i: -C3_ROWS[i])[:3]
     order = [i for i in range(len(C3_ROWS)) if i not in big] + sorted(big)  # hot (largest) tables last
@@ -703,7 +719,7 @@ def run_c5_arm(a):
     from cloudtik_b200.mlp import enable_bf16_shadows
     enable_bf16_shadows([net.bot_l, net.top_l], opt)
     # Adagrad is not linear in the gradient scale: every rank divides its loss by world, MLP gradients are summed
-    sync_dense = ext_dist.DenseGradAllreduce(dense, average=False) if world > 1 else (lambda: None)
+    sync_dense = ext_dist.DenseGradAllreduce(dense, average=False) if world > 1 else None
 
     def bags(rs, n_rows_list):
         idx = np.stack([np.floor(rs.rand(B_glob * P) * n).astype(np.int64) for n in n_rows_list])
@@ -722,69 +738,113 @@ def run_c5_arm(a):
         host = [torch.from_numpy(v).pin_memory() for v in host]
         sets.append({"host": host, "dev": [h.to(dev, non_blocking=True) for h in host]})
     torch.cuda.synchronize()
+    scale = 1.0 / world
 
-    def step(t):
-        X, Y, idx, off = t[:4]
-        Z = (net(X, idx, off, None, t[4], t[5]) if n_rw else net(X, idx, off, None)).float()
-        E = net.loss_fn(Z, Y)
-        opt.zero_grad(set_to_none=True)
-        (E / world).backward()
-        sync_dense()
-        opt.step()
-        return E.detach()
-
-    stage = [torch.empty_like(t) for t in sets[0]["dev"]]
-
-    def step_e2e(i):
-        for d, h in zip(stage, sets[i % 2]["host"]):
-            d.copy_(h, non_blocking=True)
-        return float(step(stage).cpu())
-
-    def timed(fn, steps):
+    def barrier():
         if world > 1:
             torch.distributed.barrier()
         torch.cuda.synchronize()
+
+    def timed(fn, n):
+        barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         last = None
-        for i in range(steps):
+        for i in range(n):
             last = fn(i)
         e1.record()
-        if world > 1:
-            torch.distributed.barrier()
-        torch.cuda.synchronize()
+        barrier()
         ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
         if world > 1:
             torch.distributed.all_reduce(ms, op=torch.distributed.ReduceOp.MAX)
         return float(ms.item()), last
 
-    for i in range(max(a.warmup, 3)):
-        step(sets[i % 2]["dev"])
-    clocks = ClockSampler(local_rank) if rank == 0 else None
-    ms_total, last = timed(lambda i: step(sets[i % 2]["dev"]), a.steps)
+    use_graph = not a.no_graph
+    if use_graph:
+        gs = GraphedTrainStep(net, opt, sets[0]["dev"], post_backward=sync_dense, loss_scale=scale)
+
+        def step(i):
+            return gs.step(*sets[i % 2]["dev"])
+    else:
+        def step(i):
+            return train_step_chunked(net, opt, sets[i % 2]["dev"], sync_dense, scale)
+    for i in range(max(warmup, 3)):
+        step(i)
+    ms_total, last = timed(step, steps)
     loss_val = float(last.cpu())
+    # end to end: pinned-host inputs copied in every step, loss read back every step
+    stage = [torch.empty_like(t) for t in sets[0]["dev"]]
+
+    def step_e2e(i):
+        for d, h in zip(stage, sets[i % 2]["host"]):
+            d.copy_(h, non_blocking=True)
+        E = gs.step(*stage) if use_graph else train_step_chunked(net, opt, stage, sync_dense, scale)
+        return float(E.cpu())
     step_e2e(0)
-    ms_e2e, _ = timed(step_e2e, a.steps)
-    clk = clocks.stop() if clocks else None
+    ms_e2e, _ = timed(step_e2e, steps)
+    # kernel-level roofline of the multi-hot update (the dominant embedding kernel of this config): an eager pass
+    # with CUDA events around the launches (local tables of this rank: 23/W table-wise ones)
+    emb = net.emb_l
+    emb.profile = {}
+    timed(lambda i: train_step_chunked(net, opt, sets[i % 2]["dev"], sync_dense, scale), min(steps, 5))
+    prof, emb.profile = emb.profile, None
+    overflow = int(net.rowwise.error_flag.item()) if (net.rowwise is not None and net.rowwise.error_flag is not None) else 0
     if rank != 0:
-        return
+        return None
+    T_loc = len(local_ids)
+    nnz = T_loc * B_glob * P
+    roof = None
+    if prof.get("emb_bwd_apply"):
+        kms = statistics.mean(x.elapsed_time(y) for x, y in prof["emb_bwd_apply"])
+        # distinct rows touched per step, per table: n * (1 - exp(-lookups / n)) for uniform ids
+        U = sum(rows[i] * (1.0 - np.exp(-B_glob * P / rows[i])) for i in local_ids)
+        # bf16 gradient rows + ids + offsets + (fp32 row + fp32 Adagrad state) read and written
+        alg = T_loc * B_glob * D * 2 + nnz * 8 + (T_loc * B_glob + 1) * 8 + 2 * U * D * 4 + 2 * U * D * 4
+        peak, pk = peak_hbm()
+        roof = {"kernel": "emb_bwd_apply (multi-hot, fused Adagrad, table-wise tables of rank 0)", "bound": "hbm",
+                "achieved": round(alg / (kms * 1e-3) / 1e9, 1), "peak": peak, "unit": "GB/s",
+                "frac": round(alg / (kms * 1e-3) / 1e9 / peak, 4), "peak_source": pk, "kernel_ms": round(kms, 4),
+                "algorithmic_bytes": int(alg), "distinct_rows_estimate": int(U),
+                "others": {k: round(statistics.mean(x.elapsed_time(y) for x, y in v), 4)
+                           for k, v in prof.items() if k != "emb_bwd_apply" and v}}
     h2d = sum(t.numel() * t.element_size() for t in sets[0]["host"])
-    line = {"metric": "dlrm_train_samples_per_sec", "value": round(B_glob * a.steps / (ms_total / 1e3), 1),
-            "unit": "samples/s", "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
-            "ms_per_step": round(ms_total / a.steps, 4), "higher_is_better": True, "scaling": "weak",
+    return {"metric": "dlrm_train_samples_per_sec", "value": round(B_glob * steps / (ms_total / 1e3), 1),
+            "unit": "samples/s", "n_gpus": world, "steps": steps, "warmup": max(warmup, 3),
+            "ms_per_step": round(ms_total / steps, 4), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": "dlrm_multihot_rowwise_adagrad_c5", "batch_per_gpu": B_loc, "global_batch": B_glob,
                        "dim": D, "tables": len(rows), "pooling": P, "rows_cap": cap or None,
+                       "lookups_per_step": int(len(rows) * B_glob * P),
                        "row_wise_tables": n_rw, "row_wise_rows": [int(r) for r in rows[n_tw:]] if n_rw else [],
-                       "optimizer": "fused sparse Adagrad (tables) + torch SGD (MLPs)", "table_dtype": "fp32",
+                       "optimizer": "fused sparse Adagrad (tables, initial accumulator 0.1) + torch SGD (MLPs)",
+                       "table_dtype": "fp32",
                        "parallelism": "single" if world == 1 else
-                       f"table-wise x{world} (fused peer-memory exchange) + row-wise x{world} (NCCL reduce-scatter / "
-                       "all-gather) + data-parallel MLPs",
-                       "l2": "inputs larger than L2", "launch": "eager"},
-            "e2e": {"value": round(B_glob * a.steps / (ms_e2e / 1e3), 1), "unit": "samples/s",
-                    "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4, "ms_per_step": round(ms_e2e / a.steps, 4)},
-            "clocks": clk, "final_loss": loss_val, "roofline": None, "cpu_baseline": None}
-    print(json.dumps(line), flush=True)
+                       f"table-wise x{world} + row-wise x{world} (both exchanges fused over peer memory) + "
+                       "data-parallel MLPs",
+                       "l2": "inputs larger than L2",
+                       "launch": "whole step replayed as one CUDA graph" if use_graph else "eager",
+                       "row_filter_overflow": overflow},
+            "e2e": {"value": round(B_glob * steps / (ms_e2e / 1e3), 1), "unit": "samples/s",
+                    "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4, "ms_per_step": round(ms_e2e / steps, 4)},
+            "final_loss": loss_val, "roofline": roof}
+
+
+def run_c5_arm(a):
+    from cloudtik_b200 import ext_dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        ext_dist.init_distributed(rank=rank, size=world, backend="nccl")
+    clocks = ClockSampler(local_rank) if rank == 0 else None
+    line = c5_measure(a, world, rank, dev, a.steps, a.warmup)
+    clk = clocks.stop() if clocks else None
+    if rank == 0:
+        line["clocks"] = clk
+        line["cpu_baseline"] = None
+        print(json.dumps(line), flush=True)
 
 
 def main():

@@ -78,6 +78,10 @@ __device__ __forceinline__ void red_add_v4_bf16x2(void* p, uint32_t a, uint32_t 
                : "memory");
 }
 
+__device__ __forceinline__ void red_add_v2_bf16x2(void* p, uint32_t a, uint32_t b) {
+  asm volatile("red.global.add.noftz.v2.bf16x2 [%0], {%1,%2};" ::"l"(p), "r"(a), "r"(b) : "memory");
+}
+
 // ---- mbarrier + 1-D bulk async copy (TMA engine; SASS: UBLKCP / SYNCS)
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
@@ -237,6 +241,23 @@ template <>
 __device__ __forceinline__ void store_vec<__nv_bfloat16, 8, false>(__nv_bfloat16* p, const float* v) {
   st_v4(p, make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
                       pack_bf16x2(v[6], v[7])));
+}
+
+// add N consecutive fp32 values into OT memory at p with fire-and-forget vector reductions (p 8/16-byte aligned)
+template <typename OT, int N>
+__device__ __forceinline__ void red_vec(OT* p, const float* v) {
+  if constexpr (sizeof(OT) == 4) {
+#pragma unroll
+    for (int h = 0; h < N / 4; ++h)
+      red_add_v4_f32(reinterpret_cast<float*>(p) + 4 * h, v[4 * h], v[4 * h + 1], v[4 * h + 2], v[4 * h + 3]);
+  } else if constexpr (N == 4) {
+    red_add_v2_bf16x2(p, pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]));
+  } else {
+#pragma unroll
+    for (int h = 0; h < N / 8; ++h)
+      red_add_v4_bf16x2(p + 8 * h, pack_bf16x2(v[8 * h], v[8 * h + 1]), pack_bf16x2(v[8 * h + 2], v[8 * h + 3]),
+                        pack_bf16x2(v[8 * h + 4], v[8 * h + 5]), pack_bf16x2(v[8 * h + 6], v[8 * h + 7]));
+  }
 }
 
 template <typename T>

@@ -33,6 +33,7 @@ constexpr int MIN_NG = UPD_THREADS / 32;  // fewest windows per block (one warp 
 struct BwdLayout {
   uint32_t *keys, *vals, *skeys, *svals, *unique, *seg, *win_run, *first_val;
   int32_t* num_unique;
+  int64_t* n_valid;  // sorted positions that hold real keys (= nnz, or fewer after b200_emb_bwd_prepare_partial)
   float* partial;   // [2 * nblk][D], nblk = blocks of the window kernel (<= ceil(nwin / MIN_NG))
   void* sort_ws;
   size_t total;
@@ -50,7 +51,8 @@ static BwdLayout bwd_layout(void* ws, int64_t n, int64_t D) {
   L.unique = reinterpret_cast<uint32_t*>(w + o), o += s;
   L.first_val = reinterpret_cast<uint32_t*>(w + o), o += s;
   L.seg = reinterpret_cast<uint32_t*>(w + o), o += align_up((size_t)(n + 1) * 4, 256);
-  L.num_unique = reinterpret_cast<int32_t*>(w + o), o += 256;
+  L.num_unique = reinterpret_cast<int32_t*>(w + o);
+  L.n_valid = reinterpret_cast<int64_t*>(w + o + 64), o += 256;
   L.win_run = reinterpret_cast<uint32_t*>(w + o), o += align_up((size_t)(ceil_div(n, HOT_CH) + 1) * 4, 256);
   L.partial = reinterpret_cast<float*>(w + o),
   o += align_up((size_t)(2 * ceil_div(ceil_div(n, HOT_CH), MIN_NG)) * D * 4, 256);
@@ -61,6 +63,20 @@ static BwdLayout bwd_layout(void* ws, int64_t n, int64_t D) {
 
 // ------------------------------------------------------------------ 1. keys
 // grid = (ceil(B/256), T); one warp per 32 consecutive bags of one table.
+// Positions [*d_valid, n) of a partially filled key array (b200_emb_bwd_prepare_partial) get the sentinel key
+// `sentinel` (one past the last real row id): they sort behind every real key and the update kernels stop at
+// *n_valid.  Also publishes n_valid in the workspace.
+__global__ void __launch_bounds__(256)
+    keys_tail_kernel(uint32_t* __restrict__ keys, uint32_t* __restrict__ vals, const int64_t* __restrict__ d_valid,
+                     int64_t n, uint32_t sentinel, int64_t* __restrict__ n_valid_out) {
+  const int64_t nv = d_valid ? min(max(*d_valid, (int64_t)0), n) : n;
+  if (blockIdx.x == 0 && threadIdx.x == 0) *n_valid_out = nv;
+  for (int64_t j = nv + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (int64_t)gridDim.x * blockDim.x) {
+    keys[j] = sentinel;
+    vals[j] = 0u;
+  }
+}
+
 __global__ void __launch_bounds__(KEYS_THREADS)
     build_keys_kernel(const int64_t* __restrict__ indices, const int64_t* __restrict__ offsets,
                       const int64_t* __restrict__ rows, const int64_t* __restrict__ row_base, int64_t B,
@@ -134,7 +150,8 @@ struct UpdParams {
   int64_t lN, F, feat0;
   int T;
   float* partial;
-  int64_t n;
+  int64_t n;            // capacity of the sorted arrays (sizes the grid)
+  const int64_t* d_n;   // real keys among them, read at kernel time (the sort puts them first)
 };
 
 // load VE consecutive gradient elements (GT) as fp32
@@ -308,9 +325,11 @@ __global__ void __launch_bounds__(UPD_THREADS, (sizeof(GT) == 2 && !TRAIL && OPT
     }
   }
   constexpr bool has_trail = TRAIL;  // compile-time: plain bf16 tables carry no trail registers
+  const int64_t n_eff = p.d_n ? min(*p.d_n, p.n) : p.n;
+  if ((int64_t)blockIdx.x * NG * C >= n_eff) return;  // whole block behind the last real key (uniform: before any barrier)
   const int64_t w = (int64_t)blockIdx.x * NG + gid;
   const int64_t a = w * C;
-  const int cnt = a < p.n ? (int)min((int64_t)C, p.n - a) : 0;
+  const int cnt = a < n_eff ? (int)min((int64_t)C, n_eff - a) : 0;
   for (int i = lane; i < cnt; i += G) {
     const uint32_t g = p.svals[a + i];
     const uint32_t tt = g / p.B;
@@ -329,7 +348,7 @@ __global__ void __launch_bounds__(UPD_THREADS, (sizeof(GT) == 2 && !TRAIL && OPT
   if (lane == 0 && cnt > 0) {
     // sentinels: a key that differs from its neighbour when there is no neighbour
     s_key[gid][0] = a > 0 ? p.skeys[a - 1] : ~p.skeys[a];
-    s_key[gid][cnt + 1] = a + cnt < p.n ? p.skeys[a + cnt] : ~p.skeys[a + cnt - 1];
+    s_key[gid][cnt + 1] = a + cnt < n_eff ? p.skeys[a + cnt] : ~p.skeys[a + cnt - 1];
   }
   const float lr = p.d_lr ? *p.d_lr : p.lr;
   __syncthreads();
@@ -495,8 +514,8 @@ __global__ void __launch_bounds__(UPD_THREADS, (sizeof(GT) == 2 && !TRAIL && OPT
   // slot-0 pieces of the following windows (window order) and finishes the run; group 0 does the same
   // for the run that enters the block from the left.  What crosses a block border goes to p.partial.
   const int64_t blk_first = (int64_t)blockIdx.x * NG * C;
-  const int ngv = (int)min((int64_t)NG, (p.n - blk_first + C - 1) / C);  // windows of this block with data
-  const int cnt_last = (int)min((int64_t)C, p.n - (blk_first + (int64_t)(ngv - 1) * C));
+  const int ngv = (int)min((int64_t)NG, (n_eff - blk_first + C - 1) / C);  // windows of this block with data
+  const int cnt_last = (int)min((int64_t)C, n_eff - (blk_first + (int64_t)(ngv - 1) * C));
   const uint32_t key_after_block = s_key[ngv - 1][cnt_last + 1];
   // run entering from the previous window covers this whole window and goes on: some earlier group owns it
   const bool pass_through = cont0 && open_r && s_key[gid][1] == s_key[gid][cnt];
@@ -617,7 +636,8 @@ __global__ void __launch_bounds__(UPD_THREADS) window_join_kernel(const UpdParam
   const int64_t k = (int64_t)blockIdx.x * NG + gid + 1;  // border between positions k*BC-1 and k*BC
   // Does a run cross this border, and is this the FIRST border it crosses (the one that owns it)?
   // These checks read the sort/dedup outputs only, so they run before the window kernel has finished.
-  bool mine = k * BC < p.n && p.skeys[k * BC - 1] == p.skeys[k * BC];
+  const int64_t n_eff = p.d_n ? min(*p.d_n, p.n) : p.n;
+  bool mine = k * BC < n_eff && p.skeys[k * BC - 1] == p.skeys[k * BC];
   int64_t u = 0, s = 0, e = 0;
   if (mine) {
     u = p.win_run[k * NG];
@@ -694,6 +714,7 @@ __global__ void emb_update_scalar_kernel(const UpdParams p, int64_t n_max) {
     const int64_t u = i / p.D;
     const int d = (int)(i % p.D);
     const uint32_t s = p.seg[u], e = p.seg[u + 1];
+    if (p.d_n && (int64_t)s >= *p.d_n) continue;  // the run of sentinel keys behind the real ones
     const uint32_t t = p.svals[s] / p.B;
     const int64_t row = (int64_t)p.unique[u] - p.row_base[t];
     float acc = 0.f;
@@ -830,11 +851,12 @@ static int check_bwd_common(int64_t T, int64_t B, int64_t D, int64_t nnz, int64_
   return B200_OK;
 }
 
-extern "C" int b200_emb_bwd_prepare(const int64_t* d_rows, const int64_t* d_row_base,
-                                    const int64_t* d_indices, const int64_t* d_offsets, int64_t nnz,
-                                    int64_t T, int64_t B, int64_t D, int64_t total_rows, void* ws, size_t ws_bytes,
-                                    int32_t* d_error, b200_stream_t stream) {
-  int rc = check_bwd_common(T, B, D, nnz, total_rows);
+static int emb_bwd_prepare_impl(const int64_t* d_rows, const int64_t* d_row_base, const int64_t* d_indices,
+                                const int64_t* d_offsets, int64_t nnz, const int64_t* d_nnz_valid, int64_t T,
+                                int64_t B, int64_t D, int64_t total_rows, void* ws, size_t ws_bytes,
+                                int32_t* d_error, b200_stream_t stream) {
+  // a partially filled index array needs one more key value (the sentinel) behind the real row ids
+  int rc = check_bwd_common(T, B, D, nnz, total_rows + (d_nnz_valid ? 1 : 0));
   if (rc) return rc;
   if (T == 0 || B == 0 || nnz == 0) return B200_OK;
   B200_REQUIRE(d_rows && d_row_base && d_indices && d_offsets && ws, B200_EINVAL,
@@ -843,13 +865,33 @@ extern "C" int b200_emb_bwd_prepare(const int64_t* d_rows, const int64_t* d_row_
                "emb_bwd: workspace too small");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   BwdLayout L = bwd_layout(ws, nnz, D);
+  keys_tail_kernel<<<d_nnz_valid ? 256 : 1, 256, 0, st>>>(L.keys, L.vals, d_nnz_valid, nnz, (uint32_t)total_rows,
+                                                          L.n_valid);
   dim3 kgrid((unsigned)ceil_div(B, KEYS_THREADS), (unsigned)T);
   build_keys_kernel<<<kgrid, KEYS_THREADS, 0, st>>>(d_indices, d_offsets, d_rows, d_row_base, B, L.keys,
                                                     L.vals, d_error);
   B200_CHECK_LAUNCH("build_keys");
-  rc = sort_pairs(L.keys, L.vals, nnz, (uint64_t)total_rows, L.skeys, L.svals, L.sort_ws, st);
+  rc = sort_pairs(L.keys, L.vals, nnz, (uint64_t)total_rows + (d_nnz_valid ? 1 : 0), L.skeys, L.svals, L.sort_ws, st);
   if (rc) return rc;
   return dedup_runs(L.skeys, nnz, L.unique, L.seg, L.num_unique, L.sort_ws, st, L.win_run, L.svals, L.first_val);
+}
+
+extern "C" int b200_emb_bwd_prepare(const int64_t* d_rows, const int64_t* d_row_base,
+                                    const int64_t* d_indices, const int64_t* d_offsets, int64_t nnz,
+                                    int64_t T, int64_t B, int64_t D, int64_t total_rows, void* ws, size_t ws_bytes,
+                                    int32_t* d_error, b200_stream_t stream) {
+  return emb_bwd_prepare_impl(d_rows, d_row_base, d_indices, d_offsets, nnz, nullptr, T, B, D, total_rows, ws,
+                              ws_bytes, d_error, stream);
+}
+
+extern "C" int b200_emb_bwd_prepare_partial(const int64_t* d_rows, const int64_t* d_row_base,
+                                            const int64_t* d_indices, const int64_t* d_offsets, int64_t nnz_capacity,
+                                            const int64_t* d_nnz_valid, int64_t T, int64_t B, int64_t D,
+                                            int64_t total_rows, void* ws, size_t ws_bytes, int32_t* d_error,
+                                            b200_stream_t stream) {
+  B200_REQUIRE(d_nnz_valid, B200_EINVAL, "emb_bwd_prepare_partial: null count");
+  return emb_bwd_prepare_impl(d_rows, d_row_base, d_indices, d_offsets, nnz_capacity, d_nnz_valid, T, B, D,
+                              total_rows, ws, ws_bytes, d_error, stream);
 }
 
 static int emb_bwd_apply_impl(void* const* d_weights, float* const* d_state, uint16_t* const* d_trail,
@@ -896,6 +938,7 @@ static int emb_bwd_apply_impl(void* const* d_weights, float* const* d_state, uin
   p.T = (int)T;
   p.partial = L.partial;
   p.n = nnz;
+  p.d_n = L.n_valid;
   p.values = nullptr;
   p.by_key = 0;
   p.grad_ptrs = d_grad_ptrs;
@@ -987,6 +1030,7 @@ static int store_run_sums(const int64_t* d_row_base, int64_t nnz, const void* d_
   p.values = d_values;
   p.by_key = by_key;
   p.n = nnz;
+  p.d_n = L.n_valid;
   p.T = (int)T;
   const int gsz = dtype_size(grad_dtype);
   const bool vec_ok = (D * 4) % 16 == 0 && p.V <= 128 && (reinterpret_cast<uintptr_t>(d_grad) % 16) == 0 &&

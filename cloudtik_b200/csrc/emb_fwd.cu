@@ -43,6 +43,10 @@ struct EmbFwdParams {
   int64_t F;
   int64_t feat0;
   const float* const* scales;  // int8 tables: per-table pointer to the fp32 row scales (else unused)
+  // accumulate != 0: ADD the pooled row into the output (vector reductions; the caller zeroed it) instead of
+  // storing it, and skip bags that hold no index -- row-wise sharded tables, where every rank contributes the
+  // partial sum of the rows it owns to the same slot of the destination rank's interaction input
+  int accumulate;
 };
 
 // acc += row (fp32 / bf16 tables) or acc += scale * row (int8 tables)
@@ -172,7 +176,17 @@ __global__ void __launch_bounds__(FWD_THREADS) emb_fwd_kernel(const EmbFwdParams
 #pragma unroll
           for (int k = 0; k < NV; ++k) {
             if (lane + k * G < p.V) {
-              if constexpr (sizeof(WT) == sizeof(OT)) {
+              if (p.accumulate) {
+                if (row[u] != 0xffffffffu) {
+                  float f[VE];
+                  Vec16<WT>::unpack(f, v[u][k]);
+                  if constexpr (Q8) {
+#pragma unroll
+                    for (int x = 0; x < VE; ++x) f[x] *= sc[u];
+                  }
+                  red_vec<OT, VE>(dst + k * G * VE, f);
+                }
+              } else if constexpr (sizeof(WT) == sizeof(OT)) {
                 st_cs_v4(dst + k * G * VE, v[u][k]);
               } else {
                 float f[VE];
@@ -219,6 +233,14 @@ __global__ void __launch_bounds__(FWD_THREADS) emb_fwd_kernel(const EmbFwdParams
           for (int k = 0; k < NV; ++k) accum_row<WT>(acc[k], v[q][k], sc[q]);
       }
       OT* dst = outl + (int64_t)bag * p.out_stride_bag;
+      if (p.accumulate) {
+        if (eb > sb) {
+#pragma unroll
+          for (int k = 0; k < NV; ++k)
+            if (lane + k * G < p.V) red_vec<OT, VE>(dst + k * G * VE, acc[k]);
+        }
+        continue;
+      }
 #pragma unroll
       for (int k = 0; k < NV; ++k)
         if (lane + k * G < p.V) store_vec<OT, VE, true>(dst + k * G * VE, acc[k]);
@@ -259,6 +281,14 @@ __global__ void __launch_bounds__(FWD_THREADS) emb_fwd_kernel(const EmbFwdParams
         for (int k = 0; k < NV; ++k) accum_row<WT>(acc[k], v[q][k], sc[q]);
     }
     OT* dst = outl + (int64_t)bag * p.out_stride_bag;
+    if (p.accumulate) {
+      if (eb > sb) {
+#pragma unroll
+        for (int k = 0; k < NV; ++k)
+          if (lane + k * G < p.V) red_vec<OT, VE>(dst + k * G * VE, acc[k]);
+      }
+      continue;
+    }
 #pragma unroll
     for (int k = 0; k < NV; ++k)
       if (lane + k * G < p.V) store_vec<OT, VE, true>(dst + k * G * VE, acc[k]);
@@ -474,7 +504,17 @@ __global__ void __launch_bounds__(FWD_THREADS, 4)
 #pragma unroll
             for (int k = 0; k < NV; ++k) {
               if (lane + k * G < p.V) {
-                if constexpr (sizeof(WT) == sizeof(OT)) {
+                if (p.accumulate) {
+                  if (row[u] != 0xffffffffu) {
+                    float f[VE];
+                    Vec16<WT>::unpack(f, v[u][k]);
+                    if constexpr (Q8) {
+#pragma unroll
+                      for (int x = 0; x < VE; ++x) f[x] *= sc[u];
+                    }
+                    red_vec<OT, VE>(dst + k * G * VE, f);
+                  }
+                } else if constexpr (sizeof(WT) == sizeof(OT)) {
                   st_cs_v4(dst + k * G * VE, v[u][k]);
                 } else {
                   float f[VE];
@@ -519,6 +559,14 @@ __global__ void __launch_bounds__(FWD_THREADS, 4)
             for (int k = 0; k < NV; ++k) accum_row<WT>(acc[k], v[q][k], sc[q]);
         }
         OT* dst = outl + (int64_t)bag * p.out_stride_bag;
+        if (p.accumulate) {
+          if (eb > sb) {
+#pragma unroll
+            for (int k = 0; k < NV; ++k)
+              if (lane + k * G < p.V) red_vec<OT, VE>(dst + k * G * VE, acc[k]);
+          }
+          continue;
+        }
 #pragma unroll
         for (int k = 0; k < NV; ++k)
           if (lane + k * G < p.V) store_vec<OT, VE, true>(dst + k * G * VE, acc[k]);
@@ -558,6 +606,14 @@ __global__ void __launch_bounds__(FWD_THREADS, 4)
             for (int k = 0; k < NV; ++k) accum_row<WT>(acc[k], v[q][k], sc[q]);
         }
         OT* dst = outl + (int64_t)bag * p.out_stride_bag;
+        if (p.accumulate) {
+          if (eb > sb) {
+#pragma unroll
+            for (int k = 0; k < NV; ++k)
+              if (lane + k * G < p.V) red_vec<OT, VE>(dst + k * G * VE, acc[k]);
+          }
+          continue;
+        }
 #pragma unroll
         for (int k = 0; k < NV; ++k)
           if (lane + k * G < p.V) store_vec<OT, VE, true>(dst + k * G * VE, acc[k]);
@@ -697,7 +753,7 @@ static int emb_fwd_impl(const void* const* d_weights, const int64_t* d_rows, con
                         const int64_t* d_offsets, void* d_out, int64_t nnz, int64_t T, int64_t B, int64_t D,
                         int64_t out_stride_table, int64_t out_stride_bag, int w_dtype, int out_dtype,
                         int32_t* d_error, b200_stream_t stream, void* const* d_out_ptrs, int64_t lN, int64_t F,
-                        int64_t feat0, const float* const* d_scales = nullptr) {
+                        int64_t feat0, const float* const* d_scales = nullptr, int accumulate = 0) {
   B200_REQUIRE(T >= 0 && B >= 0 && D > 0 && nnz >= 0, B200_EINVAL, "emb_fwd: negative size");
   if (T == 0 || B == 0) return B200_OK;
   B200_REQUIRE(d_weights && d_rows && d_offsets && (d_out || d_out_ptrs) && (d_indices || nnz == 0), B200_EINVAL,
@@ -707,6 +763,7 @@ static int emb_fwd_impl(const void* const* d_weights, const int64_t* d_rows, con
                    (out_dtype == B200_F32 || out_dtype == B200_BF16),
                B200_EINVAL, "emb_fwd: bad dtype");
   EmbFwdParams p;
+  p.accumulate = accumulate;
   p.scales = d_scales;
   p.weights = d_weights;
   p.rows = d_rows;
@@ -742,6 +799,8 @@ static int emb_fwd_impl(const void* const* d_weights, const int64_t* d_rows, con
                                   : ((reinterpret_cast<uintptr_t>(d_out) & 15) == 0 &&
                                      (out_stride_table * os) % 16 == 0 && (out_stride_bag * os) % 16 == 0));
   B200_REQUIRE(vec_ok || !d_out_ptrs, B200_EUNSUPPORTED, "emb_fwd_sharded: row size must be a multiple of 16 bytes");
+  B200_REQUIRE(!accumulate || (vec_ok && ((16 / ws) * os) % 8 == 0), B200_EUNSUPPORTED,
+               "emb_fwd (accumulate): row size must be a multiple of 16 bytes");
 #define B200_DISPATCH(FN)                                                          \
   (w_dtype == B200_F32                                                             \
        ? (out_dtype == B200_F32 ? FN<float, float>(p, T, st)                       \
@@ -774,6 +833,16 @@ extern "C" int b200_emb_fwd_q8(const void* const* d_weights, const float* const*
   B200_REQUIRE(d_scales || T == 0 || B == 0, B200_EINVAL, "emb_fwd_q8: null scale table");
   return emb_fwd_impl(d_weights, d_rows, d_indices, d_offsets, d_out, nnz, T, B, D, out_stride_table,
                       out_stride_bag, B200_I8, out_dtype, d_error, stream, nullptr, 0, 0, 0, d_scales);
+}
+
+extern "C" int b200_emb_fwd_sharded_add(const void* const* d_weights, const int64_t* d_rows,
+                                        const int64_t* d_indices, const int64_t* d_offsets,
+                                        void* const* d_out_ptrs, int64_t nnz, int64_t T, int64_t B, int64_t D,
+                                        int64_t lN, int64_t F, int64_t feat0, int w_dtype, int out_dtype,
+                                        int32_t* d_error, b200_stream_t stream) {
+  B200_REQUIRE(d_out_ptrs, B200_EINVAL, "emb_fwd_sharded_add: null pointer table");
+  return emb_fwd_impl(d_weights, d_rows, d_indices, d_offsets, nullptr, nnz, T, B, D, 0, 0, w_dtype, out_dtype,
+                      d_error, stream, d_out_ptrs, lN, F, feat0, nullptr, 1);
 }
 
 extern "C" int b200_emb_fwd_sharded(const void* const* d_weights, const int64_t* d_rows,

@@ -316,7 +316,7 @@ def train_step(dlrm, optimizer, X, emb_args, T, lr=None):
     return E.detach()
 
 
-def train_step_chunked(dlrm, optimizer, batch, post_backward=None):
+def train_step_chunked(dlrm, optimizer, batch, post_backward=None, loss_scale=1.0):
     """One iteration on a batch given as the flat tuple ``(X, Y, indices_0, offsets_0[, indices_1, offsets_1, ...])``:
     one (indices, offsets) pair of linearised bags per micro-batch (a single pair = the plain step above), followed --
     only for a model with replicated small tables (``emb_dense``) -- by one more pair: this rank's LOCAL bags of
@@ -324,11 +324,15 @@ def train_step_chunked(dlrm, optimizer, batch, post_backward=None):
     covers ``X[c*n:(c+1)*n]`` of this rank's samples and, in ``indices_c``, the same slice of EVERY rank's samples
     (rank-major), i.e. the global micro-batch this rank's tables are looked up for.  MLP gradients accumulate over
     the chunks; each chunk's loss is scaled by 1/n_chunks so that their sum is the batch mean the reference
-    back-propagates.  ``post_backward`` (the MLP-gradient all-reduce) runs once, before the optimizer step.
+    back-propagates (``loss_scale``: one more factor on the back-propagated loss, e.g. 1/world when a scale-sensitive
+    table optimiser wants the MLP gradients summed instead of averaged).  ``post_backward`` (the MLP-gradient all-reduce) runs once, before the optimizer step.
     Returns the batch-mean loss tensor."""
     X, Y = batch[0], batch[1]
     pairs = [(batch[2 + 2 * c], batch[3 + 2 * c]) for c in range((len(batch) - 2) // 2)]
-    dense_bags = pairs.pop() if getattr(dlrm, "emb_dense", None) is not None else None  # LAST pair: replicated tables
+    # trailing pairs: GLOBAL-batch bags of the row-wise sharded tables (global row ids), and before them this rank's
+    # LOCAL bags of the replicated small tables
+    rw_bags = pairs.pop() if getattr(dlrm, "rowwise", None) is not None else None
+    dense_bags = pairs.pop() if getattr(dlrm, "emb_dense", None) is not None else None
     n = len(pairs)
     optimizer.zero_grad(set_to_none=True)
     if hasattr(post_backward, "begin"):
@@ -344,10 +348,11 @@ def train_step_chunked(dlrm, optimizer, batch, post_backward=None):
         rep.defer = True  # dense gradients of the replicated tables off the main chain; joined before the all-reduce
     for c, (idx, off) in enumerate(pairs):
         Xc, Yc = (X, Y) if n == 1 else (X[c * per:(c + 1) * per], Y[c * per:(c + 1) * per])
-        Z = (dlrm(Xc, idx, off, None, chunk=c) if dense_bags is None
-             else dlrm(Xc, idx, off, None, chunk=c, dense_bags=dense_bags)).float()
+        emb_args = (idx, off, None) if rw_bags is None else (idx, off, None, rw_bags[0], rw_bags[1])
+        Z = (dlrm(Xc, *emb_args, chunk=c) if dense_bags is None
+             else dlrm(Xc, *emb_args, chunk=c, dense_bags=dense_bags)).float()
         E = dlrm.loss_fn(Z, Yc)
-        (E if n == 1 else E / n).backward()
+        (E * (loss_scale / n) if (n > 1 or loss_scale != 1.0) else E).backward()
         total = E.detach() if total is None else total + E.detach()
     if rep is not None:
         rep.defer = False

@@ -14,13 +14,14 @@ import torch
 
 
 class GraphedTrainStep:
-    def __init__(self, net, optimizer, example, warmup: int = 3, post_backward=None):
+    def __init__(self, net, optimizer, example, warmup: int = 3, post_backward=None, loss_scale: float = 1.0):
         """``example`` = (X, Y, indices, offsets) device tensors with the shapes of every later batch -- or, for a
         micro-batched step, (X, Y, indices_0, offsets_0, indices_1, offsets_1, ...), see ``dlrm.train_step_chunked``.
         ``post_backward``: optional callable run between backward and the optimizer step (the flat
         all-reduce of the MLP gradients in the multi-GPU case; NCCL collectives are captured too)."""
         self.net, self.opt = net, optimizer
         self.post_backward = post_backward
+        self.loss_scale = loss_scale
         self.static = [torch.empty_like(t) for t in example]
         for d, s in zip(self.static, example):
             d.copy_(s)
@@ -49,7 +50,7 @@ class GraphedTrainStep:
 
     def _eager(self):
         from .dlrm import train_step_chunked
-        return train_step_chunked(self.net, self.opt, self.static, self.post_backward)
+        return train_step_chunked(self.net, self.opt, self.static, self.post_backward, self.loss_scale)
 
     # ---- host-fed operation: pinned-host batches are staged by a copy stream one step ahead ----
     def prefetch(self, host_batch):

@@ -150,15 +150,46 @@ def emb_bwd_update(tables: TableSet, indices, offsets, B: int, grad: torch.Tenso
 
 
 def emb_bwd_prepare(tables: TableSet, indices, offsets, B: int, ws: torch.Tensor,
-                    error: torch.Tensor | None = None):
-    """Index stage of the backward (keys, stable sort, dedup) into ``ws``.  See b200_emb_bwd_prepare."""
+                    error: torch.Tensor | None = None, nnz_valid: torch.Tensor | None = None):
+    """Index stage of the backward (keys, stable sort, dedup) into ``ws``.  See b200_emb_bwd_prepare.
+    ``nnz_valid``: device int64 scalar -- ``indices`` is a fixed-capacity array filled up to that count
+    (b200_emb_bwd_prepare_partial)."""
     _cuda(indices, "indices", torch.int64)
     _cuda(offsets, "offsets", torch.int64)
+    if nnz_valid is not None:
+        _cuda(nnz_valid, "nnz_valid", torch.int64)
+        check(lib.b200_emb_bwd_prepare_partial(
+            tables.d_rows.data_ptr(), tables.d_row_base.data_ptr(), indices.data_ptr(), offsets.data_ptr(),
+            indices.numel(), nnz_valid.data_ptr(), len(tables), B, tables.D, tables.total_rows, ws.data_ptr(),
+            ws.numel() * ws.element_size(), error.data_ptr() if error is not None else None, _stream()),
+            "b200_emb_bwd_prepare_partial")
+        return
     check(lib.b200_emb_bwd_prepare(tables.d_rows.data_ptr(), tables.d_row_base.data_ptr(), indices.data_ptr(),
                                    offsets.data_ptr(), indices.numel(), len(tables), B, tables.D,
                                    tables.total_rows, ws.data_ptr(), ws.numel() * ws.element_size(),
                                    error.data_ptr() if error is not None else None, _stream()),
           "b200_emb_bwd_prepare")
+
+
+def rowwise_filter(indices, offsets, world: int, rank: int, capacity: int, error: torch.Tensor | None = None,
+                   out=None):
+    """Bags over global row ids -> bags over the rows rank ``rank`` of ``world`` owns (id % world == rank, local id =
+    id // world) in a FIXED-capacity index array; ``offsets[-1]`` of the result is the fill level (it stays on the
+    device).  Returns (local_indices int64[capacity], local_offsets int64[n_bags + 1]).  See b200_rowwise_filter."""
+    _cuda(indices, "indices", torch.int64)
+    _cuda(offsets, "offsets", torch.int64)
+    nb = offsets.numel() - 1
+    dev = indices.device
+    if out is None:
+        out = (torch.empty(max(capacity, 1), dtype=torch.int64, device=dev),
+               torch.empty(nb + 1, dtype=torch.int64, device=dev))
+    li, lo = out
+    nbytes = int(lib.b200_rowwise_filter_workspace_bytes(nb))
+    ws = torch.empty(max(nbytes, 8), dtype=torch.uint8, device=dev)
+    check(lib.b200_rowwise_filter(indices.data_ptr(), offsets.data_ptr(), nb, world, rank, li.data_ptr(), capacity,
+                                  lo.data_ptr(), error.data_ptr() if error is not None else None, ws.data_ptr(),
+                                  nbytes, _stream()), "b200_rowwise_filter")
+    return li, lo
 
 
 def emb_bwd_apply(tables: TableSet, nnz: int, B: int, grad: torch.Tensor, stride_table: int, stride_bag: int,
@@ -178,13 +209,15 @@ def emb_bwd_apply(tables: TableSet, nnz: int, B: int, grad: torch.Tensor, stride
 
 
 def emb_fwd_sharded(tables: TableSet, indices, offsets, B: int, out_ptrs_dev: int, lN: int, F: int, feat0: int,
-                    out_dtype: torch.dtype, error: torch.Tensor | None = None):
+                    out_dtype: torch.dtype, error: torch.Tensor | None = None, accumulate: bool = False):
     """Pooled lookup of this rank's tables for the GLOBAL batch, written straight into every rank's
     interaction input over peer memory.  ``out_ptrs_dev``: device address of the [world] pointer table.
-    See b200_emb_fwd_sharded."""
+    ``accumulate``: ADD into the (zeroed) destination instead of storing -- row-wise sharded tables.
+    See b200_emb_fwd_sharded / b200_emb_fwd_sharded_add."""
     _cuda(indices, "indices", torch.int64)
     _cuda(offsets, "offsets", torch.int64)
-    check(lib.b200_emb_fwd_sharded(tables.d_ptrs.data_ptr(), tables.d_rows.data_ptr(), indices.data_ptr(),
+    fn = lib.b200_emb_fwd_sharded_add if accumulate else lib.b200_emb_fwd_sharded
+    check(fn(tables.d_ptrs.data_ptr(), tables.d_rows.data_ptr(), indices.data_ptr(),
                                    offsets.data_ptr(), out_ptrs_dev, indices.numel(), len(tables), B, tables.D,
                                    lN, F, feat0, _dt(tables.dtype), _dt(out_dtype),
                                    error.data_ptr() if error is not None else None, _stream()),

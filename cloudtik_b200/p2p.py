@@ -87,9 +87,11 @@ class _ShardedEmbInteractFn(torch.autograd.Function):
                 if train:  # sort / dedup on the side stream: only a backward consumes it
                     emb._launch_prepare(indices, offsets, B_glob, chunk=exch.chunk)
         ctx.rw_ctx = None
-        if rowwise is not None:  # row-wise sharded hot tables occupy the LAST feature slots
-            rw_out, ctx.rw_ctx = rowwise.pool(rw_indices, rw_offsets, exch.lN)
-            exch.T[:, exch.F - rowwise.k:].copy_(rw_out)
+        if rowwise is not None:
+            # row-wise sharded hot tables occupy the LAST feature slots: every rank ADDS its partial pooled rows
+            # into every rank's T over peer memory (each rank zeroed its slots before the previous step's B2, or
+            # when the buffers were created)
+            ctx.rw_ctx = rowwise.pool_to_peers(rw_indices, rw_offsets, exch)
         exch.T[:, 0].copy_(x)
         exch.barrier(0)  # B1
         R = ops.interact_fwd(exch.T, pad_to=pad_to)
@@ -97,6 +99,8 @@ class _ShardedEmbInteractFn(torch.autograd.Function):
             # forward-only (eval / no_grad): there is no backward and hence no B2 -- without a second barrier a
             # faster rank could start the NEXT forward and store into this rank's T while interact_fwd above is
             # still reading it
+            if rowwise is not None:
+                exch.T[:, exch.F - rowwise.k:].zero_()
             exch.barrier(1)
         ctx.emb, ctx.exch, ctx.feat0, ctx.rowwise = emb, exch, feat0, rowwise
         ctx.repl, ctx.repl_bags = repl, (repl_indices, repl_offsets)
@@ -110,11 +114,15 @@ class _ShardedEmbInteractFn(torch.autograd.Function):
         indices, offsets = ctx.saved_tensors
         B_glob = exch.lN * exch.world
         ops.interact_bwd(exch.T, dR.contiguous().to(exch.dtype), out=exch.dT)
+        if ctx.rowwise is not None:
+            # T is read for the last time above: clear the row-wise slots for the next step's partial sums.  A peer
+            # starts adding into them only after it passed B2, i.e. after this
+            exch.T[:, exch.F - ctx.rowwise.k:].zero_()
         exch.barrier(1)  # B2
         if emb is not None:
             emb._apply_update_sharded(indices, offsets, B_glob, exch, ctx.feat0)
         if ctx.rowwise is not None:
-            ctx.rowwise.update(exch.dT[:, exch.F - ctx.rowwise.k:], ctx.rw_ctx)
+            ctx.rowwise.update_from_peers(ctx.rw_ctx, exch)
         dx = exch.dT[:, 0].clone()  # dT is overwritten by the next step; the bottom MLP backward runs now
         rg = ()
         if ctx.repl is not None:  # dense gradients of the replicated tables (all-reduced with the MLPs' by the caller)

@@ -1,13 +1,22 @@
 """Row-wise sharded hot tables (BASELINE config 5; SURVEY.md section 8e -- not in the reference, which only
 shards table-wise).  Rank r of W owns rows {i : i mod W == r} of every hot table, stored densely as local
-row i // W.  For the GLOBAL batch every rank pools the rows it owns (partial sums), a reduce-scatter over
-the batch dimension gives each rank the complete pooled rows of ITS samples; backward all-gathers the
-output gradients and every rank runs the fused sort / dedup / update on the rows it owns.
+row i // W.  For the GLOBAL batch every rank pools the rows it owns (partial sums); the partial sums of the W ranks
+have to be added up for each sample's rank (a reduce-scatter over the batch dimension), and in backward every rank
+needs the output gradients of ALL samples (an all-gather) to run the fused sort / dedup / update on its rows.
 
-Kernels: the same ``b200_emb_fwd`` / ``b200_emb_bwd_*`` entry points, fed with the bags filtered down to
-the owned rows (a mask + prefix sum over the CSR arrays).  Collectives: NCCL reduce_scatter / all_gather
-(a real exchange step: partial sums have to be added).  Sharded-table learning rate is lr / W for the same
-reason as table-wise sharding (every rank contributes the gradient of a local-mean loss).
+Both exchanges are fused into the embedding kernels over NVLink peer memory, like the table-wise ones
+(``cloudtik_b200.p2p``):
+* ``b200_rowwise_filter`` keeps the owned indices of every bag in a FIXED-capacity array (fill level on the device:
+  no data-dependent shape, no host sync -- the step is graph-capturable);
+* forward: ``b200_emb_fwd_sharded_add`` ADDS each partial pooled row straight into the destination rank's slot of
+  the interaction input (``red.global.add`` over peer memory; the destination zeroed the slot; bags without an
+  owned index send nothing) -- the reduce-scatter;
+* backward: ``b200_emb_bwd_prepare_partial`` + ``b200_emb_bwd_apply_sharded`` read the gradient rows of every
+  rank's samples from the owning rank's ``dT`` -- the all-gather.
+(``pool`` / ``update`` keep the NCCL reduce_scatter / all_gather formulation: the reference point the fused one was
+checked against, and the path for a job without peer access.)
+Sharded-table learning rate is lr / W for the same reason as table-wise sharding (every rank contributes the
+gradient of a local-mean loss).
 """
 from __future__ import annotations
 
@@ -51,6 +60,7 @@ class RowWiseShardedTables(nn.Module):
         self.emb.reserve_dense_slot = False
         self.emb.output_dtype = out_dtype
         self.emb.overlap_prepare = False
+        self.error_flag = None  # int32[1]: 2 = a step owned more indices than the fixed capacity (bags truncated)
 
     def pool(self, indices, offsets, lN: int):
         """indices / offsets: linearised GLOBAL-batch bags of the k hot tables (global row ids).
@@ -71,6 +81,36 @@ class RowWiseShardedTables(nn.Module):
         gall = torch.empty(B_glob, self.k, self.dim, dtype=g.dtype, device=g.device)
         dist.all_gather_into_tensor(gall, g)
         self.emb._apply_update(li, lo, B_glob, gall, self.dim, self.k * self.dim)
+
+    # ---- fused over peer memory -------------------------------------------------------
+    def capacity(self, nnz: int) -> int:
+        """Fixed size of the filtered index array: the expected share nnz / W with 25 % head-room (row ids spread
+        by ``mod W``; a fuller step sets the error flag instead of reallocating)."""
+        return max(1024, int(nnz / self.world * 1.25) + 1024) // 2 * 2
+
+    def pool_to_peers(self, indices, offsets, exch):
+        """indices / offsets: linearised GLOBAL-batch bags of the k hot tables (global row ids).  Adds this rank's
+        partial pooled rows into the LAST k feature slots of every rank's ``exch.T`` (which that rank zeroed).
+        Returns the ctx for ``update_from_peers``."""
+        B_glob = exch.lN * self.world
+        if self.error_flag is None:
+            self.error_flag = torch.zeros(1, dtype=torch.int32, device=indices.device)
+        li, lo = ops.rowwise_filter(indices, offsets, self.world, self.rank, self.capacity(indices.numel()),
+                                    self.error_flag)
+        ops.emb_fwd_sharded(self.emb.tables, li, lo, B_glob, exch.T_ptrs_dev, exch.lN, exch.F, exch.F - self.k,
+                            exch.dtype, self.emb.error_flag, accumulate=True)
+        return li, lo, B_glob
+
+    def update_from_peers(self, ctx, exch):
+        """Fused update of the owned rows; the gradient rows come from every rank's ``exch.dT`` (after barrier B2)."""
+        li, lo, B_glob = ctx
+        emb = self.emb
+        ws = emb._workspace(li.numel())
+        ops.emb_bwd_prepare(emb.tables, li, lo, B_glob, ws, emb.error_flag, nnz_valid=lo[-1:])
+        opt = ops.OPT_ADAGRAD if emb.optimizer_kind == "adagrad" else ops.OPT_SGD
+        ops.emb_bwd_apply_sharded(emb.tables, li.numel(), B_glob, exch.dT_ptrs_dev, exch.lN, exch.F, exch.F - self.k,
+                                  exch.dtype, emb.sgd_args.lr, ws, optimizer=opt, eps=emb.eps,
+                                  lr_tensor=emb.lr_tensor)
 
     def full_table(self, t: int) -> torch.Tensor:
         """Reassemble hot table t from every rank's shard (tests / checkpoints)."""

@@ -177,6 +177,38 @@ int b200_emb_bwd_apply_sharded(void* const* d_weights, float* const* d_state, ui
                                void* ws, size_t ws_bytes, b200_stream_t stream);
 
 /*
+ * Row-wise sharded hot tables (BASELINE configs[4]; not in the reference, whose distributed_forward shards table-wise
+ * only, T/dlrm_s_pytorch.py:483-522).  Rank r of W owns the rows {i : i mod W == r} of a table, stored densely as
+ * local row i / W.
+ *   b200_rowwise_filter          bags over global row ids (CSR d_offsets[n_bags+1]) -> bags over the rows this rank
+ *                                owns: d_out_indices (local ids, FIXED capacity) and d_out_offsets[n_bags+1], whose
+ *                                last entry is the number of indices kept.  The fill level never reaches the host,
+ *                                so the step has no data-dependent shape (graph-capturable).  If more indices are
+ *                                owned than out_capacity, the overflow is dropped and *d_error is set to 2.
+ *   b200_emb_fwd_sharded_add     b200_emb_fwd_sharded, but the pooled partial sum is ADDED (red.global.add over
+ *                                peer memory) to the destination slot, which the destination rank zeroed; bags
+ *                                without an owned index send nothing.  W ranks together build the pooled row: the
+ *                                reduce-scatter of the row-wise scheme fused into the lookup.
+ *   b200_emb_bwd_prepare_partial b200_emb_bwd_prepare for an index array filled up to *d_nnz_valid (device-side,
+ *                                = d_out_offsets[n_bags] of the filter): the unused tail sorts behind the real keys
+ *                                and the following b200_emb_bwd_apply[_sharded] stops at the fill level.
+ * The backward needs no extra entry point: b200_emb_bwd_apply_sharded already gathers the gradient rows of every
+ * rank's samples (the all-gather of the row-wise scheme).
+ */
+size_t b200_rowwise_filter_workspace_bytes(int64_t n_bags);
+int b200_rowwise_filter(const int64_t* d_indices, const int64_t* d_offsets, int64_t n_bags, int64_t world,
+                        int64_t rank, int64_t* d_out_indices, int64_t out_capacity, int64_t* d_out_offsets,
+                        int32_t* d_error, void* ws, size_t ws_bytes, b200_stream_t stream);
+int b200_emb_fwd_sharded_add(const void* const* d_weights, const int64_t* d_rows, const int64_t* d_indices,
+                             const int64_t* d_offsets, void* const* d_out_ptrs, int64_t nnz, int64_t T, int64_t B,
+                             int64_t D, int64_t lN, int64_t F, int64_t feat0, int w_dtype, int out_dtype,
+                             int32_t* d_error, b200_stream_t stream);
+int b200_emb_bwd_prepare_partial(const int64_t* d_rows, const int64_t* d_row_base, const int64_t* d_indices,
+                                 const int64_t* d_offsets, int64_t nnz_capacity, const int64_t* d_nnz_valid,
+                                 int64_t T, int64_t B, int64_t D, int64_t total_rows, void* ws, size_t ws_bytes,
+                                 int32_t* d_error, b200_stream_t stream);
+
+/*
  * EmbeddingBag backward as a COALESCED sparse gradient (no optimiser fused): for callers that keep
  * the per-table `nn.EmbeddingBag(sparse=True)` seam of DLRM_Net.apply_emb (P/dlrm_s_pytorch.py:299-305)
  * and let torch.optim.SGD / Adagrad consume the sparse gradient (P/dlrm_s_pytorch.py:805,1059).

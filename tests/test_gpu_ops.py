@@ -633,3 +633,94 @@ def test_survey_named_entry_points_match_update():
         torch.cuda.synchronize()
         for wa, wb in zip(a.weights, b.weights):
             assert torch.equal(wa, wb)
+
+
+@pytest.mark.parametrize("W", [2, 3, 8])
+def test_rowwise_filter_matches_mask_and_prefix_sum(W):
+    """b200_rowwise_filter (fixed capacity, fill level on the device) against the torch formulation
+    (cloudtik_b200.rowwise.filter_owned: mask + prefix sum); an undersized capacity raises the overflow flag."""
+    ops = _ops()
+    from cloudtik_b200.rowwise import filter_owned
+    rs = np.random.RandomState(W)
+    lens = rs.randint(0, 7, size=5000)
+    off = torch.tensor(np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)).cuda()
+    idx = torch.tensor(rs.randint(0, 100000, size=int(lens.sum())).astype(np.int64)).cuda()
+    for r in range(W):
+        want_i, want_o = filter_owned(idx, off, W, r)
+        err = torch.zeros(1, dtype=torch.int32, device="cuda")
+        li, lo = ops.rowwise_filter(idx, off, W, r, idx.numel(), err)
+        n = int(lo[-1].item())
+        assert n == want_i.numel() and int(err.item()) == 0
+        assert torch.equal(lo, want_o) and torch.equal(li[:n], want_i)
+    err = torch.zeros(1, dtype=torch.int32, device="cuda")
+    li, lo = ops.rowwise_filter(idx, off, W, 0, 10, err)
+    assert int(err.item()) == 2 and int(lo[-1].item()) == 10
+
+
+@pytest.mark.parametrize("opt", ["sgd", "adagrad"])
+def test_partial_prepare_stops_at_the_fill_level(opt):
+    """A fixed-capacity index array filled up to a device-side count (b200_emb_bwd_prepare_partial): the update must
+    equal the one of the exactly sized array -- the tail sorts behind the real keys and is never touched."""
+    ops = _ops()
+    rs = np.random.RandomState(3)
+    rows, B, D = [700, 5, 3000], 300, 128
+    idx_l, off_l = _make_bags(rs, rows, B, 4, True)
+    indices, offsets, _ = ref.linearize_indices_and_offsets(idx_l, off_l, rows)
+    n = len(indices)
+    g = torch.tensor(rs.randn(B, len(rows), D).astype(np.float32)).cuda()
+    W0 = [torch.tensor(rs.uniform(-1, 1, size=(r, D)).astype(np.float32)).cuda() for r in rows]
+    res = []
+    for cap in (n, n + 777):
+        ts = ops.TableSet([w.clone() for w in W0])
+        if opt == "adagrad":
+            ts.set_states([torch.full((r, D), 0.1, device="cuda") for r in rows])
+        ind = torch.full((cap,), 123456789, dtype=torch.int64, device="cuda")  # garbage behind the fill level
+        ind[:n] = torch.tensor(indices)
+        off = torch.tensor(offsets).cuda()
+        ws = torch.empty(ops.emb_bwd_workspace_bytes(cap, D), dtype=torch.uint8, device="cuda")
+        ops.emb_bwd_prepare(ts, ind, off, B, ws, nnz_valid=off[-1:] if cap != n else None)
+        ops.emb_bwd_apply(ts, cap, B, g, D, len(rows) * D, 0.2, ws,
+                          optimizer=ops.OPT_ADAGRAD if opt == "adagrad" else ops.OPT_SGD)
+        torch.cuda.synchronize()
+        res.append([w.clone() for w in ts.weights])
+    for a_, b_ in zip(*res):
+        assert torch.equal(a_, b_)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_rowwise_partial_sums_add_up_over_emulated_ranks(dtype):
+    """b200_emb_fwd_sharded_add on one GPU with W emulated ranks: every "rank" filters the global bags down to its
+    rows and ADDS its partial pooled rows into the destination buffers; together they must give the pooled rows of
+    the unsharded table (the reduce-scatter of the row-wise scheme)."""
+    ops = _ops()
+    W, lN, D, k = 4, 32, 128, 2
+    F = 1 + k
+    B = W * lN
+    rs = np.random.RandomState(12)
+    rows = [1000, 37]
+    full = [rs.uniform(-1, 1, size=(n, D)).astype(np.float32) for n in rows]
+    idx_l, off_l = _make_bags(rs, rows, B, 5, True)
+    # global row ids per table are table-local here: one filter call per table keeps ids table-local
+    T_dst = [torch.zeros(lN, F, D, dtype=dtype, device="cuda") for _ in range(W)]
+    ptrs = torch.tensor([t.data_ptr() for t in T_dst], dtype=torch.int64, device="cuda")
+    for r in range(W):
+        shards = [torch.tensor(np.ascontiguousarray(f[r::W])).cuda() for f in full]
+        ts = ops.TableSet(shards)
+        lis, los, base = [], [], 0
+        for t in range(k):
+            off = torch.tensor(np.concatenate([off_l[t], [len(idx_l[t])]]).astype(np.int64)).cuda()
+            li, lo = ops.rowwise_filter(torch.tensor(idx_l[t]).cuda(), off, W, r, len(idx_l[t]) + 2)
+            n = int(lo[-1].item())
+            lis.append(li[:n])
+            los.append(lo[:-1] + base)
+            base += n
+        li = torch.cat(lis)
+        lo = torch.cat(los + [torch.tensor([base], dtype=torch.int64, device="cuda")])
+        ops.emb_fwd_sharded(ts, li, lo, B, ptrs.data_ptr(), lN, F, 1, dtype, accumulate=True)
+    torch.cuda.synchronize()
+    got = torch.cat(T_dst, dim=0).float().cpu().numpy()  # [B, F, D]
+    for t in range(k):
+        want = ref.embedding_bag_sum(full[t], idx_l[t], off_l[t])
+        tol = dict(rtol=1e-5, atol=1e-5) if dtype == torch.float32 else dict(rtol=3e-2, atol=6e-2)
+        np.testing.assert_allclose(got[:, 1 + t], want, **tol)
+    assert not got[:, 0].any()

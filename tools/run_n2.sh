@@ -1,3 +1,5 @@
 python -m pytest tests -m gpu -x -q 2>&1 | tail -4
-python -m cloudtik_b200.launcher --nproc-per-node 2 --master-port 29511 -m cloudtik_b200.train --arch-sparse-feature-size=128 --arch-mlp-bot=13-512-128 --arch-mlp-top=512-256-1 --arch-embedding-size=100000-37-5000-3-20000-800-64-3000000 --mini-batch-size=4096 --num-batches=6 --loss-function=bce --round-targets=True --num-indices-per-lookup=4 --learning-rate=0.1 --print-time --print-freq=2 2>&1 | grep -v Warning | tail -6
-python -m cloudtik_b200.launcher --nproc-per-node 2 --master-port 29512 bench.py --gpus 2 --steps 20 --warmup 5 --global-batch 65536 > gpurun_out/b_n2_strong.log 2>&1; tail -c 400 gpurun_out/b_n2_strong.log
+run() { p=$1; shift; timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port $p "$@"; }
+run 29501 tests/dist_parity.py --p2p --rowwise 2 2>&1 | tail -3
+run 29502 tests/dist_parity.py --p2p --rowwise 2 --adagrad --bf16 2>&1 | tail -3
+run 29503 bench.py --workload c5 --gpus 2 --steps 10 --warmup 3 > gpurun_out/b_n2_c5.log 2>&1; tail -c 1500 gpurun_out/b_n2_c5.log
