@@ -29,11 +29,17 @@ constexpr int UPD_THREADS = 256;
 // (the fp32 SGD variant issues ONE vector reduction per 16 bytes of a row, from one group).
 constexpr int OPT_STORE = 2;  // internal "optimizer": write the per-row gradient sums to values[run index]
 constexpr int MIN_NG = UPD_THREADS / 32;  // fewest windows per block (one warp per window)
+// A run that crosses more than HOT_BLOCKS block borders (a row with tens of thousands of duplicates: the 3-row Criteo
+// table under multi-hot bags receives B * P / 3 gradients per step) is not added up by ONE group of the join kernel
+// any more: the join kernel only lists it, and hot_join_kernel gives it a whole CTA.
+constexpr int HOT_BLOCKS = 16;
 
 struct BwdLayout {
   uint32_t *keys, *vals, *skeys, *svals, *unique, *seg, *win_run, *first_val;
   int32_t* num_unique;
   int64_t* n_valid;  // sorted positions that hold real keys (= nnz, or fewer after b200_emb_bwd_prepare_partial)
+  int32_t* hot_count;  // runs that span more than HOT_BLOCKS blocks of the window kernel (zeroed by prepare)
+  uint32_t* hot_list;  // their run indices, [ceil(nblk / HOT_BLOCKS) + 2]
   float* partial;   // [2 * nblk][D], nblk = blocks of the window kernel (<= ceil(nwin / MIN_NG))
   void* sort_ws;
   size_t total;
@@ -52,7 +58,10 @@ static BwdLayout bwd_layout(void* ws, int64_t n, int64_t D) {
   L.first_val = reinterpret_cast<uint32_t*>(w + o), o += s;
   L.seg = reinterpret_cast<uint32_t*>(w + o), o += align_up((size_t)(n + 1) * 4, 256);
   L.num_unique = reinterpret_cast<int32_t*>(w + o);
-  L.n_valid = reinterpret_cast<int64_t*>(w + o + 64), o += 256;
+  L.n_valid = reinterpret_cast<int64_t*>(w + o + 64);
+  L.hot_count = reinterpret_cast<int32_t*>(w + o + 128), o += 256;
+  L.hot_list = reinterpret_cast<uint32_t*>(w + o),
+  o += align_up((size_t)(ceil_div(ceil_div(ceil_div(n, HOT_CH), MIN_NG), HOT_BLOCKS) + 2) * 4, 256);
   L.win_run = reinterpret_cast<uint32_t*>(w + o), o += align_up((size_t)(ceil_div(n, HOT_CH) + 1) * 4, 256);
   L.partial = reinterpret_cast<float*>(w + o),
   o += align_up((size_t)(2 * ceil_div(ceil_div(n, HOT_CH), MIN_NG)) * D * 4, 256);
@@ -68,9 +77,12 @@ static BwdLayout bwd_layout(void* ws, int64_t n, int64_t D) {
 // *n_valid.  Also publishes n_valid in the workspace.
 __global__ void __launch_bounds__(256)
     keys_tail_kernel(uint32_t* __restrict__ keys, uint32_t* __restrict__ vals, const int64_t* __restrict__ d_valid,
-                     int64_t n, uint32_t sentinel, int64_t* __restrict__ n_valid_out) {
+                     int64_t n, uint32_t sentinel, int64_t* __restrict__ n_valid_out, int32_t* __restrict__ hot_count) {
   const int64_t nv = d_valid ? min(max(*d_valid, (int64_t)0), n) : n;
-  if (blockIdx.x == 0 && threadIdx.x == 0) *n_valid_out = nv;
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    *n_valid_out = nv;
+    *hot_count = 0;
+  }
   for (int64_t j = nv + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (int64_t)gridDim.x * blockDim.x) {
     keys[j] = sentinel;
     vals[j] = 0u;
@@ -152,6 +164,8 @@ struct UpdParams {
   float* partial;
   int64_t n;            // capacity of the sorted arrays (sizes the grid)
   const int64_t* d_n;   // real keys among them, read at kernel time (the sort puts them first)
+  int32_t* hot_count;
+  uint32_t* hot_list;
 };
 
 // load VE consecutive gradient elements (GT) as fp32
@@ -626,6 +640,44 @@ __device__ __forceinline__ void add_partial_rows(float (*acc)[VE], const float* 
   }
 }
 
+// one update of run u's row with the gradient sum `acc` (lane l of the group holds vectors l, l + G, ...)
+template <typename WT, int G, int NV, int OPT, bool RED>
+__device__ __forceinline__ void finish_run(const UpdParams& p, int64_t u, float (*acc)[Vec16<WT>::VE], int lane) {
+  constexpr int VE = Vec16<WT>::VE;
+  const float lr = p.d_lr ? *p.d_lr : p.lr;
+  char* wp;
+  float* sp = nullptr;
+  char* tp = nullptr;
+  if (OPT == OPT_STORE) {
+    wp = reinterpret_cast<char*>(p.values) + ((size_t)(p.by_key ? (int64_t)p.unique[u] : u) * p.D + lane * VE) * sizeof(WT);
+  } else {
+    const uint32_t tt = p.first_val[u] / p.B;
+    const int64_t row = (int64_t)p.unique[u] - p.row_base[tt];
+    wp = static_cast<char*>(p.weights[tt]) + ((size_t)row * p.D + lane * VE) * sizeof(WT);
+    if (OPT == B200_OPT_ADAGRAD) sp = p.state[tt] + (size_t)row * p.D + lane * VE;
+    if constexpr (sizeof(WT) == 2) {
+      if (p.trail != nullptr) tp = wp + (reinterpret_cast<char*>(p.trail[tt]) - static_cast<char*>(p.weights[tt]));
+    }
+  }
+#pragma unroll
+  for (int kk = 0; kk < NV; ++kk)
+    if (lane + kk * G < p.V) {
+      if constexpr (RED) {
+        red_add_v4_f32(reinterpret_cast<float*>(wp + (size_t)kk * G * 16), -lr * acc[kk][0], -lr * acc[kk][1],
+                       -lr * acc[kk][2], -lr * acc[kk][3]);
+      } else {
+        float wf[VE] = {};
+        uint4 tv = make_uint4(0, 0, 0, 0);
+        if constexpr (OPT != OPT_STORE) {
+          Vec16<WT>::unpack(wf, ld_v4(wp + (size_t)kk * G * 16));
+          if (tp) tv = ld_v4(tp + (size_t)kk * G * 16);
+        }
+        apply_row<OPT, WT>(wp + (size_t)kk * G * 16, sp ? sp + kk * G * VE : nullptr, acc[kk], wf, lr, p.eps,
+                           tp ? tp + (size_t)kk * G * 16 : nullptr, tv);
+      }
+    }
+}
+
 template <typename WT, int G, int NV, int OPT, bool RED>
 __global__ void __launch_bounds__(UPD_THREADS) window_join_kernel(const UpdParams p) {
   constexpr int VE = Vec16<WT>::VE;
@@ -653,34 +705,9 @@ __global__ void __launch_bounds__(UPD_THREADS) window_join_kernel(const UpdParam
   asm volatile("griddepcontrol.wait;" ::: "memory");
   if (!mine) return;
   const int64_t w0 = s / BC, w1 = (e - 1) / BC;
-  const float lr = p.d_lr ? *p.d_lr : p.lr;
-  char* wp;
-  float* sp = nullptr;
-  if (OPT == OPT_STORE) {
-    wp = reinterpret_cast<char*>(p.values) + ((size_t)(p.by_key ? (int64_t)p.unique[u] : u) * p.D + lane * VE) * sizeof(WT);
-  } else {
-    const uint32_t tt = p.first_val[u] / p.B;
-    const int64_t row = (int64_t)p.unique[u] - p.row_base[tt];
-    wp = static_cast<char*>(p.weights[tt]) + ((size_t)row * p.D + lane * VE) * sizeof(WT);
-    if (OPT == B200_OPT_ADAGRAD) sp = p.state[tt] + (size_t)row * p.D + lane * VE;
-  }
-  uint4 wv[NV], tv[NV];
-  char* tp = nullptr;
-#pragma unroll
-  for (int kk = 0; kk < NV; ++kk) wv[kk] = tv[kk] = make_uint4(0, 0, 0, 0);
-  if constexpr (!RED && OPT != OPT_STORE) {
-#pragma unroll
-    for (int kk = 0; kk < NV; ++kk)
-      if (lane + kk * G < p.V) wv[kk] = ld_v4(wp + (size_t)kk * G * 16);
-    if constexpr (sizeof(WT) == 2) {
-      if (p.trail != nullptr) {
-        const uint32_t tt2 = p.first_val[u] / p.B;
-        tp = wp + (reinterpret_cast<char*>(p.trail[tt2]) - static_cast<char*>(p.weights[tt2]));
-#pragma unroll
-        for (int kk = 0; kk < NV; ++kk)
-          if (lane + kk * G < p.V) tv[kk] = ld_v4(tp + (size_t)kk * G * 16);
-      }
-    }
+  if (w1 - w0 >= HOT_BLOCKS) {  // a very long run: listed here, reduced by a whole CTA in hot_join_kernel
+    if (lane == 0) p.hot_list[atomicAdd(p.hot_count, 1)] = (uint32_t)u;
+    return;
   }
   float acc[NV][VE];
 #pragma unroll
@@ -688,19 +715,78 @@ __global__ void __launch_bounds__(UPD_THREADS) window_join_kernel(const UpdParam
 #pragma unroll
     for (int x = 0; x < VE; ++x) acc[kk][x] = 0.f;
   add_partial_rows<G, NV, VE, PB>(acc, p.partial, w0, w1, s, BC, p.D, p.V, lane);
+  finish_run<WT, G, NV, OPT, RED>(p, u, acc, lane);
+}
+
+// ---- 3c. hot runs: one CTA per listed run.  Group g adds the partial rows of blocks w0 + g, w0 + g + NG, ... (PB in
+// flight), the NG group sums meet in shared memory and group 0 adds them in group order and updates the row.
+template <typename WT, int G, int NV, int OPT, bool RED>
+__global__ void __launch_bounds__(UPD_THREADS) hot_join_kernel(const UpdParams p) {
+  constexpr int VE = Vec16<WT>::VE;
+  constexpr int NG = UPD_THREADS / G;
+  constexpr int64_t BC = (int64_t)NG * HOT_CH;
+  constexpr int PB = (NV * VE >= 32) ? 2 : (NV * VE >= 16 ? 4 : 8);
+  extern __shared__ __align__(16) float s_sum[];  // [NG][D]
+  const int gid = threadIdx.x / G, lane = threadIdx.x % G;
+  const int n_hot = *p.hot_count;
+  for (int ent = blockIdx.x; ent < n_hot; ent += gridDim.x) {  // (uniform per CTA: the barriers below are safe)
+  const int64_t u = p.hot_list[ent];
+  const int64_t s = p.seg[u], e = p.seg[u + 1];
+  const int64_t w0 = s / BC, w1 = (e - 1) / BC;
+  float acc[NV][VE];
+#pragma unroll
+  for (int kk = 0; kk < NV; ++kk)
+#pragma unroll
+    for (int x = 0; x < VE; ++x) acc[kk][x] = 0.f;
+  for (int64_t ib = w0 + gid; ib <= w1; ib += (int64_t)NG * PB) {
+    uint4 f[PB][NV][VE / 4];
+#pragma unroll
+    for (int c = 0; c < PB; ++c) {
+      const int64_t i = ib + (int64_t)c * NG;
+      const bool ok = i <= w1;
+      // slot rule of the window kernel: a block the run ENTERS from the left wrote slot 0, the block holding its head slot 1
+      const float* src = p.partial + (size_t)(2 * (ok ? i : w0) + ((ok && s > i * BC) ? 1 : 0)) * p.D + lane * VE;
+#pragma unroll
+      for (int kk = 0; kk < NV; ++kk)
+#pragma unroll
+        for (int h = 0; h < VE / 4; ++h)
+          f[c][kk][h] = (ok && lane + kk * G < p.V) ? ld_v4(src + kk * G * VE + 4 * h) : make_uint4(0, 0, 0, 0);
+    }
+#pragma unroll
+    for (int c = 0; c < PB; ++c)
+#pragma unroll
+      for (int kk = 0; kk < NV; ++kk)
+#pragma unroll
+        for (int h = 0; h < VE / 4; ++h) keep(f[c][kk][h]);
+#pragma unroll
+    for (int c = 0; c < PB; ++c)
+#pragma unroll
+      for (int kk = 0; kk < NV; ++kk)
+#pragma unroll
+        for (int h = 0; h < VE / 4; ++h) Vec16<float>::accum(acc[kk] + 4 * h, f[c][kk][h]);
+  }
+  float* mine = s_sum + (size_t)gid * p.D + lane * VE;
 #pragma unroll
   for (int kk = 0; kk < NV; ++kk)
     if (lane + kk * G < p.V) {
-      if constexpr (RED) {
-        red_add_v4_f32(reinterpret_cast<float*>(wp + (size_t)kk * G * 16), -lr * acc[kk][0], -lr * acc[kk][1],
-                       -lr * acc[kk][2], -lr * acc[kk][3]);
-      } else {
-        float wf[VE];
-        Vec16<WT>::unpack(wf, wv[kk]);
-        apply_row<OPT, WT>(wp + (size_t)kk * G * 16, sp ? sp + kk * G * VE : nullptr, acc[kk], wf, lr, p.eps,
-                           tp ? tp + (size_t)kk * G * 16 : nullptr, tv[kk]);
-      }
+#pragma unroll
+      for (int x = 0; x < VE; ++x) mine[kk * G * VE + x] = acc[kk][x];
     }
+  __syncthreads();
+  if (gid == 0) {
+    for (int g = 1; g < NG; ++g) {
+      const float* q = s_sum + (size_t)g * p.D + lane * VE;
+#pragma unroll
+      for (int kk = 0; kk < NV; ++kk)
+        if (lane + kk * G < p.V) {
+#pragma unroll
+          for (int x = 0; x < VE; ++x) acc[kk][x] += q[kk * G * VE + x];
+        }
+    }
+    finish_run<WT, G, NV, OPT, RED>(p, u, acc, lane);
+  }
+  __syncthreads();  // s_sum is reused by the next listed run
+  }
 }
 
 // scalar fallback (rows not a whole number of 16-byte vectors): thread per (unique row, d)
@@ -809,6 +895,12 @@ static int launch_update(const UpdParams& p, int64_t n, bool vec_ok, cudaStream_
       cfg.attrs = at;                                                                                             \
       cfg.numAttrs = use_pdl ? 1 : 0;                                                                             \
       cudaLaunchKernelEx(&cfg, window_join_kernel<WT, G, NV, OPT, RED>, p);                                       \
+      if (nblk > HOT_BLOCKS) { /* only then can a run cross more than HOT_BLOCKS borders */                        \
+        auto hk = hot_join_kernel<WT, G, NV, OPT, RED>;                                                           \
+        const size_t hs = (size_t)NG_ * p.D * sizeof(float);                                                      \
+        if (hs > 48 * 1024) cudaFuncSetAttribute(hk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hs);       \
+        hk<<<(unsigned)std::min<int64_t>(ceil_div(nblk, HOT_BLOCKS) + 1, 4096), UPD_THREADS, hs, st>>>(p);        \
+      }                                                                                                           \
     }                                                                                                             \
   }
 #define B200_UPD_CASE(G, NV)                 \
@@ -866,7 +958,7 @@ static int emb_bwd_prepare_impl(const int64_t* d_rows, const int64_t* d_row_base
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   BwdLayout L = bwd_layout(ws, nnz, D);
   keys_tail_kernel<<<d_nnz_valid ? 256 : 1, 256, 0, st>>>(L.keys, L.vals, d_nnz_valid, nnz, (uint32_t)total_rows,
-                                                          L.n_valid);
+                                                          L.n_valid, L.hot_count);
   dim3 kgrid((unsigned)ceil_div(B, KEYS_THREADS), (unsigned)T);
   build_keys_kernel<<<kgrid, KEYS_THREADS, 0, st>>>(d_indices, d_offsets, d_rows, d_row_base, B, L.keys,
                                                     L.vals, d_error);
@@ -939,6 +1031,8 @@ static int emb_bwd_apply_impl(void* const* d_weights, float* const* d_state, uin
   p.partial = L.partial;
   p.n = nnz;
   p.d_n = L.n_valid;
+  p.hot_count = L.hot_count;
+  p.hot_list = L.hot_list;
   p.values = nullptr;
   p.by_key = 0;
   p.grad_ptrs = d_grad_ptrs;
@@ -1031,6 +1125,8 @@ static int store_run_sums(const int64_t* d_row_base, int64_t nnz, const void* d_
   p.by_key = by_key;
   p.n = nnz;
   p.d_n = L.n_valid;
+  p.hot_count = L.hot_count;
+  p.hot_list = L.hot_list;
   p.T = (int)T;
   const int gsz = dtype_size(grad_dtype);
   const bool vec_ok = (D * 4) % 16 == 0 && p.V <= 128 && (reinterpret_cast<uintptr_t>(d_grad) % 16) == 0 &&

@@ -431,6 +431,18 @@ class MergedEmbeddingBagWithSGD(nn.Module):
         chunk = exch.chunk
         ws = self._workspace(indices.numel(), chunk)
         prep = self._take_prep(chunk)
+        # multi-hot bags: stage the peers' gradient rows locally first (see PeerExchange.gather_grads)
+        staged = indices.numel() >= 2 * self.n_tables * B
+
+        def apply():
+            if staged:
+                G = exch.gather_grads(feat0, self.n_tables)
+                ops.emb_bwd_apply(self.tables, indices.numel(), B, G, self.dim, self.n_tables * self.dim,
+                                  self.sgd_args.lr, ws, optimizer=opt, eps=self.eps, lr_tensor=self.lr_tensor)
+            else:
+                ops.emb_bwd_apply_sharded(self.tables, indices.numel(), B, exch.dT_ptrs_dev, exch.lN, exch.F, feat0,
+                                          exch.dtype, self.sgd_args.lr, ws, optimizer=opt, eps=self.eps,
+                                          lr_tensor=self.lr_tensor)
         if self.overlap_sharded and prep is not None and self.profile is None:
             # NVLink-bound gather of the peers' gradient rows: run it on the side stream (already behind the index
             # stage) while the current stream does the bottom-MLP backward, the all-reduce and the optimizer -- or,
@@ -438,9 +450,7 @@ class MergedEmbeddingBagWithSGD(nn.Module):
             side = self._side_stream
             side.wait_stream(torch.cuda.current_stream())  # dT complete on every rank (barrier B2 is before us)
             with torch.cuda.stream(side):
-                ops.emb_bwd_apply_sharded(self.tables, indices.numel(), B, exch.dT_ptrs_dev, exch.lN, exch.F, feat0,
-                                          exch.dtype, self.sgd_args.lr, ws, optimizer=opt, eps=self.eps,
-                                          lr_tensor=self.lr_tensor)
+                apply()
                 ev = torch.cuda.Event()
                 ev.record(side)
             self._apply_event = ev
@@ -450,9 +460,7 @@ class MergedEmbeddingBagWithSGD(nn.Module):
         else:
             ops.emb_bwd_prepare(self.tables, indices, offsets, B, ws, self.error_flag)
         with self._timed("emb_bwd_apply"):
-            ops.emb_bwd_apply_sharded(self.tables, indices.numel(), B, exch.dT_ptrs_dev, exch.lN, exch.F, feat0,
-                                      exch.dtype, self.sgd_args.lr, ws, optimizer=opt, eps=self.eps,
-                                      lr_tensor=self.lr_tensor)
+            apply()
 
     def _apply_update(self, indices, offsets, B, grad_base, stride_table, stride_bag):
         opt = ops.OPT_ADAGRAD if self.optimizer_kind == "adagrad" else ops.OPT_SGD

@@ -53,6 +53,8 @@ class PeerExchange:
         self.hdT = symm.rendezvous(self.dT, group)
         self.T_ptrs_dev = int(self.hT.buffer_ptrs_dev)
         self.dT_ptrs_dev = int(self.hdT.buffer_ptrs_dev)
+        # every rank's dT as a tensor over peer memory (gather_grads)
+        self.dT_peers = [self.hdT.get_buffer(r, (lN, F, D), dtype) for r in range(self.world)]
         self.T.zero_()
         self.dT.zero_()
         torch.cuda.synchronize()
@@ -60,6 +62,16 @@ class PeerExchange:
 
     def barrier(self, channel: int = 0):
         self.hT.barrier(channel=channel)
+
+    def gather_grads(self, feat0: int, n_feat: int) -> torch.Tensor:
+        """Copy the gradient rows of feature slots ``feat0 .. feat0 + n_feat`` of EVERY rank's dT into one local
+        ``[B_glob, n_feat, D]`` tensor (the mirror all-to-all as W strided peer reads).  For multi-hot bags the fused
+        update reads each bag's gradient row once per index: from a local copy those re-reads hit L2 / HBM, whereas
+        peer memory is not cached in the local L2 and every one of them would cross NVLink again."""
+        G = torch.empty(self.lN * self.world, n_feat, self.D, dtype=self.dtype, device=self.T.device)
+        for r in range(self.world):
+            G[r * self.lN:(r + 1) * self.lN].copy_(self.dT_peers[r][:, feat0:feat0 + n_feat])
+        return G
 
 
 class _ShardedEmbInteractFn(torch.autograd.Function):

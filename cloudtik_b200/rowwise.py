@@ -108,6 +108,13 @@ class RowWiseShardedTables(nn.Module):
         ws = emb._workspace(li.numel())
         ops.emb_bwd_prepare(emb.tables, li, lo, B_glob, ws, emb.error_flag, nnz_valid=lo[-1:])
         opt = ops.OPT_ADAGRAD if emb.optimizer_kind == "adagrad" else ops.OPT_SGD
+        if li.numel() >= 2 * self.k * B_glob:
+            # multi-hot: every bag's gradient row is read once per owned index -- from a local copy, not W times
+            # over NVLink (peer memory is not cached in the local L2)
+            G = exch.gather_grads(exch.F - self.k, self.k)
+            ops.emb_bwd_apply(emb.tables, li.numel(), B_glob, G, self.dim, self.k * self.dim, emb.sgd_args.lr, ws,
+                              optimizer=opt, eps=emb.eps, lr_tensor=emb.lr_tensor)
+            return
         ops.emb_bwd_apply_sharded(emb.tables, li.numel(), B_glob, exch.dT_ptrs_dev, exch.lN, exch.F, exch.F - self.k,
                                   exch.dtype, emb.sgd_args.lr, ws, optimizer=opt, eps=emb.eps,
                                   lr_tensor=emb.lr_tensor)

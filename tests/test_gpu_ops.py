@@ -724,3 +724,59 @@ def test_rowwise_partial_sums_add_up_over_emulated_ranks(dtype):
         tol = dict(rtol=1e-5, atol=1e-5) if dtype == torch.float32 else dict(rtol=3e-2, atol=6e-2)
         np.testing.assert_allclose(got[:, 1 + t], want, **tol)
     assert not got[:, 0].any()
+
+
+@pytest.mark.parametrize("variant", ["sgd_fp32", "adagrad_bf16grad", "bf16_trail", "dense"])
+def test_emb_bwd_very_hot_rows_cta_join(variant):
+    """Rows with tens of thousands of duplicates (multi-hot bags on a 3-row table: runs that cross far more than
+    HOT_BLOCKS block borders) take the CTA-wide hot join; integer gradients make the sums exact."""
+    ops = _ops()
+    D, rows, B, P = 128, [3, 50, 7], 6000, 8
+    rs = np.random.RandomState(1)
+    idx_l = [rs.randint(0, n, size=B * P).astype(np.int64) for n in rows]
+    off_l = [np.arange(B, dtype=np.int64) * P for _ in rows]
+    indices, offsets, _ = ref.linearize_indices_and_offsets(idx_l, off_l, rows)
+    T = len(rows)
+    gdt = torch.bfloat16 if variant in ("adagrad_bf16grad", "bf16_trail") else torch.float32
+    g = torch.tensor(rs.randint(-2, 3, size=(B, T, D)).astype(np.float32)).to(gdt).cuda()
+    gr = g.float().cpu().numpy().astype(np.float64)
+    G = []
+    for t in range(T):
+        Gt = np.zeros((rows[t], D))
+        np.add.at(Gt, idx_l[t], np.repeat(gr[:, t], P, axis=0))
+        G.append(Gt)
+    ti, to = torch.tensor(indices).cuda(), torch.tensor(offsets).cuda()
+    ws = torch.empty(ops.emb_bwd_workspace_bytes(len(indices), D), dtype=torch.uint8, device="cuda")
+    if variant == "dense":
+        ts = ops.TableSet([torch.zeros(n, D, device="cuda") for n in rows])
+        ops.emb_bwd_prepare(ts, ti, to, B, ws)
+        out = torch.zeros(sum(rows), D, device="cuda")
+        ops.emb_bwd_dense_grad(ts, len(indices), B, g, D, T * D, out, ws)
+        np.testing.assert_array_equal(out.cpu().numpy(), np.concatenate(G))
+        return
+    lr = 2.0 ** -10
+    if variant == "bf16_trail":
+        W = [torch.zeros(n, D, dtype=torch.bfloat16, device="cuda") for n in rows]
+        ts = ops.TableSet(W)
+        trails = [torch.zeros(n, D, dtype=torch.int16, device="cuda") for n in rows]
+        ts.set_trails(trails)
+    else:
+        W = [torch.zeros(n, D, device="cuda") for n in rows]
+        ts = ops.TableSet(W)
+    opt = ops.OPT_SGD
+    if variant == "adagrad_bf16grad":
+        ts.set_states([torch.zeros(n, D, device="cuda") for n in rows])
+        opt = ops.OPT_ADAGRAD
+    ops.emb_bwd_update(ts, ti, to, B, g, D, T * D, lr, ws, optimizer=opt)
+    torch.cuda.synchronize()
+    for t in range(T):
+        if variant == "adagrad_bf16grad":
+            np.testing.assert_array_equal(ts.states[t].cpu().numpy(), (G[t] * G[t]).astype(np.float32))
+            want = -lr * G[t] / (np.abs(G[t]) + 1e-10)
+            np.testing.assert_allclose(W[t].cpu().numpy(), want, rtol=1e-5, atol=1e-7)
+        elif variant == "bf16_trail":
+            hi = W[t].view(torch.int16).to(torch.int32) << 16
+            lo = trails[t].to(torch.int32) & 0xFFFF
+            np.testing.assert_array_equal((hi | lo).view(torch.float32).cpu().numpy(), (-lr * G[t]).astype(np.float32))
+        else:
+            np.testing.assert_array_equal(W[t].cpu().numpy(), (-lr * G[t]).astype(np.float32))
