@@ -257,6 +257,10 @@ def _p2p_forward(self, dense_x, *emb_args, chunk=0, dense_bags=None):
                                                           else exch.world > 2)
     if first:
         prelaunch(self.emb_l, exch, indices, offsets, feat0)
+    if train and self.emb_dense is not None and len(self.peer_exchanges) == 1:
+        # the replicated tables' local lookup (and the index stage of their backward) next to the bottom MLP too
+        self.emb_dense.pool_into_async(dense_bags[0], dense_bags[1], exch.lN, exch.T[:, 1:1 + self.emb_dense.n_tables],
+                                       exch.D, exch.F * exch.D)
     with torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.bf16):
         x = self.apply_mlp(self._pad_dense(dense_x), self.bot_l)
         if train and len(self.peer_exchanges) == 1 and not first:

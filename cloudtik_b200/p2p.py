@@ -84,9 +84,11 @@ class _ShardedEmbInteractFn(torch.autograd.Function):
         if repl is not None:
             # replicated small tables: LOCAL batch, feature slots 1 .. n right behind x.  Local reads and writes only,
             # so it goes first and runs under the tail of the exchange the next lines wait for
-            repl.pool_into(repl_indices, repl_offsets, exch.lN, exch.T[:, 1:1 + repl.n_tables], exch.D, exch.F * exch.D)
-            if train:
-                repl.launch_prepare(repl_indices, repl_offsets, exch.lN)
+            if not repl.wait_pool(repl_indices, repl_offsets):  # (else: launched ahead of the bottom MLP)
+                repl.pool_into(repl_indices, repl_offsets, exch.lN, exch.T[:, 1:1 + repl.n_tables], exch.D,
+                               exch.F * exch.D)
+                if train:
+                    repl.launch_prepare(repl_indices, repl_offsets, exch.lN)
         if emb is not None:
             pend = emb._take_pending_sharded(exch.chunk)
             if pend is not None and pend[0] is indices and pend[1] is offsets:

@@ -49,6 +49,7 @@ class ReplicatedEmbeddingBags(nn.Module):
         self._stream = None
         self._grad_event = None
         self._pending_grads = None
+        self._pool_event = None
         self.defer = False
         self._rebuild()
 
@@ -81,6 +82,33 @@ class ReplicatedEmbeddingBags(nn.Module):
         """Pooled rows of the B local bags of every replicated table into ``out`` (a view of the interaction
         input: table t of bag b at ``out.data_ptr + (t * stride_table + b * stride_bag)`` elements)."""
         ops.emb_fwd(self._tables_checked(), indices, offsets, B, out, stride_table, stride_bag, self.error_flag)
+
+    def pool_into_async(self, indices, offsets, B: int, out: torch.Tensor, stride_table: int, stride_bag: int,
+                        prepare: bool = True):
+        """``pool_into`` (+ the index stage of the backward) on this module's own stream, to be called before the
+        caller runs something else on the current stream (the bottom MLP); ``wait_pool()`` orders the current stream
+        behind the lookup.  ``out`` must not be read by anything still queued on the current stream."""
+        side = self._own_stream()
+        side.wait_stream(torch.cuda.current_stream())
+        tables = self._tables_checked()
+        with torch.cuda.stream(side):
+            ops.emb_fwd(tables, indices, offsets, B, out, stride_table, stride_bag, self.error_flag)
+            ev = torch.cuda.Event()
+            ev.record(side)
+            self._pool_event = (indices, offsets, ev)
+            if prepare:
+                ops.emb_bwd_prepare(tables, indices, offsets, B, self._workspace(indices.numel()), self.error_flag)
+                pe = torch.cuda.Event()
+                pe.record(side)
+                self._prep_event = pe
+
+    def wait_pool(self, indices, offsets) -> bool:
+        """True (and the current stream now waits for it) if ``pool_into_async`` ran for these very tensors."""
+        pend, self._pool_event = self._pool_event, None
+        if pend is not None and pend[0] is indices and pend[1] is offsets:
+            torch.cuda.current_stream().wait_event(pend[2])
+            return True
+        return False
 
     def _own_stream(self):
         if self._stream is None:
