@@ -44,6 +44,7 @@ SIGNATURES = {
     "b200_emb_bwd_coalesce": (_int, [_p, _p, _p, _p, _i64, _p, _i64, _i64, _i64, _i64, _i64, _int, _i64, _p, _p, _p,
                                      _p, _c.c_size_t, _p, _p]),
     "b200_emb_bwd_dense_grad": (_int, [_p, _i64, _p, _i64, _i64, _i64, _i64, _i64, _int, _p, _p, _c.c_size_t, _p]),
+    "b200_interact_fwd_tf32": (_int, [_p, _p, _i64, _i64, _i64, _i64, _p]),
     "b200_interact_fwd_ex": (_int, [_p, _p, _i64, _i64, _i64, _i64, _int, _int, _p]),
     "b200_interact_bwd_ex": (_int, [_p, _p, _p, _i64, _i64, _i64, _i64, _int, _int, _p]),
     "b200_workspace_bytes": (_c.c_size_t, [_i64, _i64]),

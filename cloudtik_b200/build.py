@@ -17,7 +17,7 @@ CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB_DIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIB_DIR, "libb200dlrm.so")
-SOURCES = ["api.cu", "emb_fwd.cu", "sort_dedup.cu", "emb_bwd.cu", "interact_simt.cu", "interact_tc.cu", "interact_f32.cu", "criteo_input.cu", "mlp_eltwise.cu", "rowwise.cu"]
+SOURCES = ["api.cu", "emb_fwd.cu", "sort_dedup.cu", "emb_bwd.cu", "interact_simt.cu", "interact_tc.cu", "interact_tf32.cu", "interact_f32.cu", "criteo_input.cu", "mlp_eltwise.cu", "rowwise.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
          "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-Xptxas", "-v"]

@@ -19,6 +19,8 @@ int interact_bwd_simt(const void*, const void*, void*, int64_t, int64_t, int64_t
 bool interact_tc_supported(int64_t B, int64_t F, int64_t D, int dtype, const void* T, int64_t ldr);
 int interact_fwd_tc(const void*, void*, int64_t, int64_t, int64_t, int64_t, cudaStream_t);
 int interact_bwd_tc(const void*, const void*, void*, int64_t, int64_t, int64_t, int64_t, cudaStream_t);
+bool interact_tf32_supported(int64_t B, int64_t F, int64_t D, int dtype, const void* T, int64_t ldr);
+int interact_fwd_tf32(const void*, void*, int64_t, int64_t, int64_t, int64_t, cudaStream_t);
 bool interact_f32_supported(int64_t B, int64_t F, int64_t D, int dtype, const void* T, const void* R, int64_t ldr);
 int interact_fwd_f32(const void*, void*, int64_t, int64_t, int64_t, int64_t, cudaStream_t);
 int interact_bwd_f32(const void*, const void*, void*, int64_t, int64_t, int64_t, int64_t, cudaStream_t);
@@ -46,6 +48,7 @@ extern "C" int b200_interact_fwd(const void* d_T, void* d_R, int64_t B, int64_t 
   if (rc || B == 0) return rc;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (interact_tc_supported(B, F, D, dtype, d_T, ldr)) return interact_fwd_tc(d_T, d_R, B, F, D, ldr, st);
+  if (interact_tf32_supported(B, F, D, dtype, d_T, ldr)) return interact_fwd_tf32(d_T, d_R, B, F, D, ldr, st);
   if (interact_f32_supported(B, F, D, dtype, d_T, d_R, ldr)) return interact_fwd_f32(d_T, d_R, B, F, D, ldr, st);
   return interact_fwd_simt(d_T, d_R, B, F, D, ldr, dtype, st);
 }

@@ -271,6 +271,17 @@ int b200_interact_bwd_ex(const void* d_T, const void* d_dR, void* d_dT, int64_t 
                          int64_t ldr, int dtype, int flags, b200_stream_t stream);
 
 /*
+ * fp32 interaction forward on the tensor cores: 3xTF32 (every operand split into two TF32 numbers, three
+ * tcgen05.mma kind::tf32 products, fp32 accumulators in TMEM), same result layout as b200_interact_fwd with
+ * dtype B200_F32 and the same 1e-5 bound (reference default precision, P/dlrm_s_pytorch.py:315-333).
+ * F <= 32, D in {32, 64, 128}.  b200_interact_fwd dispatches fp32 to the CUDA-core kernel by default (faster on
+ * B200: this variant is bound by shared-memory operand bandwidth); B200_INTERACT_TF32=1 in the environment makes it
+ * take this one.
+ */
+int b200_interact_fwd_tf32(const void* d_T, void* d_R, int64_t B, int64_t F, int64_t D, int64_t ldr,
+                           b200_stream_t stream);
+
+/*
  * The names SURVEY.md section 8b lists for the fused backward, as thin forms of b200_emb_bwd_update with the
  * optimiser fixed (SGD: torch.optim.SGD on the sparse gradients, P/dlrm_s_pytorch.py:805,1059; Adagrad: torch's
  * sparse Adagrad branch, no call site in the reference), and of b200_emb_bwd_workspace_bytes.

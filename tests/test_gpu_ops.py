@@ -780,3 +780,25 @@ def test_emb_bwd_very_hot_rows_cta_join(variant):
             np.testing.assert_array_equal((hi | lo).view(torch.float32).cpu().numpy(), (-lr * G[t]).astype(np.float32))
         else:
             np.testing.assert_array_equal(W[t].cpu().numpy(), (-lr * G[t]).astype(np.float32))
+
+
+@pytest.mark.parametrize("B,F,D,pad", [(1, 27, 128, 1), (5, 27, 128, 8), (1000, 27, 128, 8), (4099, 27, 128, 1),
+                                       (333, 27, 64, 8), (777, 9, 32, 1), (64, 32, 128, 1)])
+def test_interaction_fp32_on_tensor_cores_3xtf32(B, F, D, pad):
+    """fp32 forward on tcgen05 (3xTF32, b200_interact_fwd_tf32) against a float64 evaluation of the same inputs at
+    the north_star fp32 bound (1e-5 relative) -- the same check as the CUDA-core fp32 kernel."""
+    from cloudtik_b200._lib import check, lib
+    rs = np.random.RandomState(B + D)
+    Tn = rs.randn(B, F, D).astype(np.float32)
+    T = torch.tensor(Tn).cuda()
+    W = D + F * (F - 1) // 2
+    ldr = (W + pad - 1) // pad * pad
+    R = torch.full((B, ldr), 7.0, device="cuda")
+    check(lib.b200_interact_fwd_tf32(T.data_ptr(), R.data_ptr(), B, F, D, ldr, torch.cuda.current_stream().cuda_stream),
+          "b200_interact_fwd_tf32")
+    T64 = Tn.astype(np.float64)
+    want = ref.interact_fwd(T64[:, 0], [T64[:, k] for k in range(1, F)])
+    got = R.cpu().numpy()
+    np.testing.assert_allclose(got[:, :W], want, rtol=1e-5, atol=1e-5 * np.sqrt(D))
+    np.testing.assert_array_equal(got[:, :D], Tn[:, 0])
+    assert (got[:, W:] == 0).all()
