@@ -251,7 +251,8 @@ struct GradVec<__nv_bfloat16, 4> {
 // Every weight row is written by exactly one group: deterministic, no atomics.
 template <int OPT, typename WT>
 __device__ __forceinline__ void apply_row(char* wp, float* sp, const float* acc, const float* w_in, float lr,
-                                          float eps, char* tp = nullptr, uint4 tv = make_uint4(0, 0, 0, 0)) {
+                                          float eps, char* tp = nullptr, uint4 tv = make_uint4(0, 0, 0, 0),
+                                          const uint4* sv = nullptr) {
   constexpr int VE = Vec16<WT>::VE;
   float w[VE];
 #pragma unroll
@@ -271,7 +272,7 @@ __device__ __forceinline__ void apply_row(char* wp, float* sp, const float* acc,
 #pragma unroll
     for (int h = 0; h < VE / 4; ++h) {
       float st[4];
-      Vec16<float>::unpack(st, ld_v4(sp + 4 * h));
+      Vec16<float>::unpack(st, sv != nullptr ? sv[h] : ld_v4(sp + 4 * h));  // sv: state vectors fetched with the batch
 #pragma unroll
       for (int x = 0; x < 4; ++x) {
         const float g = acc[4 * h + x];
@@ -315,7 +316,9 @@ __global__ void __launch_bounds__(UPD_THREADS, (sizeof(GT) == 2 && !TRAIL && OPT
   constexpr int NG = UPD_THREADS / G;
   constexpr int C = HOT_CH;
   constexpr int BS0 = (NV * VE >= 32) ? 1 : (NV * VE >= 16 ? 2 : (NV * VE >= 8 ? 4 : 8));
-  constexpr int BS = RED ? 2 * BS0 : BS0;  // gradient rows in flight per lane
+  // gradient rows in flight per lane; Adagrad also keeps the state rows of the batch in flight (below), so it takes
+  // half the batch to stay inside the register budget
+  constexpr int BS = RED ? 2 * BS0 : ((OPT == B200_OPT_ADAGRAD && BS0 > 1) ? BS0 / 2 : BS0);
   __shared__ int64_t s_base[UPD_TMAX];
   __shared__ char* s_wptr[UPD_TMAX];
   __shared__ float* s_sptr[UPD_TMAX];
@@ -405,6 +408,9 @@ __global__ void __launch_bounds__(UPD_THREADS, (sizeof(GT) == 2 && !TRAIL && OPT
     GradVec<GT, VE> g[BS][NV];
     uint4 wv[RED ? 1 : BS][NV];
     [[maybe_unused]] uint4 tv[TRAIL ? BS : 1][NV];  // trail halves of the rows in wv
+    // Adagrad: the fp32 state vectors of the rows in wv, loaded with the batch -- fetched inside the update they cost
+    // one exposed memory latency per finished run
+    [[maybe_unused]] uint4 sv[(OPT == B200_OPT_ADAGRAD) ? BS : 1][NV][VE / 4];
     [[maybe_unused]] int64_t tdel[TRAIL ? BS : 1];
     char* wp[RED ? 1 : BS];
     float* sp[RED ? 1 : BS];
@@ -446,6 +452,13 @@ __global__ void __launch_bounds__(UPD_THREADS, (sizeof(GT) == 2 && !TRAIL && OPT
 #pragma unroll
             for (int k = 0; k < NV; ++k)
               if (lane + k * G < p.V) wv[c][k] = ld_v4(wp[c] + (size_t)k * G * 16);
+            if constexpr (OPT == B200_OPT_ADAGRAD) {
+#pragma unroll
+              for (int k = 0; k < NV; ++k)
+#pragma unroll
+                for (int h = 0; h < VE / 4; ++h)
+                  sv[c][k][h] = (lane + k * G < p.V) ? ld_v4(sp[c] + k * G * VE + 4 * h) : make_uint4(0, 0, 0, 0);
+            }
             if constexpr (TRAIL) {
               tdel[c] = cached ? s_tdelta[tt] : reinterpret_cast<char*>(p.trail[tt]) - static_cast<char*>(p.weights[tt]);
 #pragma unroll
@@ -483,12 +496,14 @@ __global__ void __launch_bounds__(UPD_THREADS, (sizeof(GT) == 2 && !TRAIL && OPT
               } else {
                 float wf[VE];
                 Vec16<WT>::unpack(wf, wv[c][k]);
+                const uint4* svp = nullptr;
+                if constexpr (OPT == B200_OPT_ADAGRAD) svp = &sv[c][k][0];
                 if constexpr (TRAIL) {
                   apply_row<OPT, WT>(wp[c] + (size_t)k * G * 16, sp[c] ? sp[c] + k * G * VE : nullptr, acc[k], wf, lr,
-                                     p.eps, wp[c] + tdel[c] + (size_t)k * G * 16, tv[c][k]);
+                                     p.eps, wp[c] + tdel[c] + (size_t)k * G * 16, tv[c][k], svp);
                 } else {
                   apply_row<OPT, WT>(wp[c] + (size_t)k * G * 16, sp[c] ? sp[c] + k * G * VE : nullptr, acc[k], wf, lr,
-                                     p.eps);
+                                     p.eps, nullptr, make_uint4(0, 0, 0, 0), svp);
                 }
               }
             }

@@ -88,7 +88,7 @@ int b200_sort_dedup(const uint32_t* d_keys, const uint32_t* d_vals, int64_t n, u
  * cannot own a device buffer).  No counterpart in the reference: this entry point exists only for
  * such callers.
  *
- * The scratch is a fixed array inside the library image (about 4.3 MB on every GPU that loads the
+ * The scratch is a fixed array inside the library image (about 4.5 MB on every GPU that loads the
  * library, kept until the process exits); the call allocates nothing, neither on the device nor
  * through any library.  Limits and rules:
  *   - n <= B200_SORT_NOALLOC_MAX_KEYS, otherwise B200_EUNSUPPORTED and nothing is launched;
