@@ -636,8 +636,14 @@ def run_b200_arm(a):
             for k, v in kt.items()}, "note": "rank 0; measured in the eager pass with the side-stream overlap off"}
     bits = max(1, int(sum(rows_local) - 1).bit_length())
     n_relu = (len(LN_BOT) - 1) + (len(LN_TOP) - 2)  # every MLP layer but the sigmoid one: relu_bwd_bias + chunk sum
-    # fwd, keys, radix passes, dedup, update + join, interaction f/b, MLP backward glue (bf16 path only)
-    launches = 1 + 1 + 3 * ((bits + 7) // 8) + 3 + 2 + 2 + (2 * n_relu if bf16 else 0)
+    # fwd, key tail + keys, radix passes (one-sweep: all-pass histogram + one kernel per pass, up to 2 M keys; else three
+    # kernels per pass), dedup (3), update (the cross-block join runs inside it), interaction f/b, MLP backward glue
+    # (bf16 path only); with replicated small tables: their forward, index stage and dense-gradient kernel as well
+    passes = (bits + 7) // 8
+    sort_l = (1 + passes) if nnz <= (2 << 20) else 3 * passes
+    launches = 1 + 2 + sort_l + 3 + 1 + 2 + (2 * n_relu if bf16 else 0)
+    if rows_repl:
+        launches += 1 + 2 + (1 + 2) + 3 + 1  # lookup, key tail + keys, one-sweep sort (<= 16 bits), dedup, dense gradient
     line = {"metric": "dlrm_train_samples_per_sec", "value": round(value, 1), "unit": "samples/s", "n_gpus": world,
             "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": round(ms_step, 4), "higher_is_better": True,
             "scaling": scaling, "vs_baseline": None, "dtype": a.dtype, "data": "synthetic",

@@ -63,6 +63,11 @@ __device__ __forceinline__ uint4 ld_v4(const void* p) {  // coherent load for re
   asm volatile("ld.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
   return r;
 }
+__device__ __forceinline__ uint4 ld_cg_v4(const void* p) {  // straight from L2: data another SM has just written
+  uint4 r;
+  asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
 __device__ __forceinline__ void keep(uint4& v) { asm volatile("" : "+r"(v.x), "+r"(v.y), "+r"(v.z), "+r"(v.w)); }
 __device__ __forceinline__ void keep(uint2& v) { asm volatile("" : "+r"(v.x), "+r"(v.y)); }
 __device__ __forceinline__ void st_cs_v4(void* p, uint4 v) { __stcs(reinterpret_cast<uint4*>(p), v); }

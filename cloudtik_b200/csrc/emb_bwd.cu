@@ -9,8 +9,9 @@
 //   3. update     : the sorted positions are cut into windows of HOT_CH; one sub-warp group per
 //                   window sums the gradient rows run by run (fp32, in bag order) and gives every
 //                   row ONE read-modify-write (weight row, Adagrad state row, bf16 trail); runs that
-//                   cross windows are joined in shared memory, runs that cross CTAs by a small
-//                   second kernel.  The [nnz, D] COO gradient is never materialised.
+//                   cross windows are joined in shared memory, runs that cross CTAs by the CTA that
+//                   draws the last ticket on the run's counter (same kernel, no second launch).
+//                   The [nnz, D] COO gradient is never materialised.
 #include <stdlib.h>
 
 #include <algorithm>
@@ -29,17 +30,13 @@ constexpr int UPD_THREADS = 256;
 // (the fp32 SGD variant issues ONE vector reduction per 16 bytes of a row, from one group).
 constexpr int OPT_STORE = 2;  // internal "optimizer": write the per-row gradient sums to values[run index]
 constexpr int MIN_NG = UPD_THREADS / 32;  // fewest windows per block (one warp per window)
-// A run that crosses more than HOT_BLOCKS block borders (a row with tens of thousands of duplicates: the 3-row Criteo
-// table under multi-hot bags receives B * P / 3 gradients per step) is not added up by ONE group of the join kernel
-// any more: the join kernel only lists it, and hot_join_kernel gives it a whole CTA.
-constexpr int HOT_BLOCKS = 16;
+
 
 struct BwdLayout {
   uint32_t *keys, *vals, *skeys, *svals, *unique, *seg, *win_run, *first_val;
   int32_t* num_unique;
   int64_t* n_valid;  // sorted positions that hold real keys (= nnz, or fewer after b200_emb_bwd_prepare_partial)
-  int32_t* hot_count;  // runs that span more than HOT_BLOCKS blocks of the window kernel (zeroed by prepare)
-  uint32_t* hot_list;  // their run indices, [ceil(nblk / HOT_BLOCKS) + 2]
+  int32_t* blk_cnt;  // [nblk]: tickets of the cross-block join, per head block (zero between calls)
   float* partial;   // [2 * nblk][D], nblk = blocks of the window kernel (<= ceil(nwin / MIN_NG))
   void* sort_ws;
   size_t total;
@@ -59,9 +56,8 @@ static BwdLayout bwd_layout(void* ws, int64_t n, int64_t D) {
   L.seg = reinterpret_cast<uint32_t*>(w + o), o += align_up((size_t)(n + 1) * 4, 256);
   L.num_unique = reinterpret_cast<int32_t*>(w + o);
   L.n_valid = reinterpret_cast<int64_t*>(w + o + 64);
-  L.hot_count = reinterpret_cast<int32_t*>(w + o + 128), o += 256;
-  L.hot_list = reinterpret_cast<uint32_t*>(w + o),
-  o += align_up((size_t)(ceil_div(ceil_div(ceil_div(n, HOT_CH), MIN_NG), HOT_BLOCKS) + 2) * 4, 256);
+  o += 256;
+  L.blk_cnt = reinterpret_cast<int32_t*>(w + o), o += align_up((size_t)(ceil_div(ceil_div(n, HOT_CH), MIN_NG) + 1) * 4, 256);
   L.win_run = reinterpret_cast<uint32_t*>(w + o), o += align_up((size_t)(ceil_div(n, HOT_CH) + 1) * 4, 256);
   L.partial = reinterpret_cast<float*>(w + o),
   o += align_up((size_t)(2 * ceil_div(ceil_div(n, HOT_CH), MIN_NG)) * D * 4, 256);
@@ -77,12 +73,12 @@ static BwdLayout bwd_layout(void* ws, int64_t n, int64_t D) {
 // *n_valid.  Also publishes n_valid in the workspace.
 __global__ void __launch_bounds__(256)
     keys_tail_kernel(uint32_t* __restrict__ keys, uint32_t* __restrict__ vals, const int64_t* __restrict__ d_valid,
-                     int64_t n, uint32_t sentinel, int64_t* __restrict__ n_valid_out, int32_t* __restrict__ hot_count) {
+                     int64_t n, uint32_t sentinel, int64_t* __restrict__ n_valid_out, int32_t* __restrict__ blk_cnt,
+                     int64_t n_blk_cnt) {
   const int64_t nv = d_valid ? min(max(*d_valid, (int64_t)0), n) : n;
-  if (blockIdx.x == 0 && threadIdx.x == 0) {
-    *n_valid_out = nv;
-    *hot_count = 0;
-  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) *n_valid_out = nv;
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n_blk_cnt; j += (int64_t)gridDim.x * blockDim.x)
+    blk_cnt[j] = 0;  // tickets of the cross-block join (the join also leaves them at zero)
   for (int64_t j = nv + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (int64_t)gridDim.x * blockDim.x) {
     keys[j] = sentinel;
     vals[j] = 0u;
@@ -164,8 +160,7 @@ struct UpdParams {
   float* partial;
   int64_t n;            // capacity of the sorted arrays (sizes the grid)
   const int64_t* d_n;   // real keys among them, read at kernel time (the sort puts them first)
-  int32_t* hot_count;
-  uint32_t* hot_list;
+  int32_t* blk_cnt;
 };
 
 // load VE consecutive gradient elements (GT) as fp32
@@ -247,7 +242,7 @@ struct GradVec<__nv_bfloat16, 4> {
 //     barrier the group holding the head of such a run adds the pieces of the following windows
 //     in window order and finishes the row -- no trip through global memory, no extra launch;
 //   * only a run that crosses a BLOCK border leaves a partial row in global memory (same slot
-//     rule, per block); window_join_kernel adds those in block order and updates the row.
+//     rule, per block); the cross-block join at the end of the kernel adds those in block order and updates the row.
 // Every weight row is written by exactly one group: deterministic, no atomics.
 template <int OPT, typename WT>
 __device__ __forceinline__ void apply_row(char* wp, float* sp, const float* acc, const float* w_in, float lr,
@@ -302,6 +297,44 @@ __device__ __forceinline__ void apply_row(char* wp, float* sp, const float* acc,
   store_vec<WT, VE, false>(reinterpret_cast<WT*>(wp), w);
 }
 
+// one update of run u's row with the gradient sum `acc` (lane l of the group holds vectors l, l + G, ...)
+template <typename WT, int G, int NV, int OPT, bool RED>
+__device__ __forceinline__ void finish_run(const UpdParams& p, int64_t u, float (*acc)[Vec16<WT>::VE], int lane) {
+  constexpr int VE = Vec16<WT>::VE;
+  const float lr = p.d_lr ? *p.d_lr : p.lr;
+  char* wp;
+  float* sp = nullptr;
+  char* tp = nullptr;
+  if (OPT == OPT_STORE) {
+    wp = reinterpret_cast<char*>(p.values) + ((size_t)(p.by_key ? (int64_t)p.unique[u] : u) * p.D + lane * VE) * sizeof(WT);
+  } else {
+    const uint32_t tt = p.first_val[u] / p.B;
+    const int64_t row = (int64_t)p.unique[u] - p.row_base[tt];
+    wp = static_cast<char*>(p.weights[tt]) + ((size_t)row * p.D + lane * VE) * sizeof(WT);
+    if (OPT == B200_OPT_ADAGRAD) sp = p.state[tt] + (size_t)row * p.D + lane * VE;
+    if constexpr (sizeof(WT) == 2) {
+      if (p.trail != nullptr) tp = wp + (reinterpret_cast<char*>(p.trail[tt]) - static_cast<char*>(p.weights[tt]));
+    }
+  }
+#pragma unroll
+  for (int kk = 0; kk < NV; ++kk)
+    if (lane + kk * G < p.V) {
+      if constexpr (RED) {
+        red_add_v4_f32(reinterpret_cast<float*>(wp + (size_t)kk * G * 16), -lr * acc[kk][0], -lr * acc[kk][1],
+                       -lr * acc[kk][2], -lr * acc[kk][3]);
+      } else {
+        float wf[VE] = {};
+        uint4 tv = make_uint4(0, 0, 0, 0);
+        if constexpr (OPT != OPT_STORE) {
+          Vec16<WT>::unpack(wf, ld_v4(wp + (size_t)kk * G * 16));
+          if (tp) tv = ld_v4(tp + (size_t)kk * G * 16);
+        }
+        apply_row<OPT, WT>(wp + (size_t)kk * G * 16, sp ? sp + kk * G * VE : nullptr, acc[kk], wf, lr, p.eps,
+                           tp ? tp + (size_t)kk * G * 16 : nullptr, tv);
+      }
+    }
+}
+
 constexpr int UPD_TMAX = 256;  // tables whose base pointers / row bases are cached in shared memory
 
 // RED (fp32 SGD only): the row update W += -lr * sum is linear, so it is issued as ONE vector
@@ -328,9 +361,6 @@ __global__ void __launch_bounds__(UPD_THREADS, (sizeof(GT) == 2 && !TRAIL && OPT
   __shared__ uint16_t s_tab[NG][C];
   extern __shared__ __align__(16) float s_part[];  // [NG][2][D]: pieces of the runs that cross window borders
   const int gid = threadIdx.x / G, lane = threadIdx.x % G;
-  // programmatic dependent launch: once every block of this grid is resident, the join grid may be
-  // scheduled into the SM slots the last wave leaves free (it waits for this grid before reading p.partial)
-  asm volatile("griddepcontrol.launch_dependents;");
   const bool cached = p.T <= UPD_TMAX && OPT != OPT_STORE;
   if (cached) {
     for (int i = threadIdx.x; i < p.T; i += UPD_THREADS) {
@@ -370,6 +400,27 @@ __global__ void __launch_bounds__(UPD_THREADS, (sizeof(GT) == 2 && !TRAIL && OPT
   const float lr = p.d_lr ? *p.d_lr : p.lr;
   __syncthreads();
   // (a group whose window lies beyond the end has cnt == 0: it skips the work but keeps the barriers)
+  // Does a run cross this block's left / right border?  Known now from the staged keys (block-uniform); thread 0
+  // fetches what the cross-block join at the end needs about those runs right away, so that those dependent loads
+  // are long done when it gets there.
+  const int64_t x_first = (int64_t)blockIdx.x * NG * C;
+  const int x_ngv = (int)min((int64_t)NG, (n_eff - x_first + C - 1) / C);
+  const int x_cntl = (int)min((int64_t)C, n_eff - (x_first + (int64_t)(x_ngv - 1) * C));
+  const bool x_enters = s_key[0][0] == s_key[0][1];
+  const bool x_leaves = s_key[x_ngv - 1][x_cntl] == s_key[x_ngv - 1][x_cntl + 1];
+  __shared__ int64_t s_x[6];  // thread 0 only: {run, start, end} of the entering and of the leaving run
+  if (threadIdx.x == 0) {
+    int64_t uE = -1, uL = -2;
+    if (x_enters) {
+      uE = p.win_run[(int64_t)blockIdx.x * NG];
+      s_x[1] = p.seg[uE], s_x[2] = p.seg[uE + 1];
+    }
+    if (x_leaves) {
+      uL = p.win_run[((int64_t)blockIdx.x + 1) * NG];
+      s_x[4] = p.seg[uL], s_x[5] = p.seg[uL + 1];
+    }
+    s_x[0] = uE, s_x[3] = uL;
+  }
 
   float acc[NV][VE];
 #pragma unroll
@@ -537,8 +588,7 @@ __global__ void __launch_bounds__(UPD_THREADS, (sizeof(GT) == 2 && !TRAIL && OPT
       }
   }
   __syncthreads();
-  if (cnt == 0) return;
-
+  if (cnt > 0) {
   // ---- in-block join.  The group holding the HEAD of a run that crosses its right border adds the
   // slot-0 pieces of the following windows (window order) and finishes the run; group 0 does the same
   // for the run that enters the block from the left.  What crosses a block border goes to p.partial.
@@ -567,7 +617,7 @@ __global__ void __launch_bounds__(UPD_THREADS, (sizeof(GT) == 2 && !TRAIL && OPT
       }
     }
     const bool to_right = open && j == ngv && key_after_block == key;
-    if (from_left || to_right) {  // crosses a block border: per-block partial row, finished by window_join_kernel
+    if (from_left || to_right) {  // crosses a block border: per-block partial row, finished by the cross-block join below
       const int bslot = (from_left || (gid == 0 && slot == 0)) ? 0 : 1;
       float* dst = p.partial + (size_t)(2 * (int64_t)blockIdx.x + bslot) * p.D + lane * VE;
 #pragma unroll
@@ -617,190 +667,95 @@ __global__ void __launch_bounds__(UPD_THREADS, (sizeof(GT) == 2 && !TRAIL && OPT
     finish(0, s_key[0][1], true, pass_through, 0, uidx0, false);
   if (open_r && !pass_through)  // the run whose head is in this window and that crosses its right border
     finish(tail_slot, s_key[gid][cnt], false, true, cnt - 1, uidx, pre_ok);
-}
+  }
 
-// ---- 3b. join: runs that cross BLOCK borders of the window kernel (a block = NG windows = NG * HOT_CH
-// positions).  One group per block border; the border a run crosses FIRST owns it, adds the run's
-// per-block partial rows in block order (PB rows in flight) and updates the row.  A row with m duplicates
-// costs m / (NG * HOT_CH) sequential row adds here -- 43 for the hottest Criteo row at batch 32768.
-template <int G, int NV, int VE, int PB>
-__device__ __forceinline__ void add_partial_rows(float (*acc)[VE], const float* base, int64_t first, int64_t last,
-                                                 int64_t s_pos, int64_t unit, int D, int V, int lane) {
-  // adds rows base[2 * i + slot(i)] for i in [first, last], slot = (s_pos > i * unit), PB rows in flight
-  for (int64_t ib = first; ib <= last; ib += PB) {
-    uint4 f[PB][NV][VE / 4];
-#pragma unroll
-    for (int c = 0; c < PB; ++c) {
-      const int64_t i = ib + c;
-      const bool ok = i <= last;
-      const float* src = base + (size_t)(2 * i + ((ok && s_pos > i * unit) ? 1 : 0)) * D + lane * VE;
-#pragma unroll
-      for (int kk = 0; kk < NV; ++kk)
-#pragma unroll
-        for (int h = 0; h < VE / 4; ++h)
-          f[c][kk][h] = (ok && lane + kk * G < V) ? ld_v4(src + kk * G * VE + 4 * h) : make_uint4(0, 0, 0, 0);
-    }
-#pragma unroll
-    for (int c = 0; c < PB; ++c)
-#pragma unroll
-      for (int kk = 0; kk < NV; ++kk)
-#pragma unroll
-        for (int h = 0; h < VE / 4; ++h) keep(f[c][kk][h]);
-#pragma unroll
-    for (int c = 0; c < PB; ++c)
-#pragma unroll
-      for (int kk = 0; kk < NV; ++kk)
-#pragma unroll
-        for (int h = 0; h < VE / 4; ++h) Vec16<float>::accum(acc[kk] + 4 * h, f[c][kk][h]);
-  }
-}
-
-// one update of run u's row with the gradient sum `acc` (lane l of the group holds vectors l, l + G, ...)
-template <typename WT, int G, int NV, int OPT, bool RED>
-__device__ __forceinline__ void finish_run(const UpdParams& p, int64_t u, float (*acc)[Vec16<WT>::VE], int lane) {
-  constexpr int VE = Vec16<WT>::VE;
-  const float lr = p.d_lr ? *p.d_lr : p.lr;
-  char* wp;
-  float* sp = nullptr;
-  char* tp = nullptr;
-  if (OPT == OPT_STORE) {
-    wp = reinterpret_cast<char*>(p.values) + ((size_t)(p.by_key ? (int64_t)p.unique[u] : u) * p.D + lane * VE) * sizeof(WT);
-  } else {
-    const uint32_t tt = p.first_val[u] / p.B;
-    const int64_t row = (int64_t)p.unique[u] - p.row_base[tt];
-    wp = static_cast<char*>(p.weights[tt]) + ((size_t)row * p.D + lane * VE) * sizeof(WT);
-    if (OPT == B200_OPT_ADAGRAD) sp = p.state[tt] + (size_t)row * p.D + lane * VE;
-    if constexpr (sizeof(WT) == 2) {
-      if (p.trail != nullptr) tp = wp + (reinterpret_cast<char*>(p.trail[tt]) - static_cast<char*>(p.weights[tt]));
-    }
-  }
-#pragma unroll
-  for (int kk = 0; kk < NV; ++kk)
-    if (lane + kk * G < p.V) {
-      if constexpr (RED) {
-        red_add_v4_f32(reinterpret_cast<float*>(wp + (size_t)kk * G * 16), -lr * acc[kk][0], -lr * acc[kk][1],
-                       -lr * acc[kk][2], -lr * acc[kk][3]);
-      } else {
-        float wf[VE] = {};
-        uint4 tv = make_uint4(0, 0, 0, 0);
-        if constexpr (OPT != OPT_STORE) {
-          Vec16<WT>::unpack(wf, ld_v4(wp + (size_t)kk * G * 16));
-          if (tp) tv = ld_v4(tp + (size_t)kk * G * 16);
-        }
-        apply_row<OPT, WT>(wp + (size_t)kk * G * 16, sp ? sp + kk * G * VE : nullptr, acc[kk], wf, lr, p.eps,
-                           tp ? tp + (size_t)kk * G * 16 : nullptr, tv);
-      }
-    }
-}
-
-template <typename WT, int G, int NV, int OPT, bool RED>
-__global__ void __launch_bounds__(UPD_THREADS) window_join_kernel(const UpdParams p) {
-  constexpr int VE = Vec16<WT>::VE;
-  constexpr int NG = UPD_THREADS / G;
-  constexpr int64_t BC = (int64_t)NG * HOT_CH;  // positions per block of the window kernel
-  constexpr int PB = (NV * VE >= 32) ? 2 : (NV * VE >= 16 ? 4 : (NV * VE >= 8 ? 8 : 16));  // partial rows in flight
-  const int gid = threadIdx.x / G, lane = threadIdx.x % G;
-  const int64_t k = (int64_t)blockIdx.x * NG + gid + 1;  // border between positions k*BC-1 and k*BC
-  // Does a run cross this border, and is this the FIRST border it crosses (the one that owns it)?
-  // These checks read the sort/dedup outputs only, so they run before the window kernel has finished.
-  const int64_t n_eff = p.d_n ? min(*p.d_n, p.n) : p.n;
-  bool mine = k * BC < n_eff && p.skeys[k * BC - 1] == p.skeys[k * BC];
-  int64_t u = 0, s = 0, e = 0;
-  if (mine) {
-    u = p.win_run[k * NG];
-    s = p.seg[u];
-    e = p.seg[u + 1];
-    mine = s / BC + 1 == k;  // otherwise an earlier border owns this run
-  }
-  // EVERY thread waits for the window kernel, including those with nothing to join: a dependent grid
-  // launched with programmatic serialization is ordered behind its primary only through this instruction,
-  // and the next kernel on the stream is ordered behind THIS grid -- if a group left without waiting, a
-  // step with no border-crossing run would let that next kernel start while weight rows are still being
-  // written.  (No-op when launched without the attribute.)
-  asm volatile("griddepcontrol.wait;" ::: "memory");
-  if (!mine) return;
-  const int64_t w0 = s / BC, w1 = (e - 1) / BC;
-  if (w1 - w0 >= HOT_BLOCKS) {  // a very long run: listed here, reduced by a whole CTA in hot_join_kernel
-    if (lane == 0) p.hot_list[atomicAdd(p.hot_count, 1)] = (uint32_t)u;
-    return;
-  }
-  float acc[NV][VE];
-#pragma unroll
-  for (int kk = 0; kk < NV; ++kk)
-#pragma unroll
-    for (int x = 0; x < VE; ++x) acc[kk][x] = 0.f;
-  add_partial_rows<G, NV, VE, PB>(acc, p.partial, w0, w1, s, BC, p.D, p.V, lane);
-  finish_run<WT, G, NV, OPT, RED>(p, u, acc, lane);
-}
-
-// ---- 3c. hot runs: one CTA per listed run.  Group g adds the partial rows of blocks w0 + g, w0 + g + NG, ... (PB in
-// flight), the NG group sums meet in shared memory and group 0 adds them in group order and updates the row.
-template <typename WT, int G, int NV, int OPT, bool RED>
-__global__ void __launch_bounds__(UPD_THREADS) hot_join_kernel(const UpdParams p) {
-  constexpr int VE = Vec16<WT>::VE;
-  constexpr int NG = UPD_THREADS / G;
-  constexpr int64_t BC = (int64_t)NG * HOT_CH;
-  constexpr int PB = (NV * VE >= 32) ? 2 : (NV * VE >= 16 ? 4 : 8);
-  extern __shared__ __align__(16) float s_sum[];  // [NG][D]
-  const int gid = threadIdx.x / G, lane = threadIdx.x % G;
-  const int n_hot = *p.hot_count;
-  for (int ent = blockIdx.x; ent < n_hot; ent += gridDim.x) {  // (uniform per CTA: the barriers below are safe)
-  const int64_t u = p.hot_list[ent];
-  const int64_t s = p.seg[u], e = p.seg[u + 1];
-  const int64_t w0 = s / BC, w1 = (e - 1) / BC;
-  float acc[NV][VE];
-#pragma unroll
-  for (int kk = 0; kk < NV; ++kk)
-#pragma unroll
-    for (int x = 0; x < VE; ++x) acc[kk][x] = 0.f;
-  for (int64_t ib = w0 + gid; ib <= w1; ib += (int64_t)NG * PB) {
-    uint4 f[PB][NV][VE / 4];
-#pragma unroll
-    for (int c = 0; c < PB; ++c) {
-      const int64_t i = ib + (int64_t)c * NG;
-      const bool ok = i <= w1;
-      // slot rule of the window kernel: a block the run ENTERS from the left wrote slot 0, the block holding its head slot 1
-      const float* src = p.partial + (size_t)(2 * (ok ? i : w0) + ((ok && s > i * BC) ? 1 : 0)) * p.D + lane * VE;
-#pragma unroll
-      for (int kk = 0; kk < NV; ++kk)
-#pragma unroll
-        for (int h = 0; h < VE / 4; ++h)
-          f[c][kk][h] = (ok && lane + kk * G < p.V) ? ld_v4(src + kk * G * VE + 4 * h) : make_uint4(0, 0, 0, 0);
-    }
-#pragma unroll
-    for (int c = 0; c < PB; ++c)
-#pragma unroll
-      for (int kk = 0; kk < NV; ++kk)
-#pragma unroll
-        for (int h = 0; h < VE / 4; ++h) keep(f[c][kk][h]);
-#pragma unroll
-    for (int c = 0; c < PB; ++c)
-#pragma unroll
-      for (int kk = 0; kk < NV; ++kk)
-#pragma unroll
-        for (int h = 0; h < VE / 4; ++h) Vec16<float>::accum(acc[kk] + 4 * h, f[c][kk][h]);
-  }
-  float* mine = s_sum + (size_t)gid * p.D + lane * VE;
-#pragma unroll
-  for (int kk = 0; kk < NV; ++kk)
-    if (lane + kk * G < p.V) {
-#pragma unroll
-      for (int x = 0; x < VE; ++x) mine[kk * G * VE + x] = acc[kk][x];
-    }
+  // ---- cross-block join, inside this kernel.  A run that crosses block borders has left one partial row per block
+  // it touches (above).  Every such block takes a ticket on the counter of the run's HEAD block once its partial row
+  // is visible device-wide; the block that draws the last ticket adds the partial rows of all the run's blocks in
+  // block order (whoever does it, the order is the same: deterministic) with all its groups -- strided rows, PB in
+  // flight, combined in shared memory -- and gives the row its one update.  No second kernel, no launch gap: the
+  // join used to cost two small launches (~20 us of a 118 us update on the Criteo-Terabyte tables).
+  constexpr int64_t BC = (int64_t)NG * C;
+  __shared__ int64_t s_job[2][3];  // {run index, first position of the run, last block of the run}
+  __shared__ int s_njobs;
+  if (!(x_enters || x_leaves)) return;  // (block-uniform) no run crosses this block's borders: the common case
+  __threadfence();
   __syncthreads();
-  if (gid == 0) {
-    for (int g = 1; g < NG; ++g) {
-      const float* q = s_sum + (size_t)g * p.D + lane * VE;
-#pragma unroll
-      for (int kk = 0; kk < NV; ++kk)
-        if (lane + kk * G < p.V) {
-#pragma unroll
-          for (int x = 0; x < VE; ++x) acc[kk][x] += q[kk * G * VE + x];
-        }
-    }
-    finish_run<WT, G, NV, OPT, RED>(p, u, acc, lane);
+  if (threadIdx.x == 0) {
+    int nj = 0;
+    auto ticket = [&](int64_t u, int64_t s0, int64_t e0) {
+      const int64_t h = s0 / BC, w1 = (min(e0, n_eff) - 1) / BC;
+      const int need = (int)(w1 - h + 1);
+      if (atomicAdd(&p.blk_cnt[h], 1) + 1 == need) {
+        p.blk_cnt[h] = 0;  // every contributor has drawn: ready for the next call on this workspace
+        __threadfence();
+        s_job[nj][0] = u, s_job[nj][1] = s0, s_job[nj][2] = w1;
+        ++nj;
+      }
+    };
+    if (x_enters) ticket(s_x[0], s_x[1], s_x[2]);
+    if (x_leaves && s_x[3] != s_x[0]) ticket(s_x[3], s_x[4], s_x[5]);
+    s_njobs = nj;
   }
-  __syncthreads();  // s_sum is reused by the next listed run
+  __syncthreads();
+  const int njobs = s_njobs;
+  for (int jb = 0; jb < njobs; ++jb) {
+    constexpr int PB = (NV * VE >= 32) ? 2 : (NV * VE >= 16 ? 4 : 8);
+    const int64_t u = s_job[jb][0], s0 = s_job[jb][1], w1 = s_job[jb][2];
+    const int64_t w0 = s0 / BC;
+    float sum[NV][VE];
+#pragma unroll
+    for (int kk = 0; kk < NV; ++kk)
+#pragma unroll
+      for (int x = 0; x < VE; ++x) sum[kk][x] = 0.f;
+    for (int64_t ib = w0 + gid; ib <= w1; ib += (int64_t)NG * PB) {
+      uint4 f[PB][NV][VE / 4];
+#pragma unroll
+      for (int c = 0; c < PB; ++c) {
+        const int64_t i = ib + (int64_t)c * NG;
+        const bool ok = i <= w1;
+        // slot rule: the block holding the run's head wrote slot 1 (slot 0 if the run starts at its first position)
+        const float* src = p.partial + (size_t)(2 * (ok ? i : w0) + ((ok && s0 > i * BC) ? 1 : 0)) * p.D + lane * VE;
+#pragma unroll
+        for (int kk = 0; kk < NV; ++kk)
+#pragma unroll
+          for (int h = 0; h < VE / 4; ++h)
+            f[c][kk][h] = (ok && lane + kk * G < p.V) ? ld_cg_v4(src + kk * G * VE + 4 * h) : make_uint4(0, 0, 0, 0);
+      }
+#pragma unroll
+      for (int c = 0; c < PB; ++c)
+#pragma unroll
+        for (int kk = 0; kk < NV; ++kk)
+#pragma unroll
+          for (int h = 0; h < VE / 4; ++h) keep(f[c][kk][h]);
+#pragma unroll
+      for (int c = 0; c < PB; ++c)
+#pragma unroll
+        for (int kk = 0; kk < NV; ++kk)
+#pragma unroll
+          for (int h = 0; h < VE / 4; ++h) Vec16<float>::accum(sum[kk] + 4 * h, f[c][kk][h]);
+    }
+    float* mine = s_part + (size_t)gid * p.D + lane * VE;  // (the in-block pieces are consumed: reuse the buffer)
+#pragma unroll
+    for (int kk = 0; kk < NV; ++kk)
+      if (lane + kk * G < p.V) {
+#pragma unroll
+        for (int x = 0; x < VE; ++x) mine[kk * G * VE + x] = sum[kk][x];
+      }
+    __syncthreads();
+    if (gid == 0) {
+      for (int g = 1; g < NG; ++g) {
+        const float* q = s_part + (size_t)g * p.D + lane * VE;
+#pragma unroll
+        for (int kk = 0; kk < NV; ++kk)
+          if (lane + kk * G < p.V) {
+#pragma unroll
+            for (int x = 0; x < VE; ++x) sum[kk][x] += q[kk * G * VE + x];
+          }
+      }
+      finish_run<WT, G, NV, OPT, RED>(p, u, sum, lane);
+    }
+    __syncthreads();
   }
 }
 
@@ -872,10 +827,6 @@ static int launch_update(const UpdParams& p, int64_t n, bool vec_ok, cudaStream_
     const char* e = getenv("B200_SGD_RED");
     return e == nullptr || e[0] != '0';
   }();
-  static const bool use_pdl = []() {
-    const char* e = getenv("B200_PDL");
-    return e == nullptr || e[0] != '0';
-  }();
 #define B200_UPD_LAUNCH(G, NV, RED)                                                                               \
   if constexpr (sizeof(WT) == 2) {                                                                                \
     if (p.trail != nullptr) {                                                                                     \
@@ -899,24 +850,6 @@ static int launch_update(const UpdParams& p, int64_t n, bool vec_ok, cudaStream_
     }                                                                                                             \
     const int64_t nblk = ceil_div(nwin, NG_);                                                                     \
     kern<<<(unsigned)nblk, UPD_THREADS, part_bytes, st>>>(p);                                                     \
-    if (nblk > 1) {                                                                                               \
-      cudaLaunchConfig_t cfg = {};                                                                                \
-      cfg.gridDim = dim3((unsigned)ceil_div(nblk - 1, NG_));                                                      \
-      cfg.blockDim = dim3(UPD_THREADS);                                                                           \
-      cfg.stream = st;                                                                                            \
-      cudaLaunchAttribute at[1];                                                                                  \
-      at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                                              \
-      at[0].val.programmaticStreamSerializationAllowed = 1;                                                       \
-      cfg.attrs = at;                                                                                             \
-      cfg.numAttrs = use_pdl ? 1 : 0;                                                                             \
-      cudaLaunchKernelEx(&cfg, window_join_kernel<WT, G, NV, OPT, RED>, p);                                       \
-      if (nblk > HOT_BLOCKS) { /* only then can a run cross more than HOT_BLOCKS borders */                        \
-        auto hk = hot_join_kernel<WT, G, NV, OPT, RED>;                                                           \
-        const size_t hs = (size_t)NG_ * p.D * sizeof(float);                                                      \
-        if (hs > 48 * 1024) cudaFuncSetAttribute(hk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hs);       \
-        hk<<<(unsigned)std::min<int64_t>(ceil_div(nblk, HOT_BLOCKS) + 1, 4096), UPD_THREADS, hs, st>>>(p);        \
-      }                                                                                                           \
-    }                                                                                                             \
   }
 #define B200_UPD_CASE(G, NV)                 \
   if constexpr (CAN_RED) {                   \
@@ -972,8 +905,9 @@ static int emb_bwd_prepare_impl(const int64_t* d_rows, const int64_t* d_row_base
                "emb_bwd: workspace too small");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   BwdLayout L = bwd_layout(ws, nnz, D);
-  keys_tail_kernel<<<d_nnz_valid ? 256 : 1, 256, 0, st>>>(L.keys, L.vals, d_nnz_valid, nnz, (uint32_t)total_rows,
-                                                          L.n_valid, L.hot_count);
+  const int64_t n_blk_cnt = ceil_div(ceil_div(nnz, HOT_CH), MIN_NG) + 1;
+  keys_tail_kernel<<<(unsigned)std::min<int64_t>(d_nnz_valid ? 256 : ceil_div(n_blk_cnt, 256), 256), 256, 0, st>>>(
+      L.keys, L.vals, d_nnz_valid, nnz, (uint32_t)total_rows, L.n_valid, L.blk_cnt, n_blk_cnt);
   dim3 kgrid((unsigned)ceil_div(B, KEYS_THREADS), (unsigned)T);
   build_keys_kernel<<<kgrid, KEYS_THREADS, 0, st>>>(d_indices, d_offsets, d_rows, d_row_base, B, L.keys,
                                                     L.vals, d_error);
@@ -1046,8 +980,7 @@ static int emb_bwd_apply_impl(void* const* d_weights, float* const* d_state, uin
   p.partial = L.partial;
   p.n = nnz;
   p.d_n = L.n_valid;
-  p.hot_count = L.hot_count;
-  p.hot_list = L.hot_list;
+  p.blk_cnt = L.blk_cnt;
   p.values = nullptr;
   p.by_key = 0;
   p.grad_ptrs = d_grad_ptrs;
@@ -1140,8 +1073,7 @@ static int store_run_sums(const int64_t* d_row_base, int64_t nnz, const void* d_
   p.by_key = by_key;
   p.n = nnz;
   p.d_n = L.n_valid;
-  p.hot_count = L.hot_count;
-  p.hot_list = L.hot_list;
+  p.blk_cnt = L.blk_cnt;
   p.T = (int)T;
   const int gsz = dtype_size(grad_dtype);
   const bool vec_ok = (D * 4) % 16 == 0 && p.V <= 128 && (reinterpret_cast<uintptr_t>(d_grad) % 16) == 0 &&
