@@ -56,6 +56,8 @@ def parse():
                          "NVLink exchange runs under another chunk's compute (measured slower at 2 GPUs: the step's "
                          "many small kernels do not shrink with the chunk)")
     ap.add_argument("--no-parity", action="store_true", help="multi-GPU: skip the pre-flight parity check")
+    ap.add_argument("--nccl-tail", action="store_true",
+                    help="multi-GPU: NCCL instead of the symmetric-memory two-shot all-reduce for the end-of-step bucket")
     ap.add_argument("--sparse-dense-boundary", type=int, default=2048,
                     help="multi-GPU: tables with fewer rows are replicated on every rank instead of sharded (the "
                          "reference training variant's flag and default, T/dlrm_s_pytorch.py:266-269); 0 = shard all")
@@ -345,7 +347,7 @@ def parity_preflight(world, rank, dev, use_p2p, n_chunks, use_graph, boundary=0,
         dense_r = [p for p in ref.parameters() if p.requires_grad]
         dense_n = [p for p in net.parameters() if p.requires_grad]
         opt_r, opt_n = torch.optim.SGD(dense_r, lr=lr), torch.optim.SGD(dense_n, lr=lr)
-        sync = ext_dist.DenseGradAllreduce(dense_n, early=list(net.top_l.parameters()))
+        sync = ext_dist.DenseGradAllreduce(dense_n, early=list(net.top_l.parameters()), symmetric_tail=use_p2p)
         rs = np.random.RandomState(5)
         batches = []
         for _ in range(steps):
@@ -471,7 +473,8 @@ def run_b200_arm(a):
     # MLPs are data-parallel: one flat all-reduce of their 2.4 M gradients per step (the fused bf16 MLP
     # path bypasses DDP.forward, so the averaging the reference gets from DDP is done explicitly)
     # (the top MLP's share is reduced from inside backward, under the interaction backward and the table update)
-    sync_dense = (ext_dist.DenseGradAllreduce(dense_params, early=list(net.top_l.parameters()))
+    sync_dense = (ext_dist.DenseGradAllreduce(dense_params, early=list(net.top_l.parameters()),
+                                              symmetric_tail=use_p2p and not a.nccl_tail)
                   if world > 1 else (lambda: None))
     sets = make_batches(a, rows_local, B_loc, B_glob, dev, rank, n_chunks, rows_repl)
     emb = net.emb_l

@@ -39,6 +39,8 @@ SIGNATURES = {
                                           _c.c_float, _p, _c.c_float, _p, _c.c_size_t, _p]),
     "b200_rowwise_filter_workspace_bytes": (_c.c_size_t, [_i64]),
     "b200_rowwise_filter": (_int, [_p, _p, _i64, _i64, _i64, _p, _i64, _p, _p, _p, _c.c_size_t, _p]),
+    "b200_emb_fwd_sharded_from": (_int, [_p, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i64, _i64, _int, _int, _int,
+                                         _i64, _p, _p]),
     "b200_emb_fwd_sharded_add": (_int, [_p, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i64, _i64, _int, _int, _p, _p]),
     "b200_emb_bwd_prepare_partial": (_int, [_p, _p, _p, _p, _i64, _p, _i64, _i64, _i64, _i64, _p, _c.c_size_t, _p, _p]),
     "b200_emb_bwd_coalesce": (_int, [_p, _p, _p, _p, _i64, _p, _i64, _i64, _i64, _i64, _i64, _int, _i64, _p, _p, _p,

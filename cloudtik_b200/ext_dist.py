@@ -331,7 +331,7 @@ class DenseGradAllreduce(object):
     ``ext_dist.DDP(bot_l) / DDP(top_l)`` (``P/dlrm_s_pytorch.py:955-957``: mean over ranks); used when the
     MLPs run through the fused bf16 path, whose autograd functions bypass ``DDP.forward``."""
 
-    def __init__(self, params, average: bool = True, early=None):
+    def __init__(self, params, average: bool = True, early=None, symmetric_tail: bool = False):
         """``average=False`` sums instead (use it when every rank already divides its loss by the world
         size -- the way to keep a scale-sensitive table optimiser such as Adagrad exact, see tests/dist_parity.py).
 
@@ -339,24 +339,42 @@ class DenseGradAllreduce(object):
         the dense parameters of a DLRM).  Their part of the buffer is all-reduced asynchronously as soon as the
         last of them has its gradient (post-accumulate hooks), i.e. under the interaction backward, the embedding
         update and the bottom-MLP backward, the way DDP overlaps its buckets; ``__call__`` then only reduces the
-        rest and waits.  Call ``begin(n)`` before a step whose backward runs in n passes (micro-batches)."""
+        rest and waits.  Call ``begin(n)`` before a step whose backward runs in n passes (micro-batches).
+
+        ``symmetric_tail`` (one NVLink box, NCCL backend): that end-of-step remainder (the bottom MLP and replicated
+        small tables: ~2 MB) lives in a symmetric-memory buffer and is reduced by torch's two-shot peer-memory
+        all-reduce (reduce-scatter + all-gather through plain peer loads / stores, two signal-pad barriers) instead of
+        an NCCL call whose 8-rank latency (~60 us) sits on the critical path at the very end of the step."""
         self.average = average
         early = [p for p in (early or []) if p.requires_grad]
         early_ids = {id(p) for p in early}
         rest = [p for p in params if p.requires_grad and id(p) not in early_ids]
         self.params = early + rest
         self.n_early = len(early)
-        n = sum(p.numel() for p in self.params)
-        self.flat = torch.zeros(n, dtype=torch.float32, device=self.params[0].device)
+        dev = self.params[0].device
+        n_early = sum(p.numel() for p in early)
+        n_rest = sum(p.numel() for p in rest)
+        self.early_numel = n_early
+        self._symm_group = None
+        self.flat_rest = None
+        if symmetric_tail and my_size > 1 and n_rest > 0 and dist.get_backend() == "nccl":
+            import torch.distributed._symmetric_memory as symm
+            pad = -(-n_rest // (1024 * my_size)) * (1024 * my_size)  # whole 16-byte vectors per rank's share
+            self.flat_rest = symm.empty(pad, dtype=torch.float32, device=dev)
+            self._symm_group = dist.group.WORLD.group_name
+            symm.rendezvous(self.flat_rest, self._symm_group)
+            self.flat_rest.zero_()
+            self.flat = torch.zeros(max(n_early, 1), dtype=torch.float32, device=dev)
+        else:
+            self.flat = torch.zeros(n_early + n_rest, dtype=torch.float32, device=dev)
         self.views = []
         o = 0
         for k, p in enumerate(self.params):
             if k == self.n_early:
-                self.early_numel = o
-            self.views.append(self.flat[o:o + p.numel()].view_as(p))
+                o = 0 if self.flat_rest is not None else n_early
+            buf = self.flat if (k < self.n_early or self.flat_rest is None) else self.flat_rest
+            self.views.append(buf[o:o + p.numel()].view_as(p))
             o += p.numel()
-        if self.n_early == len(self.params):
-            self.early_numel = o
         self._pending = 0
         self._passes = 1
         self._work = None
@@ -393,7 +411,14 @@ class DenseGradAllreduce(object):
         if rest:
             grads = [p.grad if p.grad is not None else torch.zeros_like(p) for p in rest]
             torch._foreach_copy_(self.views[k:], grads)
-            dist.all_reduce(self.flat[self.early_numel if k else 0:], op=self._op())
+            if self.flat_rest is not None:
+                if k == 0 and self.n_early:  # the early bucket was not reduced from inside backward this time
+                    dist.all_reduce(self.flat[:self.early_numel], op=self._op())
+                torch.ops.symm_mem.two_shot_all_reduce_(self.flat_rest, "sum", self._symm_group)
+                if self.average:
+                    self.flat_rest.mul_(1.0 / my_size)
+            else:
+                dist.all_reduce(self.flat[self.early_numel if k else 0:], op=self._op())
         if self._work is not None:
             self._work.wait()
             self._work = None

@@ -414,7 +414,7 @@ class MergedEmbeddingBagWithSGD(nn.Module):
         with torch.cuda.stream(side):
             for idx, off, exch in chunks:  # every chunk reads the tables BEFORE any chunk's update (queued later)
                 ops.emb_fwd_sharded(self.tables, idx, off, exch.lN * exch.world, exch.T_ptrs_dev, exch.lN, exch.F,
-                                    feat0, exch.dtype, self.error_flag)
+                                    feat0, exch.dtype, self.error_flag, first_dest=(exch.rank + 1) % exch.world)
                 ev = torch.cuda.Event()
                 ev.record(side)
                 self._pending_sharded[exch.chunk] = (idx, off, ev)

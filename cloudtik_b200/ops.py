@@ -209,18 +209,19 @@ def emb_bwd_apply(tables: TableSet, nnz: int, B: int, grad: torch.Tensor, stride
 
 
 def emb_fwd_sharded(tables: TableSet, indices, offsets, B: int, out_ptrs_dev: int, lN: int, F: int, feat0: int,
-                    out_dtype: torch.dtype, error: torch.Tensor | None = None, accumulate: bool = False):
+                    out_dtype: torch.dtype, error: torch.Tensor | None = None, accumulate: bool = False,
+                    first_dest: int = 0):
     """Pooled lookup of this rank's tables for the GLOBAL batch, written straight into every rank's
     interaction input over peer memory.  ``out_ptrs_dev``: device address of the [world] pointer table.
     ``accumulate``: ADD into the (zeroed) destination instead of storing -- row-wise sharded tables.
     See b200_emb_fwd_sharded / b200_emb_fwd_sharded_add."""
     _cuda(indices, "indices", torch.int64)
     _cuda(offsets, "offsets", torch.int64)
-    fn = lib.b200_emb_fwd_sharded_add if accumulate else lib.b200_emb_fwd_sharded
-    check(fn(tables.d_ptrs.data_ptr(), tables.d_rows.data_ptr(), indices.data_ptr(),
-                                   offsets.data_ptr(), out_ptrs_dev, indices.numel(), len(tables), B, tables.D,
-                                   lN, F, feat0, _dt(tables.dtype), _dt(out_dtype),
-                                   error.data_ptr() if error is not None else None, _stream()),
+    # first_dest: rank whose bags are visited first ((own rank + 1) % world spreads the ranks over the destinations)
+    check(lib.b200_emb_fwd_sharded_from(tables.d_ptrs.data_ptr(), tables.d_rows.data_ptr(), indices.data_ptr(),
+                                        offsets.data_ptr(), out_ptrs_dev, indices.numel(), len(tables), B, tables.D,
+                                        lN, F, feat0, _dt(tables.dtype), _dt(out_dtype), 1 if accumulate else 0,
+                                        int(first_dest), error.data_ptr() if error is not None else None, _stream()),
           "b200_emb_fwd_sharded")
 
 

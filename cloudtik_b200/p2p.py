@@ -69,7 +69,8 @@ class PeerExchange:
         update reads each bag's gradient row once per index: from a local copy those re-reads hit L2 / HBM, whereas
         peer memory is not cached in the local L2 and every one of them would cross NVLink again."""
         G = torch.empty(self.lN * self.world, n_feat, self.D, dtype=self.dtype, device=self.T.device)
-        for r in range(self.world):
+        for k in range(self.world):  # start with the next rank: the ranks then read from different peers at a time
+            r = (self.rank + 1 + k) % self.world
             G[r * self.lN:(r + 1) * self.lN].copy_(self.dT_peers[r][:, feat0:feat0 + n_feat])
         return G
 
@@ -97,7 +98,7 @@ class _ShardedEmbInteractFn(torch.autograd.Function):
                 emb.join()
                 with emb._timed("emb_fwd"):
                     ops.emb_fwd_sharded(emb.tables, indices, offsets, B_glob, exch.T_ptrs_dev, exch.lN, exch.F,
-                                        feat0, exch.dtype, emb.error_flag)
+                                        feat0, exch.dtype, emb.error_flag, first_dest=(exch.rank + 1) % exch.world)
                 if train:  # sort / dedup on the side stream: only a backward consumes it
                     emb._launch_prepare(indices, offsets, B_glob, chunk=exch.chunk)
         ctx.rw_ctx = None

@@ -112,7 +112,9 @@ class ReplicatedEmbeddingBags(nn.Module):
 
     def _own_stream(self):
         if self._stream is None:
-            self._stream = torch.cuda.Stream(device=self.tables.device)
+            # high priority: the lookup feeds the interaction, the dense gradients feed the end-of-step all-reduce --
+            # queued behind the thousands of blocks of the (low-priority) NVLink-bound update they arrive 200 us late
+            self._stream = torch.cuda.Stream(device=self.tables.device, priority=-1)
         return self._stream
 
     def launch_prepare(self, indices, offsets, B: int):

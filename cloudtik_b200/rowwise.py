@@ -98,7 +98,7 @@ class RowWiseShardedTables(nn.Module):
         li, lo = ops.rowwise_filter(indices, offsets, self.world, self.rank, self.capacity(indices.numel()),
                                     self.error_flag)
         ops.emb_fwd_sharded(self.emb.tables, li, lo, B_glob, exch.T_ptrs_dev, exch.lN, exch.F, exch.F - self.k,
-                            exch.dtype, self.emb.error_flag, accumulate=True)
+                            exch.dtype, self.emb.error_flag, accumulate=True, first_dest=(exch.rank + 1) % exch.world)
         return li, lo, B_glob
 
     def update_from_peers(self, ctx, exch):

@@ -169,6 +169,14 @@ int b200_emb_fwd_sharded(const void* const* d_weights, const int64_t* d_rows, co
                          const int64_t* d_offsets, void* const* d_out_ptrs, int64_t nnz, int64_t T,
                          int64_t B, int64_t D, int64_t lN, int64_t F, int64_t feat0, int w_dtype,
                          int out_dtype, int32_t* d_error, b200_stream_t stream);
+/* b200_emb_fwd_sharded (accumulate = 0) / b200_emb_fwd_sharded_add (accumulate = 1) with the order of the bag tiles
+ * rotated so that the kernel starts with the bags of rank `first_dest_rank` and goes round from there.  Every rank
+ * of a job passes (its own rank + 1) mod world: at any moment the ranks then write to DIFFERENT destinations, the
+ * schedule of an all-to-all, instead of all converging on rank 0's NVLink ingress first, then on rank 1's, ... */
+int b200_emb_fwd_sharded_from(const void* const* d_weights, const int64_t* d_rows, const int64_t* d_indices,
+                              const int64_t* d_offsets, void* const* d_out_ptrs, int64_t nnz, int64_t T, int64_t B,
+                              int64_t D, int64_t lN, int64_t F, int64_t feat0, int w_dtype, int out_dtype,
+                              int accumulate, int64_t first_dest_rank, int32_t* d_error, b200_stream_t stream);
 int b200_emb_bwd_apply_sharded(void* const* d_weights, float* const* d_state, uint16_t* const* d_trail,
                                const int64_t* d_row_base,
                                int64_t nnz, const void* const* d_grad_ptrs, int64_t T, int64_t B,

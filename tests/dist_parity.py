@@ -50,7 +50,7 @@ def main():
     world, rank = ext_dist.my_size, ext_dist.my_rank
     dev = torch.device("cuda", torch.cuda.current_device())
     D = 128
-    rows = [5000, 37, 20000, 3, 1200, 800, 64, 100000][:a.tables]
+    rows = [5000, 37, 20000, 3, 1200, 800, 64, 100000, 3000, 150, 7000, 11, 2500, 9000, 450, 60000][:a.tables]
     if a.boundary:  # small tables first: the model's feature order (dense tables, then sharded ones) is then the
         rows = [r for r in rows if r < a.boundary] + [r for r in rows if r >= a.boundary]  # oracle's natural order
     F = len(rows) + 1

@@ -539,10 +539,13 @@ def test_sharded_entry_points_on_one_gpu(W, lN, dtype):
     ops.emb_fwd(ts, d_idx, d_off, B, plain, D, T * D)
     bufs = [torch.full((lN, F, D), -7.0, dtype=dtype, device="cuda") for _ in range(W)]
     ptrs = torch.tensor([b.data_ptr() for b in bufs], dtype=torch.int64, device="cuda")
-    ops.emb_fwd_sharded(ts, d_idx, d_off, B, ptrs.data_ptr(), lN, F, feat0, dtype)
-    for r in range(W):
-        assert torch.equal(bufs[r][:, feat0:feat0 + T], plain[r * lN:(r + 1) * lN])
-        assert bool((bufs[r][:, :feat0] == -7).all()) and bool((bufs[r][:, feat0 + T:] == -7).all())
+    for first_dest in range(W):  # the visiting order of the destinations must not change what lands where
+        for b_ in bufs:
+            b_.fill_(-7.0)
+        ops.emb_fwd_sharded(ts, d_idx, d_off, B, ptrs.data_ptr(), lN, F, feat0, dtype, first_dest=first_dest)
+        for r in range(W):
+            assert torch.equal(bufs[r][:, feat0:feat0 + T], plain[r * lN:(r + 1) * lN])
+            assert bool((bufs[r][:, :feat0] == -7).all()) and bool((bufs[r][:, feat0 + T:] == -7).all())
     # backward: gradients scattered over W buffers vs one contiguous gradient
     g = torch.tensor(rs.randint(-3, 4, size=(B, F, D)).astype(np.float32)).to(dtype).cuda()
     gbufs = [g[r * lN:(r + 1) * lN].contiguous() for r in range(W)]
