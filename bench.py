@@ -709,7 +709,12 @@ def c5_measure(a, world, rank, dev, steps, warmup):
     n_rw = 3 if world > 1 else 0
     P, B_loc = a.pooling, a.batch
     B_glob = B_loc * world
-    lr, lr_emb = 0.01, 1e-3  # Adagrad's first steps are +-lr per touched element: keep them small next to U(+-sqrt(1/n))
+    # Adagrad's first steps are +-lr per touched element: keep them small next to U(+-sqrt(1/n)).  MLP rate: with 20
+    # rows pooled per bag the tiny tables (3 ... 63 rows, U(+-0.58) entries) give interaction values in the thousands,
+    # and at 1e-2 the first top-MLP layer blows up within a few steps whenever the batch composition is unlucky (seen
+    # at 4 and 8 GPUs: every prediction saturated, loss 50.45 = 100 x the share of positive targets); the kernels'
+    # work does not depend on it
+    lr, lr_emb = 1e-4, 1e-3
     np.random.seed(727)
     torch.manual_seed(727 + rank)
     net = DLRM_Net(D, np.array(rows), np.array(LN_BOT), np.array(LN_TOP), sigmoid_top=len(LN_TOP) - 2,
