@@ -167,8 +167,19 @@ def main():
             with torch.no_grad():
                 with torch.autocast("cpu", dtype=torch.bfloat16, enabled=a.bf16):
                     want = port(torch.tensor(X), [torch.tensor(o) for o in lS_o], [torch.tensor(i) for i in lS_i]).float()
-                Z = net(torch.tensor(X[rank * lN:(rank + 1) * lN]).to(dev), [torch.tensor(lS_o[t]).to(dev) for t in local],
-                        [torch.tensor(lS_i[t]).to(dev) for t in local]).float()
+                if a.boundary:  # the training variant's input: every table's bags of the LOCAL batch
+                    def loc(t):
+                        o = torch.tensor(lS_o[t])
+                        s0 = int(o[rank * lN])
+                        s1 = int(o[(rank + 1) * lN]) if (rank + 1) * lN < N else len(lS_i[t])
+                        return (o[rank * lN:(rank + 1) * lN] - s0).to(dev), torch.tensor(lS_i[t][s0:s1]).to(dev)
+                    bl = [loc(t) for t in range(len(rows))]
+                    Z = net(torch.tensor(X[rank * lN:(rank + 1) * lN]).to(dev), [b[0] for b in bl],
+                            [b[1] for b in bl]).float()
+                else:
+                    Z = net(torch.tensor(X[rank * lN:(rank + 1) * lN]).to(dev),
+                            [torch.tensor(lS_o[t]).to(dev) for t in local],
+                            [torch.tensor(lS_i[t]).to(dev) for t in local]).float()
             np.testing.assert_allclose(Z.cpu().numpy(), want[rank * lN:(rank + 1) * lN].numpy(), rtol=10 * tol,
                                        atol=10 * tol, err_msg=f"forward-only pass {step}")
         net.train()

@@ -1,3 +1,4 @@
-run() { p=$1; shift; timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port $p "$@"; }
-run 29504 bench.py --gpus 2 --steps 20 --warmup 5 --no-c5 --timeline gpurun_out/tl_n2g > gpurun_out/b_n2g.log 2>&1; tail -c 400 gpurun_out/b_n2g.log
-run 29505 bench.py --gpus 2 --steps 20 --warmup 5 --no-c5 --nccl-tail > gpurun_out/b_n2h.log 2>&1; tail -c 200 gpurun_out/b_n2h.log
+N=2
+L="python -m cloudtik_b200.launcher --nproc-per-node $N"
+$L --master-port 29521 bench.py --gpus $N --steps 20 --warmup 5 > gpurun_out/final_n${N}_weak.log 2>&1; tail -c 100 gpurun_out/final_n${N}_weak.log; echo
+$L --master-port 29522 bench.py --gpus $N --steps 20 --warmup 5 --global-batch 65536 --no-c5 --no-parity > gpurun_out/final_n${N}_strong.log 2>&1; tail -c 100 gpurun_out/final_n${N}_strong.log; echo
