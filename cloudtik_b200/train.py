@@ -9,7 +9,7 @@ generator's flags, LR policy, ``--sparse-dense-boundary`` -- the same progress l
 (``Finished training it j/N of epoch k, X ms/it, loss L, accuracy A %``, ``T/dlrm_s_pytorch.py:1277-1283``) and the
 final ``Throughput: X fps`` line the shell wrapper of the product variant greps (``P/dlrm_s_pytorch.py:964-970``).
 
-Data: ``--data-generation=random`` only (this image has no Criteo files), through the mirror of the reference's
+Data: ``--data-generation=random|synthetic`` (this image has no Criteo files), through the mirror of the reference's
 ``RandomDataset`` (``cloudtik_b200.data``): the same numpy stream in the same order, and the tables drawn from the
 per-table seeds like ``T/dlrm_s_pytorch.py:240-243``.  With the reference's own test flags
 (``T/test/dlrm_s_test.sh:24``: ``--mini-batch-size=2 --data-size=4 --nepochs=1 --arch-interaction-op=dot
@@ -58,7 +58,9 @@ def parse(argv=None):
     # data (random generator flags, T/dlrm_s_pytorch.py:677-697)
     p.add_argument("--data-size", type=int, default=1)
     p.add_argument("--num-batches", type=int, default=0)
-    p.add_argument("--data-generation", type=str, default="random")
+    p.add_argument("--data-generation", type=str, default="random")  # random | synthetic (trace-driven)
+    p.add_argument("--data-trace-file", type=str, default="./input/dist_emb_j.log")
+    p.add_argument("--data-trace-enable-padding", type=bool, default=False)
     p.add_argument("--num-indices-per-lookup", type=int, default=10)
     p.add_argument("--num-indices-per-lookup-fixed", type=bool, default=False)
     # training (T/dlrm_s_pytorch.py:701-707)
@@ -107,8 +109,8 @@ def make_loss(args, dev):
 
 def run(argv=None):
     args = parse(argv)
-    if args.data_generation != "random":
-        sys.exit("ERROR: only --data-generation=random is available (no dataset files in this build)")
+    if args.data_generation not in ("random", "synthetic"):
+        sys.exit("ERROR: --data-generation=" + args.data_generation + " is not available (no dataset files in this build)")
     ext_dist.init_distributed(backend=args.backend)
     world, rank = max(ext_dist.my_size, 1), max(ext_dist.my_rank, 0)
     dev = torch.device("cuda", torch.cuda.current_device())

@@ -468,6 +468,50 @@ def gen_T_options():
     np.savez_compressed(os.path.join(OUT, "t_options.npz"), **out)
 
 
+def gen_trace_synth():
+    """The trace-driven index generator (``--data-generation=synthetic``), run through the reference's own functions:
+    ``trace_profile`` (T/dlrm_data_pytorch.py:954) on a seeded skewed id trace per table, the distribution built as
+    the module's ``__main__`` does (:1088-1112; restated here, a script body cannot be imported), the three-line
+    files (:1045), then ``trace_generate_lru`` (:902) and ``generate_synthetic_input_batch`` (:807) under
+    ``np.random.seed``.  The file contents are stored in the fixture (the test writes them back out)."""
+    import collections
+    import tempfile
+    G = load_T_generator()
+    rs = np.random.RandomState(99)
+    ln_emb = [50, 400, 7]
+    out = {"ln_emb": np.array(ln_emb)}
+    tmp = tempfile.mkdtemp()
+    for t, rows in enumerate(ln_emb):
+        trace = np.minimum((rs.pareto(1.2, size=600) * 3).astype(np.int64), rows - 1)
+        out[f"trace{t}"] = trace
+        for pad in (False, True):
+            _, sds, lines = G.trace_profile([np.uint64(x) for x in trace], pad)
+            sds.reverse()
+            lines.reverse()
+            n = len(sds)
+            dc = sorted(collections.Counter(sds).items(), key=lambda kv: kv[0])
+            list_sd = [int(k) for k, _ in dc]
+            cumm = []
+            for i, (_, k) in enumerate(dc):
+                cumm.append(k / float(n) if i == 0 else cumm[i - 1] + k / float(n))
+            tag = f"{t}_{int(pad)}"
+            out[f"lines{tag}"] = np.array([int(x) for x in lines], dtype=np.int64)
+            out[f"dist{tag}"] = np.array(list_sd, dtype=np.int64)
+            out[f"cumm{tag}"] = np.array(cumm, dtype=np.float64)
+            G.write_dist_to_file(os.path.join(tmp, f"dist{int(pad)}_emb_{t}.log"), [int(x) for x in lines], list_sd, cumm)
+            np.random.seed(7 + t)
+            la, sd, cs = G.read_dist_from_file(os.path.join(tmp, f"dist{int(pad)}_emb_{t}.log"))
+            out[f"lru{tag}"] = np.array(G.trace_generate_lru(la, sd, cs, 300, pad), dtype=np.uint64)
+    for tag, fixed, pad in (("ragged", False, False), ("fixed", True, False), ("ragged_pad", False, True)):
+        np.random.seed(123)
+        X, lS_o, lS_i = G.generate_synthetic_input_batch(4, ln_emb, 6, 5, fixed, os.path.join(tmp, f"dist{int(pad)}_emb_j.log"), pad)
+        out[f"{tag}_X"] = X.numpy()
+        for t in range(len(ln_emb)):
+            out[f"{tag}_o{t}"] = lS_o[t].numpy()
+            out[f"{tag}_i{t}"] = lS_i[t].numpy()
+    np.savez_compressed(os.path.join(OUT, "trace_synth.npz"), **out)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     G = load_T_generator()
@@ -482,6 +526,7 @@ def main():
     gen_tricks()
     gen_T_smoke()
     gen_T_options()
+    gen_trace_synth()
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

@@ -283,3 +283,47 @@ def test_batch_producers_reproduce_the_reference_stream(golden):
         for t in range(len(sm["ln_emb"])):
             np.testing.assert_array_equal(lS_o[t].numpy(), sm[f"o{s}_{t}"])
             np.testing.assert_array_equal(lS_i[t].numpy(), sm[f"i{s}_{t}"])
+
+
+def test_trace_driven_producer_reproduces_the_reference(golden, tmp_path):
+    """--data-generation=synthetic (cloudtik_b200.data.StackDistanceModel / generate_synthetic_input_batch) against
+    tests/golden/trace_synth.npz, every array of which the reference's own trace_profile / trace_generate_lru /
+    generate_synthetic_input_batch wrote (oracle/gen_golden.py gen_trace_synth): the profile of a trace (first-touch
+    lines, distances, cumulative probabilities -- bit-equal floats), the LRU replay under the same seed, the file
+    round trip, and whole batches (ragged, fixed bag size, padding on)."""
+    import types
+    from cloudtik_b200 import data as D
+    g = golden("trace_synth")
+    ln_emb = [int(x) for x in g["ln_emb"]]
+    for t in range(len(ln_emb)):
+        for pad in (False, True):
+            tag = f"{t}_{int(pad)}"
+            m = D.StackDistanceModel.from_trace(g[f"trace{t}"], pad)
+            np.testing.assert_array_equal(np.array(m.lines), g[f"lines{tag}"])
+            np.testing.assert_array_equal(np.array(m.distances), g[f"dist{tag}"])
+            np.testing.assert_array_equal(m.cumulative, g[f"cumm{tag}"])
+            path = str(tmp_path / f"dist{int(pad)}_emb_{t}.log")
+            m.write(path)
+            back = D.StackDistanceModel.read(path)
+            assert back.lines == m.lines and back.distances == m.distances
+            np.testing.assert_array_equal(back.cumulative, m.cumulative)  # repr() round-trips a double
+            ids = back.generate_lru(300, pad, ra=np.random.RandomState(7 + t))
+            np.testing.assert_array_equal(ids, g[f"lru{tag}"])
+            assert m.lines == back.lines  # the replay works on a copy
+    for tag, fixed, pad in (("ragged", False, False), ("fixed", True, False), ("ragged_pad", False, True)):
+        X, lS_o, lS_i = D.generate_synthetic_input_batch(4, ln_emb, 6, 5, fixed, str(tmp_path / f"dist{int(pad)}_emb_j.log"),
+                                                         pad, ra=np.random.RandomState(123))
+        np.testing.assert_array_equal(X.numpy(), g[f"{tag}_X"])
+        for t in range(len(ln_emb)):
+            np.testing.assert_array_equal(lS_o[t].numpy(), g[f"{tag}_o{t}"])
+            np.testing.assert_array_equal(lS_i[t].numpy(), g[f"{tag}_i{t}"])
+    # through the dataset / loader the train CLI uses
+    args = types.SimpleNamespace(data_size=12, num_batches=0, mini_batch_size=6, num_indices_per_lookup=5,
+                                 num_indices_per_lookup_fixed=False, round_targets=False, data_generation="synthetic",
+                                 data_trace_file=str(tmp_path / "dist0_emb_j.log"), data_trace_enable_padding=False,
+                                 numpy_rand_seed=123)
+    _, ld = D.make_random_data_and_loader(args, ln_emb, 4)
+    X, lS_o, lS_i, T = next(iter(ld))
+    np.testing.assert_array_equal(X.numpy(), g["ragged_X"])
+    np.testing.assert_array_equal(lS_i[1].numpy(), g["ragged_i1"])
+    assert T.shape == (6, 1)
