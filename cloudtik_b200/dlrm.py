@@ -41,25 +41,30 @@ class DLRM_Net(nn.Module):
         # P/dlrm_s_pytorch.py:213-238; np_init_emb_weight=True draws every table from the numpy
         # stream on the host (parity runs); otherwise rows are drawn on the device with the same
         # U(-sqrt(1/n), sqrt(1/n)) law (Terabyte-size tables never exist on the host).
-        weights = []
         ids = range(ln.size) if local_ln_emb is None else local_ln_emb
+        weights = self._draw_tables(m, ln, ids, np_init_emb_weight, lambda i: device)
+        return MergedEmbeddingBagWithSGD(weights, lr=lr, optimizer=optimizer)
+
+    def _draw_tables(self, m, ln, ids, np_init_emb_weight, device_of):
+        """Tables ``ids`` drawn in that order (the order fixes the numpy stream), table i placed on ``device_of(i)``."""
+        weights = []
         for i in ids:
             n = int(ln[i])
             if np_init_emb_weight:
                 ra = np.random.RandomState(self.l_emb_seeds[i]) if self.np_emb_seeds else np.random
                 W = ra.uniform(low=-np.sqrt(1 / n), high=np.sqrt(1 / n), size=(n, m)).astype(np.float32)
-                weights.append(torch.from_numpy(W).to(device))
+                weights.append(torch.from_numpy(W).to(device_of(i)))
             else:
-                w = torch.empty(n, m, dtype=torch.float32, device=device)
+                w = torch.empty(n, m, dtype=torch.float32, device=device_of(i))
                 w.uniform_(-float(np.sqrt(1 / n)), float(np.sqrt(1 / n)))
                 weights.append(w)
-        return MergedEmbeddingBagWithSGD(weights, lr=lr, optimizer=optimizer)
+        return weights
 
     def __init__(self, m_spa=None, ln_emb=None, ln_bot=None, ln_top=None, sigmoid_bot=-1, sigmoid_top=-1,
                  weighted_pooling=None, loss_threshold=0.0, np_init_emb_weight=False, device="cuda",
                  lr=0.01, emb_optimizer="sgd", bf16=False, n_rowwise=0, distributed=None,
                  sparse_dense_boundary=0, dense_tables_first=False, arch_interaction_op="dot",
-                 arch_interaction_itself=False, np_emb_seeds=False):
+                 arch_interaction_itself=False, np_emb_seeds=False, ndevices=-1):
         """``distributed=False`` builds the single-process model (all tables local) even inside an initialised
         process group -- the oracle of the multi-GPU parity checks runs that way next to the sharded model.
 
@@ -71,6 +76,8 @@ class DLRM_Net(nn.Module):
         single-process model the same table order (``table_order``), which makes it the parity oracle of such a
         run (the reference's own sequential_forward keeps the natural order, SURVEY.md section 8c caveat)."""
         super().__init__()
+        # single-process multi-GPU mode of the training variant (T/dlrm_s_pytorch.py:306,524-630): see parallel_forward
+        self.ndevices = int(ndevices)
         # model options of the training variant (T/dlrm_s_pytorch.py:289-305,407-444)
         if arch_interaction_op not in ("dot", "cat"):
             sys.exit("ERROR: --arch-interaction-op=" + str(arch_interaction_op) + " is not supported")
@@ -118,6 +125,27 @@ class DLRM_Net(nn.Module):
         self.dense_pad = (-int(ln_bot[0])) % 8  # 13 dense features -> 16 zero-padded columns (aligned GEMM K)
         self.top_l = self.create_mlp(np.asarray(ln_top), sigmoid_top, pad_first=True).to(device)
         self.interaction_pad = 8  # interaction output rounded up to a multiple of 8 columns
+        if self.ndevices > 1:
+            if self.world > 1 or self.ln_emb_dense or self.n_rowwise:
+                raise NotImplementedError("ndevices > 1 is the single-process mode: no process group, no table split")
+            if str(torch.device(device)) not in ("cuda", "cuda:0"):
+                raise RuntimeError("ndevices > 1 keeps the MLP parameters on cuda:0 like the reference")
+            self.ndevices = min(self.ndevices, len(ln_emb))
+            self.device_ids = list(range(self.ndevices))
+            # table k lives on device k % ndevices (T/dlrm_s_pytorch.py:543-548), one merged module per device
+            ws = self._draw_tables(m_spa, ln_emb, range(len(ln_emb)), np_init_emb_weight,
+                                   lambda i: torch.device("cuda", i % self.ndevices))
+            self.tables_of_device = [list(range(d, len(ln_emb), self.ndevices)) for d in self.device_ids]
+            self.emb_l = nn.ModuleList(
+                [MergedEmbeddingBagWithSGD([ws[k] for k in ks], lr=lr, optimizer=emb_optimizer)
+                 for ks in self.tables_of_device])
+            for mod in self.emb_l:
+                mod.reserve_dense_slot = False  # their pooled rows travel before they reach an interaction input
+                if bf16:
+                    mod.output_dtype = torch.bfloat16
+            self.need_linearize_indices_and_offsets = torch.BoolTensor([True])
+            self.loss_fn = torch.nn.BCELoss(reduction="mean")
+            return
         self.emb_l = self.create_emb(m_spa, ln_emb, self.local_ln_emb, np_init_emb_weight, device, lr,
                                      emb_optimizer)
         if self.world > 1 and self.ln_emb_dense:
@@ -169,6 +197,8 @@ class DLRM_Net(nn.Module):
         small tables, linearised in ``ln_emb_dense`` order (models built with ``sparse_dense_boundary`` only)."""
         if self.world > 1:
             return self.distributed_forward(dense_x, *emb_args, chunk=chunk, dense_bags=dense_bags)
+        if self.ndevices > 1:
+            return self.parallel_forward(dense_x, *emb_args)
         return self.sequential_forward(dense_x, *emb_args)
 
     def begin_step(self, chunk_args):
@@ -199,6 +229,51 @@ class DLRM_Net(nn.Module):
             z = self.interact_features(x, ly)
             p = self.apply_mlp(z, self.top_l)
         return self._clamp(p)
+
+    def parallel_forward(self, dense_x, lS_o, lS_i):
+        """One process driving ``ndevices`` GPUs (T/dlrm_s_pytorch.py:524-630): MLPs data-parallel (replicas of the
+        cuda:0 parameters, re-made every call so their gradients sum back onto cuda:0), tables model-parallel (table k
+        on device k % ndevices, each device pools its tables for the WHOLE batch with one ``b200_emb_fwd`` launch), then
+        every device receives its batch slice of every table (the reference's "butterfly shuffle": here one
+        device-to-device copy per (source, destination) pair instead of one per table), interacts and runs the top MLP
+        on its slice; the predictions are gathered on cuda:0.  One host thread issues everything: the launches are
+        asynchronous, so the devices run concurrently without ``parallel_apply``'s worker threads.  The fused sparse
+        update of a device's tables runs inside backward on that device, with the full learning rate (the loss is the
+        mean over the gathered batch).  The device count is fixed at construction: a batch smaller than it is refused
+        (the reference re-distributes the model instead)."""
+        from torch.nn.parallel import gather, replicate, scatter
+        devs, nd = self.device_ids, len(self.device_ids)
+        batch_size = dense_x.size()[0]
+        if batch_size < nd:
+            sys.exit("ERROR: batch_size (%d) must be at least the number of devices (%d) in parallel_forward call"
+                     % (batch_size, nd))
+        n_tables = sum(len(ks) for ks in self.tables_of_device)
+        if len(lS_o) != n_tables or len(lS_i) != n_tables:
+            sys.exit("ERROR: corrupted model input detected in parallel_forward call")
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.bf16):
+            bot = replicate(self.bot_l, devs)
+            top = replicate(self.top_l, devs)
+            xs = scatter(self._pad_dense(dense_x), devs, dim=0)
+            pooled = []  # per source device: [B, T_d, D] pooled rows of its tables, whole batch
+            for d, ks in enumerate(self.tables_of_device):
+                dev = torch.device("cuda", devs[d])
+                with torch.cuda.device(dev):
+                    ly = self.emb_l[d](([lS_i[k].to(dev, non_blocking=True) for k in ks],
+                                        [lS_o[k].to(dev, non_blocking=True) for k in ks], [False] * len(ks)), True)
+                    pooled.append(torch.stack(list(ly), dim=1))
+            x = []
+            for d in range(nd):
+                with torch.cuda.device(devs[d]):
+                    x.append(bot[d](xs[d]))
+            # slices[s][j]: rows of device j's batch slice from source device s (same cut as the dense features)
+            slices = [scatter(t, devs, dim=0) for t in pooled]
+            p = []
+            for j in range(nd):
+                with torch.cuda.device(devs[j]):
+                    ly_j = [slices[k % nd][j][:, k // nd] for k in range(n_tables)]
+                    p.append(top[j](self.interact_features(x[j], ly_j)))
+            p0 = gather(p, devs[0], dim=0)
+        return self._clamp(p0)
 
     def distributed_forward(self, dense_x, *emb_args, chunk=0, dense_bags=None):
         # P/dlrm_s_pytorch.py:342-369: local tables on the GLOBAL batch -> all-to-all -> local batch
