@@ -47,6 +47,7 @@ def parse():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--no-fp32", action="store_true", help="skip the extra fp32 leg of the 1-GPU line")
     ap.add_argument("--batch", type=int, default=32768, help="samples per GPU (weak scaling: fixed as N grows)")
     ap.add_argument("--global-batch", type=int, default=0,
                     help="strong scaling: fixed GLOBAL batch split over the GPUs (BASELINE configs[3]: 65536); "
@@ -260,6 +261,46 @@ def make_batches(a, rows_local, B_loc, B_glob, dev, rank, n_chunks=1, rows_repl=
         sets.append({"host": host, "dev": devt, "uniq": uniq, "host_rec": host_rec})
     torch.cuda.synchronize()
     return sets
+
+
+def fp32_leg(a, rows, sets, dev):
+    """The reference's DEFAULT precision (fp32 everywhere: P/dlrm_s_pytorch.py:707,1029 turn bf16 autocast on only with
+    --bf16) on the same config-3 workload and the same device batches: fp32 MLPs (cuBLAS), fp32 pooled rows, fp32
+    interaction (CUDA-core kernels; the 3xTF32 tcgen05 forward is opt-in), fused fp32 update; one CUDA graph per step.
+    Runs last (the bf16 model is gone by then) and is contained: a failure becomes an "error" entry."""
+    import gc
+
+    from cloudtik_b200.dlrm import DLRM_Net
+    from cloudtik_b200.graph import GraphedTrainStep
+    try:
+        gc.collect()
+        torch.cuda.empty_cache()
+        np.random.seed(727)
+        torch.manual_seed(727)
+        net = DLRM_Net(D, np.array(rows), np.array(LN_BOT), np.array(LN_TOP), sigmoid_top=len(LN_TOP) - 2,
+                       np_init_emb_weight=False, device=dev, lr=LR, bf16=False)
+        opt = torch.optim.SGD([p for p in net.parameters() if p.requires_grad], lr=LR)
+        gs = GraphedTrainStep(net, opt, sets[0]["dev"])
+        last = None
+        for i in range(max(a.warmup, 3)):
+            last = gs.step(*sets[i % len(sets)]["dev"])
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(a.steps):
+            last = gs.step(*sets[i % len(sets)]["dev"])
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / a.steps
+        out = {"value": round(a.batch / (ms / 1e3), 1), "unit": "samples/s", "ms_per_step": round(ms, 4),
+               "dtype": "fp32", "steps": a.steps, "final_loss": float(last.float().cpu()),
+               "interaction": "fp32 CUDA-core kernels" + (" / 3xTF32 tcgen05 forward" if os.environ.get(
+                   "B200_INTERACT_TF32") == "1" else ""),
+               "note": "same workload, batches and graph replay as the headline leg, inputs resident in HBM"}
+        del gs, net, opt
+        return out
+    except Exception as e:  # noqa: BLE001 -- reported in the line, the headline legs are already measured
+        return {"error": f"{type(e).__name__}: {e}"[:300]}
 
 
 def embeddingbag_microbench(net, gs):
@@ -690,6 +731,10 @@ def run_b200_arm(a):
         line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
     else:
         line["cpu_baseline"] = None
+    if world == 1 and bf16 and not a.no_fp32 and not a.global_batch:
+        net.emb_l = None  # (already released when the micro-benchmark or config 5 ran)
+        gs = step_fn = e2e_fn = None
+        line["fp32"] = fp32_leg(a, rows, sets, dev)
     print(json.dumps(line), flush=True)
 
 
