@@ -28,6 +28,7 @@ constexpr int UPD_THREADS = 256;
 // group serially: every window pre-reduces the (at most two) runs that cross its borders into fp32
 // pieces and the pieces of a row are added in window order.  Deterministic, no data-path atomics
 // (the fp32 SGD variant issues ONE vector reduction per 16 bytes of a row, from one group).
+constexpr int PERSIST_DEFAULT = 0;  // window_update_kernel launch mode when B200_UPD_PERSIST is unset (see launch_update)
 constexpr int OPT_STORE = 2;  // internal "optimizer": write the per-row gradient sums to values[run index]
 constexpr int MIN_NG = UPD_THREADS / 32;  // fewest windows per block (one warp per window)
 
@@ -57,7 +58,7 @@ static BwdLayout bwd_layout(void* ws, int64_t n, int64_t D) {
   L.num_unique = reinterpret_cast<int32_t*>(w + o);
   L.n_valid = reinterpret_cast<int64_t*>(w + o + 64);
   o += 256;
-  L.blk_cnt = reinterpret_cast<int32_t*>(w + o), o += align_up((size_t)(ceil_div(ceil_div(n, HOT_CH), MIN_NG) + 1) * 4, 256);
+  L.blk_cnt = reinterpret_cast<int32_t*>(w + o), o += align_up((size_t)(ceil_div(ceil_div(n, HOT_CH), MIN_NG) + 3) * 4, 256);  // + chunk scheduler (2 ints)
   L.win_run = reinterpret_cast<uint32_t*>(w + o), o += align_up((size_t)(ceil_div(n, HOT_CH) + 1) * 4, 256);
   L.partial = reinterpret_cast<float*>(w + o),
   o += align_up((size_t)(2 * ceil_div(ceil_div(n, HOT_CH), MIN_NG)) * D * 4, 256);
@@ -161,6 +162,11 @@ struct UpdParams {
   int64_t n;            // capacity of the sorted arrays (sizes the grid)
   const int64_t* d_n;   // real keys among them, read at kernel time (the sort puts them first)
   int32_t* blk_cnt;
+  // persistent launch: the grid is one wave of blocks, each claims further 256-key chunks from sched[0]
+  // (sched[1] counts finished blocks; the last one leaves both at zero)
+  int32_t* sched;
+  int persist;
+  int kflush;  // persistent launch: chunks with border runs a block collects before it takes their tickets (<= 16)
 };
 
 // load VE consecutive gradient elements (GT) as fp32
@@ -373,8 +379,30 @@ __global__ void __launch_bounds__(UPD_THREADS, (sizeof(GT) == 2 && !TRAIL && OPT
   }
   constexpr bool has_trail = TRAIL;  // compile-time: plain bf16 tables carry no trail registers
   const int64_t n_eff = p.d_n ? min(*p.d_n, p.n) : p.n;
-  if ((int64_t)blockIdx.x * NG * C >= n_eff) return;  // whole block behind the last real key (uniform: before any barrier)
-  const int64_t w = (int64_t)blockIdx.x * NG + gid;
+  const float lr = p.d_lr ? *p.d_lr : p.lr;
+  // A block works on CHUNKS of NG windows (BC keys): the one of its index and, in a persistent launch, further ones
+  // claimed from a device counter (the claim for the next chunk is issued at the top of the current one).  What the
+  // cross-block join needs about a chunk's border runs is recorded per chunk and the join itself (fence, tickets,
+  // finishing) is taken once per KMAX chunks: its fence has to drain every update the block still has in flight, which
+  // costs ~2 us of a block's ~15 us when it is paid per chunk.
+  constexpr int64_t BC = (int64_t)NG * C;
+  constexpr int KMAX = 16;
+  __shared__ int64_t s_xs[KMAX][6];  // per recorded chunk: {run, start, end} of the entering and of the leaving run
+  __shared__ int64_t s_job[2 * KMAX][3];  // {run index, first position of the run, last block of the run}
+  __shared__ int s_njobs;
+  __shared__ int64_t s_claim;
+  int64_t blk = blockIdx.x;
+  bool more = true;
+  while (more) {
+  int nrec = 0;  // chunks of this round with a run across a border (block-uniform)
+  for (;;) {
+  if (blk * BC >= n_eff) {  // behind the last real key (uniform)
+    more = false;
+    break;
+  }
+  int64_t nxt = 0;
+  if (p.persist && threadIdx.x == 0) nxt = (int64_t)gridDim.x + atomicAdd(&p.sched[0], 1);
+  const int64_t w = blk * NG + gid;
   const int64_t a = w * C;
   const int cnt = a < n_eff ? (int)min((int64_t)C, n_eff - a) : 0;
   for (int i = lane; i < cnt; i += G) {
@@ -397,26 +425,25 @@ __global__ void __launch_bounds__(UPD_THREADS, (sizeof(GT) == 2 && !TRAIL && OPT
     s_key[gid][0] = a > 0 ? p.skeys[a - 1] : ~p.skeys[a];
     s_key[gid][cnt + 1] = a + cnt < n_eff ? p.skeys[a + cnt] : ~p.skeys[a + cnt - 1];
   }
-  const float lr = p.d_lr ? *p.d_lr : p.lr;
   __syncthreads();
   // (a group whose window lies beyond the end has cnt == 0: it skips the work but keeps the barriers)
   // Does a run cross this block's left / right border?  Known now from the staged keys (block-uniform); thread 0
   // fetches what the cross-block join at the end needs about those runs right away, so that those dependent loads
   // are long done when it gets there.
-  const int64_t x_first = (int64_t)blockIdx.x * NG * C;
+  const int64_t x_first = blk * BC;
   const int x_ngv = (int)min((int64_t)NG, (n_eff - x_first + C - 1) / C);
   const int x_cntl = (int)min((int64_t)C, n_eff - (x_first + (int64_t)(x_ngv - 1) * C));
   const bool x_enters = s_key[0][0] == s_key[0][1];
   const bool x_leaves = s_key[x_ngv - 1][x_cntl] == s_key[x_ngv - 1][x_cntl + 1];
-  __shared__ int64_t s_x[6];  // thread 0 only: {run, start, end} of the entering and of the leaving run
-  if (threadIdx.x == 0) {
+  if (threadIdx.x == 0 && (x_enters || x_leaves)) {
+    int64_t* s_x = s_xs[nrec];
     int64_t uE = -1, uL = -2;
     if (x_enters) {
-      uE = p.win_run[(int64_t)blockIdx.x * NG];
+      uE = p.win_run[blk * NG];
       s_x[1] = p.seg[uE], s_x[2] = p.seg[uE + 1];
     }
     if (x_leaves) {
-      uL = p.win_run[((int64_t)blockIdx.x + 1) * NG];
+      uL = p.win_run[(blk + 1) * NG];
       s_x[4] = p.seg[uL], s_x[5] = p.seg[uL + 1];
     }
     s_x[0] = uE, s_x[3] = uL;
@@ -592,7 +619,7 @@ __global__ void __launch_bounds__(UPD_THREADS, (sizeof(GT) == 2 && !TRAIL && OPT
   // ---- in-block join.  The group holding the HEAD of a run that crosses its right border adds the
   // slot-0 pieces of the following windows (window order) and finishes the run; group 0 does the same
   // for the run that enters the block from the left.  What crosses a block border goes to p.partial.
-  const int64_t blk_first = (int64_t)blockIdx.x * NG * C;
+  const int64_t blk_first = blk * BC;
   const int ngv = (int)min((int64_t)NG, (n_eff - blk_first + C - 1) / C);  // windows of this block with data
   const int cnt_last = (int)min((int64_t)C, n_eff - (blk_first + (int64_t)(ngv - 1) * C));
   const uint32_t key_after_block = s_key[ngv - 1][cnt_last + 1];
@@ -619,7 +646,7 @@ __global__ void __launch_bounds__(UPD_THREADS, (sizeof(GT) == 2 && !TRAIL && OPT
     const bool to_right = open && j == ngv && key_after_block == key;
     if (from_left || to_right) {  // crosses a block border: per-block partial row, finished by the cross-block join below
       const int bslot = (from_left || (gid == 0 && slot == 0)) ? 0 : 1;
-      float* dst = p.partial + (size_t)(2 * (int64_t)blockIdx.x + bslot) * p.D + lane * VE;
+      float* dst = p.partial + (size_t)(2 * blk + bslot) * p.D + lane * VE;
 #pragma unroll
       for (int k = 0; k < NV; ++k)
         if (lane + k * G < p.V) {
@@ -669,40 +696,90 @@ __global__ void __launch_bounds__(UPD_THREADS, (sizeof(GT) == 2 && !TRAIL && OPT
     finish(tail_slot, s_key[gid][cnt], false, true, cnt - 1, uidx, pre_ok);
   }
 
-  // ---- cross-block join, inside this kernel.  A run that crosses block borders has left one partial row per block
-  // it touches (above).  Every such block takes a ticket on the counter of the run's HEAD block once its partial row
-  // is visible device-wide; the block that draws the last ticket adds the partial rows of all the run's blocks in
-  // block order (whoever does it, the order is the same: deterministic) with all its groups -- strided rows, PB in
-  // flight, combined in shared memory -- and gives the row its one update.  No second kernel, no launch gap: the
-  // join used to cost two small launches (~20 us of a 118 us update on the Criteo-Terabyte tables).
-  constexpr int64_t BC = (int64_t)NG * C;
-  __shared__ int64_t s_job[2][3];  // {run index, first position of the run, last block of the run}
-  __shared__ int s_njobs;
-  if (!(x_enters || x_leaves)) return;  // (block-uniform) no run crosses this block's borders: the common case
+  if (x_enters || x_leaves) ++nrec;
+  if (!p.persist) {
+    more = false;
+    break;
+  }
+  if (threadIdx.x == 0) s_claim = nxt;
+  __syncthreads();  // (also: every group is done with this chunk's shared-memory pieces)
+  blk = s_claim;
+  if (nrec >= min(p.kflush, KMAX)) break;
+  }  // chunks of one round
+
+  // ---- cross-block join, inside this kernel.  A run that crosses chunk borders has left one partial row per chunk
+  // it touches (above).  Every such chunk takes a ticket on the counter of the run's HEAD chunk once its partial row
+  // is visible device-wide; whoever draws the last ticket adds the partial rows of all the run's chunks in chunk
+  // order (whoever does it, the order is the same: deterministic) with all its groups -- strided rows, PB in
+  // flight, combined in shared memory -- and gives the row its one update.  No second kernel, no launch gap.
+  if (nrec == 0) continue;  // (block-uniform) no run crossed a border of this round's chunks
   __threadfence();
+  if (threadIdx.x == 0) s_njobs = 0;
   __syncthreads();
-  if (threadIdx.x == 0) {
-    int nj = 0;
+  if (threadIdx.x < 2 * nrec) {  // one thread per (chunk, border): the atomics' round trips overlap
+    const int64_t* x = s_xs[threadIdx.x >> 1];
+    const bool left = (threadIdx.x & 1) == 0;
     auto ticket = [&](int64_t u, int64_t s0, int64_t e0) {
       const int64_t h = s0 / BC, w1 = (min(e0, n_eff) - 1) / BC;
       const int need = (int)(w1 - h + 1);
       if (atomicAdd(&p.blk_cnt[h], 1) + 1 == need) {
         p.blk_cnt[h] = 0;  // every contributor has drawn: ready for the next call on this workspace
         __threadfence();
-        s_job[nj][0] = u, s_job[nj][1] = s0, s_job[nj][2] = w1;
-        ++nj;
+        const int j = atomicAdd(&s_njobs, 1);
+        s_job[j][0] = u, s_job[j][1] = s0, s_job[j][2] = w1;
       }
     };
-    if (x_enters) ticket(s_x[0], s_x[1], s_x[2]);
-    if (x_leaves && s_x[3] != s_x[0]) ticket(s_x[3], s_x[4], s_x[5]);
-    s_njobs = nj;
+    if (left && x[0] >= 0) ticket(x[0], x[1], x[2]);
+    if (!left && x[3] >= 0 && x[3] != x[0]) ticket(x[3], x[4], x[5]);
   }
   __syncthreads();
   const int njobs = s_njobs;
-  for (int jb = 0; jb < njobs; ++jb) {
-    constexpr int PB = (NV * VE >= 32) ? 2 : (NV * VE >= 16 ? 4 : 8);
+  constexpr int PB = (NV * VE >= 32) ? 2 : (NV * VE >= 16 ? 4 : 8);
+  // Runs over at most NG chunks (nearly all of them): one GROUP per job, the jobs of a block side by side and without
+  // block barriers.  The rows are added in chunk order, which is also the order of the cooperative path below for
+  // such a run (one row per group, groups combined in order): the result does not depend on the path.
+  for (int jb = gid; jb < njobs; jb += NG) {
     const int64_t u = s_job[jb][0], s0 = s_job[jb][1], w1 = s_job[jb][2];
     const int64_t w0 = s0 / BC;
+    if (w1 - w0 >= NG) continue;
+    float sum[NV][VE];
+#pragma unroll
+    for (int kk = 0; kk < NV; ++kk)
+#pragma unroll
+      for (int x = 0; x < VE; ++x) sum[kk][x] = 0.f;
+    for (int64_t ib = w0; ib <= w1; ib += PB) {
+      uint4 f[PB][NV][VE / 4];
+#pragma unroll
+      for (int c = 0; c < PB; ++c) {
+        const int64_t i = ib + c;
+        const bool ok = i <= w1;
+        const float* src = p.partial + (size_t)(2 * (ok ? i : w0) + ((ok && s0 > i * BC) ? 1 : 0)) * p.D + lane * VE;
+#pragma unroll
+        for (int kk = 0; kk < NV; ++kk)
+#pragma unroll
+          for (int h = 0; h < VE / 4; ++h)
+            f[c][kk][h] = (ok && lane + kk * G < p.V) ? ld_cg_v4(src + kk * G * VE + 4 * h) : make_uint4(0, 0, 0, 0);
+      }
+#pragma unroll
+      for (int c = 0; c < PB; ++c)
+#pragma unroll
+        for (int kk = 0; kk < NV; ++kk)
+#pragma unroll
+          for (int h = 0; h < VE / 4; ++h) keep(f[c][kk][h]);
+#pragma unroll
+      for (int c = 0; c < PB; ++c)
+#pragma unroll
+        for (int kk = 0; kk < NV; ++kk)
+#pragma unroll
+          for (int h = 0; h < VE / 4; ++h) Vec16<float>::accum(sum[kk] + 4 * h, f[c][kk][h]);
+    }
+    finish_run<WT, G, NV, OPT, RED>(p, u, sum, lane);
+  }
+  // longer runs (hot rows of tiny tables): all groups of the block on one job
+  for (int jb = 0; jb < njobs; ++jb) {
+    const int64_t u = s_job[jb][0], s0 = s_job[jb][1], w1 = s_job[jb][2];
+    const int64_t w0 = s0 / BC;
+    if (w1 - w0 < NG) continue;  // (block-uniform) done above
     float sum[NV][VE];
 #pragma unroll
     for (int kk = 0; kk < NV; ++kk)
@@ -756,6 +833,11 @@ __global__ void __launch_bounds__(UPD_THREADS, (sizeof(GT) == 2 && !TRAIL && OPT
       finish_run<WT, G, NV, OPT, RED>(p, u, sum, lane);
     }
     __syncthreads();
+  }
+  }  // rounds
+  if (p.persist && threadIdx.x == 0) {
+    // the last block to finish leaves the scheduler at zero for the next launch on this workspace
+    if (atomicAdd(&p.sched[1], 1) + 1 == (int)gridDim.x) p.sched[0] = 0, p.sched[1] = 0;
   }
 }
 
@@ -827,6 +909,21 @@ static int launch_update(const UpdParams& p, int64_t n, bool vec_ok, cudaStream_
     const char* e = getenv("B200_SGD_RED");
     return e == nullptr || e[0] != '0';
   }();
+  // B200_UPD_PERSIST: 0 = one chunk per block, 1 = always one wave of chunk-claiming blocks, unset / "auto" = from two
+  // waves of chunks on; B200_UPD_GRID overrides the size of that wave (tests)
+  static const int persist_mode = []() {
+    const char* e = getenv("B200_UPD_PERSIST");
+    return e == nullptr ? PERSIST_DEFAULT : (e[0] == '0' ? 0 : (e[0] == '1' ? 1 : 2));
+  }();
+  static const int persist_kflush = []() {
+    const char* e = getenv("B200_UPD_KFLUSH");
+    const int v = e == nullptr ? 16 : atoi(e);
+    return v < 1 ? 1 : (v > 16 ? 16 : v);
+  }();
+  static const int64_t persist_grid = []() {
+    const char* e = getenv("B200_UPD_GRID");
+    return e == nullptr ? (int64_t)0 : (int64_t)atoll(e);
+  }();
 #define B200_UPD_LAUNCH(G, NV, RED)                                                                               \
   if constexpr (sizeof(WT) == 2) {                                                                                \
     if (p.trail != nullptr) {                                                                                     \
@@ -849,7 +946,23 @@ static int launch_update(const UpdParams& p, int64_t n, bool vec_ok, cudaStream_
                    "emb_update: row too long for the in-block join");                                             \
     }                                                                                                             \
     const int64_t nblk = ceil_div(nwin, NG_);                                                                     \
-    kern<<<(unsigned)nblk, UPD_THREADS, part_bytes, st>>>(p);                                                     \
+    UpdParams q = p;                                                                                              \
+    int64_t grid = nblk;                                                                                          \
+    q.persist = 0;                                                                                                \
+    q.kflush = persist_kflush;                                                                                    \
+    if (persist_mode != 0 && p.sched != nullptr) {                                                                \
+      int occ = 0, dev = 0, sms = 0;                                                                              \
+      cudaGetDevice(&dev);                                                                                        \
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);                                          \
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, UPD_THREADS, part_bytes);                         \
+      const int64_t wave = persist_grid > 0 ? persist_grid : (int64_t)occ * sms;                                  \
+      /* one wave of blocks claiming chunks pays when there are several waves of chunks */                        \
+      if (wave > 0 && (persist_mode == 1 || nblk >= 2 * wave)) {                                                  \
+        q.persist = 1;                                                                                            \
+        grid = std::min(nblk, wave);                                                                              \
+      }                                                                                                           \
+    }                                                                                                             \
+    kern<<<(unsigned)grid, UPD_THREADS, part_bytes, st>>>(q);                                                     \
   }
 #define B200_UPD_CASE(G, NV)                 \
   if constexpr (CAN_RED) {                   \
@@ -905,7 +1018,7 @@ static int emb_bwd_prepare_impl(const int64_t* d_rows, const int64_t* d_row_base
                "emb_bwd: workspace too small");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   BwdLayout L = bwd_layout(ws, nnz, D);
-  const int64_t n_blk_cnt = ceil_div(ceil_div(nnz, HOT_CH), MIN_NG) + 1;
+  const int64_t n_blk_cnt = ceil_div(ceil_div(nnz, HOT_CH), MIN_NG) + 3;  // tickets + the chunk scheduler's two counters
   keys_tail_kernel<<<(unsigned)std::min<int64_t>(d_nnz_valid ? 256 : ceil_div(n_blk_cnt, 256), 256), 256, 0, st>>>(
       L.keys, L.vals, d_nnz_valid, nnz, (uint32_t)total_rows, L.n_valid, L.blk_cnt, n_blk_cnt);
   dim3 kgrid((unsigned)ceil_div(B, KEYS_THREADS), (unsigned)T);
@@ -981,6 +1094,9 @@ static int emb_bwd_apply_impl(void* const* d_weights, float* const* d_state, uin
   p.n = nnz;
   p.d_n = L.n_valid;
   p.blk_cnt = L.blk_cnt;
+  p.sched = L.blk_cnt + ceil_div(ceil_div(nnz, HOT_CH), MIN_NG) + 1;
+  p.persist = 0;
+  p.kflush = 16;
   p.values = nullptr;
   p.by_key = 0;
   p.grad_ptrs = d_grad_ptrs;
@@ -1074,6 +1190,9 @@ static int store_run_sums(const int64_t* d_row_base, int64_t nnz, const void* d_
   p.n = nnz;
   p.d_n = L.n_valid;
   p.blk_cnt = L.blk_cnt;
+  p.sched = L.blk_cnt + ceil_div(ceil_div(nnz, HOT_CH), MIN_NG) + 1;
+  p.persist = 0;
+  p.kflush = 16;
   p.T = (int)T;
   const int gsz = dtype_size(grad_dtype);
   const bool vec_ok = (D * 4) % 16 == 0 && p.V <= 128 && (reinterpret_cast<uintptr_t>(d_grad) % 16) == 0 &&
