@@ -664,7 +664,7 @@ def run_b200_arm(a):
         roof = {"kernel": dom, "bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
                 "frac": round(ach / peak, 4), "frac_of_8TBps_nominal": round(ach / 8000.0, 4),
                 "peak_source": pk, "traffic": ncu_traffic(dom) if world == 1 else None,
-                "traffic_source": "profiles/roofline_traffic.json <- profiles/r2_ncu_traffic_fullsize.csv (ncu DRAM read + "
+                "traffic_source": "profiles/roofline_traffic.json <- profiles/r2b_ncu_full.summary.md (ncu DRAM read + "
                                   "write bytes per launch of this bench at the FULL 96 GB table sizes, eager launch order)",
                 "algorithmic_bytes": int(alg[dom]),
                 "kernel_ms": round(kt[dom], 4), "measured_in": "eager pass of the same steps, CUDA events",
