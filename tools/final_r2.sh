@@ -1,11 +1,4 @@
-# Final round-2 validation on one B200: GPU test suite, then the default bench line.
+# driver entry points, last check of the round: smoke() and the reference arm
 set -x
-timeout 200 python -m pytest tests -m gpu -x -q > gpurun_out/final_gpu_tests.log 2>&1; echo "tests rc=$?"
-tail -3 gpurun_out/final_gpu_tests.log
-timeout 300 python bench.py > gpurun_out/final_n1_default.log 2> gpurun_out/final_n1_default.err; echo "bench rc=$?"
-python - <<PY
-import json
-for l in open("gpurun_out/final_n1_default.log"):
-    if l.startswith("{"):
-        j=json.loads(l); print(j["value"], j["ms_per_step"], j["e2e"]["value"], j["roofline"]["kernel"], j["roofline"]["kernel_ms"], j["roofline"]["frac"], j["final_loss"]); print(j.get("fp32")); print(j["config5"]["value"], j["config5"]["final_loss"])
-PY
+timeout 100 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/final_smoke.log 2>&1; echo "smoke rc=$?"; tail -2 gpurun_out/final_smoke.log
+timeout 100 python bench.py --impl reference --steps 3 --warmup 3 > gpurun_out/final_ref.log 2>&1; echo "ref rc=$?"; tail -c 700 gpurun_out/final_ref.log
