@@ -130,7 +130,10 @@ class DLRM_Net(nn.Module):
                 raise NotImplementedError("ndevices > 1 is the single-process mode: no process group, no table split")
             if str(torch.device(device)) not in ("cuda", "cuda:0"):
                 raise RuntimeError("ndevices > 1 keeps the MLP parameters on cuda:0 like the reference")
-            self.ndevices = min(self.ndevices, len(ln_emb))
+            # (the reference's caller passes min(#GPUs, batch, #tables), T/dlrm_s_pytorch.py:938)
+            self.ndevices = min(self.ndevices, len(ln_emb), max(torch.cuda.device_count(), 1))
+            if self.ndevices < 2:
+                raise RuntimeError("ndevices > 1 needs at least two visible GPUs and two tables")
             self.device_ids = list(range(self.ndevices))
             # table k lives on device k % ndevices (T/dlrm_s_pytorch.py:543-548), one merged module per device
             ws = self._draw_tables(m_spa, ln_emb, range(len(ln_emb)), np_init_emb_weight,
