@@ -2,7 +2,8 @@
 
 Mirrors of the reference's random-data path, ``T/dlrm_data_pytorch.py``: ``RandomDataset`` (``:541-640``),
 ``generate_uniform_input_batch`` (``:759-803``), ``generate_random_output_batch`` (``:748-755``),
-``collate_wrapper_random`` (``:646-652``) and ``make_random_data_and_loader`` (``:655-682``).  Same argument
+``collate_wrapper_random`` (``:646-652``), ``collate_wrapper_criteo`` (``:339-352``) and
+``make_random_data_and_loader`` (``:655-682``).  Same argument
 meaning, same return format ``(X, lS_o, lS_i, T)`` and -- because the reference draws everything from the legacy
 numpy stream in a fixed order -- the SAME VALUES for the same seed: a run started with the reference's flags sees
 the reference's batches (pinned by ``tests/golden/t_smoke.npz`` and ``small_model.npz``).
@@ -212,6 +213,22 @@ def collate_wrapper_random(list_of_tuples):
     """DataLoader(batch_size=1) collate: unwrap the single pre-built batch; offsets become one ``[T, B]`` tensor."""
     X, lS_o, lS_i, T = list_of_tuples[0]
     return X, torch.stack(lS_o), lS_i, T
+
+
+def collate_wrapper_criteo(list_of_tuples):
+    """DataLoader collate of the per-sample Criteo path (``T/dlrm_data_pytorch.py:339-352``): samples
+    ``(X_int[13], X_cat[T], y)`` -> ``(log(X_int + 1) fp32 [B, 13], lS_o int64 [T, B] = arange(B) per table (one id per
+    bag), lS_i int64 [T, B] = X_cat transposed, targets fp32 [B, 1])``.  One conversion per field instead of the
+    reference's per-sample tensor construction; the whole-batch binary path does the same on the device
+    (``cloudtik_b200.criteo_input``)."""
+    x_int = np.asarray([t[0] for t in list_of_tuples])
+    x_cat = np.asarray([t[1] for t in list_of_tuples])
+    y = np.asarray([t[2] for t in list_of_tuples])
+    X = torch.log(torch.as_tensor(x_int).to(torch.float) + 1)
+    lS_i = torch.as_tensor(x_cat).to(torch.long).t().contiguous()
+    B, T = x_cat.shape
+    lS_o = torch.arange(B, dtype=torch.long).repeat(T, 1)
+    return X, lS_o, lS_i, torch.as_tensor(y).to(torch.float32).view(-1, 1)
 
 
 def make_random_data_and_loader(args, ln_emb, m_den, world_size=1):

@@ -512,6 +512,18 @@ def gen_trace_synth():
     np.savez_compressed(os.path.join(OUT, "trace_synth.npz"), **out)
 
 
+def gen_collate_criteo():
+    """The per-sample Criteo collate (T/dlrm_data_pytorch.py:339-352) run on seeded integer samples."""
+    G = load_T_generator()
+    rs = np.random.RandomState(17)
+    samples = [(rs.randint(0, 5000, size=13).astype(np.int32), rs.randint(0, 10 ** 6, size=26).astype(np.int32),
+                np.int32(rs.randint(0, 2))) for _ in range(9)]
+    X, lS_o, lS_i, T = G.collate_wrapper_criteo([(a.tolist(), b.tolist(), int(c)) for a, b, c in samples])
+    np.savez_compressed(os.path.join(OUT, "collate_criteo.npz"), x_int=np.stack([s_[0] for s_ in samples]),
+                        x_cat=np.stack([s_[1] for s_ in samples]), y=np.array([s_[2] for s_ in samples]),
+                        X=X.numpy(), lS_o=lS_o.numpy(), lS_i=lS_i.numpy(), T=T.numpy())
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     G = load_T_generator()
@@ -527,6 +539,7 @@ def main():
     gen_T_smoke()
     gen_T_options()
     gen_trace_synth()
+    gen_collate_criteo()
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

@@ -327,3 +327,20 @@ def test_trace_driven_producer_reproduces_the_reference(golden, tmp_path):
     np.testing.assert_array_equal(X.numpy(), g["ragged_X"])
     np.testing.assert_array_equal(lS_i[1].numpy(), g["ragged_i1"])
     assert T.shape == (6, 1)
+
+
+def test_criteo_collate_matches_the_reference(golden):
+    """cloudtik_b200.data.collate_wrapper_criteo against the batch the reference's function built from the same
+    per-sample tuples (tests/golden/collate_criteo.npz): bit-equal dense features (log(x + 1) in fp32), offsets,
+    transposed ids and targets, for list and for array samples."""
+    from cloudtik_b200 import data as D
+    g = golden("collate_criteo")
+    for as_list in (True, False):
+        samples = [((a.tolist(), b.tolist(), int(c)) if as_list else (a, b, c))
+                   for a, b, c in zip(g["x_int"], g["x_cat"], g["y"])]
+        X, lS_o, lS_i, T = D.collate_wrapper_criteo(samples)
+        np.testing.assert_array_equal(X.numpy(), g["X"])
+        np.testing.assert_array_equal(lS_o.numpy(), g["lS_o"])
+        np.testing.assert_array_equal(lS_i.numpy(), g["lS_i"])
+        np.testing.assert_array_equal(T.numpy(), g["T"])
+        assert X.dtype == torch.float32 and lS_o.dtype == torch.int64 and lS_i.dtype == torch.int64
